@@ -1,0 +1,289 @@
+// oracle/ref_harness.cpp — TEST INFRASTRUCTURE ONLY (never linked into the product).
+//
+// A thin extern "C" harness around the reference's OWN object code: it is
+// compiled against the headers under /root/reference/src (L-HEAD) or against the
+// patched scratch copy in oracle/_ref/abc_src (L-ABC) and linked
+// with the reference's Renderer.o + SettingData.o.  Nothing of the reference is
+// copied here; the harness only
+//   * drives png::LoadData / png::SphereObject (src/SettingData.cpp:6-12,192-196),
+//   * calls png::PathTracing (src/Renderer.cpp:57, external linkage) and
+//     png::Object::Intersect (src/SettingData.cpp:197) directly,
+//   * restates the ~12 lines of camera set-up and per-sample accumulation that
+//     live inside Renderer::Render (src/Renderer.cpp:202-208,223-248) and cannot
+//     be called separately, with a PRIVATE std::mt19937 per image row instead of
+//     the reference's shared, data-raced one.
+// Built by oracle/Makefile into oracle/_ref/libref_{head,abc}.so.
+#include "Renderer.h"
+#include "SettingData.h"
+
+#include <cstdint>
+#include <cstring>
+#include <random>
+#include <omp.h>
+
+#ifdef RTM_REF_ABC
+typedef png::vec3& normal_arg_t;   // patched signature (F3 fixed)
+#else
+typedef png::vec3 normal_arg_t;    // HEAD signature: normal passed by value
+#endif
+
+namespace png {
+// src/Renderer.cpp:57 — defined there with external linkage, declared nowhere.
+vec3 PathTracing(const Ray ray, SettingData& data, const std::function<double()>& randomGene);
+}
+
+namespace {
+
+thread_local uint64_t t_intersect_calls = 0;
+
+// Forwards to a reference object and counts calls; installed as object[0]
+// during refh_render so that rays = calls (one Intersect on object 0 per
+// PathTracing invocation, src/Renderer.cpp:62-66).
+struct CountingProxy : public png::Object {
+    const png::Object* inner;
+    explicit CountingProxy(const png::Object* o) : png::Object(o->m_material), inner(o) {}
+    png::vec3 ComputeSurfacePoint(const std::function<double()> g) const override { return inner->ComputeSurfacePoint(g); }
+    bool Intersect(const png::Ray& ray, double& out_dis, normal_arg_t out_normal) const override {
+        ++t_intersect_calls;
+        return inner->Intersect(ray, out_dis, out_normal);
+    }
+};
+
+struct Scene {
+    png::SettingData data;
+};
+
+struct CameraFrame {
+    png::vec3 camX, camY, camZ;
+    double fovx, fovy;
+};
+
+// src/Renderer.cpp:202-208
+CameraFrame make_frame(const png::SettingData& d) {
+    CameraFrame f;
+    auto direction = Normalize(d.camera.target - d.camera.origin);
+    f.camX = -Normalize(Cross(direction, d.camera.upVec));
+    f.camY = Cross(f.camX, direction);
+    f.camZ = direction;
+    f.fovx = d.camera.fov;
+    f.fovy = f.fovx * d.height / d.width;
+    return f;
+}
+
+// src/Renderer.cpp:227-232 (the float `rate`, the 2.0f/1.0f literals and the
+// left-to-right evaluation order are part of the contract)
+inline png::vec3 camera_dir(const png::SettingData& data, const CameraFrame& f, int x, int y, int sx, int sy) {
+    const float rate = 1.0 / (1 + data.superSamples);
+    return Normalize(
+        f.camX * f.fovx * (2.0f * ((double)x + rate * sx) / data.width - 1.0f) +
+        f.camY * f.fovy * (2.0f * ((double)y + rate * sy) / data.height - 1.0f) +
+        f.camZ);
+}
+
+// src/Renderer.cpp:43-49
+inline png::vec3 clamp_color(const png::vec3& ref, double min, float max) {
+    return png::vec3(
+        std::min<double>(std::max<double>(ref.x, min), max),
+        std::min<double>(std::max<double>(ref.y, min), max),
+        std::min<double>(std::max<double>(ref.z, min), max));
+}
+
+}  // namespace
+
+extern "C" {
+
+int refh_level(void) {
+#ifdef RTM_REF_ABC
+    return 1;
+#else
+    return 0;
+#endif
+}
+
+// Scene through the reference's own parser (needs a HEAD-schema file).
+void* refh_scene_from_json(const char* path) {
+    Scene* s = new Scene();
+    s->data.width = s->data.height = s->data.samples = s->data.superSamples = 0;
+    png::LoadData ld{std::string(path)};
+    s->data = ld.data;
+    return s;
+}
+
+// Scene built directly from flat arrays through the reference's SphereObject
+// constructor (src/SettingData.cpp:192-196); used for synthetic/random scenes.
+void* refh_scene_from_arrays(int width, int height, int samples, int superSamples,
+                             const double* cam9, float fov, int n,
+                             const double* pos3, const float* radius,
+                             const double* color3, const double* emission3) {
+    Scene* s = new Scene();
+    s->data.width = width; s->data.height = height;
+    s->data.samples = samples; s->data.superSamples = superSamples;
+    s->data.camera.origin = png::vec3(cam9[0], cam9[1], cam9[2]);
+    s->data.camera.target = png::vec3(cam9[3], cam9[4], cam9[5]);
+    s->data.camera.upVec = png::vec3(cam9[6], cam9[7], cam9[8]);
+    s->data.camera.fov = fov;
+    for (int i = 0; i < n; ++i) {
+        png::Material m;
+        m.color = png::vec3(color3[3 * i], color3[3 * i + 1], color3[3 * i + 2]);
+        m.emission = png::vec3(emission3[3 * i], emission3[3 * i + 1], emission3[3 * i + 2]);
+        s->data.object.push_back(new png::SphereObject(
+            png::vec3(pos3[3 * i], pos3[3 * i + 1], pos3[3 * i + 2]), radius[i], m));
+    }
+    return s;
+}
+
+void refh_scene_destroy(void* h) {
+    Scene* s = (Scene*)h;
+    for (auto* o : s->data.object) delete o;
+    delete s;
+}
+
+void refh_scene_info(void* h, int* width, int* height, int* samples, int* superSamples, int* n) {
+    Scene* s = (Scene*)h;
+    *width = s->data.width; *height = s->data.height;
+    *samples = s->data.samples; *superSamples = s->data.superSamples;
+    *n = (int)s->data.object.size();
+}
+
+void refh_scene_set_dims(void* h, int width, int height, int samples, int superSamples) {
+    Scene* s = (Scene*)h;
+    if (width > 0) s->data.width = width;
+    if (height > 0) s->data.height = height;
+    if (samples > 0) s->data.samples = samples;
+    if (superSamples > 0) s->data.superSamples = superSamples;
+}
+
+// What the reference actually parsed (exposes F2 in L-HEAD).
+void refh_scene_get(void* h, double* cam9, float* fov, double* pos3, float* radius,
+                    double* color3, double* emission3) {
+    Scene* s = (Scene*)h;
+    const auto& c = s->data.camera;
+    const double cc[9] = {c.origin.x, c.origin.y, c.origin.z, c.target.x, c.target.y, c.target.z,
+                          c.upVec.x, c.upVec.y, c.upVec.z};
+    std::memcpy(cam9, cc, sizeof cc);
+    *fov = c.fov;
+    for (size_t i = 0; i < s->data.object.size(); ++i) {
+        auto* o = static_cast<png::SphereObject*>(s->data.object[i]);
+        pos3[3 * i] = o->m_position.x; pos3[3 * i + 1] = o->m_position.y; pos3[3 * i + 2] = o->m_position.z;
+        radius[i] = o->m_size;
+        color3[3 * i] = o->m_material.color.x; color3[3 * i + 1] = o->m_material.color.y; color3[3 * i + 2] = o->m_material.color.z;
+        emission3[3 * i] = o->m_material.emission.x; emission3[3 * i + 1] = o->m_material.emission.y; emission3[3 * i + 2] = o->m_material.emission.z;
+    }
+}
+
+// Single ray–sphere query on the reference's SphereObject::Intersect
+// (src/SettingData.cpp:197-226) for the known-answer tests.  In L-HEAD the
+// normal never comes back (F3) and normal3 is left untouched.
+int refh_intersect(void* h, int obj, const double* org3, const double* dir3, double* t_out, double* normal3) {
+    Scene* s = (Scene*)h;
+    png::Ray ray(png::vec3(org3[0], org3[1], org3[2]), png::vec3(dir3[0], dir3[1], dir3[2]));
+    double t = 0.0;
+    png::vec3 n(normal3[0], normal3[1], normal3[2]);
+    bool hit = s->data.object[obj]->Intersect(ray, t, n);
+    *t_out = t;
+    normal3[0] = n.x; normal3[1] = n.y; normal3[2] = n.z;
+    return hit ? 1 : 0;
+}
+
+// Primary-hit index map int32[H][W][ss][ss] (last two axes: sx-1, sy-1); -1 = miss.
+// mode 0: the closest-hit loop of src/Renderer.cpp:58-73 restated over the
+//         reference's virtual Intersect;
+// mode 1: through the reference's own png::PathTracing: emission.x of object i
+//         is temporarily set to i+1 and the RNG returns 2.0, so the RR test at
+//         src/Renderer.cpp:78 fails and PathTracing returns the emission of the
+//         object ITS closest-hit loop picked (src/Renderer.cpp:112).
+int refh_primary_hits(void* h, int32_t* out, int mode) {
+    Scene* s = (Scene*)h;
+    png::SettingData& data = s->data;
+    const CameraFrame f = make_frame(data);
+    const int ss = data.superSamples;
+    const int n = (int)data.object.size();
+    std::vector<png::vec3> saved(n);
+    if (mode == 1)
+        for (int i = 0; i < n; ++i) {
+            saved[i] = data.object[i]->m_material.emission;
+            data.object[i]->m_material.emission = png::vec3((double)(i + 1), 0, 0);
+        }
+    const std::function<double()> two = []() { return 2.0; };
+#pragma omp parallel for schedule(dynamic)
+    for (int y = 0; y < data.height; ++y)
+        for (int x = 0; x < data.width; ++x)
+            for (int sx = 1; sx <= ss; ++sx)
+                for (int sy = 1; sy <= ss; ++sy) {
+                    const png::vec3 dir = camera_dir(data, f, x, y, sx, sy);
+                    const png::Ray ray(data.camera.origin, dir);
+                    int hitObject = -1;
+                    if (mode == 1) {
+                        const png::vec3 e = png::PathTracing(ray, data, two);
+                        hitObject = (int)e.x - 1;
+                    } else {
+                        double dis = std::numeric_limits<double>::max();
+                        for (int i = 0; i < n; ++i) {
+                            double tmp_dis;
+                            png::vec3 tmp_normal;
+                            if (data.object[i]->Intersect(ray, tmp_dis, tmp_normal) && tmp_dis < dis && tmp_dis > 0) {
+                                dis = tmp_dis;
+                                hitObject = i;
+                            }
+                        }
+                    }
+                    out[(((size_t)y * data.width + x) * ss + (sx - 1)) * ss + (sy - 1)] = hitObject;
+                }
+    if (mode == 1)
+        for (int i = 0; i < n; ++i) data.object[i]->m_material.emission = saved[i];
+    return 0;
+}
+
+// Linear double image [H][W][3] exactly as src/Renderer.cpp:223-248 accumulates
+// it, with rnd = std::mt19937(seed + y) private to row y.  rays = number of
+// PathTracing invocations, samples = innermost-loop iterations.
+int refh_render(void* h, uint32_t seed, double* image, uint64_t* rays_out, uint64_t* samples_out, int nthreads) {
+    Scene* s = (Scene*)h;
+    png::SettingData& data = s->data;
+    if (data.object.empty()) return -1;
+    const CameraFrame f = make_frame(data);
+    png::Object* real0 = data.object[0];
+    CountingProxy proxy(real0);
+    data.object[0] = &proxy;
+    uint64_t rays = 0, samples = 0;
+    if (nthreads <= 0) nthreads = omp_get_max_threads();
+#pragma omp parallel for schedule(dynamic) num_threads(nthreads) reduction(+ : rays, samples)
+    for (int y = 0; y < data.height; ++y) {
+        std::mt19937 rnd(seed + (uint32_t)y);
+        std::uniform_real_distribution<double> dist(0.0, 1.0);
+        const std::function<double()> randomGene = [&rnd, &dist]() { return dist(rnd); };
+        const uint64_t before = t_intersect_calls;
+        for (int x = 0; x < data.width; ++x) {
+            png::vec3 accumulatedColor(0, 0, 0);
+            for (int sx = 1; sx <= data.superSamples; ++sx)
+                for (int sy = 1; sy <= data.superSamples; ++sy)
+                    for (int smp = 0; smp < data.samples; ++smp) {
+                        const png::vec3 dir = camera_dir(data, f, x, y, sx, sy);
+                        png::vec3 cal(0, 0, 0);
+                        if (randomGene() >= 1.0) {
+                            // SurfaeSample branch (src/Renderer.cpp:234-236): unreachable for U[0,1)
+                        } else {
+                            cal = png::PathTracing(png::Ray(data.camera.origin, dir), data, randomGene);
+                        }
+                        cal = cal / data.superSamples / data.superSamples / data.samples;
+                        cal = clamp_color(cal, 0, 1);
+                        accumulatedColor += cal;
+                        ++samples;
+                    }
+            double* px = image + ((size_t)y * data.width + x) * 3;
+            px[0] = accumulatedColor.x; px[1] = accumulatedColor.y; px[2] = accumulatedColor.z;
+        }
+        rays += t_intersect_calls - before;
+    }
+    data.object[0] = real0;
+    if (rays_out) *rays_out = rays;
+    if (samples_out) *samples_out = samples;
+    return 0;
+}
+
+// 8-bit conversion exactly as src/Renderer.cpp:251-254.
+void refh_to_u8(const double* image, unsigned char* out, size_t n) {
+    for (size_t i = 0; i < n; ++i) out[i] = (unsigned char)255 * std::min(image[i], 1.0);
+}
+
+}  // extern "C"
