@@ -1,0 +1,181 @@
+/* include/rtm_b200.h — C ABI of the B200 renderer for RaytracingMin's radiance loop.
+ *
+ * The reference has no FFI of its own: the hot path sits behind the C++ class
+ * png::Renderer (reference src/Renderer.h:9-17: ctor taking SettingData&, and
+ * Render(std::string)), fed by the struct png::SettingData
+ * (src/SettingData.h:43-51) and driven by src/main.cpp:41-44.  This header is
+ * what an FFI for that path binds:
+ *
+ *   renderer_create   <-  png::Renderer::Renderer(SettingData&)   src/Renderer.cpp:20-23
+ *   renderer_render   <-  png::Renderer::Render(std::string), the loop nest only
+ *                         (src/Renderer.cpp:202-248); the 8-bit conversion of
+ *                         :251-254 is renderer_read_u8, the stb writes of
+ *                         :256-257 stay with the host caller
+ *   renderer_destroy  <-  ~Renderer (implicit)
+ *
+ * Plain pointers and sizes only.  The library copies everything it needs in
+ * renderer_create (the caller may free the scene arrays immediately), owns all
+ * device memory, and never throws across the boundary: every entry point
+ * returns 0 or a negative RTM_E_* code; renderer_last_error() holds the text
+ * (thread-local).  There is no CPU fallback: without a CUDA device
+ * renderer_create fails with RTM_E_CUDA.
+ */
+#ifndef RTM_B200_H
+#define RTM_B200_H
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define RTM_ABI_VERSION 1
+
+enum {
+    RTM_OK = 0,
+    RTM_E_INVALID = -1,   /* bad argument / scene the reference would crash on */
+    RTM_E_CUDA = -2,      /* CUDA runtime error (text in renderer_last_error) */
+    RTM_E_NCCL = -3,      /* NCCL error or libnccl not loadable (multi-GPU only) */
+    RTM_E_UNSUPPORTED = -4
+};
+
+/* Semantics level. */
+enum {
+    RTM_COMPAT_HEAD = 0,  /* the reference exactly as written: normals never reach the
+                             caller (src/SettingData.h:21), every sample evaluates to the
+                             emission of the primary hit.  Deterministic; the double image
+                             is bit-exact against the reference. */
+    RTM_COMPAT_ABC = 1    /* the intended renderer (8 patched lines): diffuse GI with
+                             Russian roulette.  Default. */
+};
+
+/* Arithmetic of the bounce loop (the primary-hit pass is always the exact FP64 one). */
+enum {
+    RTM_PRECISION_F32 = 0,  /* product path: FP32 bounces, cancellation-free sphere test */
+    RTM_PRECISION_F64 = 1   /* reference-faithful: the reference's own double/float-mixed
+                               formulas line by line (incl. sqrtf Normalize); slow, used as
+                               the on-device statistical anchor */
+};
+
+/* Kernel organisation of the FP32 bounce loop. */
+enum {
+    RTM_VARIANT_MEGA = 0,      /* persistent megakernel with per-lane path refill */
+    RTM_VARIANT_WAVEFRONT = 1  /* extend / shade kernels over compacted SoA ray queues */
+};
+
+/* Closest-hit search. */
+enum {
+    RTM_ACCEL_AUTO = 0,   /* brute force when n_spheres <= 64, else BVH */
+    RTM_ACCEL_BRUTE = 1,  /* the reference's O(N) loop (src/Renderer.cpp:62-72) */
+    RTM_ACCEL_BVH = 2     /* same per-candidate arithmetic and tie rule behind a BVH */
+};
+
+/* What png::SettingData holds after LoadData::from_json (src/SettingData.cpp:129-186),
+ * flattened.  Doubles in, so the FP64 primary pass sees exactly what the reference parsed. */
+typedef struct rtm_scene_desc {
+    int32_t width, height;          /* "00 width", "00 height" */
+    int32_t samples, superSamples;  /* "00 samples", "00 superSamples"; spp = samples*superSamples^2 */
+    double cam_origin[3];           /* "01 camera".origin */
+    double cam_target[3];           /* .target */
+    double cam_up[3];               /* .upVec */
+    float fov;                      /* .fov: FLOAT (src/SettingData.h:45), tangent-space half width */
+    int32_t n_spheres;
+    const double* position;         /* [n][3] SphereObject::m_position */
+    const float* radius;            /* [n]    SphereObject::m_size (FLOAT, src/SettingData.h:31) */
+    const double* color;            /* [n][3] Material::color */
+    const double* emission;         /* [n][3] Material::emission */
+} rtm_scene_desc;
+
+typedef struct rtm_options {
+    int32_t device;        /* CUDA ordinal of the (first) GPU */
+    int32_t n_gpus;        /* 1: this device only.  >1: devices device..device+n_gpus-1 driven by
+                              this process, sample budget sliced across them, partial buffers
+                              summed with one ncclReduce to `device` */
+    int32_t compat;        /* RTM_COMPAT_* */
+    int32_t precision;     /* RTM_PRECISION_* */
+    int32_t variant;       /* RTM_VARIANT_* */
+    int32_t accel;         /* RTM_ACCEL_* */
+    int32_t max_depth;     /* hits per path before forced termination; 0 = default (256).  The
+                              reference recurses without bound (src/Renderer.cpp:108). */
+    int32_t sample_begin;  /* slice [sample_begin, sample_end) of the "samples" loop */
+    int32_t sample_end;    /*   (src/Renderer.cpp:226) this handle renders; 0,0 = all.  The divisor
+                              of :240 stays the GLOBAL samples count, so slices add up exactly. */
+    uint64_t seed;         /* Philox key; the image is a pure function of (scene, seed) */
+} rtm_options;
+
+typedef struct rtm_stats {
+    uint64_t samples;        /* innermost-loop iterations (src/Renderer.cpp:226) evaluated */
+    uint64_t rays;           /* PathTracing invocations the reference would have made for them
+                                (src/Renderer.cpp:57): sum of path lengths, primary included */
+    uint64_t rays_traced;    /* closest-hit queries actually executed on the device (the primary
+                                query is shared by the `samples` samples of a sub-pixel) */
+    uint64_t sphere_tests;   /* ray-sphere tests actually executed */
+    double device_ms;        /* CUDA-event time of the kernels (+ reduce), max over GPUs */
+    double e2e_ms;           /* host wall time of the renderer_render call */
+    int32_t kernel_launches; /* kernels launched by the call */
+    int32_t n_gpus;
+} rtm_stats;
+
+typedef struct rtm_renderer rtm_renderer;
+
+int renderer_abi_version(void);
+
+/* Fills *opt with the defaults (device 0, 1 GPU, ABC, F32, MEGA, AUTO, seed 0x5EED). */
+void renderer_default_options(rtm_options* opt);
+
+int renderer_create(const rtm_scene_desc* scene, const rtm_options* opt, rtm_renderer** out);
+
+/* Host-buffer entry point (the drop-in call).  Renders the whole image and copies back.
+ *   rgb_out          float[H][W][3] linear radiance sums as src/Renderer.cpp:246-248, or NULL
+ *   primary_hit_out  int32[H][W][ss][ss] (axes y, x, sx-1, sy-1), -1 = miss, or NULL
+ *   stats            or NULL */
+int renderer_render(rtm_renderer* r, float* rgb_out, int32_t* primary_hit_out, rtm_stats* stats);
+
+/* Device-resident entry point: enqueues the kernels of ONE pass on `stream`
+ * (a cudaStream_t; NULL = the legacy default stream) and returns without
+ * synchronising.  Results stay in the buffers below. */
+int renderer_render_async(rtm_renderer* r, void* stream);
+
+/* After the stream has been synchronised: counters of the last pass. */
+int renderer_read_stats(rtm_renderer* r, rtm_stats* stats);
+
+/* Device pointers (valid until destroy): the float4[H][W] accumulation buffer
+ * {r,g,b,0} and the int32 primary-hit map. */
+void* renderer_device_accum(rtm_renderer* r);
+void* renderer_device_hits(rtm_renderer* r);
+
+/* Let the caller own the accumulation buffer (e.g. a registered NCCL send
+ * buffer): float4[H][W] device memory on the handle's device. */
+int renderer_set_accum_buffer(rtm_renderer* r, void* device_float4);
+
+/* COMPAT_HEAD only: the double image double[H][W][3], bit-exact against the reference. */
+int renderer_read_image_f64(rtm_renderer* r, double* image_out);
+
+/* src/Renderer.cpp:251-254 on the device: u8[H][W][3] = (unsigned char)(255*min(v,1)). */
+int renderer_read_u8(rtm_renderer* r, unsigned char* rgb8_out);
+
+void renderer_destroy(rtm_renderer* r);
+
+const char* renderer_last_error(void);
+
+/* ---- test hooks (deterministic building blocks, used by tests/ only) ---- */
+
+/* Philox4x32-10 on the device: out[i] = philox(ctr = {i, c1, c2, c3}, key). */
+int rtm_debug_philox(int32_t device, uint32_t n, uint32_t c1, uint32_t c2, uint32_t c3,
+                     uint32_t key0, uint32_t key1, uint32_t* out4n);
+
+/* One closest-hit query per ray through the handle's scene.
+ *   mode 0: the exact FP64 test (bit-comparable with src/SettingData.cpp:197-226)
+ *   mode 1: the FP32 product test; origin_id[i] >= 0 marks a ray leaving that sphere's surface
+ * org/dir double[n][3]; hit_out int32[n]; t_out double[n]. */
+int rtm_debug_closest_hit(rtm_renderer* r, int32_t mode, uint32_t n, const double* org, const double* dir,
+                          const int32_t* origin_id, int32_t* hit_out, double* t_out);
+
+/* FP32 FMA-chain microbenchmark: measured FP32 peak of the device in TFLOP/s. */
+int rtm_debug_fp32_peak(int32_t device, double* tflops_out, double* sm_clock_mhz_out);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* RTM_B200_H */

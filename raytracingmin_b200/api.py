@@ -1,0 +1,247 @@
+"""ctypes binding of the C ABI in include/rtm_b200.h (librtm_b200.so).
+
+The class below plays the role png::Renderer plays in the reference
+(src/Renderer.h:9-17): construct from the parsed scene, call render().  There
+is no CPU fallback — a missing library or GPU raises RtmError.
+"""
+from __future__ import annotations
+
+import ctypes as C
+import os
+from dataclasses import dataclass
+from typing import Optional
+
+import numpy as np
+
+from .scene import Scene
+
+COMPAT_HEAD, COMPAT_ABC = 0, 1
+PRECISION_F32, PRECISION_F64 = 0, 1
+VARIANT_MEGA, VARIANT_WAVEFRONT = 0, 1
+ACCEL_AUTO, ACCEL_BRUTE, ACCEL_BVH = 0, 1, 2
+
+_COMPAT = {"head": COMPAT_HEAD, "abc": COMPAT_ABC}
+_PRECISION = {"f32": PRECISION_F32, "f64": PRECISION_F64}
+_VARIANT = {"mega": VARIANT_MEGA, "wavefront": VARIANT_WAVEFRONT}
+_ACCEL = {"auto": ACCEL_AUTO, "brute": ACCEL_BRUTE, "bvh": ACCEL_BVH}
+
+
+class RtmError(RuntimeError):
+    def __init__(self, code: int, msg: str):
+        super().__init__(f"rtm error {code}: {msg}")
+        self.code = code
+
+
+class _SceneDesc(C.Structure):
+    _fields_ = [
+        ("width", C.c_int32), ("height", C.c_int32), ("samples", C.c_int32), ("superSamples", C.c_int32),
+        ("cam_origin", C.c_double * 3), ("cam_target", C.c_double * 3), ("cam_up", C.c_double * 3),
+        ("fov", C.c_float), ("n_spheres", C.c_int32),
+        ("position", C.POINTER(C.c_double)), ("radius", C.POINTER(C.c_float)),
+        ("color", C.POINTER(C.c_double)), ("emission", C.POINTER(C.c_double)),
+    ]
+
+
+class _Options(C.Structure):
+    _fields_ = [
+        ("device", C.c_int32), ("n_gpus", C.c_int32), ("compat", C.c_int32), ("precision", C.c_int32),
+        ("variant", C.c_int32), ("accel", C.c_int32), ("max_depth", C.c_int32),
+        ("sample_begin", C.c_int32), ("sample_end", C.c_int32), ("seed", C.c_uint64),
+    ]
+
+
+class _Stats(C.Structure):
+    _fields_ = [
+        ("samples", C.c_uint64), ("rays", C.c_uint64), ("rays_traced", C.c_uint64), ("sphere_tests", C.c_uint64),
+        ("device_ms", C.c_double), ("e2e_ms", C.c_double), ("kernel_launches", C.c_int32), ("n_gpus", C.c_int32),
+    ]
+
+
+@dataclass
+class Stats:
+    samples: int
+    rays: int
+    rays_traced: int
+    sphere_tests: int
+    device_ms: float
+    e2e_ms: float
+    kernel_launches: int
+    n_gpus: int
+
+
+@dataclass
+class RenderResult:
+    image: Optional[np.ndarray]  # float32 [H][W][3] linear sums (src/Renderer.cpp:246-248)
+    hits: Optional[np.ndarray]   # int32 [H][W][ss][ss], -1 = miss
+    stats: Stats
+
+
+EXPORTS = [
+    "renderer_abi_version", "renderer_default_options", "renderer_create", "renderer_render",
+    "renderer_render_async", "renderer_read_stats", "renderer_device_accum", "renderer_device_hits",
+    "renderer_set_accum_buffer", "renderer_read_image_f64", "renderer_read_u8", "renderer_destroy",
+    "renderer_last_error", "rtm_debug_philox", "rtm_debug_closest_hit", "rtm_debug_fp32_peak",
+]
+
+
+def lib_path() -> str:
+    return os.path.join(os.path.dirname(os.path.abspath(__file__)), "librtm_b200.so")
+
+
+_lib = None
+
+
+def load_library():
+    """Loads librtm_b200.so (built in-tree by `make -C raytracingmin_b200/csrc`).  Fails loudly."""
+    global _lib
+    if _lib is not None:
+        return _lib
+    path = lib_path()
+    if not os.path.exists(path):
+        raise RtmError(-2, f"{path} is not built (run `make -C raytracingmin_b200/csrc`); there is no CPU fallback")
+    lib = C.CDLL(path)
+    P = C.POINTER
+    vp = C.c_void_p
+    lib.renderer_abi_version.restype = C.c_int
+    lib.renderer_default_options.argtypes = [P(_Options)]
+    lib.renderer_default_options.restype = None
+    lib.renderer_create.argtypes = [P(_SceneDesc), P(_Options), P(vp)]
+    lib.renderer_render.argtypes = [vp, vp, vp, P(_Stats)]
+    lib.renderer_render_async.argtypes = [vp, vp]
+    lib.renderer_read_stats.argtypes = [vp, P(_Stats)]
+    lib.renderer_device_accum.argtypes = [vp]
+    lib.renderer_device_accum.restype = vp
+    lib.renderer_device_hits.argtypes = [vp]
+    lib.renderer_device_hits.restype = vp
+    lib.renderer_set_accum_buffer.argtypes = [vp, vp]
+    lib.renderer_read_image_f64.argtypes = [vp, vp]
+    lib.renderer_read_u8.argtypes = [vp, vp]
+    lib.renderer_destroy.argtypes = [vp]
+    lib.renderer_destroy.restype = None
+    lib.renderer_last_error.restype = C.c_char_p
+    lib.rtm_debug_philox.argtypes = [C.c_int32] + [C.c_uint32] * 6 + [vp]
+    lib.rtm_debug_closest_hit.argtypes = [vp, C.c_int32, C.c_uint32, vp, vp, vp, vp, vp]
+    lib.rtm_debug_fp32_peak.argtypes = [C.c_int32, P(C.c_double), P(C.c_double)]
+    _lib = lib
+    return lib
+
+
+def _check(lib, rc: int):
+    if rc != 0:
+        raise RtmError(rc, lib.renderer_last_error().decode("utf-8", "replace"))
+
+
+def _stats(s: _Stats) -> Stats:
+    return Stats(s.samples, s.rays, s.rays_traced, s.sphere_tests, s.device_ms, s.e2e_ms, s.kernel_launches, s.n_gpus)
+
+
+class Renderer:
+    """One handle = one scene on one device (or n_gpus devices of this process)."""
+
+    def __init__(self, scene: Scene, *, device: int = 0, n_gpus: int = 1, compat: str = "abc", precision: str = "f32",
+                 variant: str = "mega", accel: str = "auto", max_depth: int = 0, seed: int = 0x5EED,
+                 sample_begin: int = 0, sample_end: int = 0):
+        self._lib = load_library()
+        self._h = C.c_void_p()
+        sc = scene.normalized()
+        self.scene = sc
+        d = _SceneDesc()
+        d.width, d.height, d.samples, d.superSamples = sc.width, sc.height, sc.samples, sc.superSamples
+        d.cam_origin[:] = list(sc.cam_origin)
+        d.cam_target[:] = list(sc.cam_target)
+        d.cam_up[:] = list(sc.cam_up)
+        d.fov = sc.fov
+        d.n_spheres = sc.n
+        d.position = sc.position.ctypes.data_as(C.POINTER(C.c_double))
+        d.radius = sc.radius.ctypes.data_as(C.POINTER(C.c_float))
+        d.color = sc.color.ctypes.data_as(C.POINTER(C.c_double))
+        d.emission = sc.emission.ctypes.data_as(C.POINTER(C.c_double))
+        o = _Options()
+        self._lib.renderer_default_options(C.byref(o))
+        o.device, o.n_gpus = device, n_gpus
+        o.compat, o.precision = _COMPAT[compat], _PRECISION[precision]
+        o.variant, o.accel = _VARIANT[variant], _ACCEL[accel]
+        o.max_depth, o.seed = max_depth, seed
+        o.sample_begin, o.sample_end = sample_begin, sample_end
+        self.compat = compat
+        _check(self._lib, self._lib.renderer_create(C.byref(d), C.byref(o), C.byref(self._h)))
+
+    # -- the drop-in call: host buffers in, host buffers out
+    def render(self, want_image: bool = True, want_hits: bool = False) -> RenderResult:
+        sc = self.scene
+        img = np.empty((sc.height, sc.width, 3), np.float32) if want_image else None
+        hits = np.empty((sc.height, sc.width, sc.superSamples, sc.superSamples), np.int32) if want_hits else None
+        st = _Stats()
+        _check(self._lib, self._lib.renderer_render(
+            self._h, img.ctypes.data if img is not None else None, hits.ctypes.data if hits is not None else None, C.byref(st)))
+        return RenderResult(img, hits, _stats(st))
+
+    # -- device-resident pass on a caller-supplied CUDA stream (0 = default stream)
+    def render_async(self, stream: int = 0) -> None:
+        _check(self._lib, self._lib.renderer_render_async(self._h, C.c_void_p(stream)))
+
+    def read_stats(self) -> Stats:
+        st = _Stats()
+        _check(self._lib, self._lib.renderer_read_stats(self._h, C.byref(st)))
+        return _stats(st)
+
+    def device_accum_ptr(self) -> int:
+        return int(self._lib.renderer_device_accum(self._h) or 0)
+
+    def set_accum_buffer(self, device_ptr: int) -> None:
+        _check(self._lib, self._lib.renderer_set_accum_buffer(self._h, C.c_void_p(device_ptr)))
+
+    def read_image_f64(self) -> np.ndarray:
+        sc = self.scene
+        out = np.empty((sc.height, sc.width, 3), np.float64)
+        _check(self._lib, self._lib.renderer_read_image_f64(self._h, out.ctypes.data))
+        return out
+
+    def read_u8(self) -> np.ndarray:
+        sc = self.scene
+        out = np.empty((sc.height, sc.width, 3), np.uint8)
+        _check(self._lib, self._lib.renderer_read_u8(self._h, out.ctypes.data))
+        return out
+
+    def closest_hit(self, org: np.ndarray, dir: np.ndarray, mode: str = "f64", origin_id: Optional[np.ndarray] = None):
+        org = np.ascontiguousarray(org, np.float64).reshape(-1, 3)
+        dir = np.ascontiguousarray(dir, np.float64).reshape(-1, 3)
+        n = org.shape[0]
+        hit = np.empty(n, np.int32)
+        t = np.empty(n, np.float64)
+        oid = None if origin_id is None else np.ascontiguousarray(origin_id, np.int32)
+        _check(self._lib, self._lib.rtm_debug_closest_hit(
+            self._h, 0 if mode == "f64" else 1, n, org.ctypes.data, dir.ctypes.data,
+            oid.ctypes.data if oid is not None else None, hit.ctypes.data, t.ctypes.data))
+        return hit, t
+
+    def close(self) -> None:
+        if getattr(self, "_h", None) and self._h.value:
+            self._lib.renderer_destroy(self._h)
+            self._h = C.c_void_p()
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+    def __enter__(self):
+        return self
+
+    def __exit__(self, *a):
+        self.close()
+
+
+def philox_device(n: int, c1: int, c2: int, c3: int, k0: int, k1: int, device: int = 0) -> np.ndarray:
+    lib = load_library()
+    out = np.empty((n, 4), np.uint32)
+    _check(lib, lib.rtm_debug_philox(device, n, c1, c2, c3, k0, k1, out.ctypes.data))
+    return out
+
+
+def fp32_peak_tflops(device: int = 0):
+    lib = load_library()
+    tf, mhz = C.c_double(), C.c_double()
+    _check(lib, lib.rtm_debug_fp32_peak(device, C.byref(tf), C.byref(mhz)))
+    return tf.value, mhz.value

@@ -1,0 +1,242 @@
+// kernels_exact.cu — the FP64 kernels whose results are compared BIT-FOR-BIT with
+// the reference: camera-ray generation, ray/sphere test, closest-hit search,
+// the L-HEAD image, and the reference-faithful FP64 bounce loop.
+//
+// This translation unit is compiled with -fmad=false: the reference is built
+// without FMA contraction (x86-64 SSE2), and one fused multiply-add would change
+// hit indices.  IEEE sqrt/div for float and double are nvcc's defaults
+// (-prec-sqrt=true -prec-div=true).  Citations are to /root/reference/src.
+#include "rtm_internal.h"
+#include "philox.cuh"
+
+#include <float.h>
+
+namespace {
+
+struct d3 {
+    double x, y, z;
+};
+__device__ __forceinline__ d3 mk(double x, double y, double z) { return d3{x, y, z}; }
+__device__ __forceinline__ d3 add(d3 a, d3 b) { return mk(a.x + b.x, a.y + b.y, a.z + b.z); }
+__device__ __forceinline__ d3 sub(d3 a, d3 b) { return mk(a.x - b.x, a.y - b.y, a.z - b.z); }
+__device__ __forceinline__ d3 mul(d3 a, d3 b) { return mk(a.x * b.x, a.y * b.y, a.z * b.z); }
+__device__ __forceinline__ d3 scale(d3 a, double s) { return mk(a.x * s, a.y * s, a.z * s); }
+__device__ __forceinline__ d3 divs(d3 a, double s) { return mk(a.x / s, a.y / s, a.z / s); }
+// Ray.h:61-63: (ax*bx + ay*by) + az*bz
+__device__ __forceinline__ double dot(d3 a, d3 b) { return a.x * b.x + a.y * b.y + a.z * b.z; }
+// Ray.h:64-66: the y component is written -a.x*b.z + a.z*b.x
+__device__ __forceinline__ d3 cross(d3 a, d3 b) {
+    return mk(a.y * b.z - a.z * b.y, -a.x * b.z + a.z * b.x, a.x * b.y - a.y * b.x);
+}
+// Ray.h:67-72: Magnitude is sqrtf of the double sum (float argument, float
+// sqrt); Normalize is three divides by that float-rounded length.
+__device__ __forceinline__ d3 normalize(d3 a) {
+    const double m = (double)__fsqrt_rn(__double2float_rn(a.x * a.x + a.y * a.y + a.z * a.z));
+    return divs(a, m);
+}
+
+// SettingData.cpp:197-223 (distance only; the normal is derived for the winner).
+__device__ __forceinline__ bool sphere_test(d3 c, double r2, d3 o, d3 d, double& t) {
+    const d3 p_o = sub(c, o);
+    const double b = dot(p_o, d);
+    const double D4 = b * b - dot(p_o, p_o) + r2;
+    if (D4 < 0.0) return false;  // a NaN discriminant passes, as in the reference
+    const double s = sqrt(D4);
+    const double t1 = b - s, t2 = b + s;
+    const double minValue = (double)1e-5f;  // `const float minValue = 1e-5`
+    if (t1 < minValue && t2 < minValue) return false;
+    t = (t1 > 0.001) ? t1 : t2;
+    return true;
+}
+
+// Renderer.cpp:58-73: strict `<` keeps the lowest index on exact ties; `t > 0`.
+__device__ __forceinline__ int closest_hit(const RtmSceneF64& sc, d3 o, d3 d, double& best) {
+    int id = -1;
+    best = DBL_MAX;
+    for (int i = 0; i < sc.n; ++i) {
+        double t;
+        if (sphere_test(mk(__ldg(sc.cx + i), __ldg(sc.cy + i), __ldg(sc.cz + i)), __ldg(sc.r2 + i), o, d, t) &&
+            t < best && t > 0.0) {
+            best = t;
+            id = i;
+        }
+    }
+    return id;
+}
+
+__device__ __forceinline__ d3 sphere_center(const RtmSceneF64& sc, int i) {
+    return mk(__ldg(sc.cx + i), __ldg(sc.cy + i), __ldg(sc.cz + i));
+}
+
+// Renderer.cpp:227-232.  `rate` is float, rate*sx is a float product, the
+// 2.0f / 1.0f literals widen to double; evaluation is left to right.
+__device__ __forceinline__ d3 camera_dir(const RtmFrame& f, int x, int y, int sx, int sy) {
+    const float fx = f.rate * (float)sx, fy = f.rate * (float)sy;
+    const double px = 2.0 * ((double)x + (double)fx) / (double)f.W - 1.0;
+    const double py = 2.0 * ((double)y + (double)fy) / (double)f.H - 1.0;
+    const d3 v = mk(f.ax[0] * px + f.ay[0] * py + f.az[0], f.ax[1] * px + f.ay[1] * py + f.az[1],
+                    f.ax[2] * px + f.ay[2] * py + f.az[2]);
+    return normalize(v);
+}
+
+__device__ __forceinline__ void decode_sub(const RtmFrame& f, uint64_t q, int& x, int& y, int& sx, int& sy) {
+    const uint32_t ss = (uint32_t)f.ss;
+    sy = (int)(q % ss) + 1;
+    q /= ss;
+    sx = (int)(q % ss) + 1;
+    q /= ss;
+    x = (int)(q % (uint32_t)f.W);
+    y = (int)(q / (uint32_t)f.W);
+}
+
+// Renderer.cpp:43-49 with std::max/std::min semantics
+__device__ __forceinline__ double clamp01(double v) {
+    const double lo = (v < 0.0) ? 0.0 : v;
+    return (1.0 < lo) ? 1.0 : lo;
+}
+
+// ---- K1: primary pass, one thread per sub-pixel ----------------------------
+__global__ void __launch_bounds__(256) primary_f64_kernel(RtmSceneF64 sc, RtmPassParams p, int32_t* __restrict__ hits,
+                                                          float4* __restrict__ records) {
+    const uint64_t q = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (q >= p.n_sub) return;
+    int x, y, sx, sy;
+    decode_sub(p.frame, q, x, y, sx, sy);
+    const d3 o = mk(p.frame.o[0], p.frame.o[1], p.frame.o[2]);
+    const d3 d = camera_dir(p.frame, x, y, sx, sy);
+    double t;
+    const int id = closest_hit(sc, o, d, t);
+    if (hits) hits[q] = id;
+    if (records) {
+        float4 rec;
+        if (id < 0) {
+            rec = make_float4(0.f, 0.f, 0.f, __uint_as_float(RTM_REC_MISS));
+        } else {
+            const d3 hp = add(scale(d, t), o);                          // Renderer.cpp:79
+            const d3 n = normalize(sub(add(o, scale(d, t)), sphere_center(sc, id)));  // SettingData.cpp:214-215
+            const uint32_t flip = (dot(n, d) < 0.0) ? 0u : RTM_REC_FLIP;   // Renderer.cpp:82-83
+            rec = make_float4((float)(hp.x - p.refd[0]), (float)(hp.y - p.refd[1]), (float)(hp.z - p.refd[2]),
+                              __uint_as_float((uint32_t)id | flip));
+        }
+        records[q] = rec;
+    }
+}
+
+// ---- L-HEAD image: one thread per pixel -------------------------------------
+// At HEAD the hit normal never reaches PathTracing (SettingData.h:21 takes it by
+// value), the bounce ray is NaN and misses, so every sample is the emission of
+// the primary hit (Renderer.cpp:109,112); accumulation as Renderer.cpp:223-248.
+__global__ void __launch_bounds__(128) head_image_kernel(RtmSceneF64 sc, RtmPassParams p, const int32_t* __restrict__ hits,
+                                                         double* __restrict__ image64, float4* __restrict__ accum) {
+    const uint32_t pix = blockIdx.x * blockDim.x + threadIdx.x;
+    const uint32_t npix = (uint32_t)p.frame.W * (uint32_t)p.frame.H;
+    if (pix >= npix) return;
+    const int ss = p.frame.ss;
+    d3 acc = mk(0, 0, 0);
+    for (int j = 0; j < ss * ss; ++j) {
+        const int id = hits[(uint64_t)pix * (ss * ss) + j];
+        d3 cal = (id < 0) ? mk(0, 0, 0)
+                          : mk(__ldg(sc.emission + 3 * id), __ldg(sc.emission + 3 * id + 1), __ldg(sc.emission + 3 * id + 2));
+        cal = divs(divs(divs(cal, (double)ss), (double)ss), (double)p.frame.S);  // Renderer.cpp:240
+        cal = mk(clamp01(cal.x), clamp01(cal.y), clamp01(cal.z));               // :241
+        for (int s = p.s_begin; s < p.s_end; ++s) acc = add(acc, cal);          // :242
+    }
+    if (image64) {
+        image64[3 * (uint64_t)pix + 0] = acc.x;
+        image64[3 * (uint64_t)pix + 1] = acc.y;
+        image64[3 * (uint64_t)pix + 2] = acc.z;
+    }
+    accum[pix] = make_float4((float)acc.x, (float)acc.y, (float)acc.z, 0.f);
+}
+
+// ---- reference-faithful FP64 bounce loop: one thread per sub-pixel -----------
+// Renderer.cpp:57-117 line by line (L-ABC), the recursion unrolled forward:
+// L = e0 + k0*(e1 + k1*(...)) is accumulated as L += T*e, T *= k.
+__global__ void __launch_bounds__(128) radiance_f64_kernel(RtmSceneF64 sc, RtmPassParams p, float4* __restrict__ records,
+                                                           RtmCounters* __restrict__ counters) {
+    const uint64_t q = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    unsigned long long rays = 0;
+    if (q < p.n_sub) {
+        int x, y, sx, sy;
+        decode_sub(p.frame, q, x, y, sx, sy);
+        const d3 o0 = mk(p.frame.o[0], p.frame.o[1], p.frame.o[2]);
+        const d3 d0 = camera_dir(p.frame, x, y, sx, sy);
+        const double PI = 3.14159265358979323846;
+        d3 acc = mk(0, 0, 0);
+        for (int s = p.s_begin; s < p.s_end; ++s) {
+            d3 o = o0, d = d0, L = mk(0, 0, 0), T = mk(1, 1, 1);
+            for (int depth = 0; depth < p.max_depth; ++depth) {
+                ++rays;
+                double t;
+                const int id = closest_hit(sc, o, d, t);
+                if (id < 0) break;
+                const d3 e = mk(__ldg(sc.emission + 3 * id), __ldg(sc.emission + 3 * id + 1), __ldg(sc.emission + 3 * id + 2));
+                L = add(L, mul(T, e));
+                const uint4 r = rtm_philox4x32_10(make_uint4((uint32_t)q, (uint32_t)(q >> 32), (uint32_t)s, (uint32_t)depth),
+                                                  p.seed_lo, p.seed_hi);
+                const double kd = __ldg(sc.kd + id);
+                if (!(rtm_u01_f64(r.x, r.y) <= kd)) break;  // :78 / :112
+                const d3 col = mk(__ldg(sc.color + 3 * id), __ldg(sc.color + 3 * id + 1), __ldg(sc.color + 3 * id + 2));
+                T = mul(T, divs(col, kd));                   // colorKD(), SettingData.h:11-13
+                const d3 hp = add(scale(d, t), o);           // :79
+                const d3 n = normalize(sub(add(o, scale(d, t)), sphere_center(sc, id)));
+                const d3 w = (dot(n, d) < 0.0) ? n : scale(n, -1.0);  // :82-83,87
+                const double r1 = 2 * PI * rtm_u01_f64_32(r.z);       // :88
+                const double r2 = rtm_u01_f64_32(r.w);                // :89
+                const double r2s = sqrt(r2);                          // :90
+                d3 u;
+                if (fabs(w.x) > (double)FLT_MIN) u = normalize(cross(mk(0, 1, 0), w));  // :96-101
+                else u = normalize(cross(mk(1, 0, 0), w));
+                const d3 v = cross(w, u);                                               // :102
+                d = normalize(add(add(scale(scale(u, cos(r1)), r2s), scale(scale(v, sin(r1)), r2s)),
+                                  scale(w, sqrt(1.0 - r2))));                          // :103-107
+                o = hp;
+            }
+            d3 cal = divs(divs(divs(L, (double)p.frame.ss), (double)p.frame.ss), (double)p.frame.S);
+            acc = add(acc, mk(clamp01(cal.x), clamp01(cal.y), clamp01(cal.z)));
+        }
+        records[q] = make_float4((float)acc.x, (float)acc.y, (float)acc.z, 0.f);
+    }
+    // one atomic per warp
+    for (int off = 16; off > 0; off >>= 1) rays += __shfl_down_sync(0xffffffffu, rays, off);
+    if ((threadIdx.x & 31) == 0 && rays) {
+        atomicAdd(&counters->rays_ref, rays);
+        atomicAdd(&counters->rays_traced, rays);
+        atomicAdd(&counters->tests, rays * (unsigned long long)sc.n);
+    }
+}
+
+// ---- test hook: arbitrary rays through the exact closest-hit loop -----------
+__global__ void closest_hit_f64_kernel(RtmSceneF64 sc, uint32_t n, const double* __restrict__ org,
+                                       const double* __restrict__ dir, int32_t* __restrict__ hit, double* __restrict__ tout) {
+    const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    double t;
+    const int id = closest_hit(sc, mk(org[3 * i], org[3 * i + 1], org[3 * i + 2]), mk(dir[3 * i], dir[3 * i + 1], dir[3 * i + 2]), t);
+    hit[i] = id;
+    tout[i] = t;
+}
+
+}  // namespace
+
+void rtm_launch_primary_f64(const RtmSceneF64& sc, const RtmPassParams& p, int32_t* hits, float4* records, cudaStream_t st) {
+    const uint32_t blocks = (uint32_t)((p.n_sub + 255) / 256);
+    primary_f64_kernel<<<blocks, 256, 0, st>>>(sc, p, hits, records);
+}
+
+void rtm_launch_head_image(const RtmSceneF64& sc, const RtmPassParams& p, const int32_t* hits, double* image64,
+                           float4* accum, cudaStream_t st) {
+    const uint32_t npix = (uint32_t)p.frame.W * (uint32_t)p.frame.H;
+    head_image_kernel<<<(npix + 127) / 128, 128, 0, st>>>(sc, p, hits, image64, accum);
+}
+
+void rtm_launch_radiance_f64(const RtmSceneF64& sc, const RtmPassParams& p, float4* records, RtmCounters* counters,
+                             cudaStream_t st) {
+    const uint32_t blocks = (uint32_t)((p.n_sub + 127) / 128);
+    radiance_f64_kernel<<<blocks, 128, 0, st>>>(sc, p, records, counters);
+}
+
+void rtm_launch_closest_hit_f64(const RtmSceneF64& sc, uint32_t n, const double* org, const double* dir, int32_t* hit,
+                                double* t, cudaStream_t st) {
+    closest_hit_f64_kernel<<<(n + 127) / 128, 128, 0, st>>>(sc, n, org, dir, hit, t);
+}

@@ -1,0 +1,34 @@
+// philox.cuh — Philox4x32-10 (Salmon et al., "Parallel Random Numbers: As Easy
+// as 1, 2, 3", SC'11), counter-based: every (sub-pixel, sample, bounce) triple
+// owns one 128-bit counter value, so the image is a pure function of
+// (scene, seed) and independent of how the sample budget is sliced over GPUs.
+// Replaces the reference's shared std::mt19937 (src/Renderer.cpp:210-213).
+#pragma once
+#include <stdint.h>
+
+#define RTM_PHILOX_M0 0xD2511F53u
+#define RTM_PHILOX_M1 0xCD9E8D57u
+#define RTM_PHILOX_W0 0x9E3779B9u
+#define RTM_PHILOX_W1 0xBB67AE85u
+
+__device__ __forceinline__ uint4 rtm_philox4x32_10(uint4 c, uint32_t k0, uint32_t k1) {
+#pragma unroll
+    for (int r = 0; r < 10; ++r) {
+        const uint32_t hi0 = __umulhi(RTM_PHILOX_M0, c.x), lo0 = RTM_PHILOX_M0 * c.x;
+        const uint32_t hi1 = __umulhi(RTM_PHILOX_M1, c.z), lo1 = RTM_PHILOX_M1 * c.z;
+        c = make_uint4(hi1 ^ c.y ^ k0, lo1, hi0 ^ c.w ^ k1, lo0);
+        k0 += RTM_PHILOX_W0;
+        k1 += RTM_PHILOX_W1;
+    }
+    return c;
+}
+
+// [0,1) with 24 random bits (exact in float)
+__device__ __forceinline__ float rtm_u01_f32(uint32_t x) { return (float)(x >> 8) * 5.9604644775390625e-8f; }
+// [0,1) with 53 random bits
+__device__ __forceinline__ double rtm_u01_f64(uint32_t hi, uint32_t lo) {
+    const unsigned long long v = (((unsigned long long)hi << 32) | lo) >> 11;
+    return (double)v * 1.1102230246251565e-16;
+}
+// (0,1) with 32 random bits
+__device__ __forceinline__ double rtm_u01_f64_32(uint32_t x) { return ((double)x + 0.5) * 2.3283064365386963e-10; }

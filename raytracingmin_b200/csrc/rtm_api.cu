@@ -1,0 +1,615 @@
+// rtm_api.cu — implementation of the C ABI in include/rtm_b200.h: scene
+// flattening, device memory, launch orchestration, the single-process multi-GPU
+// path (sample-budget slices + one ncclReduce) and the test hooks.
+//
+// Host arithmetic that feeds the bit-exact kernels (camera frame, r*r, kd) is
+// done here in the reference's own types and order (src/Renderer.cpp:202-208,
+// src/SettingData.cpp:200, src/SettingData.h:14-16); this file is compiled with
+// -ffp-contract=off.
+#include "../../include/rtm_b200.h"
+#include "rtm_internal.h"
+
+#include <dlfcn.h>
+#include <nccl.h>  // types only; the library is dlopen'ed when n_gpus > 1
+
+#include <chrono>
+#include <cmath>
+#include <cstdarg>
+#include <cstdio>
+#include <cstring>
+#include <mutex>
+#include <string>
+#include <vector>
+
+namespace {
+
+thread_local std::string g_err;
+
+int fail(int code, const char* fmt, ...) {
+    char buf[512];
+    va_list ap;
+    va_start(ap, fmt);
+    vsnprintf(buf, sizeof buf, fmt, ap);
+    va_end(ap);
+    g_err = buf;
+    return code;
+}
+
+#define CU(call)                                                                                   \
+    do {                                                                                           \
+        cudaError_t e_ = (call);                                                                   \
+        if (e_ != cudaSuccess) return fail(RTM_E_CUDA, "%s: %s (%s:%d)", #call, cudaGetErrorString(e_), __FILE__, __LINE__); \
+    } while (0)
+
+// ---- NCCL through dlopen (only the six calls the reduce needs) ----------------
+struct NcclApi {
+    void* lib = nullptr;
+    ncclResult_t (*CommInitAll)(ncclComm_t*, int, const int*) = nullptr;
+    ncclResult_t (*CommDestroy)(ncclComm_t) = nullptr;
+    ncclResult_t (*Reduce)(const void*, void*, size_t, ncclDataType_t, ncclRedOp_t, int, ncclComm_t, cudaStream_t) = nullptr;
+    ncclResult_t (*GroupStart)() = nullptr;
+    ncclResult_t (*GroupEnd)() = nullptr;
+    const char* (*GetErrorString)(ncclResult_t) = nullptr;
+};
+NcclApi g_nccl;
+std::mutex g_nccl_mu;
+
+int load_nccl() {
+    std::lock_guard<std::mutex> lk(g_nccl_mu);
+    if (g_nccl.lib) return RTM_OK;
+    const char* names[] = {"libnccl.so.2", "libnccl.so"};
+    void* lib = nullptr;
+    for (const char* nm : names) {
+        lib = dlopen(nm, RTLD_NOW | RTLD_GLOBAL);
+        if (lib) break;
+    }
+    if (!lib) return fail(RTM_E_NCCL, "cannot dlopen libnccl.so.2: %s", dlerror());
+    NcclApi a;
+    a.lib = lib;
+    a.CommInitAll = (decltype(a.CommInitAll))dlsym(lib, "ncclCommInitAll");
+    a.CommDestroy = (decltype(a.CommDestroy))dlsym(lib, "ncclCommDestroy");
+    a.Reduce = (decltype(a.Reduce))dlsym(lib, "ncclReduce");
+    a.GroupStart = (decltype(a.GroupStart))dlsym(lib, "ncclGroupStart");
+    a.GroupEnd = (decltype(a.GroupEnd))dlsym(lib, "ncclGroupEnd");
+    a.GetErrorString = (decltype(a.GetErrorString))dlsym(lib, "ncclGetErrorString");
+    if (!a.CommInitAll || !a.CommDestroy || !a.Reduce || !a.GroupStart || !a.GroupEnd || !a.GetErrorString)
+        return fail(RTM_E_NCCL, "libnccl is missing a required symbol");
+    g_nccl = a;
+    return RTM_OK;
+}
+
+#define NC(call)                                                                                            \
+    do {                                                                                                    \
+        ncclResult_t r_ = (call);                                                                           \
+        if (r_ != ncclSuccess) return fail(RTM_E_NCCL, "%s: %s", #call, g_nccl.GetErrorString(r_));        \
+    } while (0)
+
+// ---- host-side reference arithmetic ------------------------------------------
+struct v3 {
+    double x, y, z;
+};
+v3 vsub(v3 a, v3 b) { return {a.x - b.x, a.y - b.y, a.z - b.z}; }
+v3 vneg(v3 a) { return {-a.x, -a.y, -a.z}; }
+v3 vscale(v3 a, double s) { return {a.x * s, a.y * s, a.z * s}; }
+v3 vcross(v3 a, v3 b) { return {a.y * b.z - a.z * b.y, -a.x * b.z + a.z * b.x, a.x * b.y - a.y * b.x}; }  // Ray.h:64-66
+v3 vnormalize(v3 a) {                                                                                        // Ray.h:67-72
+    const double m = (double)sqrtf((float)(a.x * a.x + a.y * a.y + a.z * a.z));
+    return {a.x / m, a.y / m, a.z / m};
+}
+
+struct GpuCtx {
+    int device = 0;
+    int sm_count = 148;
+    cudaStream_t stream = nullptr;
+    cudaEvent_t ev0 = nullptr, ev1 = nullptr;
+    double* d_scene64 = nullptr;  // one allocation: cx cy cz r2 kd [n] + emission color [3n]
+    RtmSceneF64 s64{};
+    float4* records = nullptr;
+    float4* accum = nullptr;
+    bool accum_owned = true;
+    int32_t* hits = nullptr;
+    double* image64 = nullptr;
+    unsigned char* u8 = nullptr;
+    RtmCounters* counters = nullptr;
+    float4* h_accum = nullptr;  // pinned staging
+    int32_t s_begin = 0, s_end = 0;
+    ncclComm_t comm = nullptr;
+};
+
+}  // namespace
+
+struct rtm_renderer {
+    rtm_options opt{};
+    int32_t W = 0, H = 0, S = 0, ss = 0, n = 0;
+    uint64_t n_pix = 0, n_sub = 0;
+    RtmFrame frame{};
+    RtmSceneF32Host f32{};
+    double refd[3]{};
+    std::vector<GpuCtx> gpus;
+    int32_t last_launches = 0;
+    bool hits_valid = false;
+};
+
+namespace {
+
+void free_ctx(GpuCtx& c) {
+    cudaSetDevice(c.device);
+    if (c.comm && g_nccl.CommDestroy) g_nccl.CommDestroy(c.comm);
+    if (c.d_scene64) cudaFree(c.d_scene64);
+    if (c.records) cudaFree(c.records);
+    if (c.accum && c.accum_owned) cudaFree(c.accum);
+    if (c.hits) cudaFree(c.hits);
+    if (c.image64) cudaFree(c.image64);
+    if (c.u8) cudaFree(c.u8);
+    if (c.counters) cudaFree(c.counters);
+    if (c.h_accum) cudaFreeHost(c.h_accum);
+    if (c.ev0) cudaEventDestroy(c.ev0);
+    if (c.ev1) cudaEventDestroy(c.ev1);
+    if (c.stream) cudaStreamDestroy(c.stream);
+    c = GpuCtx{};
+}
+
+RtmPassParams make_params(const rtm_renderer* r, const GpuCtx& c) {
+    RtmPassParams p{};
+    p.frame = r->frame;
+    p.s_begin = c.s_begin;
+    p.s_end = c.s_end;
+    p.max_depth = r->opt.max_depth;
+    p.seed_lo = (uint32_t)r->opt.seed;
+    p.seed_hi = (uint32_t)(r->opt.seed >> 32);
+    p.inv_norm = (float)(1.0 / ((double)r->ss * r->ss * r->S));
+    for (int k = 0; k < 3; ++k) {
+        p.refd[k] = r->refd[k];
+        p.ref[k] = (float)r->refd[k];
+    }
+    p.n_sub = r->n_sub;
+    return p;
+}
+
+int ensure_hits(rtm_renderer* r, GpuCtx& c) {
+    if (!c.hits) CU(cudaMalloc(&c.hits, r->n_sub * sizeof(int32_t)));
+    return RTM_OK;
+}
+
+// Enqueue one full pass on ctx c / stream st.  want_hits: also write the hit map.
+int enqueue_pass(rtm_renderer* r, GpuCtx& c, cudaStream_t st, bool want_hits, int* launches) {
+    CU(cudaSetDevice(c.device));
+    const RtmPassParams p = make_params(r, c);
+    CU(cudaMemsetAsync(c.counters, 0, sizeof(RtmCounters), st));
+    if (r->opt.compat == RTM_COMPAT_HEAD) {
+        int rc = ensure_hits(r, c);
+        if (rc) return rc;
+        if (!c.image64) CU(cudaMalloc(&c.image64, r->n_pix * 3 * sizeof(double)));
+        rtm_launch_primary_f64(c.s64, p, c.hits, nullptr, st);
+        rtm_launch_head_image(c.s64, p, c.hits, c.image64, c.accum, st);
+        *launches += 2;
+    } else if (r->opt.precision == RTM_PRECISION_F64) {
+        if (want_hits) {
+            int rc = ensure_hits(r, c);
+            if (rc) return rc;
+            rtm_launch_primary_f64(c.s64, p, c.hits, nullptr, st);
+            *launches += 1;
+        }
+        rtm_launch_radiance_f64(c.s64, p, c.records, c.counters, st);
+        rtm_launch_accumulate(p, c.records, c.accum, st);
+        *launches += 2;
+    } else {
+        if (want_hits) {
+            int rc = ensure_hits(r, c);
+            if (rc) return rc;
+        }
+        CU(rtm_upload_scene_f32(r->f32, st));
+        rtm_launch_primary_f64(c.s64, p, want_hits ? c.hits : nullptr, c.records, st);
+        rtm_launch_radiance_mega(r->n, p, c.records, c.counters, c.sm_count, st);
+        rtm_launch_accumulate(p, c.records, c.accum, st);
+        *launches += 3;
+    }
+    CU(cudaGetLastError());
+    return RTM_OK;
+}
+
+int fill_stats(rtm_renderer* r, rtm_stats* st) {
+    memset(st, 0, sizeof *st);
+    for (auto& c : r->gpus) {
+        CU(cudaSetDevice(c.device));
+        RtmCounters h{};
+        CU(cudaMemcpy(&h, c.counters, sizeof h, cudaMemcpyDeviceToHost));
+        const uint64_t ns = (uint64_t)(c.s_end - c.s_begin);
+        st->samples += r->n_sub * ns;
+        if (r->opt.compat == RTM_COMPAT_HEAD) {
+            // one closest-hit query per sub-pixel on the device; the reference makes
+            // 2 PathTracing calls per sample that hits a kd>0 surface, else 1 — reported
+            // conservatively as 1 per sample.
+            st->rays += r->n_sub * ns;
+            st->rays_traced += r->n_sub;
+            st->sphere_tests += r->n_sub * (uint64_t)r->n;
+        } else if (r->opt.precision == RTM_PRECISION_F64) {
+            st->rays += h.rays_ref;
+            st->rays_traced += h.rays_traced;
+            st->sphere_tests += h.tests;
+        } else {
+            st->rays += h.rays_ref;
+            st->rays_traced += h.rays_traced + r->n_sub;
+            st->sphere_tests += h.tests + r->n_sub * (uint64_t)r->n;
+        }
+    }
+    st->n_gpus = (int32_t)r->gpus.size();
+    st->kernel_launches = r->last_launches;
+    return RTM_OK;
+}
+
+}  // namespace
+
+extern "C" {
+
+int renderer_abi_version(void) { return RTM_ABI_VERSION; }
+
+const char* renderer_last_error(void) { return g_err.c_str(); }
+
+void renderer_default_options(rtm_options* o) {
+    if (!o) return;
+    memset(o, 0, sizeof *o);
+    o->device = 0;
+    o->n_gpus = 1;
+    o->compat = RTM_COMPAT_ABC;
+    o->precision = RTM_PRECISION_F32;
+    o->variant = RTM_VARIANT_MEGA;
+    o->accel = RTM_ACCEL_AUTO;
+    o->max_depth = 0;
+    o->seed = 0x5EEDull;
+}
+
+void renderer_destroy(rtm_renderer* r) {
+    if (!r) return;
+    for (auto& c : r->gpus) free_ctx(c);
+    delete r;
+}
+
+int renderer_create(const rtm_scene_desc* sc, const rtm_options* opt_in, rtm_renderer** out) {
+    if (!sc || !out) return fail(RTM_E_INVALID, "renderer_create: null argument");
+    *out = nullptr;
+    rtm_options opt;
+    if (opt_in) opt = *opt_in;
+    else renderer_default_options(&opt);
+    if (sc->width <= 0 || sc->height <= 0 || sc->samples <= 0 || sc->superSamples <= 0)
+        return fail(RTM_E_INVALID, "width/height/samples/superSamples must be positive (got %d %d %d %d)", sc->width,
+                    sc->height, sc->samples, sc->superSamples);
+    if (sc->n_spheres < 0 || (sc->n_spheres > 0 && (!sc->position || !sc->radius || !sc->color || !sc->emission)))
+        return fail(RTM_E_INVALID, "scene arrays missing for %d spheres", sc->n_spheres);
+    if (sc->n_spheres > (int32_t)RTM_REC_IDMASK) return fail(RTM_E_INVALID, "too many spheres");
+    if (opt.n_gpus < 1) opt.n_gpus = 1;
+    if (opt.max_depth <= 0) opt.max_depth = 256;
+    if (opt.compat != RTM_COMPAT_HEAD && opt.compat != RTM_COMPAT_ABC) return fail(RTM_E_INVALID, "bad compat %d", opt.compat);
+    if (opt.precision != RTM_PRECISION_F32 && opt.precision != RTM_PRECISION_F64)
+        return fail(RTM_E_INVALID, "bad precision %d", opt.precision);
+    if (opt.sample_begin == 0 && opt.sample_end == 0) opt.sample_end = sc->samples;
+    if (opt.sample_begin < 0 || opt.sample_end > sc->samples || opt.sample_begin >= opt.sample_end)
+        return fail(RTM_E_INVALID, "bad sample slice [%d,%d) of %d", opt.sample_begin, opt.sample_end, sc->samples);
+    if (opt.variant != RTM_VARIANT_MEGA) return fail(RTM_E_UNSUPPORTED, "variant %d not built", opt.variant);
+    const bool f32_path = (opt.compat == RTM_COMPAT_ABC && opt.precision == RTM_PRECISION_F32);
+    if (f32_path && sc->n_spheres > RTM_MAX_CONST_SPHERES)
+        return fail(RTM_E_UNSUPPORTED, "FP32 brute-force path holds at most %d spheres", RTM_MAX_CONST_SPHERES);
+
+    int ndev = 0;
+    cudaError_t ce = cudaGetDeviceCount(&ndev);
+    if (ce != cudaSuccess || ndev == 0)
+        return fail(RTM_E_CUDA, "no CUDA device (%s); this library has no CPU fallback", cudaGetErrorString(ce));
+    if (opt.device < 0 || opt.device + opt.n_gpus > ndev)
+        return fail(RTM_E_INVALID, "devices %d..%d requested, %d present", opt.device, opt.device + opt.n_gpus - 1, ndev);
+    if (opt.n_gpus > 1 && (opt.sample_end - opt.sample_begin) < opt.n_gpus)
+        return fail(RTM_E_INVALID, "cannot slice %d samples over %d GPUs", opt.sample_end - opt.sample_begin, opt.n_gpus);
+
+    rtm_renderer* r = new rtm_renderer();
+    r->opt = opt;
+    r->W = sc->width; r->H = sc->height; r->S = sc->samples; r->ss = sc->superSamples; r->n = sc->n_spheres;
+    r->n_pix = (uint64_t)r->W * r->H;
+    r->n_sub = r->n_pix * r->ss * r->ss;
+
+    // camera frame, src/Renderer.cpp:202-208
+    {
+        const v3 origin{sc->cam_origin[0], sc->cam_origin[1], sc->cam_origin[2]};
+        const v3 target{sc->cam_target[0], sc->cam_target[1], sc->cam_target[2]};
+        const v3 up{sc->cam_up[0], sc->cam_up[1], sc->cam_up[2]};
+        const v3 direction = vnormalize(vsub(target, origin));
+        const v3 camX = vneg(vnormalize(vcross(direction, up)));
+        const v3 camY = vcross(camX, direction);
+        const double fovx = (double)sc->fov;
+        const double fovy = fovx * r->H / r->W;
+        const v3 ax = vscale(camX, fovx), ay = vscale(camY, fovy);
+        RtmFrame& f = r->frame;
+        f.o[0] = origin.x; f.o[1] = origin.y; f.o[2] = origin.z;
+        f.ax[0] = ax.x; f.ax[1] = ax.y; f.ax[2] = ax.z;
+        f.ay[0] = ay.x; f.ay[1] = ay.y; f.ay[2] = ay.z;
+        f.az[0] = direction.x; f.az[1] = direction.y; f.az[2] = direction.z;
+        f.rate = (float)(1.0 / (1 + r->ss));  // Renderer.cpp:227
+        f.W = r->W; f.H = r->H; f.ss = r->ss; f.S = r->S;
+        r->refd[0] = origin.x; r->refd[1] = origin.y; r->refd[2] = origin.z;
+    }
+
+    // scene arrays
+    const int n = r->n;
+    std::vector<double> h64((size_t)n * 11 + 1);
+    double* cx = h64.data();
+    double* cy = cx + n;
+    double* cz = cy + n;
+    double* r2 = cz + n;
+    double* kd = r2 + n;
+    double* em = kd + n;
+    double* col = em + 3 * (size_t)n;
+    r->f32.n = n;
+    for (int i = 0; i < n; ++i) {
+        cx[i] = sc->position[3 * i]; cy[i] = sc->position[3 * i + 1]; cz[i] = sc->position[3 * i + 2];
+        const float rad = sc->radius[i];
+        const float rr = rad * rad;  // float product, SettingData.cpp:200
+        r2[i] = (double)rr;
+        const double c0 = sc->color[3 * i], c1 = sc->color[3 * i + 1], c2 = sc->color[3 * i + 2];
+        const double m01 = (c0 < c1) ? c1 : c0;
+        const float kdf = (float)((m01 < c2) ? c2 : m01);  // SettingData.h:14-16
+        kd[i] = (double)kdf;
+        for (int k = 0; k < 3; ++k) {
+            em[3 * i + k] = sc->emission[3 * i + k];
+            col[3 * i + k] = sc->color[3 * i + k];
+        }
+        if (f32_path) {
+            const double px = cx[i] - r->refd[0], py = cy[i] - r->refd[1], pz = cz[i] - r->refd[2];
+            RtmSceneF32Host& s = r->f32;
+            s.cx[i] = (float)px; s.cy[i] = (float)py; s.cz[i] = (float)pz;
+            // use the rounded centre consistently: K belongs to the sphere the FP32 kernel sees
+            const double fx = s.cx[i], fy = s.cy[i], fz = s.cz[i];
+            s.m2cx[i] = -2.0f * s.cx[i]; s.m2cy[i] = -2.0f * s.cy[i]; s.m2cz[i] = -2.0f * s.cz[i];
+            s.K[i] = (float)(fx * fx + fy * fy + fz * fz - (double)rad * (double)rad);
+            s.inv_r[i] = (float)(1.0 / (double)rad);
+            s.ex[i] = (float)em[3 * i]; s.ey[i] = (float)em[3 * i + 1]; s.ez[i] = (float)em[3 * i + 2];
+            s.kd[i] = kdf;
+            if (kdf > 0.f) {
+                s.kx[i] = (float)(c0 / (double)kdf); s.ky[i] = (float)(c1 / (double)kdf); s.kz[i] = (float)(c2 / (double)kdf);
+            } else {
+                s.kx[i] = s.ky[i] = s.kz[i] = 0.f;
+            }
+        }
+    }
+
+    // devices
+    const int S0 = opt.sample_begin, SN = opt.sample_end - opt.sample_begin;
+    r->gpus.resize(opt.n_gpus);
+    int rc = RTM_OK;
+    auto body = [&]() -> int {
+        for (int g = 0; g < opt.n_gpus; ++g) {
+            GpuCtx& c = r->gpus[g];
+            c.device = opt.device + g;
+            c.s_begin = S0 + (int)((int64_t)SN * g / opt.n_gpus);
+            c.s_end = S0 + (int)((int64_t)SN * (g + 1) / opt.n_gpus);
+            CU(cudaSetDevice(c.device));
+            cudaDeviceProp prop;
+            CU(cudaGetDeviceProperties(&prop, c.device));
+            c.sm_count = prop.multiProcessorCount;
+            CU(cudaStreamCreateWithFlags(&c.stream, cudaStreamNonBlocking));
+            CU(cudaEventCreate(&c.ev0));
+            CU(cudaEventCreate(&c.ev1));
+            CU(cudaMalloc(&c.d_scene64, h64.size() * sizeof(double)));
+            CU(cudaMemcpy(c.d_scene64, h64.data(), h64.size() * sizeof(double), cudaMemcpyHostToDevice));
+            c.s64.n = n;
+            c.s64.cx = c.d_scene64; c.s64.cy = c.s64.cx + n; c.s64.cz = c.s64.cy + n; c.s64.r2 = c.s64.cz + n;
+            c.s64.kd = c.s64.r2 + n; c.s64.emission = c.s64.kd + n; c.s64.color = c.s64.emission + 3 * (size_t)n;
+            if (opt.compat == RTM_COMPAT_ABC) CU(cudaMalloc(&c.records, r->n_sub * sizeof(float4)));
+            CU(cudaMalloc(&c.accum, r->n_pix * sizeof(float4)));
+            CU(cudaMemset(c.accum, 0, r->n_pix * sizeof(float4)));
+            CU(cudaMalloc(&c.counters, sizeof(RtmCounters)));
+            CU(cudaMemset(c.counters, 0, sizeof(RtmCounters)));
+        }
+        if (opt.n_gpus > 1) {
+            int lr = load_nccl();
+            if (lr) return lr;
+            std::vector<int> devs(opt.n_gpus);
+            std::vector<ncclComm_t> comms(opt.n_gpus);
+            for (int g = 0; g < opt.n_gpus; ++g) devs[g] = opt.device + g;
+            NC(g_nccl.CommInitAll(comms.data(), opt.n_gpus, devs.data()));
+            for (int g = 0; g < opt.n_gpus; ++g) r->gpus[g].comm = comms[g];
+        }
+        return RTM_OK;
+    };
+    rc = body();
+    if (rc != RTM_OK) {
+        const std::string keep = g_err;
+        renderer_destroy(r);
+        g_err = keep;
+        return rc;
+    }
+    *out = r;
+    return RTM_OK;
+}
+
+int renderer_render_async(rtm_renderer* r, void* stream) {
+    if (!r) return fail(RTM_E_INVALID, "null renderer");
+    if (r->gpus.size() != 1) return fail(RTM_E_UNSUPPORTED, "renderer_render_async drives one GPU per handle");
+    int launches = 0;
+    int rc = enqueue_pass(r, r->gpus[0], (cudaStream_t)stream, false, &launches);
+    r->last_launches = launches;
+    r->hits_valid = (r->opt.compat == RTM_COMPAT_HEAD);
+    return rc;
+}
+
+int renderer_read_stats(rtm_renderer* r, rtm_stats* st) {
+    if (!r || !st) return fail(RTM_E_INVALID, "null argument");
+    return fill_stats(r, st);
+}
+
+void* renderer_device_accum(rtm_renderer* r) { return r ? (void*)r->gpus[0].accum : nullptr; }
+void* renderer_device_hits(rtm_renderer* r) { return r ? (void*)r->gpus[0].hits : nullptr; }
+
+int renderer_set_accum_buffer(rtm_renderer* r, void* p) {
+    if (!r || !p) return fail(RTM_E_INVALID, "null argument");
+    if (r->gpus.size() != 1) return fail(RTM_E_UNSUPPORTED, "one GPU per handle");
+    GpuCtx& c = r->gpus[0];
+    CU(cudaSetDevice(c.device));
+    if (c.accum && c.accum_owned) CU(cudaFree(c.accum));
+    c.accum = (float4*)p;
+    c.accum_owned = false;
+    return RTM_OK;
+}
+
+int renderer_render(rtm_renderer* r, float* rgb_out, int32_t* hit_out, rtm_stats* stats) {
+    if (!r) return fail(RTM_E_INVALID, "null renderer");
+    const auto t0 = std::chrono::steady_clock::now();
+    const int G = (int)r->gpus.size();
+    int launches = 0;
+    for (int g = 0; g < G; ++g) {
+        GpuCtx& c = r->gpus[g];
+        CU(cudaSetDevice(c.device));
+        CU(cudaEventRecord(c.ev0, c.stream));
+        int rc = enqueue_pass(r, c, c.stream, hit_out != nullptr && g == 0, &launches);
+        if (rc) return rc;
+    }
+    if (G > 1) {
+        // one sum-reduce of the partial accumulation buffers to the first GPU, enqueued
+        // behind each GPU's last kernel on the same stream (no host sync in between)
+        NC(g_nccl.GroupStart());
+        for (int g = 0; g < G; ++g) {
+            GpuCtx& c = r->gpus[g];
+            NC(g_nccl.Reduce(c.accum, c.accum, r->n_pix * 4, ncclFloat32, ncclSum, 0, c.comm, c.stream));
+        }
+        NC(g_nccl.GroupEnd());
+    }
+    for (int g = 0; g < G; ++g) {
+        GpuCtx& c = r->gpus[g];
+        CU(cudaSetDevice(c.device));
+        CU(cudaEventRecord(c.ev1, c.stream));
+    }
+    GpuCtx& c0 = r->gpus[0];
+    CU(cudaSetDevice(c0.device));
+    if (rgb_out) {
+        if (!c0.h_accum) CU(cudaMallocHost(&c0.h_accum, r->n_pix * sizeof(float4)));
+        CU(cudaMemcpyAsync(c0.h_accum, c0.accum, r->n_pix * sizeof(float4), cudaMemcpyDeviceToHost, c0.stream));
+    }
+    if (hit_out) CU(cudaMemcpyAsync(hit_out, c0.hits, r->n_sub * sizeof(int32_t), cudaMemcpyDeviceToHost, c0.stream));
+    double dev_ms = 0;
+    for (int g = 0; g < G; ++g) {
+        GpuCtx& c = r->gpus[g];
+        CU(cudaSetDevice(c.device));
+        CU(cudaStreamSynchronize(c.stream));
+        float ms = 0;
+        CU(cudaEventElapsedTime(&ms, c.ev0, c.ev1));
+        if (ms > dev_ms) dev_ms = ms;
+    }
+    if (rgb_out) {
+        const float4* a = c0.h_accum;
+        for (uint64_t i = 0; i < r->n_pix; ++i) {
+            rgb_out[3 * i] = a[i].x; rgb_out[3 * i + 1] = a[i].y; rgb_out[3 * i + 2] = a[i].z;
+        }
+    }
+    r->last_launches = launches;
+    r->hits_valid = (hit_out != nullptr) || r->opt.compat == RTM_COMPAT_HEAD;
+    if (stats) {
+        int rc = fill_stats(r, stats);
+        if (rc) return rc;
+        stats->device_ms = dev_ms;
+        stats->e2e_ms = std::chrono::duration<double, std::milli>(std::chrono::steady_clock::now() - t0).count();
+    }
+    return RTM_OK;
+}
+
+int renderer_read_image_f64(rtm_renderer* r, double* out) {
+    if (!r || !out) return fail(RTM_E_INVALID, "null argument");
+    if (r->opt.compat != RTM_COMPAT_HEAD) return fail(RTM_E_UNSUPPORTED, "the double image exists in COMPAT_HEAD only");
+    GpuCtx& c = r->gpus[0];
+    if (!c.image64) return fail(RTM_E_INVALID, "render first");
+    CU(cudaSetDevice(c.device));
+    CU(cudaMemcpy(out, c.image64, r->n_pix * 3 * sizeof(double), cudaMemcpyDeviceToHost));
+    return RTM_OK;
+}
+
+int renderer_read_u8(rtm_renderer* r, unsigned char* out) {
+    if (!r || !out) return fail(RTM_E_INVALID, "null argument");
+    GpuCtx& c = r->gpus[0];
+    CU(cudaSetDevice(c.device));
+    if (!c.u8) CU(cudaMalloc(&c.u8, r->n_pix * 3));
+    rtm_launch_to_u8(c.accum, c.u8, r->n_pix, c.stream);
+    CU(cudaGetLastError());
+    CU(cudaMemcpyAsync(out, c.u8, r->n_pix * 3, cudaMemcpyDeviceToHost, c.stream));
+    CU(cudaStreamSynchronize(c.stream));
+    return RTM_OK;
+}
+
+// ---- test hooks ---------------------------------------------------------------
+
+int rtm_debug_philox(int32_t device, uint32_t n, uint32_t c1, uint32_t c2, uint32_t c3, uint32_t k0, uint32_t k1, uint32_t* out) {
+    if (!out || n == 0) return fail(RTM_E_INVALID, "bad argument");
+    CU(cudaSetDevice(device));
+    uint32_t* d = nullptr;
+    CU(cudaMalloc(&d, (size_t)n * 16));
+    rtm_launch_philox(n, c1, c2, c3, k0, k1, d, nullptr);
+    cudaError_t e = cudaMemcpy(out, d, (size_t)n * 16, cudaMemcpyDeviceToHost);
+    cudaFree(d);
+    CU(e);
+    return RTM_OK;
+}
+
+int rtm_debug_closest_hit(rtm_renderer* r, int32_t mode, uint32_t n, const double* org, const double* dir,
+                          const int32_t* origin_id, int32_t* hit_out, double* t_out) {
+    if (!r || !org || !dir || !hit_out || !t_out || n == 0) return fail(RTM_E_INVALID, "bad argument");
+    GpuCtx& c = r->gpus[0];
+    CU(cudaSetDevice(c.device));
+    if (mode == 1 && r->n > RTM_MAX_CONST_SPHERES) return fail(RTM_E_UNSUPPORTED, "too many spheres for the FP32 test");
+    double *d_org = nullptr, *d_dir = nullptr, *d_t = nullptr;
+    int32_t *d_oid = nullptr, *d_hit = nullptr;
+    int rc = RTM_OK;
+    auto body = [&]() -> int {
+        CU(cudaMalloc(&d_org, (size_t)n * 24));
+        CU(cudaMalloc(&d_dir, (size_t)n * 24));
+        CU(cudaMalloc(&d_t, (size_t)n * 8));
+        CU(cudaMalloc(&d_hit, (size_t)n * 4));
+        CU(cudaMemcpy(d_org, org, (size_t)n * 24, cudaMemcpyHostToDevice));
+        CU(cudaMemcpy(d_dir, dir, (size_t)n * 24, cudaMemcpyHostToDevice));
+        if (origin_id) {
+            CU(cudaMalloc(&d_oid, (size_t)n * 4));
+            CU(cudaMemcpy(d_oid, origin_id, (size_t)n * 4, cudaMemcpyHostToDevice));
+        }
+        if (mode == 0) {
+            rtm_launch_closest_hit_f64(c.s64, n, d_org, d_dir, d_hit, d_t, c.stream);
+        } else {
+            if (r->f32.n != r->n) return fail(RTM_E_UNSUPPORTED, "handle was not created for the FP32 path");
+            CU(rtm_upload_scene_f32(r->f32, c.stream));
+            rtm_launch_closest_hit_f32(r->n, r->refd, n, d_org, d_dir, d_oid, d_hit, d_t, c.stream);
+        }
+        CU(cudaGetLastError());
+        CU(cudaStreamSynchronize(c.stream));
+        CU(cudaMemcpy(hit_out, d_hit, (size_t)n * 4, cudaMemcpyDeviceToHost));
+        CU(cudaMemcpy(t_out, d_t, (size_t)n * 8, cudaMemcpyDeviceToHost));
+        return RTM_OK;
+    };
+    rc = body();
+    cudaFree(d_org); cudaFree(d_dir); cudaFree(d_t); cudaFree(d_hit); cudaFree(d_oid);
+    return rc;
+}
+
+int rtm_debug_fp32_peak(int32_t device, double* tflops_out, double* mhz_out) {
+    if (!tflops_out) return fail(RTM_E_INVALID, "null argument");
+    CU(cudaSetDevice(device));
+    cudaDeviceProp prop;
+    CU(cudaGetDeviceProperties(&prop, device));
+    float* sink = nullptr;
+    CU(cudaMalloc(&sink, 4));
+    cudaEvent_t e0, e1;
+    CU(cudaEventCreate(&e0));
+    CU(cudaEventCreate(&e1));
+    const int blocks = prop.multiProcessorCount * 8, iters = 4096;
+    rtm_launch_fma_peak(sink, blocks, 64, nullptr);  // warm-up
+    double best = 0;
+    for (int rep = 0; rep < 5; ++rep) {
+        CU(cudaEventRecord(e0, nullptr));
+        rtm_launch_fma_peak(sink, blocks, iters, nullptr);
+        CU(cudaEventRecord(e1, nullptr));
+        CU(cudaEventSynchronize(e1));
+        float ms = 0;
+        CU(cudaEventElapsedTime(&ms, e0, e1));
+        const double flops = (double)blocks * 256.0 * iters * 16.0 * 8.0 * 2.0;
+        const double tf = flops / (ms * 1e-3) / 1e12;
+        if (tf > best) best = tf;
+    }
+    cudaEventDestroy(e0); cudaEventDestroy(e1); cudaFree(sink);
+    *tflops_out = best;
+    if (mhz_out) *mhz_out = best * 1e12 / ((double)prop.multiProcessorCount * 128.0 * 2.0) / 1e6;  // implied SM clock
+    return RTM_OK;
+}
+
+}  // extern "C"

@@ -1,0 +1,91 @@
+// rtm_internal.h — types shared by the C-ABI implementation (rtm_api.cu) and the
+// kernel translation units.  Not part of the public interface.
+#pragma once
+#include <cuda_runtime.h>
+#include <stdint.h>
+
+#define RTM_MAX_CONST_SPHERES 256  // FP32 brute-force scene lives in __constant__ memory up to this size
+#define RTM_WARP 32
+
+// Camera frame of reference src/Renderer.cpp:202-208, precomputed on the host
+// in double without FMA: ax = camX*fovx, ay = camY*fovy, az = camZ.
+struct RtmFrame {
+    double o[3];
+    double ax[3], ay[3], az[3];
+    float rate;          // (float)(1.0/(1+ss))  src/Renderer.cpp:227
+    int32_t W, H, ss, S; // S = global "samples"
+};
+
+// Scene for the exact FP64 kernels: SoA in global memory (any N).
+struct RtmSceneF64 {
+    int32_t n;
+    const double* cx;
+    const double* cy;
+    const double* cz;
+    const double* r2;        // (double)(float)(m_size*m_size)   src/SettingData.cpp:200
+    const double* emission;  // [n][3]
+    const double* color;     // [n][3]
+    const double* kd;        // (double)(float)max(r,g,b)        src/SettingData.h:14-16
+};
+
+// Per-sphere data of the FP32 path, relative to the scene reference point
+// (the camera origin), SoA.  Filled on the host in double, rounded once.
+struct RtmSceneF32Host {
+    int32_t n;
+    float cx[RTM_MAX_CONST_SPHERES], cy[RTM_MAX_CONST_SPHERES], cz[RTM_MAX_CONST_SPHERES];
+    float m2cx[RTM_MAX_CONST_SPHERES], m2cy[RTM_MAX_CONST_SPHERES], m2cz[RTM_MAX_CONST_SPHERES];  // -2c
+    float K[RTM_MAX_CONST_SPHERES];      // |c|^2 - r^2
+    float inv_r[RTM_MAX_CONST_SPHERES];
+    float ex[RTM_MAX_CONST_SPHERES], ey[RTM_MAX_CONST_SPHERES], ez[RTM_MAX_CONST_SPHERES];        // emission
+    float kx[RTM_MAX_CONST_SPHERES], ky[RTM_MAX_CONST_SPHERES], kz[RTM_MAX_CONST_SPHERES];        // color/kd
+    float kd[RTM_MAX_CONST_SPHERES];
+};
+
+// Sub-pixel record written by the exact primary pass and consumed by the FP32
+// bounce kernels: primary hit point (relative to the reference point, rounded
+// to float from the double hit point) and the hit id.  w = id | flip<<30, or
+// 0xFFFFFFFF for a miss.  The bounce kernel overwrites the record with the
+// sub-pixel's radiance sum {r,g,b,0}.
+#define RTM_REC_MISS 0xFFFFFFFFu
+#define RTM_REC_FLIP 0x40000000u
+#define RTM_REC_IDMASK 0x3FFFFFFFu
+
+struct RtmCounters {
+    unsigned long long rays_ref;     // reference-equivalent PathTracing invocations
+    unsigned long long rays_traced;  // closest-hit queries executed
+    unsigned long long tests;        // ray-sphere tests executed
+    unsigned long long work_next;    // dynamic work cursor of the persistent megakernel
+};
+
+struct RtmPassParams {
+    RtmFrame frame;
+    int32_t s_begin, s_end;   // sample slice
+    int32_t max_depth;
+    uint32_t seed_lo, seed_hi;
+    float inv_norm;           // 1/(ss*ss*S) for the FP32 path
+    float ref[3];             // reference point (as float, informational)
+    double refd[3];           // reference point
+    uint64_t n_sub;           // W*H*ss*ss
+};
+
+// ---- launchers implemented by the kernel TUs (all asynchronous on `st`) ----
+void rtm_launch_primary_f64(const RtmSceneF64& sc, const RtmPassParams& p, int32_t* hits /*or null*/,
+                            float4* records /*or null*/, cudaStream_t st);
+void rtm_launch_head_image(const RtmSceneF64& sc, const RtmPassParams& p, const int32_t* hits,
+                           double* image64 /*[H][W][3]*/, float4* accum, cudaStream_t st);
+void rtm_launch_radiance_f64(const RtmSceneF64& sc, const RtmPassParams& p, float4* records,
+                             RtmCounters* counters, cudaStream_t st);
+void rtm_launch_closest_hit_f64(const RtmSceneF64& sc, uint32_t n, const double* org, const double* dir,
+                                int32_t* hit, double* t, cudaStream_t st);
+
+cudaError_t rtm_upload_scene_f32(const RtmSceneF32Host& h, cudaStream_t st);
+void rtm_launch_radiance_mega(int32_t n_spheres, const RtmPassParams& p, float4* records, RtmCounters* counters,
+                              int32_t sm_count, cudaStream_t st);
+void rtm_launch_accumulate(const RtmPassParams& p, const float4* records, float4* accum, cudaStream_t st);
+void rtm_launch_to_u8(const float4* accum, unsigned char* out, uint64_t n_pix, cudaStream_t st);
+void rtm_launch_closest_hit_f32(int32_t n_spheres, const double* refd, uint32_t n, const double* org,
+                                const double* dir, const int32_t* origin_id, int32_t* hit, double* t,
+                                cudaStream_t st);
+void rtm_launch_philox(uint32_t n, uint32_t c1, uint32_t c2, uint32_t c3, uint32_t k0, uint32_t k1, uint32_t* out,
+                       cudaStream_t st);
+void rtm_launch_fma_peak(float* sink, int32_t blocks, int32_t iters, cudaStream_t st);
