@@ -205,7 +205,10 @@ static v3 path_trace(const rtmo_scene* s, int level, v3 org, v3 dir, mt19937_t* 
     if (level == RTMO_LEVEL_HEAD) {
         /* F3: the normal never reaches the caller => bounce basis is NaN => the
          * recursive call misses everything and returns (0,0,0) before any draw;
-         * the call still counts as a ray (it runs the closest-hit loop).  :108-109 */
+         * the call still counts as a ray (it runs the closest-hit loop), and the two
+         * draws of :88-89 are still consumed from the stream.  :108-109 */
+        (void)mt_uniform01(rng);
+        (void)mt_uniform01(rng);
         c->rays++;
         return v3_add(v3_mul(colorKD, v3_make(0, 0, 0)), emission);
     }

@@ -1,0 +1,284 @@
+"""Parity of the CUDA path (through the C ABI) against the CPU oracle and the
+golden vectors from the reference's own object code.
+
+Bars (BASELINE.json north_star):
+  * primary-hit index maps: BIT-EXACT, L-HEAD and L-ABC;
+  * L-HEAD double image: BIT-EXACT (it is deterministic);
+  * L-ABC radiance: statistical — per-channel RMSE against a high-spp oracle
+    render must lie inside the oracle's own seed-to-seed band at equal spp
+    (tolerance written at the assertion).
+"""
+import numpy as np
+import pytest
+
+import oracle_lib as O
+import raytracingmin_b200 as rtm
+from raytracingmin_b200 import api
+from conftest import SCENE_NAMES
+from philox_ref import philox4x32_10
+
+pytestmark = pytest.mark.gpu
+
+
+def test_library_is_loaded_and_device_present(gpu_lib):
+    import torch
+    assert torch.cuda.is_available()
+    assert gpu_lib.renderer_abi_version() == 1
+
+
+def test_philox_device_matches_numpy():
+    n = 4096
+    for (c1, c2, c3, k0, k1) in [(0, 0, 0, 0, 0), (0x85A308D3, 0x13198A2E, 0x03707344, 0xA4093822, 0x299F31D0),
+                                 (7, 123456, 31, 0x5EED, 0)]:
+        got = api.philox_device(n, c1, c2, c3, k0, k1)
+        ctr = np.stack([np.arange(n, dtype=np.uint32), np.full(n, c1, np.uint32), np.full(n, c2, np.uint32),
+                        np.full(n, c3, np.uint32)], axis=1)
+        assert np.array_equal(got, philox4x32_10(ctr, (k0, k1)))
+
+
+# ---------------- bit-exact primary hits ----------------
+@pytest.mark.parametrize("level", ["head", "abc"])
+@pytest.mark.parametrize("name", SCENE_NAMES)
+def test_hits_vs_golden_small(golden, scene_path, name, level):
+    sc = rtm.load_scene(scene_path(name), level).with_dims(64, 34, 3, 2)
+    with rtm.Renderer(sc, compat=level) as r:
+        res = r.render(want_image=False, want_hits=True)
+    assert np.array_equal(res.hits, golden[f"{name}.{level}.hits_small"].astype(np.int32))
+
+
+@pytest.mark.parametrize("level", ["head", "abc"])
+@pytest.mark.parametrize("name", SCENE_NAMES)
+def test_hits_histogram_480(golden, scene_path, name, level):
+    sc = rtm.load_scene(scene_path(name), level).with_dims(480, 252, 1, 2)
+    with rtm.Renderer(sc, compat=level) as r:
+        h = r.render(want_image=False, want_hits=True).hits
+    assert np.array_equal(np.bincount(h.ravel() + 1, minlength=sc.n + 1), golden[f"{name}.{level}.hist_480"])
+
+
+@pytest.mark.parametrize("level", ["head", "abc"])
+def test_hits_cornell_default_size_bit_exact(scene_path, level):
+    """BASELINE config 2: Cornell at its default 960x504, ss=4 -> 7.74 M sub-pixels, every one equal."""
+    sc = rtm.load_scene(scene_path("cornellBox"), level).with_dims(samples=1)
+    assert (sc.width, sc.height, sc.superSamples) == (960, 504, 4)
+    want = O.oracle_primary_hits(sc)
+    for precision in ("f32", "f64"):
+        with rtm.Renderer(sc, compat=level, precision=precision) as r:
+            got = r.render(want_image=False, want_hits=True).hits
+        assert got.shape == want.shape
+        assert np.array_equal(got, want), f"{int((got != want).sum())} of {want.size} differ"
+
+
+@pytest.mark.parametrize("seed,n,ss", [(3, 0, 1), (5, 1, 3), (7, 12, 2), (9, 60, 1), (11, 200, 2)])
+def test_hits_random_scenes(seed, n, ss):
+    """ragged sizes (odd width/height, ss=3), empty scene, > 8 spheres (runtime-N kernel)."""
+    sc = rtm.random_scene(seed, n, width=61, height=37, samples=1, superSamples=ss, closed=(seed % 2 == 1))
+    want = O.oracle_primary_hits(sc)
+    with rtm.Renderer(sc) as r:
+        got = r.render(want_image=False, want_hits=True).hits
+    assert np.array_equal(got, want)
+
+
+def test_closest_hit_f64_random_rays_bit_exact(scene_path):
+    sc = rtm.load_scene(scene_path("cornellBox"), "abc")
+    rng = np.random.default_rng(42)
+    n = 3000
+    org = rng.uniform(-9, 9, (n, 3))
+    d = rng.normal(size=(n, 3))
+    d /= np.linalg.norm(d, axis=1, keepdims=True)
+    # a few degenerate ones: NaN direction, zero direction, non-unit direction
+    d[0] = np.nan
+    d[1] = 0.0
+    d[2] *= 3.0
+    hit_o, t_o, _ = O.oracle_closest_hit(sc, org, d)
+    with rtm.Renderer(sc) as r:
+        hit, t = r.closest_hit(org, d, "f64")
+    assert np.array_equal(hit, hit_o)
+    m = hit_o >= 0
+    assert np.array_equal(t[m], t_o[m])  # bit for bit
+    assert hit[0] == -1
+
+
+def test_closest_hit_f32_agrees_with_f64_on_surface_rays(scene_path):
+    """The FP32 product test: rays leaving a surface (origin_id set) must reproduce the
+    FP64 decision; |dt| stays small on the 20-unit room with r=1e4 walls."""
+    sc = rtm.load_scene(scene_path("cornellBox"), "abc")
+    rng = np.random.default_rng(1)
+    n = 20000
+    # start points: primary hits of random camera rays, then a random hemisphere direction
+    org0 = np.tile(sc.cam_origin, (n, 1))
+    d0 = rng.normal(size=(n, 3))
+    d0[:, 2] = np.abs(d0[:, 2]) + 0.2
+    d0 /= np.linalg.norm(d0, axis=1, keepdims=True)
+    with rtm.Renderer(sc) as r:
+        hit0, t0 = r.closest_hit(org0, d0, "f64")
+        assert (hit0 >= 0).all()
+        p = org0 + d0 * t0[:, None]
+        nrm = p - sc.position[hit0]
+        nrm /= np.linalg.norm(nrm, axis=1, keepdims=True)
+        nrm[np.einsum("ij,ij->i", nrm, d0) > 0] *= -1
+        d1 = rng.normal(size=(n, 3))
+        d1 /= np.linalg.norm(d1, axis=1, keepdims=True)
+        d1[np.einsum("ij,ij->i", nrm, d1) < 0] *= -1
+        d1 = d1 + 0.05 * nrm
+        d1 /= np.linalg.norm(d1, axis=1, keepdims=True)
+        h64, t64 = r.closest_hit(p, d1, "f64")
+        h32, t32 = r.closest_hit(p, d1, "f32", origin_id=hit0)
+    agree = (h64 == h32)
+    assert agree.mean() > 0.995, agree.mean()       # disagreement only at wall seams
+    both = agree & (h64 >= 0)
+    assert np.median(np.abs(t64[both] - t32[both])) < 1e-4
+    assert np.percentile(np.abs(t64[both] - t32[both]), 99) < 2e-2
+    # never a spurious self-hit at t ~ 0
+    assert (t32[h32 >= 0] > 1e-3).all()
+
+
+# ---------------- L-HEAD: deterministic, bit-exact image ----------------
+@pytest.mark.parametrize("name", SCENE_NAMES)
+def test_head_image_bit_exact(golden, scene_path, name):
+    sc = rtm.load_scene(scene_path(name), "head").with_dims(64, 34, 3, 2)
+    with rtm.Renderer(sc, compat="head") as r:
+        res = r.render()
+        img64 = r.read_image_f64()
+        u8 = r.read_u8()
+    assert np.array_equal(img64, golden[f"{name}.head.image_small"])
+    assert np.array_equal(res.image, img64.astype(np.float32))
+    assert np.array_equal(u8, O.oracle_to_u8(img64.astype(np.float32).astype(np.float64)))
+
+
+def test_head_image_default_size(scene_path):
+    sc = rtm.load_scene(scene_path("cornellBox"), "head")
+    want = O.oracle_render_head_exact(sc)
+    with rtm.Renderer(sc, compat="head") as r:
+        r.render(want_image=False)
+        got = r.read_image_f64()
+    assert np.array_equal(got, want)
+
+
+# ---------------- L-ABC radiance: statistical ----------------
+def _rmse(a, b):
+    return np.sqrt(((a - b) ** 2).reshape(-1, 3).mean(axis=0))
+
+
+@pytest.fixture(scope="module")
+def cornell_band(scene_path):
+    """High-spp oracle render + the oracle's own seed-to-seed RMSE band at the test spp."""
+    base = rtm.load_scene(scene_path("cornellBox"), "abc").with_dims(64, 34, 8, 2)   # 32 spp
+    hi = base.with_dims(samples=2048)                                                   # 8192 spp
+    ref, _, _ = O.oracle_render(hi, O.LEVEL_ABC, 999)
+    band = np.array([_rmse(O.oracle_render(base, O.LEVEL_ABC, 100 + 1000 * k)[0], ref) for k in range(8)])
+    return base, ref, band
+
+
+@pytest.mark.parametrize("precision", ["f64", "f32"])
+def test_radiance_rmse_within_seed_band(cornell_band, precision):
+    base, ref, band = cornell_band
+    with rtm.Renderer(base, precision=precision, seed=2024) as r:
+        res = r.render()
+    img = res.image.astype(np.float64)
+    rm = _rmse(img, ref)
+    # tolerance: the oracle's seed-to-seed band at equal spp, mean + 4 sigma per channel
+    tol = band.mean(axis=0) + 4.0 * band.std(axis=0)
+    assert (rm <= tol).all(), (rm, tol)
+    assert (rm >= 0.5 * band.min(axis=0)).all(), "suspiciously low noise: not the same estimator"
+    # bias: mean signed error per channel within 4 sigma of the per-pixel noise / sqrt(pixels)
+    n_pix = img.shape[0] * img.shape[1]
+    bias = (img - ref).reshape(-1, 3).mean(axis=0)
+    assert (np.abs(bias) <= 4.0 * band.mean(axis=0) / np.sqrt(n_pix) + 2e-3).all(), bias
+
+
+def test_radiance_f32_converges_to_oracle(scene_path):
+    """At 4096 spp the FP32 product path must sit on the oracle's 8192-spp image: catches
+    light leaks / black patches from self-intersection that the noise band would hide."""
+    sc = rtm.load_scene(scene_path("cornellBox"), "abc").with_dims(64, 34, 2048, 2)
+    ref, rays_o, samples_o = O.oracle_render(sc, O.LEVEL_ABC, 5)
+    with rtm.Renderer(sc.with_dims(samples=1024), seed=77) as r:
+        res = r.render()
+    img = res.image.astype(np.float64)
+    rel = np.abs(img - ref).mean() / ref.mean()
+    assert rel < 0.03, rel
+    # rays per sample is a property of the estimator: must agree to 1 %
+    rps = res.stats.rays / res.stats.samples
+    assert abs(rps - rays_o / samples_o) / (rays_o / samples_o) < 0.01, (rps, rays_o / samples_o)
+
+
+@pytest.mark.parametrize("name", ["settingData", "simple1", "simple2"])
+def test_radiance_other_scenes_mean_and_rays(scene_path, name):
+    sc = rtm.load_scene(scene_path(name), "abc").with_dims(64, 34, 512, 1)
+    ref, rays_o, samples_o = O.oracle_render(sc, O.LEVEL_ABC, 31)
+    for precision in ("f32", "f64"):
+        with rtm.Renderer(sc, precision=precision) as r:
+            res = r.render()
+        img = res.image.astype(np.float64)
+        assert abs(img.mean() - ref.mean()) <= 0.03 * ref.mean() + 1e-4, (precision, img.mean(), ref.mean())
+        rps = res.stats.rays / res.stats.samples
+        assert abs(rps - rays_o / samples_o) < 0.01 * rays_o / samples_o, (precision, rps, rays_o / samples_o)
+
+
+# ---------------- properties ----------------
+def test_deterministic_given_seed(scene_path):
+    sc = rtm.load_scene(scene_path("cornellBox"), "abc").with_dims(96, 50, 4, 2)
+    with rtm.Renderer(sc, seed=1) as r:
+        a = r.render().image
+        b = r.render().image
+    with rtm.Renderer(sc, seed=1) as r:
+        c = r.render().image
+    with rtm.Renderer(sc, seed=2) as r:
+        d = r.render().image
+    assert np.array_equal(a, b) and np.array_equal(a, c)
+    assert not np.array_equal(a, d)
+
+
+@pytest.mark.parametrize("precision", ["f32", "f64"])
+def test_sample_slices_add_up(scene_path, precision):
+    """The multi-GPU partition: slices of the `samples` loop sum to the full render
+    (global divisor, counter-based RNG keyed by the global sample index)."""
+    sc = rtm.load_scene(scene_path("cornellBox"), "abc").with_dims(80, 42, 8, 2)
+    with rtm.Renderer(sc, precision=precision) as r:
+        full = r.render()
+    parts, rays = np.zeros_like(full.image, dtype=np.float64), 0
+    for g in range(4):
+        with rtm.Renderer(sc, precision=precision, sample_begin=2 * g, sample_end=2 * g + 2) as r:
+            res = r.render()
+        parts += res.image
+        rays += res.stats.rays
+    assert rays == full.stats.rays
+    assert np.allclose(parts, full.image, rtol=2e-6, atol=1e-7)
+
+
+def test_u8_conversion(scene_path):
+    sc = rtm.load_scene(scene_path("settingData"), "abc").with_dims(120, 63, 16, 1)
+    with rtm.Renderer(sc) as r:
+        img = r.render().image
+        u8 = r.read_u8()
+    assert np.array_equal(u8, O.oracle_to_u8(img.astype(np.float64)))
+    assert u8.max() == 255 and u8.min() == 0
+
+
+def test_empty_scene_and_tiny_image():
+    sc = rtm.random_scene(1, 0, width=1, height=1, samples=1, superSamples=1, closed=False)
+    with rtm.Renderer(sc) as r:
+        res = r.render(want_hits=True)
+    assert res.hits.tolist() == [[[[-1]]]]
+    assert res.image.tolist() == [[[0.0, 0.0, 0.0]]]
+    assert res.stats.rays == 1 and res.stats.samples == 1
+
+
+def test_max_depth_cap_terminates_white_room():
+    """kd = 1 in a closed room recurses forever in the reference; the cap ends it."""
+    sc = rtm.random_scene(4, 2, width=16, height=8, samples=2, superSamples=1)
+    sc.color[:] = 1.0
+    with rtm.Renderer(sc, max_depth=32) as r:
+        res = r.render()
+    assert res.stats.rays <= res.stats.samples * 32
+    assert res.stats.rays >= res.stats.samples * 31
+    assert np.isfinite(res.image).all()
+
+
+def test_stats_counters(scene_path):
+    sc = rtm.load_scene(scene_path("cornellBox"), "abc").with_dims(64, 34, 4, 2)
+    with rtm.Renderer(sc) as r:
+        st = r.render().stats
+    assert st.samples == 64 * 34 * 4 * 4
+    assert st.rays >= st.samples
+    assert st.sphere_tests == st.rays_traced * sc.n
+    assert st.kernel_launches == 3 and st.device_ms > 0 and st.e2e_ms >= st.device_ms * 0.5
