@@ -1,0 +1,352 @@
+#!/usr/bin/env python3
+"""bench.py — the headline benchmark of BASELINE.json: Mrays/s (and Msamples/s),
+device-timed, on the Cornell box at 3840x2160 x 1024 spp (config C4 of SURVEY.md
+§8d), on N B200s of one node, with the reference's CPU path timed beside it.
+
+  python bench.py --gpus 1 --steps K --warmup W            # our arm, one GPU
+  python -m torch.distributed.run --nproc-per-node N ... bench.py --gpus N ...   # one rank per GPU
+  python bench.py --impl reference ...                     # the reference's own CPU code
+
+A "step" is one full render pass of the hot path (primary FP64 pass, radiance
+megakernel, accumulate) over the rank's slice of the sample budget, followed at
+N>1 by the single NCCL sum-reduce of the partial framebuffers to rank 0.
+Total work is fixed as N grows (the `samples` loop is sliced): scaling = strong.
+Rank 0 prints ONE JSON line.
+"""
+from __future__ import annotations
+
+import argparse
+import json
+import os
+import subprocess
+import sys
+import threading
+import time
+
+import numpy as np
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, ROOT)
+
+# Workloads.  c4 is the configuration the metric is quoted on.
+WORKLOADS = {
+    "c4": dict(scene="cornellBox", width=3840, height=2160, samples=64, superSamples=4,
+               name="cornellBox 3840x2160 x 1024 spp (64 samples x 4x4 sub-pixels)"),
+    "c2": dict(scene="cornellBox", width=960, height=504, samples=25, superSamples=4,
+               name="cornellBox 960x504 x 400 spp (file defaults)"),
+    "c3": dict(scene="simple2", width=1920, height=1080, samples=256, superSamples=1,
+               name="simpleSetting2 1920x1080 x 256 spp"),
+    "c1": dict(scene="simple1", width=960, height=504, samples=100, superSamples=1,
+               name="simpleSetting1 960x504 x 100 spp (file defaults)"),
+    "tiny": dict(scene="cornellBox", width=192, height=108, samples=8, superSamples=2,
+                 name="cornellBox 192x108 x 32 spp (plumbing check only)"),
+}
+
+
+def algorithmic_flops(n_spheres, tests, rays, samples, n_sub):
+    """SURVEY.md §8(d) counting convention, taken from the reference source:
+    17/test + 21/ray + 91/continued bounce + 18/sample + 37/sub-pixel."""
+    return 17.0 * tests + 21.0 * rays + 91.0 * (rays - samples) + 18.0 * samples + 37.0 * n_sub
+
+
+class ClockSampler:
+    """nvidia-smi clocks + throttle reasons DURING the timed region (B200_PROFILING.md)."""
+    Q = ("clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.hw_slowdown,"
+         "clocks_event_reasons.hw_thermal_slowdown,clocks_event_reasons.sw_thermal_slowdown,"
+         "clocks_event_reasons.sw_power_cap")
+
+    def __init__(self, index: int):
+        self.index, self.rows, self._stop, self._t = index, [], threading.Event(), None
+
+    def _run(self):
+        while not self._stop.is_set():
+            try:
+                out = subprocess.run(["nvidia-smi", f"--query-gpu={self.Q}", "--format=csv,noheader,nounits",
+                                      "-i", str(self.index)], capture_output=True, text=True, timeout=5).stdout.strip()
+                if out:
+                    self.rows.append([v.strip() for v in out.split(",")])
+            except Exception:
+                pass
+            self._stop.wait(0.2)
+
+    def start(self):
+        self._t = threading.Thread(target=self._run, daemon=True)
+        self._t.start()
+
+    def stop(self):
+        self._stop.set()
+        if self._t:
+            self._t.join(timeout=6)
+        sm, mx, reasons = [], [], set()
+        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
+        for r in self.rows:
+            try:
+                sm.append(float(r[0]))
+                mx.append(float(r[1]))
+            except Exception:
+                continue
+            for nm, v in zip(names, r[3:7]):
+                if v.lower().startswith("active"):
+                    reasons.add(nm)
+        return {"sm_mhz": float(np.median(sm)) if sm else None, "sm_max_mhz": max(mx) if mx else None,
+                "reasons": sorted(reasons), "samples": len(sm)}
+
+
+def load_workload(name: str):
+    import raytracingmin_b200 as rtm
+    w = WORKLOADS[name]
+    sc = rtm.load_scene(os.path.join(ROOT, "scenes", w["scene"] + ".head.json"), "abc")
+    return sc.with_dims(w["width"], w["height"], w["samples"], w["superSamples"]), w
+
+
+# --------------------------------------------------------------------------------------
+# CPU legs: the reference's own object code (oracle/_ref/libref_abc.so, built from
+# /root/reference/src with the 8-line L-ABC patch) or, if that was not built, the C
+# restatement (oracle/librtm_oracle.so).  Test infrastructure used ONLY as a timed baseline.
+def cpu_render_sample(sc, wl, target_seconds: float):
+    """Times the CPU path on a bounded sample of the workload: the same scene and ss,
+    1/8 x 1/8 of the image area (every 8th pixel's worth of solid angle is NOT sampled:
+    the image is simply rendered at lower resolution, same camera) and as many `samples`
+    as fit in ~target_seconds.  Returns dict(value Mrays/s, msamples, cores, kind, sample)."""
+    sys.path.insert(0, os.path.join(ROOT, "tests"))
+    import oracle_lib as O
+    cores = os.cpu_count() or 1
+    w, h = max(16, sc.width // 8), max(9, sc.height // 8)
+    small = sc.with_dims(w, h, 1, sc.superSamples)
+    use_ref = O.ref_available("abc")
+
+    def run(S):
+        s2 = small.with_dims(samples=S)
+        t0 = time.perf_counter()
+        if use_ref:
+            rs = O.RefScene("abc", s2)
+            _, rays, samples = rs.render(1234, 0)
+            rs.close()
+        else:
+            _, rays, samples = O.oracle_render(s2, O.LEVEL_ABC, 1234)
+        return time.perf_counter() - t0, rays, samples
+
+    S, t = 1, 0.0
+    while True:                      # grow until the run is long enough to extrapolate from
+        t, rays, samples = run(S)
+        if t >= min(1.0, target_seconds) or S >= 4096:
+            break
+        S *= 4
+    if t < 0.7 * target_seconds and S < 4096:
+        S = int(max(1, min(4096, round(S * target_seconds / t))))
+        t, rays, samples = run(S)
+    return {"value": rays / t / 1e6, "unit": "Mrays/s", "msamples_per_s": samples / t / 1e6, "cores": cores,
+            "kind": "reference" if use_ref else "port",
+            "sample": f"{wl['scene']} {w}x{h} ss={sc.superSamples} samples={S} ({samples / 1e6:.1f} Msamples, "
+                      f"{rays / 1e6:.1f} Mrays, {t:.1f} s; OpenMP over rows, private mt19937 per row)",
+            "seconds": t}
+
+
+def run_reference_arm(args):
+    rank = int(os.environ.get("RANK", "0"))
+    if rank != 0:
+        return 0
+    sc, wl = load_workload(args.workload)
+    per_step = max(2.0, min(20.0, 120.0 / max(1, args.steps + args.warmup)))
+    for _ in range(args.warmup):
+        cpu_render_sample(sc, wl, per_step / 4)
+    vals, last = [], None
+    t_all = 0.0
+    for _ in range(args.steps):
+        last = cpu_render_sample(sc, wl, per_step)
+        vals.append(last["value"])
+        t_all += last["seconds"]
+    v = float(np.mean(vals))
+    line = {
+        "impl": "reference", "metric": "Mrays/s", "value": v, "unit": "Mrays/s", "n_gpus": args.gpus,
+        "steps": args.steps, "warmup": args.warmup, "ms_per_step": 1e3 * t_all / max(1, args.steps),
+        "higher_is_better": True, "scaling": "strong", "vs_baseline": None, "dtype": "f64", "data": "synthetic",
+        "config": {"workload": wl["name"], "note": "reference CPU code on the host cores; each step is a bounded sample"},
+        "msamples_per_s": last["msamples_per_s"],
+        "cpu_baseline": {"value": v, "unit": "Mrays/s", "cores": last["cores"], "kind": last["kind"], "sample": last["sample"]},
+        "e2e": {"value": v, "unit": "Mrays/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+        "gpu_launches": 0,
+    }
+    print(json.dumps(line), flush=True)
+    return 0
+
+
+# --------------------------------------------------------------------------------------
+def run_gpu_arm(args):
+    import torch
+    import torch.distributed as dist
+    import raytracingmin_b200 as rtm
+    from raytracingmin_b200 import api
+
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    rank = int(os.environ.get("RANK", "0"))
+    local = int(os.environ.get("LOCAL_RANK", "0"))
+    if world != args.gpus:
+        if world == 1 and args.gpus > 1:
+            raise SystemExit("launch with torch.distributed.run --nproc-per-node N for --gpus N (one rank per GPU)")
+    if not torch.cuda.is_available():
+        raise SystemExit("bench.py: no CUDA device; the product path has no CPU fallback")
+    torch.cuda.set_device(local)
+    dev = torch.device("cuda", local)
+    if world > 1:
+        dist.init_process_group("nccl", device_id=dev)
+
+    sc, wl = load_workload(args.workload)
+    S = sc.samples
+    s0, s1 = S * rank // world, S * (rank + 1) // world
+    if s1 <= s0:
+        raise SystemExit(f"cannot slice {S} samples over {world} ranks")
+    n_pix, n_sub = sc.width * sc.height, sc.n_sub
+
+    # device-resident handle: the library writes its partial framebuffer straight into a
+    # torch tensor (the NCCL send buffer); no host sync between the last kernel and the reduce.
+    r = rtm.Renderer(sc, device=local, sample_begin=s0, sample_end=s1, seed=0x5EED)
+    accum = torch.zeros((sc.height, sc.width, 4), dtype=torch.float32, device=dev)
+    r.set_accum_buffer(accum.data_ptr())
+    stream = torch.cuda.current_stream()
+
+    def step():
+        r.render_async(stream.cuda_stream)
+        if world > 1:
+            dist.reduce(accum, dst=0, op=dist.ReduceOp.SUM)
+
+    def fence():
+        torch.cuda.synchronize()
+        if world > 1:
+            dist.barrier()
+            torch.cuda.synchronize()
+
+    for _ in range(args.warmup):
+        step()
+    fence()
+
+    sampler = ClockSampler(local) if rank == 0 else None
+    if sampler:
+        sampler.start()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    kms = np.zeros(3)
+    rays = samples = tests = traced = 0
+    fence()
+    e0.record(stream)
+    # per-step kernel events / counters are read after the whole timed region (no sync inside it),
+    # except that counters are per pass: read them once per step only when steps are long.
+    for i in range(args.steps):
+        step()
+    e1.record(stream)
+    fence()
+    ms_total = e0.elapsed_time(e1)
+    clocks = sampler.stop() if sampler else None
+    # counters + per-kernel events of the LAST pass (every pass does identical work: the
+    # image is a pure function of (scene, seed)).
+    st = r.read_stats()
+    kms = np.array(r.read_kernel_ms())
+    rays, samples, tests, traced = st.rays, st.samples, st.sphere_tests, st.rays_traced
+
+    t = torch.tensor([ms_total], dtype=torch.float64, device=dev)
+    cnt = torch.tensor([rays, samples, tests, traced], dtype=torch.float64, device=dev)
+    if world > 1:
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        dist.all_reduce(cnt, op=dist.ReduceOp.SUM)
+    ms_total = float(t.item())
+    rays_all, samples_all, tests_all, traced_all = (float(v) for v in cnt.tolist())
+    ms_step = ms_total / args.steps
+
+    # ---- e2e: the drop-in call with HOST buffers.  Scene arrays H2D (constant upload) and
+    # the framebuffer D2H are inside the timed region; at N>1 rank 0 reads the reduced image.
+    host_img = torch.empty((sc.height, sc.width, 4), dtype=torch.float32, pin_memory=True)
+    e2e_steps = max(1, min(args.steps, 3))
+    fence()
+    t0 = time.perf_counter()
+    for _ in range(e2e_steps):
+        step()
+        if rank == 0:
+            host_img.copy_(accum, non_blocking=True)
+        fence()
+    e2e_s = (time.perf_counter() - t0) / e2e_steps
+    te = torch.tensor([e2e_s], dtype=torch.float64, device=dev)
+    if world > 1:
+        dist.all_reduce(te, op=dist.ReduceOp.MAX)
+    e2e_s = float(te.item())
+    h2d = rtm_scene_bytes(sc)
+    d2h = n_pix * 16
+
+    line = None
+    if rank == 0:
+        fp32_peak, implied_mhz = api.fp32_peak_tflops(local)
+        # dominant kernel = the radiance megakernel; its algorithmic flops per launch
+        bounce_rays = (rays - samples)                      # this rank's continued bounces
+        # tests of the bounce rays only (17 each), 21/ray finalisation + 91/bounce for each traced
+        # ray, 18/sample accumulate.  The primary pass's 37/sub-pixel + N tests + 21 are in its own kernel.
+        f_kernel = 17.0 * (st.sphere_tests - n_sub * sc.n) + 21.0 * bounce_rays + 91.0 * bounce_rays + 18.0 * samples
+        f_total = algorithmic_flops(sc.n, tests_all, rays_all, samples_all, n_sub)
+        achieved = f_kernel / (kms[1] * 1e-3) / 1e12
+        fb_gbs = n_pix * 16 / (kms[2] * 1e-3) / 1e9 if kms[2] > 0 else None
+        peaks = {}
+        try:
+            peaks = json.load(open(os.path.join(ROOT, "MEASURED_PEAKS.json")))
+        except Exception:
+            pass
+        line = {
+            "metric": "Mrays/s", "value": rays_all / (ms_step * 1e-3) / 1e6, "unit": "Mrays/s",
+            "n_gpus": world, "steps": args.steps, "warmup": args.warmup, "ms_per_step": ms_step,
+            "higher_is_better": True, "scaling": "strong", "vs_baseline": None, "dtype": "f32",
+            "data": "synthetic",
+            "config": {"workload": wl["name"], "scene": wl["scene"], "width": sc.width, "height": sc.height,
+                       "samples": sc.samples, "superSamples": sc.superSamples, "spp": sc.spp, "n_spheres": sc.n,
+                       "partition": f"samples loop sliced over {world} rank(s)" + (", one NCCL sum-reduce to rank 0" if world > 1 else ""),
+                       "l2": "inputs larger than L2: the 2.1 GB sub-pixel record buffer is rewritten and re-read every step"
+                             if n_sub * 16 > 126e6 else "working set below L2 (plumbing workload)",
+                       "semantics": "L-ABC (SURVEY.md §0.1), FP64 bit-exact primary pass + FP32 bounces, Philox4x32-10"},
+            "msamples_per_s": samples_all / (ms_step * 1e-3) / 1e6,
+            "rays_per_sample": rays_all / samples_all,
+            "e2e": {"value": rays_all / e2e_s / 1e6, "unit": "Mrays/s", "h2d_bytes_per_step": h2d,
+                    "d2h_bytes_per_step": d2h, "ms_per_step": e2e_s * 1e3, "steps": e2e_steps},
+            "gpu_launches": 3 * args.steps,
+            "kernel_ms": {"primary_f64": kms[0], "radiance_mega": kms[1], "accumulate": kms[2]},
+            "roofline": {"bound": "fp32", "achieved": achieved, "peak": fp32_peak, "unit": "TFLOP/s",
+                         "frac": achieved / fp32_peak if fp32_peak else None, "traffic": None,
+                         "kernel": "radiance_mega_kernel",
+                         "peak_source": f"FP32 FMA-chain microbenchmark run live on this GPU (implied {implied_mhz:.0f} MHz); "
+                                        "MEASURED_PEAKS.json holds no FP32 figure",
+                         "flops_per_launch": f_kernel, "whole_pass_tflops": f_total / (ms_step * 1e-3) / 1e12,
+                         "framebuffer_store_GBs": fb_gbs, "hbm_peak_GBs": peaks.get("hbm_gbs")},
+            "clocks": clocks,
+        }
+    if world > 1:
+        dist.barrier()
+    return line, (r, sc, wl)
+
+
+def rtm_scene_bytes(sc) -> int:
+    """bytes of scene data uploaded per pass (the __constant__ SoA block of the FP32 path)."""
+    return 4 + 15 * 256 * 4
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=5)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
+    ap.add_argument("--workload", default="c4", choices=sorted(WORKLOADS))
+    ap.add_argument("--no-cpu-baseline", action="store_true")
+    args = ap.parse_args()
+    if args.impl == "reference":
+        return run_reference_arm(args)
+    args.warmup = max(args.warmup, 3)
+    line, (r, sc, wl) = run_gpu_arm(args)
+    if line is not None:
+        if int(os.environ.get("WORLD_SIZE", "1")) == 1 and not args.no_cpu_baseline:
+            cb = cpu_render_sample(sc, wl, 12.0)
+            cb.pop("seconds")
+            line["cpu_baseline"] = cb
+        print(json.dumps(line), flush=True)
+    r.close()
+    import torch.distributed as dist
+    if dist.is_initialized():
+        dist.destroy_process_group()
+    return 0
+
+
+if __name__ == "__main__":
+    sys.exit(main())

@@ -140,6 +140,11 @@ int renderer_render_async(rtm_renderer* r, void* stream);
 /* After the stream has been synchronised: counters of the last pass. */
 int renderer_read_stats(rtm_renderer* r, rtm_stats* stats);
 
+/* After the stream has been synchronised: CUDA-event durations (ms) of the three
+ * kernels of the last FP32 ABC pass, measured on the stream they ran on:
+ * ms3 = {primary FP64 pass, radiance megakernel, sub-pixel accumulate}. */
+int renderer_read_kernel_ms(rtm_renderer* r, double* ms3);
+
 /* Device pointers (valid until destroy): the float4[H][W] accumulation buffer
  * {r,g,b,0} and the int32 primary-hit map. */
 void* renderer_device_accum(rtm_renderer* r);

@@ -78,7 +78,7 @@ class RenderResult:
 
 EXPORTS = [
     "renderer_abi_version", "renderer_default_options", "renderer_create", "renderer_render",
-    "renderer_render_async", "renderer_read_stats", "renderer_device_accum", "renderer_device_hits",
+    "renderer_render_async", "renderer_read_stats", "renderer_read_kernel_ms", "renderer_device_accum", "renderer_device_hits",
     "renderer_set_accum_buffer", "renderer_read_image_f64", "renderer_read_u8", "renderer_destroy",
     "renderer_last_error", "rtm_debug_philox", "rtm_debug_closest_hit", "rtm_debug_fp32_peak",
 ]
@@ -109,6 +109,7 @@ def load_library():
     lib.renderer_render.argtypes = [vp, vp, vp, P(_Stats)]
     lib.renderer_render_async.argtypes = [vp, vp]
     lib.renderer_read_stats.argtypes = [vp, P(_Stats)]
+    lib.renderer_read_kernel_ms.argtypes = [vp, vp]
     lib.renderer_device_accum.argtypes = [vp]
     lib.renderer_device_accum.restype = vp
     lib.renderer_device_hits.argtypes = [vp]
@@ -184,6 +185,12 @@ class Renderer:
         st = _Stats()
         _check(self._lib, self._lib.renderer_read_stats(self._h, C.byref(st)))
         return _stats(st)
+
+    def read_kernel_ms(self):
+        """(primary, radiance, accumulate) CUDA-event ms of the last FP32 pass."""
+        ms = (C.c_double * 3)()
+        _check(self._lib, self._lib.renderer_read_kernel_ms(self._h, ms))
+        return tuple(ms)
 
     def device_accum_ptr(self) -> int:
         return int(self._lib.renderer_device_accum(self._h) or 0)

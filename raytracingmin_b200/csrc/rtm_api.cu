@@ -102,6 +102,8 @@ struct GpuCtx {
     int sm_count = 148;
     cudaStream_t stream = nullptr;
     cudaEvent_t ev0 = nullptr, ev1 = nullptr;
+    cudaEvent_t ek[4] = {nullptr, nullptr, nullptr, nullptr};  // around primary / radiance / accumulate
+    bool ek_valid = false;
     double* d_scene64 = nullptr;  // one allocation: cx cy cz r2 kd [n] + emission color [3n]
     RtmSceneF64 s64{};
     float4* records = nullptr;
@@ -145,6 +147,7 @@ void free_ctx(GpuCtx& c) {
     if (c.h_accum) cudaFreeHost(c.h_accum);
     if (c.ev0) cudaEventDestroy(c.ev0);
     if (c.ev1) cudaEventDestroy(c.ev1);
+    for (auto& e : c.ek) if (e) cudaEventDestroy(e);
     if (c.stream) cudaStreamDestroy(c.stream);
     c = GpuCtx{};
 }
@@ -199,9 +202,14 @@ int enqueue_pass(rtm_renderer* r, GpuCtx& c, cudaStream_t st, bool want_hits, in
             if (rc) return rc;
         }
         CU(rtm_upload_scene_f32(r->f32, st));
+        CU(cudaEventRecord(c.ek[0], st));
         rtm_launch_primary_f64(c.s64, p, want_hits ? c.hits : nullptr, c.records, st);
+        CU(cudaEventRecord(c.ek[1], st));
         rtm_launch_radiance_mega(r->n, p, c.records, c.counters, c.sm_count, st);
+        CU(cudaEventRecord(c.ek[2], st));
         rtm_launch_accumulate(p, c.records, c.accum, st);
+        CU(cudaEventRecord(c.ek[3], st));
+        c.ek_valid = true;
         *launches += 3;
     }
     CU(cudaGetLastError());
@@ -386,6 +394,7 @@ int renderer_create(const rtm_scene_desc* sc, const rtm_options* opt_in, rtm_ren
             CU(cudaStreamCreateWithFlags(&c.stream, cudaStreamNonBlocking));
             CU(cudaEventCreate(&c.ev0));
             CU(cudaEventCreate(&c.ev1));
+            for (auto& e : c.ek) CU(cudaEventCreate(&e));
             CU(cudaMalloc(&c.d_scene64, h64.size() * sizeof(double)));
             CU(cudaMemcpy(c.d_scene64, h64.data(), h64.size() * sizeof(double), cudaMemcpyHostToDevice));
             c.s64.n = n;
@@ -432,6 +441,20 @@ int renderer_render_async(rtm_renderer* r, void* stream) {
 int renderer_read_stats(rtm_renderer* r, rtm_stats* st) {
     if (!r || !st) return fail(RTM_E_INVALID, "null argument");
     return fill_stats(r, st);
+}
+
+int renderer_read_kernel_ms(rtm_renderer* r, double* ms3) {
+    if (!r || !ms3) return fail(RTM_E_INVALID, "null argument");
+    GpuCtx& c = r->gpus[0];
+    if (!c.ek_valid) return fail(RTM_E_UNSUPPORTED, "per-kernel timing exists for the FP32 ABC path after a pass");
+    CU(cudaSetDevice(c.device));
+    CU(cudaEventSynchronize(c.ek[3]));
+    for (int k = 0; k < 3; ++k) {
+        float ms = 0;
+        CU(cudaEventElapsedTime(&ms, c.ek[k], c.ek[k + 1]));
+        ms3[k] = ms;
+    }
+    return RTM_OK;
 }
 
 void* renderer_device_accum(rtm_renderer* r) { return r ? (void*)r->gpus[0].accum : nullptr; }
