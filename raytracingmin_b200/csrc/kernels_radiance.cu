@@ -46,93 +46,141 @@ __device__ __forceinline__ float fast_rcp(float x) {
     return r;
 }
 
-// One ray/sphere test, FP32.  Semantics of SettingData.cpp:197-223 + the accept
-// rule of Renderer.cpp:67 (`t < best`, lowest index wins ties).
-__device__ __forceinline__ void sphere_test_f32(int i, int oid, f3 o, f3 d, float oo, float dO, float cx, float cy, float cz,
-                                                float m2cx, float m2cy, float m2cz, float K, float& best, int& best_id) {
+__device__ __forceinline__ float fast_rsqrt(float x) {
+    float r;
+    asm("rsqrt.approx.ftz.f32 %0, %1;" : "=f"(r) : "f"(x));
+    return r;
+}
+
+// ---- ray/sphere test of the FP32 path ------------------------------------------
+// Semantics of SettingData.cpp:197-223 + the accept rule of Renderer.cpp:67, stated as
+// "the smallest root greater than RTM_T_EPS; lowest index wins exact ties".  The
+// reference takes the near root t1 when t1 > 1e-3, else the far root t2 when t2 >= 1e-5;
+// the two rules differ only for a far root inside [1e-5, 1e-3], i.e. for chords shorter
+// than 1e-3 (documented in DESIGN.md; invisible at the radiance tolerance).
+//
+// Roots without cancellation: tq = b + sign(b) sqrt(b^2 - c'), the other root is c'/tq.
+// A negative discriminant makes sqrt.approx return NaN, which propagates into both
+// candidates; the unsigned-integer minimum below ignores NaNs and negative values by
+// construction (their bit patterns are above +inf), so no explicit D >= 0 / t > 0 tests
+// are issued.
+#define RTM_T_EPS 1e-3f
+#define RTM_KEY_INF 0x7F800000u
+
+__device__ __forceinline__ void sphere_roots_f32(bool self, f3 o, f3 d, float oo, float dO, float cx, float cy, float cz,
+                                                 float m2cx, float m2cy, float m2cz, float K, float& ta, float& tb) {
     const float b = fmaf(d.x, cx, fmaf(d.y, cy, fmaf(d.z, cz, -dO)));           // (c-o).d
     float cp = fmaf(o.x, m2cx, fmaf(o.y, m2cy, fmaf(o.z, m2cz, oo + K)));       // |c-o|^2 - r^2
-    cp = (i == oid) ? 0.f : cp;
-    const float D = fmaf(b, b, -cp);
-    const float sq = fast_sqrt(fmaxf(D, 0.f));
-    const float q = b + copysignf(sq, b);
-    const float r = cp * fast_rcp(q);
-    const bool bpos = b > 0.f;
-    const float t2 = bpos ? q : r;                          // far root
-    const float t1 = bpos ? r : q;                          // near root
-    const float t = (t1 > 0.001f) ? t1 : t2;                // SettingData.cpp:212-223
-    const bool ok = (D >= 0.f) && (t2 >= 1e-5f) && (t < best);  // :202, :208-210, Renderer.cpp:67
-    best = ok ? t : best;
-    best_id = ok ? i : best_id;
+    cp = self ? 0.f : cp;                                                       // leaving this sphere's surface
+    const float s = fast_sqrt(fmaf(b, b, -cp));
+    const float tq = b + copysignf(s, b);
+    ta = tq - RTM_T_EPS;
+    tb = fmaf(cp, fast_rcp(tq), -RTM_T_EPS);
+}
+
+// Closest hit for N <= 8 (compile-time N): the candidate (t - eps) and the sphere index
+// share one 32-bit key, t in the upper 29 bits (8 ulp of t are given up: below the FP32
+// error of t itself), the index in the low 3; positive floats order like unsigned
+// integers, so one unsigned min per candidate does the accept test, the tie rule and
+// the bookkeeping.  Returns the key; RTM_KEY_INF or above = miss.
+template <int N>
+__device__ __forceinline__ unsigned trace_key_f32(int oid, f3 o, f3 d) {
+    const float oo = dot(o, o), dO = dot(d, o);
+    unsigned best = RTM_KEY_INF;
+#pragma unroll
+    for (int i = 0; i < N; ++i) {
+        float ta, tb;
+        sphere_roots_f32(i == oid, o, d, oo, dO, c_scene.cx[i], c_scene.cy[i], c_scene.cz[i], c_scene.m2cx[i],
+                         c_scene.m2cy[i], c_scene.m2cz[i], c_scene.K[i], ta, tb);
+        const unsigned ka = (__float_as_uint(ta) & ~7u) | (unsigned)i;
+        const unsigned kb = (__float_as_uint(tb) & ~7u) | (unsigned)i;
+        best = min(best, min(ka, kb));
+    }
+    return best;
+}
+
+// Runtime-N version (any N that fits constant memory): explicit (t, id) pair.
+__device__ __forceinline__ int trace_loop_f32(int n, int oid, f3 o, f3 d, float& t) {
+    const float oo = dot(o, o), dO = dot(d, o);
+    float best = FLT_MAX;
+    int id = -1;
+#pragma unroll 4
+    for (int i = 0; i < n; ++i) {
+        float ta, tb;
+        sphere_roots_f32(i == oid, o, d, oo, dO, c_scene.cx[i], c_scene.cy[i], c_scene.cz[i], c_scene.m2cx[i],
+                         c_scene.m2cy[i], c_scene.m2cz[i], c_scene.K[i], ta, tb);
+        // candidates are (root - eps); valid iff > 0; NaN fails every comparison
+        const float c1 = (ta > 0.f) ? ta : FLT_MAX, c2 = (tb > 0.f) ? tb : FLT_MAX;
+        const float c = fminf(c1, c2);
+        const bool ok = c < best;
+        best = ok ? c : best;
+        id = ok ? i : id;
+    }
+    t = best + RTM_T_EPS;
+    return id;
 }
 
 template <int N>
 __device__ __forceinline__ int trace_f32(int n_rt, int oid, f3 o, f3 d, float& t) {
-    const float oo = dot(o, o), dO = dot(d, o);
-    float best = FLT_MAX;
-    int id = -1;
     if (N > 0) {
-#pragma unroll
-        for (int i = 0; i < N; ++i)
-            sphere_test_f32(i, oid, o, d, oo, dO, c_scene.cx[i], c_scene.cy[i], c_scene.cz[i], c_scene.m2cx[i],
-                            c_scene.m2cy[i], c_scene.m2cz[i], c_scene.K[i], best, id);
-    } else {
-#pragma unroll 4
-        for (int i = 0; i < n_rt; ++i)
-            sphere_test_f32(i, oid, o, d, oo, dO, c_scene.cx[i], c_scene.cy[i], c_scene.cz[i], c_scene.m2cx[i],
-                            c_scene.m2cy[i], c_scene.m2cz[i], c_scene.K[i], best, id);
+        const unsigned key = trace_key_f32<(N > 0 ? N : 1)>(oid, o, d);
+        t = __uint_as_float(key & ~7u) + RTM_T_EPS;
+        return (key < RTM_KEY_INF) ? (int)(key & 7u) : -1;
     }
-    t = best;
-    return id;
+    return trace_loop_f32(n_rt, oid, o, d, t);
 }
 
-// Per-sphere data addressed with a per-lane index (hit id) lives in shared memory.
+// Per-sphere data addressed with a per-lane index (the hit id): shared memory, three
+// 16-byte records per sphere so that a lane needs three LDS.128 per hit.
 struct SharedScene {
-    float cx[RTM_MAX_CONST_SPHERES], cy[RTM_MAX_CONST_SPHERES], cz[RTM_MAX_CONST_SPHERES], inv_r[RTM_MAX_CONST_SPHERES];
-    float ex[RTM_MAX_CONST_SPHERES], ey[RTM_MAX_CONST_SPHERES], ez[RTM_MAX_CONST_SPHERES];
-    float kx[RTM_MAX_CONST_SPHERES], ky[RTM_MAX_CONST_SPHERES], kz[RTM_MAX_CONST_SPHERES], kd[RTM_MAX_CONST_SPHERES];
+    float4 geo[RTM_MAX_CONST_SPHERES];  // cx, cy, cz, 1/r
+    float4 emi[RTM_MAX_CONST_SPHERES];  // emission rgb, roulette threshold (uint bits)
+    float4 alb[RTM_MAX_CONST_SPHERES];  // color/kd rgb (colorKD, SettingData.h:11-13), unused
 };
 
 __device__ __forceinline__ void load_shared_scene(SharedScene& s, int n) {
     for (int i = threadIdx.x; i < n; i += blockDim.x) {
-        s.cx[i] = c_scene.cx[i]; s.cy[i] = c_scene.cy[i]; s.cz[i] = c_scene.cz[i]; s.inv_r[i] = c_scene.inv_r[i];
-        s.ex[i] = c_scene.ex[i]; s.ey[i] = c_scene.ey[i]; s.ez[i] = c_scene.ez[i];
-        s.kx[i] = c_scene.kx[i]; s.ky[i] = c_scene.ky[i]; s.kz[i] = c_scene.kz[i]; s.kd[i] = c_scene.kd[i];
+        s.geo[i] = make_float4(c_scene.cx[i], c_scene.cy[i], c_scene.cz[i], c_scene.inv_r[i]);
+        s.emi[i] = make_float4(c_scene.ex[i], c_scene.ey[i], c_scene.ez[i], __uint_as_float(c_scene.kd_thr[i]));
+        s.alb[i] = make_float4(c_scene.kx[i], c_scene.ky[i], c_scene.kz[i], 0.f);
     }
     __syncthreads();
 }
 
-// Outward unit normal at hp on sphere id, oriented against the incoming ray.
-__device__ __forceinline__ f3 oriented_normal(const SharedScene& s, int id, f3 hp, bool flip) {
-    const float ir = flip ? -s.inv_r[id] : s.inv_r[id];
-    return mk((hp.x - s.cx[id]) * ir, (hp.y - s.cy[id]) * ir, (hp.z - s.cz[id]) * ir);
-}
-
-// Cosine-weighted direction about w (Renderer.cpp:88-107).  The tangent frame is
-// the branchless one of Duff et al. 2017 instead of the reference's
-// Normalize(Cross(axis, w)): the azimuth is uniform, so the distribution of the
-// sampled direction is the same for any orthonormal frame.
-__device__ __forceinline__ f3 cosine_dir(f3 w, float u1, float u2) {
-    const float sgn = copysignf(1.0f, w.z);
-    const float a = -fast_rcp(sgn + w.z);
-    const float b = w.x * w.y * a;
-    const f3 u = mk(fmaf(sgn * w.x, w.x * a, 1.0f), sgn * b, -sgn * w.x);
-    const f3 v = mk(b, fmaf(w.y, w.y * a, sgn), -w.y);
+// Cosine-weighted direction about the unit normal w (Renderer.cpp:88-107): a uniform
+// point s on the unit sphere added to w and normalised is cosine-distributed about w,
+// which needs no tangent frame.  The reference builds u,v from Cross(axis,w); the
+// azimuth is uniform, so the distribution of the sampled direction is the same.
+//   phi = 2*pi*xi1 (from 32 bits), z = 1 - 2*xi2 (22 bits, centred: never exactly +-1)
+__device__ __forceinline__ f3 cosine_dir(f3 w, uint32_t u_phi, uint32_t u_z22) {
+    const float z = fmaf((float)u_z22, -4.76837158203125e-7f, 1.0f - 2.384185791015625e-7f);  // 1 - (2k+1)/2^22
+    const float rxy = fast_sqrt(fmaf(-z, z, 1.0f));
     float sn, cs;
-    __sincosf(6.283185307179586f * u1, &sn, &cs);  // r1 = 2*PI*xi1
-    const float r2s = fast_sqrt(u2);                // sqrt(r2)
-    const float cu = cs * r2s, cv = sn * r2s, cw = fast_sqrt(1.0f - u2);
-    return mk(fmaf(u.x, cu, fmaf(v.x, cv, w.x * cw)), fmaf(u.y, cu, fmaf(v.y, cv, w.y * cw)),
-              fmaf(u.z, cu, fmaf(v.z, cv, w.z * cw)));
+    __sincosf((float)u_phi * 1.4629180792671596e-9f, &sn, &cs);  // 2*pi / 2^32
+    const f3 v = mk(fmaf(rxy, cs, w.x), fmaf(rxy, sn, w.y), w.z + z);
+    const float inv = fast_rsqrt(fmaxf(dot(v, v), 1e-12f));
+    return mk(v.x * inv, v.y * inv, v.z * inv);
 }
 
-__device__ __forceinline__ float clamp01f(float v) { return fminf(fmaxf(v, 0.f), 1.f); }
+__device__ __forceinline__ float clamp01f(float v) { return __saturatef(v); }
 
 #define RTM_MEGA_THREADS 128
 #define RTM_MEGA_CHUNK 64u  // sub-pixels a warp reserves per global atomic
 
+// ---- the radiance megakernel ---------------------------------------------------
+// Persistent: grid = SMs x resident blocks.  A lane owns one sub-pixel (unit) at a time
+// and walks its samples; one loop iteration = one roulette decision + one bounce ray.
+// The lane state is "standing on a hit": origin o on sphere id with oriented normal w,
+// throughput T, and radiance L that already includes the emission of this hit
+// (Renderer.cpp:109 unrolled forward: L += T*e, T *= colorKD).  A path ends when the
+// roulette kills it (Renderer.cpp:112), the bounce ray misses (:116), the depth cap is
+// reached, or it lands on a surface with kd == 0 (the roulette there can never continue,
+// so the sample is closed in the same iteration instead of spending another one).
+// RNG: one Philox2x32-10 call per hit, counter = (sub-pixel, sample<<9 | depth), key
+// from the seed: x -> roulette (32-bit compare against kd*2^32), y -> azimuth,
+// the low bits of x and y -> height.
 template <int N>
-__global__ void __launch_bounds__(RTM_MEGA_THREADS, 4) radiance_mega_kernel(RtmPassParams p, float4* __restrict__ records,
+__global__ void __launch_bounds__(RTM_MEGA_THREADS, 5) radiance_mega_kernel(RtmPassParams p, float4* __restrict__ records,
                                                                             RtmCounters* __restrict__ counters, int n_rt) {
     __shared__ SharedScene sh;
     const int n = (N > 0) ? N : n_rt;
@@ -140,20 +188,19 @@ __global__ void __launch_bounds__(RTM_MEGA_THREADS, 4) radiance_mega_kernel(RtmP
 
     const unsigned lane = threadIdx.x & 31u;
     const unsigned lt_mask = (1u << lane) - 1u;
-    const unsigned long long n_sub = p.n_sub;
+    const unsigned n_sub = (unsigned)p.n_sub;   // renderer_create guarantees n_sub < 2^32
     const int s_begin = p.s_begin, s_end = p.s_end;
     const float inv_norm = p.inv_norm;
 
-    unsigned long long w_next = 0, w_end = 0;  // warp-uniform slice of the work cursor
+    unsigned w_next = 0, w_end = 0;  // warp-uniform slice of the work cursor
     bool have = false, done = false;
 
     // unit (sub-pixel) state
-    unsigned long long q = 0;
-    f3 P = mk(0, 0, 0);      // primary hit point
+    unsigned q = 0;
+    f3 P = mk(0, 0, 0), Pw = mk(0, 0, 1);  // primary hit point, oriented normal there
     int Pid = 0;
-    bool Pflip = false;
-    double ax = 0, ay = 0, az = 0;
-    // path state: sitting at a hit (o, id) with oriented normal w
+    f3 acc = mk(0, 0, 0);
+    // path state
     f3 o = mk(0, 0, 0), w = mk(0, 0, 1), T = mk(1, 1, 1), L = mk(0, 0, 0);
     int id = 0, s = 0, depth = 0;
 
@@ -167,14 +214,14 @@ __global__ void __launch_bounds__(RTM_MEGA_THREADS, 4) radiance_mega_kernel(RtmP
                 unsigned long long start = 0;
                 if (lane == 0) start = atomicAdd(&counters->work_next, (unsigned long long)RTM_MEGA_CHUNK);
                 start = __shfl_sync(0xffffffffu, start, 0);
-                if (start >= n_sub) {
+                if (start >= (unsigned long long)n_sub) {
                     if (!have) done = true;
                     break;
                 }
-                w_next = start;
-                w_end = (start + RTM_MEGA_CHUNK < n_sub) ? start + RTM_MEGA_CHUNK : n_sub;
+                w_next = (unsigned)start;
+                w_end = (start + RTM_MEGA_CHUNK < (unsigned long long)n_sub) ? (unsigned)start + RTM_MEGA_CHUNK : n_sub;
             }
-            const unsigned avail = (unsigned)(w_end - w_next);
+            const unsigned avail = w_end - w_next;
             const unsigned rank = __popc(need & lt_mask);
             const bool mine = ((need >> lane) & 1u) && rank < avail;
             if (mine) {
@@ -184,25 +231,28 @@ __global__ void __launch_bounds__(RTM_MEGA_THREADS, 4) radiance_mega_kernel(RtmP
                 const unsigned ns = (unsigned)(s_end - s_begin);
                 const bool miss = (wbits == RTM_REC_MISS);
                 Pid = miss ? 0 : (int)(wbits & RTM_REC_IDMASK);
-                if (miss || !(sh.kd[Pid] > 0.f)) {
+                const float4 e0 = sh.emi[Pid];
+                if (miss || __float_as_uint(e0.w) == 0u) {
                     // every sample of this sub-pixel is the same: nothing (miss) or the
                     // emission of a surface that never continues (kd == 0, Renderer.cpp:112)
                     float4 out = make_float4(0.f, 0.f, 0.f, 0.f);
                     if (!miss) {
-                        out.x = (float)((double)clamp01f(sh.ex[Pid] * inv_norm) * ns);
-                        out.y = (float)((double)clamp01f(sh.ey[Pid] * inv_norm) * ns);
-                        out.z = (float)((double)clamp01f(sh.ez[Pid] * inv_norm) * ns);
+                        out.x = clamp01f(e0.x * inv_norm) * (float)ns;
+                        out.y = clamp01f(e0.y * inv_norm) * (float)ns;
+                        out.z = clamp01f(e0.z * inv_norm) * (float)ns;
                     }
                     records[q] = out;
                     rays_ref += ns;
                 } else {
                     have = true;
                     P = mk(rec.x, rec.y, rec.z);
-                    Pflip = (wbits & RTM_REC_FLIP) != 0u;
-                    ax = ay = az = 0.0;
+                    const float4 g = sh.geo[Pid];
+                    const float ir = (wbits & RTM_REC_FLIP) ? -g.w : g.w;
+                    Pw = mk((P.x - g.x) * ir, (P.y - g.y) * ir, (P.z - g.z) * ir);
+                    acc = mk(0, 0, 0);
                     s = s_begin;
-                    o = P; id = Pid; w = oriented_normal(sh, Pid, P, Pflip);
-                    T = mk(1, 1, 1); L = mk(0, 0, 0); depth = 0;
+                    o = P; id = Pid; w = Pw;
+                    T = mk(1, 1, 1); L = mk(e0.x, e0.y, e0.z); depth = 0;
                 }
             }
             const unsigned took = (__popc(need) < avail) ? __popc(need) : avail;
@@ -214,43 +264,47 @@ __global__ void __launch_bounds__(RTM_MEGA_THREADS, 4) radiance_mega_kernel(RtmP
             continue;
         }
 
-        // ---- one hit per iteration
         if (have) {
-            L.x = fmaf(T.x, sh.ex[id], L.x); L.y = fmaf(T.y, sh.ey[id], L.y); L.z = fmaf(T.z, sh.ez[id], L.z);
-            const uint4 rnd = rtm_philox4x32_10(make_uint4((uint32_t)q, (uint32_t)(q >> 32), (uint32_t)s, (uint32_t)depth),
-                                                p.seed_lo, p.seed_hi);
-            // Russian roulette, Renderer.cpp:78.  `<` on a 24-bit uniform: kd == 0 never continues.
-            bool cont = (rtm_u01_f32(rnd.x) < sh.kd[id]) && (depth + 1 < p.max_depth);
-            if (cont) {
-                T.x *= sh.kx[id]; T.y *= sh.ky[id]; T.z *= sh.kz[id];   // colorKD, SettingData.h:11-13
-                const f3 d = cosine_dir(w, rtm_u01_f32(rnd.y), rtm_u01_f32(rnd.z));
+            const uint2 rnd = rtm_philox2x32_10(make_uint2(q, ((unsigned)s << 9) | (unsigned)depth), p.rk);
+            const float4 em = sh.emi[id];
+            // Russian roulette, Renderer.cpp:78
+            bool end = !((rnd.x < __float_as_uint(em.w)) && (depth + 1 < p.max_depth));
+            if (!end) {
+                const float4 al = sh.alb[id];
+                T.x *= al.x; T.y *= al.y; T.z *= al.z;   // colorKD, SettingData.h:11-13
+                const f3 d = cosine_dir(w, rnd.y, ((rnd.x & 0xFFFu) << 10) | (rnd.y & 0x3FFu));
                 float t;
                 const int id2 = trace_f32<N>(n, id, o, d, t);
                 ++traced;
                 if (id2 >= 0) {
                     o = mk(fmaf(d.x, t, o.x), fmaf(d.y, t, o.y), fmaf(d.z, t, o.z));  // Renderer.cpp:79
-                    const f3 nn = oriented_normal(sh, id2, o, false);
+                    const float4 g = sh.geo[id2];
+                    const f3 nn = mk((o.x - g.x) * g.w, (o.y - g.y) * g.w, (o.z - g.z) * g.w);
                     const bool flip = !(dot(nn, d) < 0.f);                            // :82-83
                     w = flip ? mk(-nn.x, -nn.y, -nn.z) : nn;
                     id = id2;
                     ++depth;
+                    const float4 e2 = sh.emi[id2];
+                    L.x = fmaf(T.x, e2.x, L.x); L.y = fmaf(T.y, e2.y, L.y); L.z = fmaf(T.z, e2.z, L.z);
+                    end = (__float_as_uint(e2.w) == 0u);   // kd == 0: the next roulette cannot continue
                 } else {
-                    cont = false;  // miss: the recursion returns 0 (Renderer.cpp:116)
+                    end = true;  // miss: the recursion returns 0 (Renderer.cpp:116)
                 }
             }
-            if (!cont) {
+            if (end) {
                 // Renderer.cpp:240-242
-                ax += (double)clamp01f(L.x * inv_norm);
-                ay += (double)clamp01f(L.y * inv_norm);
-                az += (double)clamp01f(L.z * inv_norm);
+                acc.x += clamp01f(L.x * inv_norm);
+                acc.y += clamp01f(L.y * inv_norm);
+                acc.z += clamp01f(L.z * inv_norm);
                 ++s;
                 if (s == s_end) {
-                    records[q] = make_float4((float)ax, (float)ay, (float)az, 0.f);
+                    records[q] = make_float4(acc.x, acc.y, acc.z, 0.f);
                     rays_ref += (unsigned)(s_end - s_begin);
                     have = false;
                 } else {
-                    o = P; id = Pid; w = oriented_normal(sh, Pid, P, Pflip);
-                    T = mk(1, 1, 1); L = mk(0, 0, 0); depth = 0;
+                    const float4 e0 = sh.emi[Pid];
+                    o = P; id = Pid; w = Pw;
+                    T = mk(1, 1, 1); L = mk(e0.x, e0.y, e0.z); depth = 0;
                 }
             }
         }

@@ -32,3 +32,18 @@ __device__ __forceinline__ double rtm_u01_f64(uint32_t hi, uint32_t lo) {
 }
 // (0,1) with 32 random bits
 __device__ __forceinline__ double rtm_u01_f64_32(uint32_t x) { return ((double)x + 0.5) * 2.3283064365386963e-10; }
+
+// ---- Philox2x32-10 (same paper): 64 random bits per call, one 32x32->64 multiply
+// per round.  The FP32 megakernel needs three numbers per hit (roulette, azimuth,
+// height) and takes them from one call.  Round keys k + r*W0 are precomputed on the
+// host (RtmPassParams::rk) so the loop carries no key arithmetic.
+#define RTM_PHILOX2_M 0xD256D193u
+
+__device__ __forceinline__ uint2 rtm_philox2x32_10(uint2 c, const uint32_t* __restrict__ rk) {
+#pragma unroll
+    for (int r = 0; r < 10; ++r) {
+        const uint32_t hi = __umulhi(RTM_PHILOX2_M, c.x), lo = RTM_PHILOX2_M * c.x;
+        c = make_uint2(hi ^ rk[r] ^ c.y, lo);
+    }
+    return c;
+}

@@ -161,6 +161,11 @@ RtmPassParams make_params(const rtm_renderer* r, const GpuCtx& c) {
     p.seed_lo = (uint32_t)r->opt.seed;
     p.seed_hi = (uint32_t)(r->opt.seed >> 32);
     p.inv_norm = (float)(1.0 / ((double)r->ss * r->ss * r->S));
+    {
+        // 32-bit Philox2x32 key from the 64-bit seed
+        uint32_t k = p.seed_lo ^ (p.seed_hi * 0x85EBCA6Bu) ^ (p.seed_hi >> 15);
+        for (int i = 0; i < 10; ++i) p.rk[i] = k + (uint32_t)i * 0x9E3779B9u;
+    }
     for (int k = 0; k < 3; ++k) {
         p.refd[k] = r->refd[k];
         p.ref[k] = (float)r->refd[k];
@@ -293,6 +298,10 @@ int renderer_create(const rtm_scene_desc* sc, const rtm_options* opt_in, rtm_ren
     if (opt.sample_begin == 0 && opt.sample_end == 0) opt.sample_end = sc->samples;
     if (opt.sample_begin < 0 || opt.sample_end > sc->samples || opt.sample_begin >= opt.sample_end)
         return fail(RTM_E_INVALID, "bad sample slice [%d,%d) of %d", opt.sample_begin, opt.sample_end, sc->samples);
+    if (opt.max_depth > 511) return fail(RTM_E_INVALID, "max_depth %d exceeds 511 (the RNG counter holds 9 depth bits)", opt.max_depth);
+    if (sc->samples >= (1 << 23)) return fail(RTM_E_INVALID, "samples %d exceeds 2^23-1", sc->samples);
+    if ((uint64_t)sc->width * sc->height * sc->superSamples * sc->superSamples >= (1ull << 32))
+        return fail(RTM_E_INVALID, "width*height*superSamples^2 must stay below 2^32 sub-pixels");
     if (opt.variant != RTM_VARIANT_MEGA) return fail(RTM_E_UNSUPPORTED, "variant %d not built", opt.variant);
     const bool f32_path = (opt.compat == RTM_COMPAT_ABC && opt.precision == RTM_PRECISION_F32);
     if (f32_path && sc->n_spheres > RTM_MAX_CONST_SPHERES)
@@ -369,6 +378,10 @@ int renderer_create(const rtm_scene_desc* sc, const rtm_options* opt_in, rtm_ren
             s.inv_r[i] = (float)(1.0 / (double)rad);
             s.ex[i] = (float)em[3 * i]; s.ey[i] = (float)em[3 * i + 1]; s.ez[i] = (float)em[3 * i + 2];
             s.kd[i] = kdf;
+            {
+                const double th = (double)kdf * 4294967296.0;
+                s.kd_thr[i] = (th >= 4294967295.0) ? 0xFFFFFFFFu : (th <= 0.0 ? 0u : (uint32_t)th);
+            }
             if (kdf > 0.f) {
                 s.kx[i] = (float)(c0 / (double)kdf); s.ky[i] = (float)(c1 / (double)kdf); s.kz[i] = (float)(c2 / (double)kdf);
             } else {

@@ -39,6 +39,7 @@ struct RtmSceneF32Host {
     float ex[RTM_MAX_CONST_SPHERES], ey[RTM_MAX_CONST_SPHERES], ez[RTM_MAX_CONST_SPHERES];        // emission
     float kx[RTM_MAX_CONST_SPHERES], ky[RTM_MAX_CONST_SPHERES], kz[RTM_MAX_CONST_SPHERES];        // color/kd
     float kd[RTM_MAX_CONST_SPHERES];
+    uint32_t kd_thr[RTM_MAX_CONST_SPHERES];  // min(kd * 2^32, 2^32-1): roulette continues iff a 32-bit draw < kd_thr
 };
 
 // Sub-pixel record written by the exact primary pass and consumed by the FP32
@@ -62,6 +63,7 @@ struct RtmPassParams {
     int32_t s_begin, s_end;   // sample slice
     int32_t max_depth;
     uint32_t seed_lo, seed_hi;
+    uint32_t rk[10];          // Philox2x32 round keys: fold(seed) + r*0x9E3779B9
     float inv_norm;           // 1/(ss*ss*S) for the FP32 path
     float ref[3];             // reference point (as float, informational)
     double refd[3];           // reference point
