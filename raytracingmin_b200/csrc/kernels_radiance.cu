@@ -78,23 +78,71 @@ __device__ __forceinline__ void sphere_roots_f32(bool self, f3 o, f3 d, float oo
     tb = fmaf(cp, fast_rcp(tq), -RTM_T_EPS);
 }
 
-// Closest hit for N <= 8 (compile-time N): the candidate (t - eps) and the sphere index
-// share one 32-bit key, t in the upper 29 bits (8 ulp of t are given up: below the FP32
-// error of t itself), the index in the low 3; positive floats order like unsigned
-// integers, so one unsigned min per candidate does the accept test, the tie rule and
-// the bookkeeping.  Returns the key; RTM_KEY_INF or above = miss.
-template <int N>
-__device__ __forceinline__ unsigned trace_key_f32(int oid, f3 o, f3 d) {
-    const float oo = dot(o, o), dO = dot(d, o);
+// ---- packed FP32 (sm_100 f32x2): two spheres per instruction ----------------------
+typedef unsigned long long u64;
+__device__ __forceinline__ u64 pk(float lo, float hi) {
+    u64 r;
+    asm("mov.b64 %0, {%1, %2};" : "=l"(r) : "f"(lo), "f"(hi));
+    return r;
+}
+__device__ __forceinline__ u64 pk(float2 v) { return pk(v.x, v.y); }
+__device__ __forceinline__ void unpk(u64 v, float& lo, float& hi) { asm("mov.b64 {%0, %1}, %2;" : "=f"(lo), "=f"(hi) : "l"(v)); }
+__device__ __forceinline__ u64 fma2(u64 a, u64 b, u64 c) {
+    u64 r;
+    asm("fma.rn.f32x2 %0, %1, %2, %3;" : "=l"(r) : "l"(a), "l"(b), "l"(c));
+    return r;
+}
+__device__ __forceinline__ u64 add2(u64 a, u64 b) {
+    u64 r;
+    asm("add.rn.f32x2 %0, %1, %2;" : "=l"(r) : "l"(a), "l"(b));
+    return r;
+}
+// (x & mask) | idx in ONE LOP3: the mask sits in a register (an immediate mask plus an
+// immediate index would take two instructions).
+__device__ __forceinline__ unsigned key_pack(unsigned x, unsigned mask_reg, unsigned idx) {
+    unsigned r;
+    asm("lop3.b32 %0, %1, %2, %3, 0xEA;" : "=r"(r) : "r"(x), "r"(mask_reg), "r"(idx));
+    return r;
+}
+
+// Closest hit for N <= 8: spheres are tested in PAIRS with FFMA2/FADD2 (one instruction
+// does the same step for two spheres; the ray operand is broadcast, the sphere constants
+// come as 64-bit uniform-register pairs from constant memory).  The candidate (t - eps)
+// and the sphere index share one 32-bit key, t in the upper 29 bits (8 ulp of t are given
+// up: below the FP32 error of t itself), the index in the low 3; positive floats order
+// like unsigned integers, so an unsigned min does the accept test, the tie rule and the
+// bookkeeping.  Returns the key; RTM_KEY_INF or above = miss.
+template <int NP>
+__device__ __forceinline__ unsigned trace_pairs_f32(int oid, f3 o, f3 d, unsigned key_mask) {
+    const float noo = -dot(o, o), ndO = -dot(d, o);
+    const u64 dx = pk(d.x, d.x), dy = pk(d.y, d.y), dz = pk(d.z, d.z);
+    const u64 ox = pk(o.x, o.x), oy = pk(o.y, o.y), oz = pk(o.z, o.z);
+    const u64 noo2 = pk(noo, noo), ndO2 = pk(ndO, ndO), neps2 = pk(-RTM_T_EPS, -RTM_T_EPS);
     unsigned best = RTM_KEY_INF;
 #pragma unroll
-    for (int i = 0; i < N; ++i) {
-        float ta, tb;
-        sphere_roots_f32(i == oid, o, d, oo, dO, c_scene.cx[i], c_scene.cy[i], c_scene.cz[i], c_scene.m2cx[i],
-                         c_scene.m2cy[i], c_scene.m2cz[i], c_scene.K[i], ta, tb);
-        const unsigned ka = (__float_as_uint(ta) & ~7u) | (unsigned)i;
-        const unsigned kb = (__float_as_uint(tb) & ~7u) | (unsigned)i;
-        best = min(best, min(ka, kb));
+    for (int j = 0; j < NP; ++j) {
+        const RtmPairF32& c = c_scene.pairs[j];
+        const u64 b2 = fma2(dx, pk(c.cx), fma2(dy, pk(c.cy), fma2(dz, pk(c.cz), ndO2)));                   // (c-o).d
+        const u64 ncp2 = fma2(ox, pk(c.p2x), fma2(oy, pk(c.p2y), fma2(oz, pk(c.p2z), add2(noo2, pk(c.nK)))));  // r^2 - |c-o|^2
+        float b0, b1, n0, n1;
+        unpk(b2, b0, b1);
+        unpk(ncp2, n0, n1);
+        n0 = (2 * j == oid) ? 0.f : n0;      // leaving this sphere's surface: c' = 0 exactly
+        n1 = (2 * j + 1 == oid) ? 0.f : n1;
+        const u64 ncp = pk(n0, n1);
+        float D0, D1;
+        unpk(fma2(b2, b2, ncp), D0, D1);
+        const float s0 = fast_sqrt(D0), s1 = fast_sqrt(D1);          // NaN when the ray misses the sphere
+        const u64 tq2 = add2(b2, pk(copysignf(s0, b0), copysignf(s1, b1)));
+        float q0, q1;
+        unpk(tq2, q0, q1);
+        const u64 rn = pk(fast_rcp(-q0), fast_rcp(-q1));
+        float ta0, ta1, tb0, tb1;
+        unpk(add2(tq2, neps2), ta0, ta1);                            // tq - eps
+        unpk(fma2(ncp, rn, neps2), tb0, tb1);                        // c'/tq - eps
+        const unsigned k0 = key_pack(min(__float_as_uint(ta0), __float_as_uint(tb0)), key_mask, 2 * j);
+        const unsigned k1 = key_pack(min(__float_as_uint(ta1), __float_as_uint(tb1)), key_mask, 2 * j + 1);
+        best = min(best, min(k0, k1));
     }
     return best;
 }
@@ -121,9 +169,9 @@ __device__ __forceinline__ int trace_loop_f32(int n, int oid, f3 o, f3 d, float&
 }
 
 template <int N>
-__device__ __forceinline__ int trace_f32(int n_rt, int oid, f3 o, f3 d, float& t) {
+__device__ __forceinline__ int trace_f32(int n_rt, int oid, f3 o, f3 d, float& t, unsigned key_mask) {
     if (N > 0) {
-        const unsigned key = trace_key_f32<(N > 0 ? N : 1)>(oid, o, d);
+        const unsigned key = trace_pairs_f32<(N + 1) / 2>(oid, o, d, key_mask);
         t = __uint_as_float(key & ~7u) + RTM_T_EPS;
         return (key < RTM_KEY_INF) ? (int)(key & 7u) : -1;
     }
@@ -205,6 +253,7 @@ __global__ void __launch_bounds__(RTM_MEGA_THREADS, 5) radiance_mega_kernel(RtmP
     int id = 0, s = 0, depth = 0;
 
     unsigned long long rays_ref = 0, traced = 0;
+    const unsigned key_mask = p.key_mask;  // 0xFFFFFFF8 from the host: kept in a register for key_pack
 
     for (;;) {
         // ---- refill: lanes without a unit take the next sub-pixels of the warp's chunk
@@ -274,7 +323,7 @@ __global__ void __launch_bounds__(RTM_MEGA_THREADS, 5) radiance_mega_kernel(RtmP
                 T.x *= al.x; T.y *= al.y; T.z *= al.z;   // colorKD, SettingData.h:11-13
                 const f3 d = cosine_dir(w, rnd.y, ((rnd.x & 0xFFFu) << 10) | (rnd.y & 0x3FFu));
                 float t;
-                const int id2 = trace_f32<N>(n, id, o, d, t);
+                const int id2 = trace_f32<N>(n, id, o, d, t, key_mask);
                 ++traced;
                 if (id2 >= 0) {
                     o = mk(fmaf(d.x, t, o.x), fmaf(d.y, t, o.y), fmaf(d.z, t, o.z));  // Renderer.cpp:79
@@ -364,7 +413,7 @@ __global__ void __launch_bounds__(256) to_u8_kernel(const float4* __restrict__ a
 }
 
 // ---- test hooks ---------------------------------------------------------------
-__global__ void closest_hit_f32_kernel(int n_sph, double rx, double ry, double rz, uint32_t n, const double* __restrict__ org,
+__global__ void closest_hit_f32_kernel(int n_sph, unsigned key_mask, double rx, double ry, double rz, uint32_t n, const double* __restrict__ org,
                                        const double* __restrict__ dir, const int32_t* __restrict__ origin_id,
                                        int32_t* __restrict__ hit, double* __restrict__ tout) {
     const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
@@ -372,7 +421,14 @@ __global__ void closest_hit_f32_kernel(int n_sph, double rx, double ry, double r
     const f3 o = mk((float)(org[3 * i] - rx), (float)(org[3 * i + 1] - ry), (float)(org[3 * i + 2] - rz));
     const f3 d = mk((float)dir[3 * i], (float)dir[3 * i + 1], (float)dir[3 * i + 2]);
     float t;
-    const int id = trace_f32<0>(n_sph, origin_id ? origin_id[i] : -1, o, d, t);
+    const int oid = origin_id ? origin_id[i] : -1;
+    int id;
+    // same code paths as the megakernel: packed pairs up to 8 spheres, the loop beyond
+    if (n_sph >= 1 && n_sph <= 2) id = trace_f32<2>(n_sph, oid, o, d, t, key_mask);
+    else if (n_sph <= 4 && n_sph >= 3) id = trace_f32<4>(n_sph, oid, o, d, t, key_mask);
+    else if (n_sph <= 6 && n_sph >= 5) id = trace_f32<6>(n_sph, oid, o, d, t, key_mask);
+    else if (n_sph <= 8 && n_sph >= 7) id = trace_f32<8>(n_sph, oid, o, d, t, key_mask);
+    else id = trace_f32<0>(n_sph, oid, o, d, t, key_mask);
     hit[i] = id;
     tout[i] = (double)t;
 }
@@ -440,7 +496,7 @@ void rtm_launch_to_u8(const float4* accum, unsigned char* out, uint64_t n_pix, c
 
 void rtm_launch_closest_hit_f32(int32_t n_spheres, const double* refd, uint32_t n, const double* org, const double* dir,
                                 const int32_t* origin_id, int32_t* hit, double* t, cudaStream_t st) {
-    closest_hit_f32_kernel<<<(n + 127) / 128, 128, 0, st>>>(n_spheres, refd[0], refd[1], refd[2], n, org, dir, origin_id, hit, t);
+    closest_hit_f32_kernel<<<(n + 127) / 128, 128, 0, st>>>(n_spheres, 0xFFFFFFF8u, refd[0], refd[1], refd[2], n, org, dir, origin_id, hit, t);
 }
 
 void rtm_launch_philox(uint32_t n, uint32_t c1, uint32_t c2, uint32_t c3, uint32_t k0, uint32_t k1, uint32_t* out, cudaStream_t st) {

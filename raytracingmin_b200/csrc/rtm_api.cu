@@ -161,6 +161,7 @@ RtmPassParams make_params(const rtm_renderer* r, const GpuCtx& c) {
     p.seed_lo = (uint32_t)r->opt.seed;
     p.seed_hi = (uint32_t)(r->opt.seed >> 32);
     p.inv_norm = (float)(1.0 / ((double)r->ss * r->ss * r->S));
+    p.key_mask = 0xFFFFFFF8u;
     {
         // 32-bit Philox2x32 key from the 64-bit seed
         uint32_t k = p.seed_lo ^ (p.seed_hi * 0x85EBCA6Bu) ^ (p.seed_hi >> 15);
@@ -386,6 +387,22 @@ int renderer_create(const rtm_scene_desc* sc, const rtm_options* opt_in, rtm_ren
                 s.kx[i] = (float)(c0 / (double)kdf); s.ky[i] = (float)(c1 / (double)kdf); s.kz[i] = (float)(c2 / (double)kdf);
             } else {
                 s.kx[i] = s.ky[i] = s.kz[i] = 0.f;
+            }
+        }
+    }
+
+    if (f32_path) {
+        RtmSceneF32Host& s = r->f32;
+        for (int j = 0; j < RTM_MAX_PAIRS; ++j) {
+            float* f = reinterpret_cast<float*>(&s.pairs[j]);
+            for (int h = 0; h < 2; ++h) {
+                const int i = 2 * j + h;
+                const bool real = i < n;
+                // dummy: centre at the reference point, -c' = -1e30 -> negative discriminant -> NaN -> never a hit
+                f[0 + h] = real ? s.cx[i] : 0.f;  f[2 + h] = real ? s.cy[i] : 0.f;  f[4 + h] = real ? s.cz[i] : 0.f;
+                f[6 + h] = real ? -s.m2cx[i] : 0.f; f[8 + h] = real ? -s.m2cy[i] : 0.f; f[10 + h] = real ? -s.m2cz[i] : 0.f;
+                f[12 + h] = real ? -s.K[i] : -1e30f;
+                f[14 + h] = 0.f;
             }
         }
     }

@@ -28,6 +28,14 @@ struct RtmSceneF64 {
     const double* kd;        // (double)(float)max(r,g,b)        src/SettingData.h:14-16
 };
 
+// Two spheres side by side for the packed (f32x2) sphere test of the FP32 megakernel:
+// lane .x = sphere 2j, lane .y = sphere 2j+1 (a never-hit dummy pads an odd count).
+// p2 = +2c and nK = r^2 - |c|^2 so that the kernel forms -c' = o.(2c) + (nK - |o|^2).
+struct __align__(16) RtmPairF32 {
+    float2 cx, cy, cz, p2x, p2y, p2z, nK, pad;
+};
+#define RTM_MAX_PAIRS 4
+
 // Per-sphere data of the FP32 path, relative to the scene reference point
 // (the camera origin), SoA.  Filled on the host in double, rounded once.
 struct RtmSceneF32Host {
@@ -39,6 +47,7 @@ struct RtmSceneF32Host {
     float ex[RTM_MAX_CONST_SPHERES], ey[RTM_MAX_CONST_SPHERES], ez[RTM_MAX_CONST_SPHERES];        // emission
     float kx[RTM_MAX_CONST_SPHERES], ky[RTM_MAX_CONST_SPHERES], kz[RTM_MAX_CONST_SPHERES];        // color/kd
     float kd[RTM_MAX_CONST_SPHERES];
+    RtmPairF32 pairs[RTM_MAX_PAIRS];     // the first 8 spheres again, paired
     uint32_t kd_thr[RTM_MAX_CONST_SPHERES];  // min(kd * 2^32, 2^32-1): roulette continues iff a 32-bit draw < kd_thr
 };
 
@@ -63,6 +72,7 @@ struct RtmPassParams {
     int32_t s_begin, s_end;   // sample slice
     int32_t max_depth;
     uint32_t seed_lo, seed_hi;
+    uint32_t key_mask;        // 0xFFFFFFF8, passed in so that it lives in a register (see key_pack)
     uint32_t rk[10];          // Philox2x32 round keys: fold(seed) + r*0x9E3779B9
     float inv_norm;           // 1/(ss*ss*S) for the FP32 path
     float ref[3];             // reference point (as float, informational)
