@@ -97,6 +97,23 @@ __device__ __forceinline__ u64 add2(u64 a, u64 b) {
     asm("add.rn.f32x2 %0, %1, %2;" : "=l"(r) : "l"(a), "l"(b));
     return r;
 }
+__device__ __forceinline__ u64 mul2(u64 a, u64 b) {
+    u64 r;
+    asm("mul.rn.f32x2 %0, %1, %2;" : "=l"(r) : "l"(a), "l"(b));
+    return r;
+}
+// Row oid+1 of this table is 1 everywhere except column oid: multiplying -c' by it zeroes
+// c' of the sphere the ray leaves (2 LDS.128 + one FMUL2 per pair instead of a compare and
+// a select per sphere).  Row 0 (oid = -1: no origin sphere) is all ones.
+struct SelfMask {
+    float4 row[9][2];
+};
+__device__ __forceinline__ void init_selfmask(SelfMask& m) {
+    for (int i = threadIdx.x; i < 9 * 8; i += blockDim.x) {
+        const int r = i >> 3, c = i & 7;
+        reinterpret_cast<float*>(&m.row[0][0])[i] = (c == r - 1) ? 0.f : 1.f;
+    }
+}
 // (x & mask) | idx in ONE LOP3: the mask sits in a register (an immediate mask plus an
 // immediate index would take two instructions).
 __device__ __forceinline__ unsigned key_pack(unsigned x, unsigned mask_reg, unsigned idx) {
@@ -113,23 +130,22 @@ __device__ __forceinline__ unsigned key_pack(unsigned x, unsigned mask_reg, unsi
 // like unsigned integers, so an unsigned min does the accept test, the tie rule and the
 // bookkeeping.  Returns the key; RTM_KEY_INF or above = miss.
 template <int NP>
-__device__ __forceinline__ unsigned trace_pairs_f32(int oid, f3 o, f3 d, unsigned key_mask) {
+__device__ __forceinline__ unsigned trace_pairs_f32(const SelfMask& sm, int oid, f3 o, f3 d, unsigned key_mask) {
     const float noo = -dot(o, o), ndO = -dot(d, o);
     const u64 dx = pk(d.x, d.x), dy = pk(d.y, d.y), dz = pk(d.z, d.z);
     const u64 ox = pk(o.x, o.x), oy = pk(o.y, o.y), oz = pk(o.z, o.z);
     const u64 noo2 = pk(noo, noo), ndO2 = pk(ndO, ndO), neps2 = pk(-RTM_T_EPS, -RTM_T_EPS);
     unsigned best = RTM_KEY_INF;
+    const float4 m0 = sm.row[oid + 1][0], m1 = sm.row[oid + 1][1];
+    const u64 mask[4] = {pk(m0.x, m0.y), pk(m0.z, m0.w), pk(m1.x, m1.y), pk(m1.z, m1.w)};
 #pragma unroll
     for (int j = 0; j < NP; ++j) {
         const RtmPairF32& c = c_scene.pairs[j];
         const u64 b2 = fma2(dx, pk(c.cx), fma2(dy, pk(c.cy), fma2(dz, pk(c.cz), ndO2)));                   // (c-o).d
         const u64 ncp2 = fma2(ox, pk(c.p2x), fma2(oy, pk(c.p2y), fma2(oz, pk(c.p2z), add2(noo2, pk(c.nK)))));  // r^2 - |c-o|^2
-        float b0, b1, n0, n1;
+        const u64 ncp = mul2(ncp2, mask[j]);   // leaving this sphere's surface: c' = 0 exactly
+        float b0, b1;
         unpk(b2, b0, b1);
-        unpk(ncp2, n0, n1);
-        n0 = (2 * j == oid) ? 0.f : n0;      // leaving this sphere's surface: c' = 0 exactly
-        n1 = (2 * j + 1 == oid) ? 0.f : n1;
-        const u64 ncp = pk(n0, n1);
         float D0, D1;
         unpk(fma2(b2, b2, ncp), D0, D1);
         const float s0 = fast_sqrt(D0), s1 = fast_sqrt(D1);          // NaN when the ray misses the sphere
@@ -169,9 +185,9 @@ __device__ __forceinline__ int trace_loop_f32(int n, int oid, f3 o, f3 d, float&
 }
 
 template <int N>
-__device__ __forceinline__ int trace_f32(int n_rt, int oid, f3 o, f3 d, float& t, unsigned key_mask) {
+__device__ __forceinline__ int trace_f32(const SelfMask& sm, int n_rt, int oid, f3 o, f3 d, float& t, unsigned key_mask) {
     if (N > 0) {
-        const unsigned key = trace_pairs_f32<(N + 1) / 2>(oid, o, d, key_mask);
+        const unsigned key = trace_pairs_f32<(N + 1) / 2>(sm, oid, o, d, key_mask);
         t = __uint_as_float(key & ~7u) + RTM_T_EPS;
         return (key < RTM_KEY_INF) ? (int)(key & 7u) : -1;
     }
@@ -231,7 +247,9 @@ template <int N>
 __global__ void __launch_bounds__(RTM_MEGA_THREADS, 5) radiance_mega_kernel(RtmPassParams p, float4* __restrict__ records,
                                                                             RtmCounters* __restrict__ counters, int n_rt) {
     __shared__ SharedScene sh;
+    __shared__ SelfMask sh_mask;
     const int n = (N > 0) ? N : n_rt;
+    init_selfmask(sh_mask);
     load_shared_scene(sh, n);
 
     const unsigned lane = threadIdx.x & 31u;
@@ -323,7 +341,7 @@ __global__ void __launch_bounds__(RTM_MEGA_THREADS, 5) radiance_mega_kernel(RtmP
                 T.x *= al.x; T.y *= al.y; T.z *= al.z;   // colorKD, SettingData.h:11-13
                 const f3 d = cosine_dir(w, rnd.y, ((rnd.x & 0xFFFu) << 10) | (rnd.y & 0x3FFu));
                 float t;
-                const int id2 = trace_f32<N>(n, id, o, d, t, key_mask);
+                const int id2 = trace_f32<N>(sh_mask, n, id, o, d, t, key_mask);
                 ++traced;
                 if (id2 >= 0) {
                     o = mk(fmaf(d.x, t, o.x), fmaf(d.y, t, o.y), fmaf(d.z, t, o.z));  // Renderer.cpp:79
@@ -416,19 +434,23 @@ __global__ void __launch_bounds__(256) to_u8_kernel(const float4* __restrict__ a
 __global__ void closest_hit_f32_kernel(int n_sph, unsigned key_mask, double rx, double ry, double rz, uint32_t n, const double* __restrict__ org,
                                        const double* __restrict__ dir, const int32_t* __restrict__ origin_id,
                                        int32_t* __restrict__ hit, double* __restrict__ tout) {
+    __shared__ SelfMask sh_mask;
+    init_selfmask(sh_mask);
+    __syncthreads();
     const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
     if (i >= n) return;
     const f3 o = mk((float)(org[3 * i] - rx), (float)(org[3 * i + 1] - ry), (float)(org[3 * i + 2] - rz));
     const f3 d = mk((float)dir[3 * i], (float)dir[3 * i + 1], (float)dir[3 * i + 2]);
     float t;
-    const int oid = origin_id ? origin_id[i] : -1;
+    int oid = origin_id ? origin_id[i] : -1;
+    if (oid < -1 || oid >= n_sph) oid = -1;
     int id;
     // same code paths as the megakernel: packed pairs up to 8 spheres, the loop beyond
-    if (n_sph >= 1 && n_sph <= 2) id = trace_f32<2>(n_sph, oid, o, d, t, key_mask);
-    else if (n_sph <= 4 && n_sph >= 3) id = trace_f32<4>(n_sph, oid, o, d, t, key_mask);
-    else if (n_sph <= 6 && n_sph >= 5) id = trace_f32<6>(n_sph, oid, o, d, t, key_mask);
-    else if (n_sph <= 8 && n_sph >= 7) id = trace_f32<8>(n_sph, oid, o, d, t, key_mask);
-    else id = trace_f32<0>(n_sph, oid, o, d, t, key_mask);
+    if (n_sph >= 1 && n_sph <= 2) id = trace_f32<2>(sh_mask, n_sph, oid, o, d, t, key_mask);
+    else if (n_sph <= 4 && n_sph >= 3) id = trace_f32<4>(sh_mask, n_sph, oid, o, d, t, key_mask);
+    else if (n_sph <= 6 && n_sph >= 5) id = trace_f32<6>(sh_mask, n_sph, oid, o, d, t, key_mask);
+    else if (n_sph <= 8 && n_sph >= 7) id = trace_f32<8>(sh_mask, n_sph, oid, o, d, t, key_mask);
+    else id = trace_f32<0>(sh_mask, n_sph, oid, o, d, t, key_mask);
     hit[i] = id;
     tout[i] = (double)t;
 }
