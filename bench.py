@@ -192,10 +192,8 @@ def run_gpu_arm(args):
         dist.init_process_group("nccl", device_id=dev)
 
     sc, wl = load_workload(args.workload)
-    S = sc.samples
-    s0, s1 = S * rank // world, S * (rank + 1) // world
-    if s1 <= s0:
-        raise SystemExit(f"cannot slice {S} samples over {world} ranks")
+    from raytracingmin_b200.partition import sample_slice, reduce_partials
+    s0, s1 = sample_slice(sc.samples, rank, world)
     n_pix, n_sub = sc.width * sc.height, sc.n_sub
 
     # device-resident handle: the library writes its partial framebuffer straight into a
@@ -207,8 +205,7 @@ def run_gpu_arm(args):
 
     def step():
         r.render_async(stream.cuda_stream)
-        if world > 1:
-            dist.reduce(accum, dst=0, op=dist.ReduceOp.SUM)
+        reduce_partials(accum, dst=0)
 
     def fence():
         torch.cuda.synchronize()
