@@ -192,13 +192,14 @@ def run_gpu_arm(args):
         dist.init_process_group("nccl", device_id=dev)
 
     sc, wl = load_workload(args.workload)
-    from raytracingmin_b200.partition import sample_slice, reduce_partials
-    s0, s1 = sample_slice(sc.samples, rank, world)
-    n_pix, n_sub = sc.width * sc.height, sc.n_sub
+    from raytracingmin_b200.partition import plan_partition, reduce_partials
+    plan = plan_partition(sc.samples, sc.superSamples, rank, world)
+    n_pix = sc.width * sc.height
+    n_sub = n_pix * (plan["sub_end"] - plan["sub_begin"])      # sub-pixels THIS rank renders
 
     # device-resident handle: the library writes its partial framebuffer straight into a
     # torch tensor (the NCCL send buffer); no host sync between the last kernel and the reduce.
-    r = rtm.Renderer(sc, device=local, sample_begin=s0, sample_end=s1, seed=0x5EED)
+    r = rtm.Renderer(sc, device=local, seed=0x5EED, **plan)
     accum = torch.zeros((sc.height, sc.width, 4), dtype=torch.float32, device=dev)
     r.set_accum_buffer(accum.data_ptr())
     stream = torch.cuda.current_stream()
@@ -275,7 +276,7 @@ def run_gpu_arm(args):
         # tests of the bounce rays only (17 each), 21/ray finalisation + 91/bounce for each traced
         # ray, 18/sample accumulate.  The primary pass's 37/sub-pixel + N tests + 21 are in its own kernel.
         f_kernel = 17.0 * (st.sphere_tests - n_sub * sc.n) + 21.0 * bounce_rays + 91.0 * bounce_rays + 18.0 * samples
-        f_total = algorithmic_flops(sc.n, tests_all, rays_all, samples_all, n_sub)
+        f_total = algorithmic_flops(sc.n, tests_all, rays_all, samples_all, sc.n_sub)
         achieved = f_kernel / (kms[1] * 1e-3) / 1e12
         fb_gbs = n_pix * 16 / (kms[2] * 1e-3) / 1e9 if kms[2] > 0 else None
         peaks = {}
@@ -290,8 +291,9 @@ def run_gpu_arm(args):
             "data": "synthetic",
             "config": {"workload": wl["name"], "scene": wl["scene"], "width": sc.width, "height": sc.height,
                        "samples": sc.samples, "superSamples": sc.superSamples, "spp": sc.spp, "n_spheres": sc.n,
-                       "partition": f"samples loop sliced over {world} rank(s)" + (", one NCCL sum-reduce to rank 0" if world > 1 else ""),
-                       "l2": "inputs larger than L2: the 2.1 GB sub-pixel record buffer is rewritten and re-read every step"
+                       "partition": (("sub-pixel grid" if plan["sub_end"] - plan["sub_begin"] < sc.superSamples ** 2 else "samples loop")
+                                     + f" sliced over {world} rank(s)" + (", one NCCL sum-reduce to rank 0" if world > 1 else "")),
+                       "l2": f"inputs larger than L2: the {n_sub * 16 / 1e9:.2f} GB sub-pixel record buffer is rewritten and re-read every step"
                              if n_sub * 16 > 126e6 else "working set below L2 (plumbing workload)",
                        "semantics": "L-ABC (SURVEY.md §0.1), FP64 bit-exact primary pass + FP32 bounces, Philox2x32-10"},
             "msamples_per_s": samples_all / (ms_step * 1e-3) / 1e6,

@@ -12,10 +12,10 @@ from .api import (  # noqa: F401
     ACCEL_AUTO, ACCEL_BRUTE, ACCEL_BVH,
 )
 
-from .partition import sample_slice, reduce_partials  # noqa: F401
+from .partition import sample_slice, plan_partition, reduce_partials  # noqa: F401
 
 __all__ = [
-    "sample_slice", "reduce_partials",
+    "sample_slice", "plan_partition", "reduce_partials",
     "Scene", "SceneError", "load_scene", "scene_from_dict", "scene_to_dict", "random_scene",
     "Renderer", "RtmError", "RenderResult", "Stats", "lib_path", "load_library",
 ]

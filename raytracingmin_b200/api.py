@@ -47,6 +47,7 @@ class _Options(C.Structure):
         ("device", C.c_int32), ("n_gpus", C.c_int32), ("compat", C.c_int32), ("precision", C.c_int32),
         ("variant", C.c_int32), ("accel", C.c_int32), ("max_depth", C.c_int32),
         ("sample_begin", C.c_int32), ("sample_end", C.c_int32), ("seed", C.c_uint64),
+        ("sub_begin", C.c_int32), ("sub_end", C.c_int32),
     ]
 
 
@@ -141,7 +142,7 @@ class Renderer:
 
     def __init__(self, scene: Scene, *, device: int = 0, n_gpus: int = 1, compat: str = "abc", precision: str = "f32",
                  variant: str = "mega", accel: str = "auto", max_depth: int = 0, seed: int = 0x5EED,
-                 sample_begin: int = 0, sample_end: int = 0):
+                 sample_begin: int = 0, sample_end: int = 0, sub_begin: int = 0, sub_end: int = 0):
         self._lib = load_library()
         self._h = C.c_void_p()
         sc = scene.normalized()
@@ -164,6 +165,7 @@ class Renderer:
         o.variant, o.accel = _VARIANT[variant], _ACCEL[accel]
         o.max_depth, o.seed = max_depth, seed
         o.sample_begin, o.sample_end = sample_begin, sample_end
+        o.sub_begin, o.sub_end = sub_begin, sub_end
         self.compat = compat
         _check(self._lib, self._lib.renderer_create(C.byref(d), C.byref(o), C.byref(self._h)))
 

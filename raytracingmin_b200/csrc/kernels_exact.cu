@@ -79,14 +79,18 @@ __device__ __forceinline__ d3 camera_dir(const RtmFrame& f, int x, int y, int sx
     return normalize(v);
 }
 
-__device__ __forceinline__ void decode_sub(const RtmFrame& f, uint64_t q, int& x, int& y, int& sx, int& sy) {
-    const uint32_t ss = (uint32_t)f.ss;
-    sy = (int)(q % ss) + 1;
-    q /= ss;
-    sx = (int)(q % ss) + 1;
-    q /= ss;
-    x = (int)(q % (uint32_t)f.W);
-    y = (int)(q / (uint32_t)f.W);
+// local record index ql (pixel-major over this handle's slice of the sub-pixel grid) ->
+// pixel, sub-pixel coordinates (1-based as src/Renderer.cpp:224-225) and the GLOBAL
+// sub-pixel index qg = pixel*ss*ss + (sx-1)*ss + (sy-1) that keys the RNG and the hit map.
+__device__ __forceinline__ void decode_sub(const RtmPassParams& p, uint64_t ql, int& x, int& y, int& sx, int& sy, uint64_t& qg) {
+    const uint32_t ss = (uint32_t)p.frame.ss, sc = (uint32_t)p.sub_count;
+    const uint32_t pix = (uint32_t)(ql / sc);
+    const uint32_t j = (uint32_t)p.sub_begin + (uint32_t)(ql % sc);
+    sy = (int)(j % ss) + 1;
+    sx = (int)(j / ss) + 1;
+    x = (int)(pix % (uint32_t)p.frame.W);
+    y = (int)(pix / (uint32_t)p.frame.W);
+    qg = (uint64_t)pix * (ss * ss) + j;
 }
 
 // Renderer.cpp:43-49 with std::max/std::min semantics
@@ -101,12 +105,13 @@ __global__ void __launch_bounds__(256) primary_f64_kernel(RtmSceneF64 sc, RtmPas
     const uint64_t q = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
     if (q >= p.n_sub) return;
     int x, y, sx, sy;
-    decode_sub(p.frame, q, x, y, sx, sy);
+    uint64_t qg;
+    decode_sub(p, q, x, y, sx, sy, qg);
     const d3 o = mk(p.frame.o[0], p.frame.o[1], p.frame.o[2]);
     const d3 d = camera_dir(p.frame, x, y, sx, sy);
     double t;
     const int id = closest_hit(sc, o, d, t);
-    if (hits) hits[q] = id;
+    if (hits) hits[qg] = id;
     if (records) {
         float4 rec;
         if (id < 0) {
@@ -158,7 +163,8 @@ __global__ void __launch_bounds__(128) radiance_f64_kernel(RtmSceneF64 sc, RtmPa
     unsigned long long rays = 0;
     if (q < p.n_sub) {
         int x, y, sx, sy;
-        decode_sub(p.frame, q, x, y, sx, sy);
+        uint64_t qg;
+        decode_sub(p, q, x, y, sx, sy, qg);
         const d3 o0 = mk(p.frame.o[0], p.frame.o[1], p.frame.o[2]);
         const d3 d0 = camera_dir(p.frame, x, y, sx, sy);
         const double PI = 3.14159265358979323846;
@@ -172,7 +178,7 @@ __global__ void __launch_bounds__(128) radiance_f64_kernel(RtmSceneF64 sc, RtmPa
                 if (id < 0) break;
                 const d3 e = mk(__ldg(sc.emission + 3 * id), __ldg(sc.emission + 3 * id + 1), __ldg(sc.emission + 3 * id + 2));
                 L = add(L, mul(T, e));
-                const uint4 r = rtm_philox4x32_10(make_uint4((uint32_t)q, (uint32_t)(q >> 32), (uint32_t)s, (uint32_t)depth),
+                const uint4 r = rtm_philox4x32_10(make_uint4((uint32_t)qg, (uint32_t)(qg >> 32), (uint32_t)s, (uint32_t)depth),
                                                   p.seed_lo, p.seed_hi);
                 const double kd = __ldg(sc.kd + id);
                 if (!(rtm_u01_f64(r.x, r.y) <= kd)) break;  // :78 / :112

@@ -261,8 +261,11 @@ __global__ void __launch_bounds__(RTM_MEGA_THREADS, 5) radiance_mega_kernel(RtmP
     unsigned w_next = 0, w_end = 0;  // warp-uniform slice of the work cursor
     bool have = false, done = false;
 
-    // unit (sub-pixel) state
-    unsigned q = 0;
+    const unsigned sub_begin = (unsigned)p.sub_begin, sub_count = (unsigned)p.sub_count;
+    const unsigned grid = (unsigned)(p.frame.ss * p.frame.ss);
+    const bool full_grid = (sub_count == grid);
+    // unit (sub-pixel) state: ql = record index in this handle's slice, q = global sub-pixel index
+    unsigned q = 0, ql = 0;
     f3 P = mk(0, 0, 0), Pw = mk(0, 0, 1);  // primary hit point, oriented normal there
     int Pid = 0;
     f3 acc = mk(0, 0, 0);
@@ -292,8 +295,10 @@ __global__ void __launch_bounds__(RTM_MEGA_THREADS, 5) radiance_mega_kernel(RtmP
             const unsigned rank = __popc(need & lt_mask);
             const bool mine = ((need >> lane) & 1u) && rank < avail;
             if (mine) {
-                q = w_next + rank;
-                const float4 rec = records[q];
+                ql = w_next + rank;
+                // RNG counter = GLOBAL sub-pixel index, so the image does not depend on the partition
+                q = full_grid ? ql : (ql / sub_count) * grid + sub_begin + (ql % sub_count);
+                const float4 rec = records[ql];
                 const unsigned wbits = __float_as_uint(rec.w);
                 const unsigned ns = (unsigned)(s_end - s_begin);
                 const bool miss = (wbits == RTM_REC_MISS);
@@ -308,7 +313,7 @@ __global__ void __launch_bounds__(RTM_MEGA_THREADS, 5) radiance_mega_kernel(RtmP
                         out.y = clamp01f(e0.y * inv_norm) * (float)ns;
                         out.z = clamp01f(e0.z * inv_norm) * (float)ns;
                     }
-                    records[q] = out;
+                    records[ql] = out;
                     rays_ref += ns;
                 } else {
                     have = true;
@@ -365,7 +370,7 @@ __global__ void __launch_bounds__(RTM_MEGA_THREADS, 5) radiance_mega_kernel(RtmP
                 acc.z += clamp01f(L.z * inv_norm);
                 ++s;
                 if (s == s_end) {
-                    records[q] = make_float4(acc.x, acc.y, acc.z, 0.f);
+                    records[ql] = make_float4(acc.x, acc.y, acc.z, 0.f);
                     rays_ref += (unsigned)(s_end - s_begin);
                     have = false;
                 } else {
@@ -503,7 +508,7 @@ void rtm_launch_radiance_mega(int32_t n, const RtmPassParams& p, float4* records
 }
 
 void rtm_launch_accumulate(const RtmPassParams& p, const float4* records, float4* accum, cudaStream_t st) {
-    const int g = p.frame.ss * p.frame.ss;
+    const int g = p.sub_count;
     const unsigned long long n_pix = (unsigned long long)p.frame.W * p.frame.H;
     if (g <= 32 && (g & (g - 1)) == 0) {
         accumulate_pow2_kernel<<<(unsigned)((p.n_sub + 255) / 256), 256, 0, st>>>(records, accum, p.n_sub, g);

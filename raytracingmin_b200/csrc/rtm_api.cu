@@ -172,6 +172,8 @@ RtmPassParams make_params(const rtm_renderer* r, const GpuCtx& c) {
         p.ref[k] = (float)r->refd[k];
     }
     p.n_sub = r->n_sub;
+    p.sub_begin = r->opt.sub_begin;
+    p.sub_count = r->opt.sub_end - r->opt.sub_begin;
     return p;
 }
 
@@ -303,6 +305,13 @@ int renderer_create(const rtm_scene_desc* sc, const rtm_options* opt_in, rtm_ren
     if (sc->samples >= (1 << 23)) return fail(RTM_E_INVALID, "samples %d exceeds 2^23-1", sc->samples);
     if ((uint64_t)sc->width * sc->height * sc->superSamples * sc->superSamples >= (1ull << 32))
         return fail(RTM_E_INVALID, "width*height*superSamples^2 must stay below 2^32 sub-pixels");
+    if (opt.sub_begin == 0 && opt.sub_end == 0) opt.sub_end = sc->superSamples * sc->superSamples;
+    if (opt.sub_begin < 0 || opt.sub_end > sc->superSamples * sc->superSamples || opt.sub_begin >= opt.sub_end)
+        return fail(RTM_E_INVALID, "bad sub-pixel slice [%d,%d) of %d", opt.sub_begin, opt.sub_end,
+                    sc->superSamples * sc->superSamples);
+    const bool full_grid = (opt.sub_end - opt.sub_begin) == sc->superSamples * sc->superSamples;
+    if (!full_grid && (opt.compat == RTM_COMPAT_HEAD || opt.n_gpus > 1))
+        return fail(RTM_E_UNSUPPORTED, "sub-pixel slices need COMPAT_ABC and one GPU per handle");
     if (opt.variant != RTM_VARIANT_MEGA) return fail(RTM_E_UNSUPPORTED, "variant %d not built", opt.variant);
     const bool f32_path = (opt.compat == RTM_COMPAT_ABC && opt.precision == RTM_PRECISION_F32);
     if (f32_path && sc->n_spheres > RTM_MAX_CONST_SPHERES)
@@ -321,7 +330,7 @@ int renderer_create(const rtm_scene_desc* sc, const rtm_options* opt_in, rtm_ren
     r->opt = opt;
     r->W = sc->width; r->H = sc->height; r->S = sc->samples; r->ss = sc->superSamples; r->n = sc->n_spheres;
     r->n_pix = (uint64_t)r->W * r->H;
-    r->n_sub = r->n_pix * r->ss * r->ss;
+    r->n_sub = r->n_pix * (uint64_t)(opt.sub_end - opt.sub_begin);   // sub-pixels this handle renders
 
     // camera frame, src/Renderer.cpp:202-208
     {
@@ -503,6 +512,8 @@ int renderer_set_accum_buffer(rtm_renderer* r, void* p) {
 
 int renderer_render(rtm_renderer* r, float* rgb_out, int32_t* hit_out, rtm_stats* stats) {
     if (!r) return fail(RTM_E_INVALID, "null renderer");
+    if (hit_out && (r->opt.sub_end - r->opt.sub_begin) != r->ss * r->ss)
+        return fail(RTM_E_UNSUPPORTED, "the primary-hit map needs a handle that covers the full sub-pixel grid");
     const auto t0 = std::chrono::steady_clock::now();
     const int G = (int)r->gpus.size();
     int launches = 0;

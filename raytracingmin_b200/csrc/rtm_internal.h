@@ -77,7 +77,8 @@ struct RtmPassParams {
     float inv_norm;           // 1/(ss*ss*S) for the FP32 path
     float ref[3];             // reference point (as float, informational)
     double refd[3];           // reference point
-    uint64_t n_sub;           // W*H*ss*ss
+    uint64_t n_sub;           // W*H*sub_count: sub-pixels THIS handle renders (records are indexed by it)
+    int32_t sub_begin, sub_count;  // slice of the ss*ss sub-pixel grid
 };
 
 // ---- launchers implemented by the kernel TUs (all asynchronous on `st`) ----

@@ -245,6 +245,36 @@ def test_sample_slices_add_up(scene_path, precision):
     assert np.allclose(parts, full.image, rtol=2e-6, atol=1e-7)
 
 
+@pytest.mark.parametrize("precision,world", [("f32", 2), ("f32", 8), ("f64", 4)])
+def test_subpixel_grid_slices_add_up(scene_path, precision, world):
+    """The preferred multi-GPU partition (plan_partition): slices of the ss*ss grid, full sample loops."""
+    sc = rtm.load_scene(scene_path("cornellBox"), "abc").with_dims(80, 42, 6, 4)
+    with rtm.Renderer(sc, precision=precision) as r:
+        full = r.render()
+    parts, rays, samples = np.zeros_like(full.image, dtype=np.float64), 0, 0
+    for g in range(world):
+        plan = rtm.plan_partition(sc.samples, sc.superSamples, g, world)
+        assert plan["sample_end"] - plan["sample_begin"] == sc.samples
+        with rtm.Renderer(sc, precision=precision, **plan) as r:
+            res = r.render()
+        parts += res.image
+        rays += res.stats.rays
+        samples += res.stats.samples
+    assert samples == full.stats.samples and rays == full.stats.rays   # same paths, bit for bit
+    assert np.allclose(parts, full.image, rtol=2e-6, atol=1e-7)
+
+
+def test_subpixel_slice_rejections(scene_path):
+    sc = rtm.load_scene(scene_path("cornellBox"), "abc").with_dims(16, 8, 1, 2)
+    with pytest.raises(rtm.RtmError):
+        rtm.Renderer(sc, sub_begin=2, sub_end=5)
+    with pytest.raises(rtm.RtmError):
+        rtm.Renderer(sc, compat="head", sub_begin=0, sub_end=2)
+    with rtm.Renderer(sc, sub_begin=0, sub_end=2) as r:
+        with pytest.raises(rtm.RtmError):
+            r.render(want_hits=True)
+
+
 def test_u8_conversion(scene_path):
     sc = rtm.load_scene(scene_path("settingData"), "abc").with_dims(120, 63, 16, 1)
     with rtm.Renderer(sc) as r:

@@ -18,7 +18,7 @@ ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 sys.path.insert(0, ROOT)
 sys.path.insert(0, os.path.join(ROOT, "tests"))
 
-from raytracingmin_b200.partition import sample_slice, reduce_partials  # noqa: E402
+from raytracingmin_b200.partition import sample_slice, plan_partition, reduce_partials  # noqa: E402
 
 
 def test_sample_slice_properties():
@@ -36,6 +36,22 @@ def test_sample_slice_properties():
     assert sample_slice(64, 3, 8) == (24, 32)
     with pytest.raises(ValueError):
         sample_slice(8, 8, 8)
+
+
+def test_plan_partition_covers_the_budget_once():
+    for S, ss in ((64, 4), (25, 4), (100, 1), (7, 3), (8, 2)):
+        for G in (1, 2, 3, 4, 8):
+            if G > 1 and (ss * ss) % G != 0 and S < G:
+                continue
+            cover = np.zeros((ss * ss, S), int)
+            for g in range(G):
+                pl = plan_partition(S, ss, g, G)
+                cover[pl["sub_begin"]:pl["sub_end"], pl["sample_begin"]:pl["sample_end"]] += 1
+            assert (cover == 1).all(), (S, ss, G)
+    # C4: 16 sub-pixels over 8 GPUs -> grid slices, full sample loops
+    assert plan_partition(64, 4, 3, 8) == dict(sub_begin=6, sub_end=8, sample_begin=0, sample_end=64)
+    # ss = 1 cannot slice the grid -> samples
+    assert plan_partition(256, 1, 1, 2) == dict(sub_begin=0, sub_end=1, sample_begin=128, sample_end=256)
 
 
 def _free_port():
