@@ -38,6 +38,8 @@ WORKLOADS = {
                name="simpleSetting2 1920x1080 x 256 spp"),
     "c1": dict(scene="simple1", width=960, height=504, samples=100, superSamples=1,
                name="simpleSetting1 960x504 x 100 spp (file defaults)"),
+    "c5": dict(scene="synth10k", file="synth10k.json", width=1920, height=1080, samples=256, superSamples=1,
+               name="synthetic 10k spheres 1920x1080 x 256 spp (closest hit through the hierarchy)"),
     "tiny": dict(scene="cornellBox", width=192, height=108, samples=8, superSamples=2,
                  name="cornellBox 192x108 x 32 spp (plumbing check only)"),
 }
@@ -95,7 +97,7 @@ class ClockSampler:
 def load_workload(name: str):
     import raytracingmin_b200 as rtm
     w = WORKLOADS[name]
-    sc = rtm.load_scene(os.path.join(ROOT, "scenes", w["scene"] + ".head.json"), "abc")
+    sc = rtm.load_scene(os.path.join(ROOT, "scenes", w.get("file", w["scene"] + ".head.json")), "abc")
     return sc.with_dims(w["width"], w["height"], w["samples"], w["superSamples"]), w
 
 
@@ -275,7 +277,11 @@ def run_gpu_arm(args):
         bounce_rays = (rays - samples)                      # this rank's continued bounces
         # tests of the bounce rays only (17 each), 21/ray finalisation + 91/bounce for each traced
         # ray, 18/sample accumulate.  The primary pass's 37/sub-pixel + N tests + 21 are in its own kernel.
-        f_kernel = 17.0 * (st.sphere_tests - n_sub * sc.n) + 21.0 * bounce_rays + 91.0 * bounce_rays + 18.0 * samples
+        # Hierarchy workloads (n > 64): tests ACTUALLY executed (kernel counters), never N*rays; the counter
+        # then includes the primary pass's own tests (< 1 % of the total at >= 64 spp), left in.
+        brute = sc.n <= 64
+        f_kernel = (17.0 * (st.sphere_tests - (n_sub * sc.n if brute else 0)) + 21.0 * bounce_rays + 91.0 * bounce_rays
+                    + 18.0 * samples)
         f_total = algorithmic_flops(sc.n, tests_all, rays_all, samples_all, sc.n_sub)
         achieved = f_kernel / (kms[1] * 1e-3) / 1e12
         fb_gbs = n_pix * 16 / (kms[2] * 1e-3) / 1e9 if kms[2] > 0 else None
@@ -291,6 +297,9 @@ def run_gpu_arm(args):
             "data": "synthetic",
             "config": {"workload": wl["name"], "scene": wl["scene"], "width": sc.width, "height": sc.height,
                        "samples": sc.samples, "superSamples": sc.superSamples, "spp": sc.spp, "n_spheres": sc.n,
+                       "closest_hit": "brute force (packed pairs)" if sc.n <= 64 else
+                                      f"hierarchy: {st.sphere_tests / max(1, st.rays_traced):.1f} sphere tests + "
+                                      f"{st.bvh_nodes / max(1, st.rays_traced):.1f} nodes per traced ray",
                        "partition": (("sub-pixel grid" if plan["sub_end"] - plan["sub_begin"] < sc.superSamples ** 2 else "samples loop")
                                      + f" sliced over {world} rank(s)" + (", one NCCL sum-reduce to rank 0" if world > 1 else "")),
                        "l2": f"inputs larger than L2: the {n_sub * 16 / 1e9:.2f} GB sub-pixel record buffer is rewritten and re-read every step"

@@ -30,7 +30,7 @@
 extern "C" {
 #endif
 
-#define RTM_ABI_VERSION 1
+#define RTM_ABI_VERSION 2
 
 enum {
     RTM_OK = 0,
@@ -120,6 +120,7 @@ typedef struct rtm_stats {
     double e2e_ms;           /* host wall time of the renderer_render call */
     int32_t kernel_launches; /* kernels launched by the call */
     int32_t n_gpus;
+    uint64_t bvh_nodes;      /* hierarchy nodes visited (RTM_ACCEL_BVH), 0 for brute force */
 } rtm_stats;
 
 typedef struct rtm_renderer rtm_renderer;
@@ -181,6 +182,13 @@ int rtm_debug_philox(int32_t device, uint32_t n, uint32_t c1, uint32_t c2, uint3
  * org/dir double[n][3]; hit_out int32[n]; t_out double[n]. */
 int rtm_debug_closest_hit(rtm_renderer* r, int32_t mode, uint32_t n, const double* org, const double* dir,
                           const int32_t* origin_id, int32_t* hit_out, double* t_out);
+
+/* The sphere hierarchy renderer_create would build for `scene` (host only, no GPU needed).
+ * info[13] = {inner nodes, leaf slots, root code, depth, n_big, big_id[8]}.  Call once with the
+ * three arrays NULL to size them: nodes_out float[16*nodes] (4 float4 per node: child boxes,
+ * child codes, rmin), leaf_geo_out float[4*slots], leaf_id_out int32[slots]. */
+int rtm_debug_bvh(const rtm_scene_desc* scene, int32_t* info, float* nodes_out, float* leaf_geo_out,
+                  int32_t* leaf_id_out);
 
 /* FP32 FMA-chain microbenchmark: measured FP32 peak of the device in TFLOP/s. */
 int rtm_debug_fp32_peak(int32_t device, double* tflops_out, double* sm_clock_mhz_out);

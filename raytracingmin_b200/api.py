@@ -55,6 +55,7 @@ class _Stats(C.Structure):
     _fields_ = [
         ("samples", C.c_uint64), ("rays", C.c_uint64), ("rays_traced", C.c_uint64), ("sphere_tests", C.c_uint64),
         ("device_ms", C.c_double), ("e2e_ms", C.c_double), ("kernel_launches", C.c_int32), ("n_gpus", C.c_int32),
+        ("bvh_nodes", C.c_uint64),
     ]
 
 
@@ -68,6 +69,7 @@ class Stats:
     e2e_ms: float
     kernel_launches: int
     n_gpus: int
+    bvh_nodes: int = 0
 
 
 @dataclass
@@ -81,7 +83,7 @@ EXPORTS = [
     "renderer_abi_version", "renderer_default_options", "renderer_create", "renderer_render",
     "renderer_render_async", "renderer_read_stats", "renderer_read_kernel_ms", "renderer_device_accum", "renderer_device_hits",
     "renderer_set_accum_buffer", "renderer_read_image_f64", "renderer_read_u8", "renderer_destroy",
-    "renderer_last_error", "rtm_debug_philox", "rtm_debug_closest_hit", "rtm_debug_fp32_peak",
+    "renderer_last_error", "rtm_debug_philox", "rtm_debug_closest_hit", "rtm_debug_fp32_peak", "rtm_debug_bvh",
 ]
 
 
@@ -124,6 +126,7 @@ def load_library():
     lib.rtm_debug_philox.argtypes = [C.c_int32] + [C.c_uint32] * 6 + [vp]
     lib.rtm_debug_closest_hit.argtypes = [vp, C.c_int32, C.c_uint32, vp, vp, vp, vp, vp]
     lib.rtm_debug_fp32_peak.argtypes = [C.c_int32, P(C.c_double), P(C.c_double)]
+    lib.rtm_debug_bvh.argtypes = [P(_SceneDesc), vp, vp, vp, vp]
     _lib = lib
     return lib
 
@@ -134,7 +137,7 @@ def _check(lib, rc: int):
 
 
 def _stats(s: _Stats) -> Stats:
-    return Stats(s.samples, s.rays, s.rays_traced, s.sphere_tests, s.device_ms, s.e2e_ms, s.kernel_launches, s.n_gpus)
+    return Stats(s.samples, s.rays, s.rays_traced, s.sphere_tests, s.device_ms, s.e2e_ms, s.kernel_launches, s.n_gpus, s.bvh_nodes)
 
 
 class Renderer:
@@ -168,6 +171,21 @@ class Renderer:
         o.sub_begin, o.sub_end = sub_begin, sub_end
         self.compat = compat
         _check(self._lib, self._lib.renderer_create(C.byref(d), C.byref(o), C.byref(self._h)))
+
+    @staticmethod
+    def _desc(sc: Scene) -> "_SceneDesc":
+        d = _SceneDesc()
+        d.width, d.height, d.samples, d.superSamples = sc.width, sc.height, sc.samples, sc.superSamples
+        d.cam_origin[:] = list(sc.cam_origin)
+        d.cam_target[:] = list(sc.cam_target)
+        d.cam_up[:] = list(sc.cam_up)
+        d.fov = sc.fov
+        d.n_spheres = sc.n
+        d.position = sc.position.ctypes.data_as(C.POINTER(C.c_double))
+        d.radius = sc.radius.ctypes.data_as(C.POINTER(C.c_float))
+        d.color = sc.color.ctypes.data_as(C.POINTER(C.c_double))
+        d.emission = sc.emission.ctypes.data_as(C.POINTER(C.c_double))
+        return d
 
     # -- the drop-in call: host buffers in, host buffers out
     def render(self, want_image: bool = True, want_hits: bool = False) -> RenderResult:
@@ -247,6 +265,22 @@ def philox_device(n: int, c1: int, c2: int, c3: int, k0: int, k1: int, device: i
     out = np.empty((n, 4), np.uint32)
     _check(lib, lib.rtm_debug_philox(device, n, c1, c2, c3, k0, k1, out.ctypes.data))
     return out
+
+
+def build_bvh(scene: Scene) -> dict:
+    """The sphere hierarchy renderer_create builds for `scene` (host code only; no GPU needed)."""
+    lib = load_library()
+    sc = scene.normalized()
+    d = Renderer._desc(sc)
+    info = np.zeros(13, np.int32)
+    rc = lib.rtm_debug_bvh(C.byref(d), info.ctypes.data, None, None, None)
+    nodes = np.zeros((int(info[0]), 4, 4), np.float32)
+    leaf_geo = np.zeros((int(info[1]), 4), np.float32)
+    leaf_id = np.zeros(int(info[1]), np.int32)
+    rc = lib.rtm_debug_bvh(C.byref(d), info.ctypes.data, nodes.ctypes.data, leaf_geo.ctypes.data, leaf_id.ctypes.data)
+    _check(lib, rc)
+    return dict(nodes=nodes, leaf_geo=leaf_geo, leaf_id=leaf_id, root=int(info[2]), depth=int(info[3]),
+                big_id=[int(v) for v in info[5:5 + int(info[4])]])
 
 
 def fp32_peak_tflops(device: int = 0):

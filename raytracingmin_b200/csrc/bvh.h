@@ -1,0 +1,41 @@
+// bvh.h — bounding-volume hierarchy over the scene's spheres (host build, device
+// traversal).  Used when the brute-force closest-hit loop of the reference
+// (src/Renderer.cpp:62-72, O(N) per ray) stops being affordable: SURVEY.md §8(d) C5,
+// 10 000 primitives.  The hierarchy only decides WHICH spheres a ray is tested
+// against; the per-candidate arithmetic and the accept/tie rule stay those of
+// src/SettingData.cpp:197-223 / src/Renderer.cpp:67, so the FP64 hit map remains
+// bit-exact against brute force (see closest_hit_bvh in kernels_exact.cu).
+#pragma once
+#include <cuda_runtime.h>
+#include <stdint.h>
+
+#include <vector>
+
+#define RTM_BVH_NONE 0x7FFFFFFF   // "no node": empty hierarchy / bottom of the traversal stack
+#define RTM_BVH_MAX_BIG 8         // spheres too large for the hierarchy, tested for every ray
+#define RTM_BVH_LEAF_MAX 4
+#define RTM_BVH_STACK 64
+
+// child code: >= 0  inner node index
+//             <  0  leaf: ~code = (first_slot << 3) | (count - 1)
+static inline int32_t rtm_bvh_leaf_code(uint32_t first, uint32_t count) { return ~(int32_t)((first << 3) | (count - 1u)); }
+
+// Inner node = 4 x float4 (64 B), boxes of BOTH children, coordinates relative to the
+// scene reference point (the camera origin), rounded OUTWARD to float after padding:
+//   q[0] = c0.lo.x c0.hi.x c0.lo.y c0.hi.y
+//   q[1] = c1.lo.x c1.hi.x c1.lo.y c1.hi.y
+//   q[2] = c0.lo.z c0.hi.z c1.lo.z c1.hi.z
+//   q[3] = child0 child1 (int bits)  rmin0 rmin1 (smallest radius below each child)
+struct RtmBvhHost {
+    std::vector<float4> nodes;       // 4 per inner node
+    std::vector<float4> leaf_geo;    // per leaf slot: centre (relative, float), r^2 (float)
+    std::vector<int32_t> leaf_id;    // per leaf slot: original sphere index
+    int32_t root = RTM_BVH_NONE;     // child code of the root
+    int32_t n_big = 0;
+    int32_t big_id[RTM_BVH_MAX_BIG] = {0};
+    int32_t depth = 0;
+};
+
+// position[n][3] / radius[n] as in rtm_scene_desc; ref = scene reference point.
+// Throws nothing; returns false when the tree would exceed RTM_BVH_STACK levels.
+bool rtm_bvh_build(int32_t n, const double* position, const float* radius, const double ref[3], RtmBvhHost& out);

@@ -1,0 +1,221 @@
+// bvh_build.cpp — host-side binned-SAH build of the sphere hierarchy (see bvh.h).
+// Runs once per renderer_create; 10 000 spheres take a few milliseconds.
+#include "bvh.h"
+
+#include <algorithm>
+#include <cfloat>
+#include <cmath>
+#include <cstring>
+
+namespace {
+
+struct Prim {
+    double lo[3], hi[3], c[3];
+    double r;
+    int32_t id;
+};
+
+struct Box {
+    double lo[3], hi[3];
+    void reset() {
+        for (int k = 0; k < 3; ++k) { lo[k] = DBL_MAX; hi[k] = -DBL_MAX; }
+    }
+    void grow(const double* l, const double* h) {
+        for (int k = 0; k < 3; ++k) { lo[k] = std::min(lo[k], l[k]); hi[k] = std::max(hi[k], h[k]); }
+    }
+    double area() const {
+        const double dx = hi[0] - lo[0], dy = hi[1] - lo[1], dz = hi[2] - lo[2];
+        return (dx < 0) ? 0.0 : 2.0 * (dx * dy + dy * dz + dz * dx);
+    }
+};
+
+float round_down(double v) {
+    float f = (float)v;
+    if ((double)f > v) f = std::nextafterf(f, -INFINITY);
+    return f;
+}
+float round_up(double v) {
+    float f = (float)v;
+    if ((double)f < v) f = std::nextafterf(f, INFINITY);
+    return f;
+}
+
+struct Builder {
+    std::vector<Prim> prims;
+    RtmBvhHost* out;
+    int max_depth = 0;
+
+    struct Sub {
+        int32_t code;
+        Box box;
+        double rmin;
+    };
+
+    Sub make_leaf(int b, int e) {
+        Sub s;
+        s.box.reset();
+        s.rmin = DBL_MAX;
+        const uint32_t first = (uint32_t)out->leaf_id.size();
+        for (int i = b; i < e; ++i) {
+            const Prim& p = prims[i];
+            s.box.grow(p.lo, p.hi);
+            s.rmin = std::min(s.rmin, p.r);
+            out->leaf_geo.push_back(make_float4((float)p.c[0], (float)p.c[1], (float)p.c[2], (float)(p.r * p.r)));
+            out->leaf_id.push_back(p.id);
+        }
+        s.code = rtm_bvh_leaf_code(first, (uint32_t)(e - b));
+        return s;
+    }
+
+    Sub build(int b, int e, int depth) {
+        max_depth = std::max(max_depth, depth);
+        const int n = e - b;
+        if (n <= 2) return make_leaf(b, e);   // a 3..4 range is still split below when SAH says it pays
+        Box bounds, cb;
+        bounds.reset();
+        cb.reset();
+        for (int i = b; i < e; ++i) {
+            bounds.grow(prims[i].lo, prims[i].hi);
+            cb.grow(prims[i].c, prims[i].c);
+        }
+        int axis = -1, split_at = -1;
+        if (depth < 32) {
+            // binned SAH over the centroid bounds, 16 bins per axis
+            const int NB = 16;
+            double best_cost = (n <= RTM_BVH_LEAF_MAX) ? (double)n * bounds.area() : DBL_MAX;
+            int best_axis = -1, best_bin = -1;
+            for (int ax = 0; ax < 3; ++ax) {
+                const double ext = cb.hi[ax] - cb.lo[ax];
+                if (!(ext > 0)) continue;
+                Box bb[NB];
+                int cnt[NB] = {0};
+                for (auto& x : bb) x.reset();
+                const double scale = NB / ext;
+                for (int i = b; i < e; ++i) {
+                    int k = (int)((prims[i].c[ax] - cb.lo[ax]) * scale);
+                    k = std::min(std::max(k, 0), NB - 1);
+                    bb[k].grow(prims[i].lo, prims[i].hi);
+                    ++cnt[k];
+                }
+                double right_area[NB];
+                int right_cnt[NB];
+                Box acc;
+                acc.reset();
+                int c = 0;
+                for (int k = NB - 1; k >= 1; --k) {
+                    if (cnt[k]) acc.grow(bb[k].lo, bb[k].hi);
+                    c += cnt[k];
+                    right_area[k] = acc.area();
+                    right_cnt[k] = c;
+                }
+                acc.reset();
+                c = 0;
+                for (int k = 0; k < NB - 1; ++k) {
+                    if (cnt[k]) acc.grow(bb[k].lo, bb[k].hi);
+                    c += cnt[k];
+                    if (c == 0 || right_cnt[k + 1] == 0) continue;
+                    const double cost = 1.0 * bounds.area() + acc.area() * c + right_area[k + 1] * right_cnt[k + 1];
+                    if (cost < best_cost) { best_cost = cost; best_axis = ax; best_bin = k; }
+                }
+            }
+            if (best_axis >= 0) {
+                const double ext = cb.hi[best_axis] - cb.lo[best_axis];
+                const double scale = NB / ext;
+                const double lo = cb.lo[best_axis];
+                auto mid = std::partition(prims.begin() + b, prims.begin() + e, [&](const Prim& p) {
+                    int k = (int)((p.c[best_axis] - lo) * scale);
+                    k = std::min(std::max(k, 0), NB - 1);
+                    return k <= best_bin;
+                });
+                split_at = (int)(mid - prims.begin());
+                axis = best_axis;
+            }
+        }
+        if (axis < 0 || split_at <= b || split_at >= e) {
+            if (n <= RTM_BVH_LEAF_MAX) return make_leaf(b, e);
+            // median split by count along the widest centroid axis (also the depth >= 32 rule:
+            // halving bounds the remaining depth by log2(n))
+            axis = 0;
+            for (int k = 1; k < 3; ++k)
+                if (cb.hi[k] - cb.lo[k] > cb.hi[axis] - cb.lo[axis]) axis = k;
+            split_at = b + n / 2;
+            std::nth_element(prims.begin() + b, prims.begin() + split_at, prims.begin() + e,
+                             [axis](const Prim& x, const Prim& y) { return x.c[axis] < y.c[axis] || (x.c[axis] == y.c[axis] && x.id < y.id); });
+        }
+        const size_t me = out->nodes.size();
+        out->nodes.resize(me + 4);
+        const Sub l = build(b, split_at, depth + 1);
+        const Sub r = build(split_at, e, depth + 1);
+        auto pad = [](const Box& bx, const double rmin, float* lo, float* hi) {
+            (void)rmin;
+            for (int k = 0; k < 3; ++k) {
+                const double m = std::max(std::fabs(bx.lo[k]), std::fabs(bx.hi[k]));
+                const double p = 1e-5 + 2e-6 * m;
+                lo[k] = round_down(bx.lo[k] - p);
+                hi[k] = round_up(bx.hi[k] + p);
+            }
+        };
+        float l0[3], h0[3], l1[3], h1[3];
+        pad(l.box, l.rmin, l0, h0);
+        pad(r.box, r.rmin, l1, h1);
+        float4* q = out->nodes.data() + me;
+        q[0] = make_float4(l0[0], h0[0], l0[1], h0[1]);
+        q[1] = make_float4(l1[0], h1[0], l1[1], h1[1]);
+        q[2] = make_float4(l0[2], h0[2], l1[2], h1[2]);
+        float4 c;
+        memcpy(&c.x, &l.code, 4);
+        memcpy(&c.y, &r.code, 4);
+        c.z = round_down(l.rmin);
+        c.w = round_down(r.rmin);
+        q[3] = c;
+        Sub s;
+        s.code = (int32_t)(me / 4);
+        s.box = l.box;
+        s.box.grow(r.box.lo, r.box.hi);
+        s.rmin = std::min(l.rmin, r.rmin);
+        return s;
+    }
+};
+
+}  // namespace
+
+bool rtm_bvh_build(int32_t n, const double* position, const float* radius, const double ref[3], RtmBvhHost& out) {
+    out = RtmBvhHost();
+    if (n <= 0) return true;
+    // Spheres far larger than the typical one (the r = 1e4 "walls" of the Cornell scenes) would
+    // overlap every box: up to RTM_BVH_MAX_BIG of them are kept out and tested for every ray.
+    std::vector<float> rs(radius, radius + n);
+    std::nth_element(rs.begin(), rs.begin() + n / 2, rs.end());
+    const double median = rs[n / 2];
+    std::vector<int32_t> cand;
+    for (int i = 0; i < n; ++i)
+        if ((double)radius[i] > 8.0 * median) cand.push_back(i);
+    std::sort(cand.begin(), cand.end(), [&](int a, int b) { return radius[a] > radius[b] || (radius[a] == radius[b] && a < b); });
+    if ((int)cand.size() > RTM_BVH_MAX_BIG) cand.resize(RTM_BVH_MAX_BIG);
+    std::sort(cand.begin(), cand.end());  // ascending original index: the tie rule of Renderer.cpp:67
+    std::vector<char> is_big(n, 0);
+    for (int32_t i : cand) {
+        is_big[i] = 1;
+        out.big_id[out.n_big++] = i;
+    }
+    Builder bl;
+    bl.out = &out;
+    bl.prims.reserve(n - out.n_big);
+    for (int i = 0; i < n; ++i) {
+        if (is_big[i]) continue;
+        Prim p;
+        p.r = (double)radius[i];
+        p.id = i;
+        for (int k = 0; k < 3; ++k) {
+            p.c[k] = position[3 * i + k] - ref[k];
+            p.lo[k] = p.c[k] - p.r;
+            p.hi[k] = p.c[k] + p.r;
+        }
+        bl.prims.push_back(p);
+    }
+    if (bl.prims.empty()) return true;
+    const Builder::Sub root = bl.build(0, (int)bl.prims.size(), 0);
+    out.root = root.code;
+    out.depth = bl.max_depth;
+    return bl.max_depth + 2 < RTM_BVH_STACK;
+}

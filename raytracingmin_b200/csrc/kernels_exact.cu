@@ -50,7 +50,7 @@ __device__ __forceinline__ bool sphere_test(d3 c, double r2, d3 o, d3 d, double&
 }
 
 // Renderer.cpp:58-73: strict `<` keeps the lowest index on exact ties; `t > 0`.
-__device__ __forceinline__ int closest_hit(const RtmSceneF64& sc, d3 o, d3 d, double& best) {
+__device__ __forceinline__ int closest_hit_brute(const RtmSceneF64& sc, d3 o, d3 d, double& best) {
     int id = -1;
     best = DBL_MAX;
     for (int i = 0; i < sc.n; ++i) {
@@ -62,6 +62,98 @@ __device__ __forceinline__ int closest_hit(const RtmSceneF64& sc, d3 o, d3 d, do
         }
     }
     return id;
+}
+
+// ---- the same search behind the hierarchy ------------------------------------------
+// Candidates are visited in tree order, so the sequential rule "t < best, lowest index
+// on ties" becomes the order-independent "(t, i) lexicographically smallest": identical
+// winner.  What must hold for bit-exactness is that no node holding the winner is culled.
+// A candidate reported by sphere_test at parameter t sits at x = o + t d with
+//     |x - c|^2 = r^2 + t^2 (|d|^2 - 1)
+// (t solves the UNIT-direction quadratic, but Normalize() divides by a float-rounded
+// length, Ray.h:67-72, so |d|^2 = 1 +- 1.8e-7): x can lie OUTSIDE the sphere by
+// t^2 eps / 2r.  With t <= 3 D (D = distance from o to the farthest corner of the node's
+// box, which holds c) the box is inflated per ray by 4.5 D^2 eps / rmin before the slab
+// test; eps is this ray's own | |d|^2 - 1 |.  Rays that are not unit to 4e-7 (only the
+// debug hook can supply them) take the brute-force loop.
+struct BvhWork {
+    unsigned tests, nodes;
+};
+__device__ __forceinline__ void consider(const RtmSceneF64& sc, int i, d3 o, d3 d, double& best, int& id) {
+    double t;
+    if (sphere_test(mk(__ldg(sc.cx + i), __ldg(sc.cy + i), __ldg(sc.cz + i)), __ldg(sc.r2 + i), o, d, t) && t > 0.0 &&
+        (t < best || (t == best && i < id))) {
+        best = t;
+        id = i;
+    }
+}
+
+__device__ __forceinline__ bool box_test_f64(double lx, double hx, double ly, double hy, double lz, double hz, double rmin,
+                                             d3 o, d3 inv, double ke, double best, double& tnear) {
+    const double fx = fmax(fabs(lx - o.x), fabs(hx - o.x)), fy = fmax(fabs(ly - o.y), fabs(hy - o.y)),
+                 fz = fmax(fabs(lz - o.z), fabs(hz - o.z));
+    const double infl = ke * (fx * fx + fy * fy + fz * fz) / rmin;
+    // fmin/fmax return the non-NaN operand: a 0*inf slab (ray inside a face plane of the
+    // padded box, which no sphere touches) degrades to the other bound.
+    double t1 = (lx - infl - o.x) * inv.x, t2 = (hx + infl - o.x) * inv.x;
+    double tmin = fmax(0.0, fmin(t1, t2)), tmax = fmin(best, fmax(t1, t2));
+    t1 = (ly - infl - o.y) * inv.y; t2 = (hy + infl - o.y) * inv.y;
+    tmin = fmax(tmin, fmin(t1, t2)); tmax = fmin(tmax, fmax(t1, t2));
+    t1 = (lz - infl - o.z) * inv.z; t2 = (hz + infl - o.z) * inv.z;
+    tmin = fmax(tmin, fmin(t1, t2)); tmax = fmin(tmax, fmax(t1, t2));
+    tnear = tmin;
+    return tmin <= tmax;
+}
+
+__device__ int closest_hit_bvh(const RtmSceneF64& sc, d3 o, d3 d, double& best, BvhWork* work = nullptr) {
+    const double dd = d.x * d.x + d.y * d.y + d.z * d.z;
+    if (!(fabs(dd - 1.0) <= 4e-7)) {
+        if (work) work->tests += sc.n;
+        return closest_hit_brute(sc, o, d, best);
+    }
+    if (work) work->tests += sc.bvh.n_big;
+    int id = -1;
+    best = DBL_MAX;
+    for (int j = 0; j < sc.bvh.n_big; ++j) consider(sc, sc.bvh.big_id[j], o, d, best, id);
+    int node = sc.bvh.root;
+    if (node == 0x7FFFFFFF) return id;
+    const double ke = 4.5 * (fabs(dd - 1.0) + 1e-14);
+    const d3 orel = mk(o.x - sc.ref[0], o.y - sc.ref[1], o.z - sc.ref[2]);
+    const d3 inv = mk(1.0 / d.x, 1.0 / d.y, 1.0 / d.z);
+    int stack[64];
+    int sp = 0;
+    stack[sp++] = 0x7FFFFFFF;
+    while (node != 0x7FFFFFFF) {
+        if (node >= 0) {
+            const float4 q0 = __ldg(sc.bvh.nodes + 4 * node), q1 = __ldg(sc.bvh.nodes + 4 * node + 1),
+                         q2 = __ldg(sc.bvh.nodes + 4 * node + 2), q3 = __ldg(sc.bvh.nodes + 4 * node + 3);
+            double n0, n1;
+            const bool h0 = box_test_f64(q0.x, q0.y, q0.z, q0.w, q2.x, q2.y, q3.z, orel, inv, ke, best, n0);
+            const bool h1 = box_test_f64(q1.x, q1.y, q1.z, q1.w, q2.z, q2.w, q3.w, orel, inv, ke, best, n1);
+            const int c0 = __float_as_int(q3.x), c1 = __float_as_int(q3.y);
+            if (work) ++work->nodes;
+            if (h0 && h1) {
+                const bool swap = n1 < n0;
+                stack[sp++] = swap ? c0 : c1;
+                node = swap ? c1 : c0;
+            } else if (h0 || h1) {
+                node = h0 ? c0 : c1;
+            } else {
+                node = stack[--sp];
+            }
+        } else {
+            const unsigned code = ~(unsigned)node;
+            const unsigned first = code >> 3, cnt = (code & 7u) + 1u;
+            for (unsigned k = 0; k < cnt; ++k) consider(sc, __ldg(sc.bvh.leaf_id + first + k), o, d, best, id);
+            if (work) work->tests += cnt;
+            node = stack[--sp];
+        }
+    }
+    return id;
+}
+
+__device__ __forceinline__ int closest_hit(const RtmSceneF64& sc, d3 o, d3 d, double& best, BvhWork* work = nullptr) {
+    return sc.use_bvh ? closest_hit_bvh(sc, o, d, best, work) : closest_hit_brute(sc, o, d, best);
 }
 
 __device__ __forceinline__ d3 sphere_center(const RtmSceneF64& sc, int i) {
@@ -100,17 +192,15 @@ __device__ __forceinline__ double clamp01(double v) {
 }
 
 // ---- K1: primary pass, one thread per sub-pixel ----------------------------
-__global__ void __launch_bounds__(256) primary_f64_kernel(RtmSceneF64 sc, RtmPassParams p, int32_t* __restrict__ hits,
-                                                          float4* __restrict__ records) {
-    const uint64_t q = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
-    if (q >= p.n_sub) return;
+__device__ __forceinline__ void primary_one(const RtmSceneF64& sc, const RtmPassParams& p, uint64_t q, int32_t* __restrict__ hits,
+                                            float4* __restrict__ records, BvhWork* work) {
     int x, y, sx, sy;
     uint64_t qg;
     decode_sub(p, q, x, y, sx, sy, qg);
     const d3 o = mk(p.frame.o[0], p.frame.o[1], p.frame.o[2]);
     const d3 d = camera_dir(p.frame, x, y, sx, sy);
     double t;
-    const int id = closest_hit(sc, o, d, t);
+    const int id = closest_hit(sc, o, d, t, work);
     if (hits) hits[qg] = id;
     if (records) {
         float4 rec;
@@ -124,6 +214,24 @@ __global__ void __launch_bounds__(256) primary_f64_kernel(RtmSceneF64 sc, RtmPas
                               __uint_as_float((uint32_t)id | flip));
         }
         records[q] = rec;
+    }
+}
+
+__global__ void __launch_bounds__(256) primary_f64_kernel(RtmSceneF64 sc, RtmPassParams p, int32_t* __restrict__ hits,
+                                                          float4* __restrict__ records, RtmCounters* __restrict__ counters) {
+    const uint64_t q = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    BvhWork work{0u, 0u};
+    if (q < p.n_sub) primary_one(sc, p, q, hits, records, sc.use_bvh ? &work : nullptr);
+    if (sc.use_bvh && counters) {   // hierarchy: tests / nodes actually executed, one atomic pair per warp
+        unsigned long long t = work.tests, n = work.nodes;
+        for (int off = 16; off > 0; off >>= 1) {
+            t += __shfl_down_sync(0xffffffffu, t, off);
+            n += __shfl_down_sync(0xffffffffu, n, off);
+        }
+        if ((threadIdx.x & 31) == 0) {
+            atomicAdd(&counters->tests, t);
+            atomicAdd(&counters->nodes, n);
+        }
     }
 }
 
@@ -161,6 +269,7 @@ __global__ void __launch_bounds__(128) radiance_f64_kernel(RtmSceneF64 sc, RtmPa
                                                            RtmCounters* __restrict__ counters) {
     const uint64_t q = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
     unsigned long long rays = 0;
+    BvhWork work{0u, 0u};
     if (q < p.n_sub) {
         int x, y, sx, sy;
         uint64_t qg;
@@ -174,7 +283,7 @@ __global__ void __launch_bounds__(128) radiance_f64_kernel(RtmSceneF64 sc, RtmPa
             for (int depth = 0; depth < p.max_depth; ++depth) {
                 ++rays;
                 double t;
-                const int id = closest_hit(sc, o, d, t);
+                const int id = closest_hit(sc, o, d, t, &work);
                 if (id < 0) break;
                 const d3 e = mk(__ldg(sc.emission + 3 * id), __ldg(sc.emission + 3 * id + 1), __ldg(sc.emission + 3 * id + 2));
                 L = add(L, mul(T, e));
@@ -204,11 +313,17 @@ __global__ void __launch_bounds__(128) radiance_f64_kernel(RtmSceneF64 sc, RtmPa
         records[q] = make_float4((float)acc.x, (float)acc.y, (float)acc.z, 0.f);
     }
     // one atomic per warp
-    for (int off = 16; off > 0; off >>= 1) rays += __shfl_down_sync(0xffffffffu, rays, off);
+    unsigned long long tests = work.tests, nodes = work.nodes;
+    for (int off = 16; off > 0; off >>= 1) {
+        rays += __shfl_down_sync(0xffffffffu, rays, off);
+        tests += __shfl_down_sync(0xffffffffu, tests, off);
+        nodes += __shfl_down_sync(0xffffffffu, nodes, off);
+    }
     if ((threadIdx.x & 31) == 0 && rays) {
         atomicAdd(&counters->rays_ref, rays);
         atomicAdd(&counters->rays_traced, rays);
-        atomicAdd(&counters->tests, rays * (unsigned long long)sc.n);
+        atomicAdd(&counters->tests, sc.use_bvh ? tests : rays * (unsigned long long)sc.n);
+        if (sc.use_bvh) atomicAdd(&counters->nodes, nodes);
     }
 }
 
@@ -225,9 +340,10 @@ __global__ void closest_hit_f64_kernel(RtmSceneF64 sc, uint32_t n, const double*
 
 }  // namespace
 
-void rtm_launch_primary_f64(const RtmSceneF64& sc, const RtmPassParams& p, int32_t* hits, float4* records, cudaStream_t st) {
+void rtm_launch_primary_f64(const RtmSceneF64& sc, const RtmPassParams& p, int32_t* hits, float4* records,
+                            RtmCounters* counters, cudaStream_t st) {
     const uint32_t blocks = (uint32_t)((p.n_sub + 255) / 256);
-    primary_f64_kernel<<<blocks, 256, 0, st>>>(sc, p, hits, records);
+    primary_f64_kernel<<<blocks, 256, 0, st>>>(sc, p, hits, records, counters);
 }
 
 void rtm_launch_head_image(const RtmSceneF64& sc, const RtmPassParams& p, const int32_t* hits, double* image64,

@@ -194,12 +194,113 @@ __device__ __forceinline__ int trace_f32(const SelfMask& sm, int n_rt, int oid, 
     return trace_loop_f32(n_rt, oid, o, d, t);
 }
 
+// ---- closest hit through the hierarchy (bvh.h), FP32 ------------------------------
+// Up to 8 "big" spheres (the r = 1e4 walls) go through the packed pair test above with the
+// cancellation-free K form; everything else sits in a two-child hierarchy walked per lane
+// (while-while, near child first, explicit stack in local memory).  Small spheres use the
+// direct form p = c - o, c' = |p|^2 - r^2: for r <= 1 the squares are small and the direct
+// form is the more accurate one next to the surface the ray leaves.
+__device__ __forceinline__ bool box_test_f32(float lx, float hx, float ly, float hy, float lz, float hz, f3 oi, f3 inv,
+                                             float tmax_in, float& tnear) {
+    // (plane - o) / d as one FMA per plane; NaN (0 * inf) drops out of fminf/fmaxf: that slab is ignored
+    float t1 = fmaf(lx, inv.x, -oi.x), t2 = fmaf(hx, inv.x, -oi.x);
+    float tmin = fmaxf(0.f, fminf(t1, t2)), tmax = fminf(tmax_in, fmaxf(t1, t2));
+    t1 = fmaf(ly, inv.y, -oi.y); t2 = fmaf(hy, inv.y, -oi.y);
+    tmin = fmaxf(tmin, fminf(t1, t2)); tmax = fminf(tmax, fmaxf(t1, t2));
+    t1 = fmaf(lz, inv.z, -oi.z); t2 = fmaf(hz, inv.z, -oi.z);
+    tmin = fmaxf(tmin, fminf(t1, t2)); tmax = fminf(tmax, fmaxf(t1, t2));
+    tnear = tmin;
+    return tmin <= tmax;
+}
+
+struct SharedBig {
+    int id[8];
+};
+
+template <int NP>
+__device__ __forceinline__ int trace_bvh_f32(const SelfMask& sm, const SharedBig& big, const RtmBvhDev& bvh, int oid, int oslot,
+                                             f3 o, f3 d, float& t, unsigned key_mask, unsigned& n_tests, unsigned& n_nodes) {
+    float best = FLT_MAX;   // candidate (root - eps)
+    int id = -1;
+    if (NP > 0) {
+        const unsigned key = trace_pairs_f32<NP>(sm, oslot, o, d, key_mask);
+        if (key < RTM_KEY_INF) {
+            best = __uint_as_float(key & ~7u);
+            id = big.id[key & 7u];
+        }
+        n_tests += 2 * NP;
+    }
+    int node = bvh.root;
+    if (node != 0x7FFFFFFF) {
+        const f3 inv = mk(fast_rcp(d.x), fast_rcp(d.y), fast_rcp(d.z));
+        const f3 oi = mk(o.x * inv.x, o.y * inv.y, o.z * inv.z);
+        int stack[RTM_BVH_STACK_DEV];
+        int sp = 0;
+        stack[sp++] = 0x7FFFFFFF;
+        while (node != 0x7FFFFFFF) {
+            if (node >= 0) {
+                const float4* q = bvh.nodes + 4 * node;
+                const float4 q0 = __ldg(q), q1 = __ldg(q + 1), q2 = __ldg(q + 2), q3 = __ldg(q + 3);
+                float n0, n1;
+                const float tm = best + 2.f * RTM_T_EPS;
+                const bool h0 = box_test_f32(q0.x, q0.y, q0.z, q0.w, q2.x, q2.y, oi, inv, tm, n0);
+                const bool h1 = box_test_f32(q1.x, q1.y, q1.z, q1.w, q2.z, q2.w, oi, inv, tm, n1);
+                const int c0 = __float_as_int(q3.x), c1 = __float_as_int(q3.y);
+                ++n_nodes;
+                if (h0 && h1) {
+                    const bool swap = n1 < n0;
+                    stack[sp++] = swap ? c0 : c1;
+                    node = swap ? c1 : c0;
+                } else if (h0 || h1) {
+                    node = h0 ? c0 : c1;
+                } else {
+                    node = stack[--sp];
+                }
+            } else {
+                const unsigned code = ~(unsigned)node;
+                const unsigned first = code >> 3, cnt = (code & 7u) + 1u;
+                for (unsigned k = 0; k < cnt; ++k) {
+                    const float4 g = __ldg(bvh.leaf_geo + first + k);
+                    const int sid = __ldg(bvh.leaf_id + first + k);
+                    const f3 p = mk(g.x - o.x, g.y - o.y, g.z - o.z);
+                    const float b = dot(p, d);
+                    float cp = dot(p, p) - g.w;
+                    cp = (sid == oid) ? 0.f : cp;                      // leaving this sphere's surface
+                    const float s = fast_sqrt(fmaf(b, b, -cp));        // NaN: the ray misses
+                    const float tq = b + copysignf(s, b);
+                    const float ta = tq - RTM_T_EPS, tb = fmaf(cp, fast_rcp(tq), -RTM_T_EPS);
+                    const float c1 = (ta > 0.f) ? ta : FLT_MAX, c2 = (tb > 0.f) ? tb : FLT_MAX;
+                    const float c = fminf(c1, c2);
+                    const bool ok = (c < best) || (c == best && sid < id);
+                    best = ok ? c : best;
+                    id = ok ? sid : id;
+                }
+                n_tests += cnt;
+                node = stack[--sp];
+            }
+        }
+    }
+    t = best + RTM_T_EPS;
+    return id;
+}
+
 // Per-sphere data addressed with a per-lane index (the hit id): shared memory, three
 // 16-byte records per sphere so that a lane needs three LDS.128 per hit.
 struct SharedScene {
     float4 geo[RTM_MAX_CONST_SPHERES];  // cx, cy, cz, 1/r
     float4 emi[RTM_MAX_CONST_SPHERES];  // emission rgb, roulette threshold (uint bits)
     float4 alb[RTM_MAX_CONST_SPHERES];  // color/kd rgb (colorKD, SettingData.h:11-13), unused
+};
+
+// Hierarchy path: the per-sphere records stay in global memory (L1/L2 resident); shared
+// memory only holds the original indices of the "big" spheres the packed test covers.
+template <bool BVH>
+struct SceneRecs {
+    const SharedScene* sh;
+    RtmMatDev m;
+    __device__ __forceinline__ float4 geo(int i) const { return BVH ? __ldg(m.geo + i) : sh->geo[i]; }
+    __device__ __forceinline__ float4 emi(int i) const { return BVH ? __ldg(m.emi + i) : sh->emi[i]; }
+    __device__ __forceinline__ float4 alb(int i) const { return BVH ? __ldg(m.alb + i) : sh->alb[i]; }
 };
 
 __device__ __forceinline__ void load_shared_scene(SharedScene& s, int n) {
@@ -243,14 +344,27 @@ __device__ __forceinline__ float clamp01f(float v) { return __saturatef(v); }
 // RNG: one Philox2x32-10 call per hit, counter = (sub-pixel, sample<<9 | depth), key
 // from the seed: x -> roulette (32-bit compare against kd*2^32), y -> azimuth,
 // the low bits of x and y -> height.
-template <int N>
-__global__ void __launch_bounds__(RTM_MEGA_THREADS, 5) radiance_mega_kernel(RtmPassParams p, float4* __restrict__ records,
-                                                                            RtmCounters* __restrict__ counters, int n_rt) {
+template <int N, bool BVH>
+__global__ void __launch_bounds__(RTM_MEGA_THREADS, BVH ? 4 : 5) radiance_mega_kernel(RtmPassParams p, float4* __restrict__ records,
+                                                                                      RtmCounters* __restrict__ counters, int n_rt,
+                                                                                      RtmBvhDev bvh, RtmMatDev mat) {
+    // brute force: N spheres (0 = runtime n_rt) with their records in shared memory;
+    // hierarchy: N = slots of the packed big-sphere test (even, 0..8), records in global memory
     __shared__ SharedScene sh;
     __shared__ SelfMask sh_mask;
+    __shared__ SharedBig sh_big;
     const int n = (N > 0) ? N : n_rt;
     init_selfmask(sh_mask);
-    load_shared_scene(sh, n);
+    if (BVH) {
+        if (threadIdx.x < 8) sh_big.id[threadIdx.x] = (threadIdx.x < (unsigned)bvh.n_big) ? bvh.big_id[threadIdx.x] : 0;
+        __syncthreads();
+    } else {
+        load_shared_scene(sh, n);
+    }
+    SceneRecs<BVH> recs;
+    recs.sh = &sh;
+    recs.m = mat;
+    unsigned n_tests = 0, n_nodes = 0;
 
     const unsigned lane = threadIdx.x & 31u;
     const unsigned lt_mask = (1u << lane) - 1u;
@@ -303,7 +417,7 @@ __global__ void __launch_bounds__(RTM_MEGA_THREADS, 5) radiance_mega_kernel(RtmP
                 const unsigned ns = (unsigned)(s_end - s_begin);
                 const bool miss = (wbits == RTM_REC_MISS);
                 Pid = miss ? 0 : (int)(wbits & RTM_REC_IDMASK);
-                const float4 e0 = sh.emi[Pid];
+                const float4 e0 = recs.emi(Pid);
                 if (miss || __float_as_uint(e0.w) == 0u) {
                     // every sample of this sub-pixel is the same: nothing (miss) or the
                     // emission of a surface that never continues (kd == 0, Renderer.cpp:112)
@@ -318,7 +432,7 @@ __global__ void __launch_bounds__(RTM_MEGA_THREADS, 5) radiance_mega_kernel(RtmP
                 } else {
                     have = true;
                     P = mk(rec.x, rec.y, rec.z);
-                    const float4 g = sh.geo[Pid];
+                    const float4 g = recs.geo(Pid);
                     const float ir = (wbits & RTM_REC_FLIP) ? -g.w : g.w;
                     Pw = mk((P.x - g.x) * ir, (P.y - g.y) * ir, (P.z - g.z) * ir);
                     acc = mk(0, 0, 0);
@@ -338,25 +452,27 @@ __global__ void __launch_bounds__(RTM_MEGA_THREADS, 5) radiance_mega_kernel(RtmP
 
         if (have) {
             const uint2 rnd = rtm_philox2x32_10(make_uint2(q, ((unsigned)s << 9) | (unsigned)depth), p.rk);
-            const float4 em = sh.emi[id];
+            const float4 em = recs.emi(id);
             // Russian roulette, Renderer.cpp:78
             bool end = !((rnd.x < __float_as_uint(em.w)) && (depth + 1 < p.max_depth));
             if (!end) {
-                const float4 al = sh.alb[id];
+                const float4 al = recs.alb(id);
                 T.x *= al.x; T.y *= al.y; T.z *= al.z;   // colorKD, SettingData.h:11-13
                 const f3 d = cosine_dir(w, rnd.y, ((rnd.x & 0xFFFu) << 10) | (rnd.y & 0x3FFu));
                 float t;
-                const int id2 = trace_f32<N>(sh_mask, n, id, o, d, t, key_mask);
+                int id2;
+                if (BVH) id2 = trace_bvh_f32<N / 2>(sh_mask, sh_big, bvh, id, __float_as_int(al.w), o, d, t, key_mask, n_tests, n_nodes);
+                else id2 = trace_f32<N>(sh_mask, n, id, o, d, t, key_mask);
                 ++traced;
                 if (id2 >= 0) {
                     o = mk(fmaf(d.x, t, o.x), fmaf(d.y, t, o.y), fmaf(d.z, t, o.z));  // Renderer.cpp:79
-                    const float4 g = sh.geo[id2];
+                    const float4 g = recs.geo(id2);
                     const f3 nn = mk((o.x - g.x) * g.w, (o.y - g.y) * g.w, (o.z - g.z) * g.w);
                     const bool flip = !(dot(nn, d) < 0.f);                            // :82-83
                     w = flip ? mk(-nn.x, -nn.y, -nn.z) : nn;
                     id = id2;
                     ++depth;
-                    const float4 e2 = sh.emi[id2];
+                    const float4 e2 = recs.emi(id2);
                     L.x = fmaf(T.x, e2.x, L.x); L.y = fmaf(T.y, e2.y, L.y); L.z = fmaf(T.z, e2.z, L.z);
                     end = (__float_as_uint(e2.w) == 0u);   // kd == 0: the next roulette cannot continue
                 } else {
@@ -374,7 +490,7 @@ __global__ void __launch_bounds__(RTM_MEGA_THREADS, 5) radiance_mega_kernel(RtmP
                     rays_ref += (unsigned)(s_end - s_begin);
                     have = false;
                 } else {
-                    const float4 e0 = sh.emi[Pid];
+                    const float4 e0 = recs.emi(Pid);
                     o = P; id = Pid; w = Pw;
                     T = mk(1, 1, 1); L = mk(e0.x, e0.y, e0.z); depth = 0;
                 }
@@ -383,14 +499,19 @@ __global__ void __launch_bounds__(RTM_MEGA_THREADS, 5) radiance_mega_kernel(RtmP
     }
 
     rays_ref += traced;
+    unsigned long long tests = BVH ? (unsigned long long)n_tests : traced * (unsigned long long)n;
+    unsigned long long nodes = n_nodes;
     for (int off = 16; off > 0; off >>= 1) {
         rays_ref += __shfl_down_sync(0xffffffffu, rays_ref, off);
         traced += __shfl_down_sync(0xffffffffu, traced, off);
+        tests += __shfl_down_sync(0xffffffffu, tests, off);
+        nodes += __shfl_down_sync(0xffffffffu, nodes, off);
     }
     if (lane == 0) {
         atomicAdd(&counters->rays_ref, rays_ref);
         atomicAdd(&counters->rays_traced, traced);
-        atomicAdd(&counters->tests, traced * (unsigned long long)n);
+        atomicAdd(&counters->tests, tests);
+        if (BVH) atomicAdd(&counters->nodes, nodes);
     }
 }
 
@@ -460,6 +581,30 @@ __global__ void closest_hit_f32_kernel(int n_sph, unsigned key_mask, double rx, 
     tout[i] = (double)t;
 }
 
+// the hierarchy variant of the hook: same trace function as radiance_mega_kernel<*, true>
+template <int NP>
+__global__ void closest_hit_bvh_f32_kernel(RtmBvhDev bvh, RtmMatDev mat, unsigned key_mask, double rx, double ry, double rz, uint32_t n,
+                                           const double* __restrict__ org, const double* __restrict__ dir,
+                                           const int32_t* __restrict__ origin_id, int n_sph, int32_t* __restrict__ hit,
+                                           double* __restrict__ tout) {
+    __shared__ SelfMask sh_mask;
+    __shared__ SharedBig sh_big;
+    init_selfmask(sh_mask);
+    if (threadIdx.x < 8) sh_big.id[threadIdx.x] = (threadIdx.x < (unsigned)bvh.n_big) ? bvh.big_id[threadIdx.x] : 0;
+    __syncthreads();
+    const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    const f3 o = mk((float)(org[3 * i] - rx), (float)(org[3 * i + 1] - ry), (float)(org[3 * i + 2] - rz));
+    const f3 d = mk((float)dir[3 * i], (float)dir[3 * i + 1], (float)dir[3 * i + 2]);
+    int oid = origin_id ? origin_id[i] : -1;
+    if (oid < -1 || oid >= n_sph) oid = -1;
+    const int oslot = (oid >= 0) ? __float_as_int(__ldg(mat.alb + oid).w) : -1;
+    float t;
+    unsigned a = 0, b = 0;
+    hit[i] = trace_bvh_f32<NP>(sh_mask, sh_big, bvh, oid, oslot, o, d, t, key_mask, a, b);
+    tout[i] = (double)t;
+}
+
 __global__ void philox_kernel(uint32_t n, uint32_t c1, uint32_t c2, uint32_t c3, uint32_t k0, uint32_t k1, uint32_t* __restrict__ out) {
     const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
     if (i >= n) return;
@@ -482,12 +627,13 @@ __global__ void __launch_bounds__(256) fma_peak_kernel(float* __restrict__ sink,
     if (r == 12345.678f) sink[0] = r;
 }
 
-template <int N>
-void launch_mega(const RtmPassParams& p, float4* records, RtmCounters* counters, int n_rt, int sm_count, cudaStream_t st) {
+template <int N, bool BVH>
+void launch_mega(const RtmPassParams& p, float4* records, RtmCounters* counters, int n_rt, int sm_count, cudaStream_t st,
+                 const RtmBvhDev& bvh = RtmBvhDev{}, const RtmMatDev& mat = RtmMatDev{}) {
     int per_sm = 0;
-    cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, radiance_mega_kernel<N>, RTM_MEGA_THREADS, 0);
+    cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, radiance_mega_kernel<N, BVH>, RTM_MEGA_THREADS, 0);
     if (per_sm < 1) per_sm = 1;
-    radiance_mega_kernel<N><<<sm_count * per_sm, RTM_MEGA_THREADS, 0, st>>>(p, records, counters, n_rt);
+    radiance_mega_kernel<N, BVH><<<sm_count * per_sm, RTM_MEGA_THREADS, 0, st>>>(p, records, counters, n_rt, bvh, mat);
 }
 
 }  // namespace
@@ -495,15 +641,27 @@ void launch_mega(const RtmPassParams& p, float4* records, RtmCounters* counters,
 void rtm_launch_radiance_mega(int32_t n, const RtmPassParams& p, float4* records, RtmCounters* counters, int32_t sm_count,
                               cudaStream_t st) {
     switch (n) {
-        case 1: launch_mega<1>(p, records, counters, n, sm_count, st); break;
-        case 2: launch_mega<2>(p, records, counters, n, sm_count, st); break;
-        case 3: launch_mega<3>(p, records, counters, n, sm_count, st); break;
-        case 4: launch_mega<4>(p, records, counters, n, sm_count, st); break;
-        case 5: launch_mega<5>(p, records, counters, n, sm_count, st); break;
-        case 6: launch_mega<6>(p, records, counters, n, sm_count, st); break;
-        case 7: launch_mega<7>(p, records, counters, n, sm_count, st); break;
-        case 8: launch_mega<8>(p, records, counters, n, sm_count, st); break;
-        default: launch_mega<0>(p, records, counters, n, sm_count, st); break;
+        case 1: launch_mega<1, false>(p, records, counters, n, sm_count, st); break;
+        case 2: launch_mega<2, false>(p, records, counters, n, sm_count, st); break;
+        case 3: launch_mega<3, false>(p, records, counters, n, sm_count, st); break;
+        case 4: launch_mega<4, false>(p, records, counters, n, sm_count, st); break;
+        case 5: launch_mega<5, false>(p, records, counters, n, sm_count, st); break;
+        case 6: launch_mega<6, false>(p, records, counters, n, sm_count, st); break;
+        case 7: launch_mega<7, false>(p, records, counters, n, sm_count, st); break;
+        case 8: launch_mega<8, false>(p, records, counters, n, sm_count, st); break;
+        default: launch_mega<0, false>(p, records, counters, n, sm_count, st); break;
+    }
+}
+
+// Hierarchy path: the packed test covers the (padded-to-even) list of big spheres.
+void rtm_launch_radiance_bvh(const RtmBvhDev& bvh, const RtmMatDev& mat, const RtmPassParams& p, float4* records,
+                             RtmCounters* counters, int32_t sm_count, cudaStream_t st) {
+    switch ((bvh.n_big + 1) / 2) {
+        case 0: launch_mega<0, true>(p, records, counters, 0, sm_count, st, bvh, mat); break;
+        case 1: launch_mega<2, true>(p, records, counters, 0, sm_count, st, bvh, mat); break;
+        case 2: launch_mega<4, true>(p, records, counters, 0, sm_count, st, bvh, mat); break;
+        case 3: launch_mega<6, true>(p, records, counters, 0, sm_count, st, bvh, mat); break;
+        default: launch_mega<8, true>(p, records, counters, 0, sm_count, st, bvh, mat); break;
     }
 }
 
@@ -524,6 +682,21 @@ void rtm_launch_to_u8(const float4* accum, unsigned char* out, uint64_t n_pix, c
 void rtm_launch_closest_hit_f32(int32_t n_spheres, const double* refd, uint32_t n, const double* org, const double* dir,
                                 const int32_t* origin_id, int32_t* hit, double* t, cudaStream_t st) {
     closest_hit_f32_kernel<<<(n + 127) / 128, 128, 0, st>>>(n_spheres, 0xFFFFFFF8u, refd[0], refd[1], refd[2], n, org, dir, origin_id, hit, t);
+}
+
+void rtm_launch_closest_hit_bvh_f32(const RtmBvhDev& bvh, const RtmMatDev& mat, int32_t n_spheres, const double* refd, uint32_t n,
+                                    const double* org, const double* dir, const int32_t* origin_id, int32_t* hit, double* t,
+                                    cudaStream_t st) {
+    const unsigned g = (n + 127) / 128;
+    switch ((bvh.n_big + 1) / 2) {
+#define RTM_CASE(NP) closest_hit_bvh_f32_kernel<NP><<<g, 128, 0, st>>>(bvh, mat, 0xFFFFFFF8u, refd[0], refd[1], refd[2], n, org, dir, origin_id, n_spheres, hit, t)
+        case 0: RTM_CASE(0); break;
+        case 1: RTM_CASE(1); break;
+        case 2: RTM_CASE(2); break;
+        case 3: RTM_CASE(3); break;
+        default: RTM_CASE(4); break;
+#undef RTM_CASE
+    }
 }
 
 void rtm_launch_philox(uint32_t n, uint32_t c1, uint32_t c2, uint32_t c3, uint32_t k0, uint32_t k1, uint32_t* out, cudaStream_t st) {

@@ -8,6 +8,7 @@
 // -ffp-contract=off.
 #include "../../include/rtm_b200.h"
 #include "rtm_internal.h"
+#include "bvh.h"
 
 #include <dlfcn.h>
 #include <nccl.h>  // types only; the library is dlopen'ed when n_gpus > 1
@@ -113,6 +114,9 @@ struct GpuCtx {
     double* image64 = nullptr;
     unsigned char* u8 = nullptr;
     RtmCounters* counters = nullptr;
+    float4* d_bvh = nullptr;    // one allocation: nodes | leaf_geo | geo | emi | alb | leaf_id
+    RtmBvhDev bvh{};
+    RtmMatDev mat{};
     float4* h_accum = nullptr;  // pinned staging
     int32_t s_begin = 0, s_end = 0;
     ncclComm_t comm = nullptr;
@@ -130,6 +134,9 @@ struct rtm_renderer {
     std::vector<GpuCtx> gpus;
     int32_t last_launches = 0;
     bool hits_valid = false;
+    bool use_bvh = false;       // closest hit through the hierarchy (bvh.h) instead of the O(N) loop
+    RtmBvhHost bvh_host;
+    std::vector<float4> mat_geo, mat_emi, mat_alb;
 };
 
 namespace {
@@ -144,6 +151,7 @@ void free_ctx(GpuCtx& c) {
     if (c.image64) cudaFree(c.image64);
     if (c.u8) cudaFree(c.u8);
     if (c.counters) cudaFree(c.counters);
+    if (c.d_bvh) cudaFree(c.d_bvh);
     if (c.h_accum) cudaFreeHost(c.h_accum);
     if (c.ev0) cudaEventDestroy(c.ev0);
     if (c.ev1) cudaEventDestroy(c.ev1);
@@ -191,14 +199,14 @@ int enqueue_pass(rtm_renderer* r, GpuCtx& c, cudaStream_t st, bool want_hits, in
         int rc = ensure_hits(r, c);
         if (rc) return rc;
         if (!c.image64) CU(cudaMalloc(&c.image64, r->n_pix * 3 * sizeof(double)));
-        rtm_launch_primary_f64(c.s64, p, c.hits, nullptr, st);
+        rtm_launch_primary_f64(c.s64, p, c.hits, nullptr, nullptr, st);
         rtm_launch_head_image(c.s64, p, c.hits, c.image64, c.accum, st);
         *launches += 2;
     } else if (r->opt.precision == RTM_PRECISION_F64) {
         if (want_hits) {
             int rc = ensure_hits(r, c);
             if (rc) return rc;
-            rtm_launch_primary_f64(c.s64, p, c.hits, nullptr, st);
+            rtm_launch_primary_f64(c.s64, p, c.hits, nullptr, nullptr, st);
             *launches += 1;
         }
         rtm_launch_radiance_f64(c.s64, p, c.records, c.counters, st);
@@ -211,9 +219,10 @@ int enqueue_pass(rtm_renderer* r, GpuCtx& c, cudaStream_t st, bool want_hits, in
         }
         CU(rtm_upload_scene_f32(r->f32, st));
         CU(cudaEventRecord(c.ek[0], st));
-        rtm_launch_primary_f64(c.s64, p, want_hits ? c.hits : nullptr, c.records, st);
+        rtm_launch_primary_f64(c.s64, p, want_hits ? c.hits : nullptr, c.records, c.counters, st);
         CU(cudaEventRecord(c.ek[1], st));
-        rtm_launch_radiance_mega(r->n, p, c.records, c.counters, c.sm_count, st);
+        if (r->use_bvh) rtm_launch_radiance_bvh(c.bvh, c.mat, p, c.records, c.counters, c.sm_count, st);
+        else rtm_launch_radiance_mega(r->n, p, c.records, c.counters, c.sm_count, st);
         CU(cudaEventRecord(c.ek[2], st));
         rtm_launch_accumulate(p, c.records, c.accum, st);
         CU(cudaEventRecord(c.ek[3], st));
@@ -246,8 +255,10 @@ int fill_stats(rtm_renderer* r, rtm_stats* st) {
         } else {
             st->rays += h.rays_ref;
             st->rays_traced += h.rays_traced + r->n_sub;
-            st->sphere_tests += h.tests + r->n_sub * (uint64_t)r->n;
+            // hierarchy path: the primary pass counts its own tests into the same counter
+            st->sphere_tests += h.tests + (r->use_bvh ? 0 : r->n_sub * (uint64_t)r->n);
         }
+        st->bvh_nodes += h.nodes;
     }
     st->n_gpus = (int32_t)r->gpus.size();
     st->kernel_launches = r->last_launches;
@@ -314,8 +325,12 @@ int renderer_create(const rtm_scene_desc* sc, const rtm_options* opt_in, rtm_ren
         return fail(RTM_E_UNSUPPORTED, "sub-pixel slices need COMPAT_ABC and one GPU per handle");
     if (opt.variant != RTM_VARIANT_MEGA) return fail(RTM_E_UNSUPPORTED, "variant %d not built", opt.variant);
     const bool f32_path = (opt.compat == RTM_COMPAT_ABC && opt.precision == RTM_PRECISION_F32);
-    if (f32_path && sc->n_spheres > RTM_MAX_CONST_SPHERES)
-        return fail(RTM_E_UNSUPPORTED, "FP32 brute-force path holds at most %d spheres", RTM_MAX_CONST_SPHERES);
+    if (opt.accel != RTM_ACCEL_AUTO && opt.accel != RTM_ACCEL_BRUTE && opt.accel != RTM_ACCEL_BVH)
+        return fail(RTM_E_INVALID, "bad accel %d", opt.accel);
+    const bool use_bvh = opt.accel == RTM_ACCEL_BVH || (opt.accel == RTM_ACCEL_AUTO && sc->n_spheres > 64);
+    if (f32_path && !use_bvh && sc->n_spheres > RTM_MAX_CONST_SPHERES)
+        return fail(RTM_E_UNSUPPORTED, "FP32 brute-force path holds at most %d spheres (use RTM_ACCEL_BVH / AUTO)",
+                    RTM_MAX_CONST_SPHERES);
 
     int ndev = 0;
     cudaError_t ce = cudaGetDeviceCount(&ndev);
@@ -329,6 +344,7 @@ int renderer_create(const rtm_scene_desc* sc, const rtm_options* opt_in, rtm_ren
     rtm_renderer* r = new rtm_renderer();
     r->opt = opt;
     r->W = sc->width; r->H = sc->height; r->S = sc->samples; r->ss = sc->superSamples; r->n = sc->n_spheres;
+    r->use_bvh = use_bvh;
     r->n_pix = (uint64_t)r->W * r->H;
     r->n_sub = r->n_pix * (uint64_t)(opt.sub_end - opt.sub_begin);   // sub-pixels this handle renders
 
@@ -379,41 +395,74 @@ int renderer_create(const rtm_scene_desc* sc, const rtm_options* opt_in, rtm_ren
         }
         if (f32_path) {
             const double px = cx[i] - r->refd[0], py = cy[i] - r->refd[1], pz = cz[i] - r->refd[2];
-            RtmSceneF32Host& s = r->f32;
-            s.cx[i] = (float)px; s.cy[i] = (float)py; s.cz[i] = (float)pz;
-            // use the rounded centre consistently: K belongs to the sphere the FP32 kernel sees
-            const double fx = s.cx[i], fy = s.cy[i], fz = s.cz[i];
-            s.m2cx[i] = -2.0f * s.cx[i]; s.m2cy[i] = -2.0f * s.cy[i]; s.m2cz[i] = -2.0f * s.cz[i];
-            s.K[i] = (float)(fx * fx + fy * fy + fz * fz - (double)rad * (double)rad);
-            s.inv_r[i] = (float)(1.0 / (double)rad);
-            s.ex[i] = (float)em[3 * i]; s.ey[i] = (float)em[3 * i + 1]; s.ez[i] = (float)em[3 * i + 2];
-            s.kd[i] = kdf;
-            {
-                const double th = (double)kdf * 4294967296.0;
-                s.kd_thr[i] = (th >= 4294967295.0) ? 0xFFFFFFFFu : (th <= 0.0 ? 0u : (uint32_t)th);
-            }
-            if (kdf > 0.f) {
-                s.kx[i] = (float)(c0 / (double)kdf); s.ky[i] = (float)(c1 / (double)kdf); s.kz[i] = (float)(c2 / (double)kdf);
+            const float fcx = (float)px, fcy = (float)py, fcz = (float)pz;
+            const float inv_r = (float)(1.0 / (double)rad);
+            const double th = (double)kdf * 4294967296.0;
+            const uint32_t thr = (th >= 4294967295.0) ? 0xFFFFFFFFu : (th <= 0.0 ? 0u : (uint32_t)th);
+            float kx = 0.f, ky = 0.f, kz = 0.f;
+            if (kdf > 0.f) { kx = (float)(c0 / (double)kdf); ky = (float)(c1 / (double)kdf); kz = (float)(c2 / (double)kdf); }
+            if (use_bvh) {
+                float4 e = make_float4((float)em[3 * i], (float)em[3 * i + 1], (float)em[3 * i + 2], 0.f);
+                memcpy(&e.w, &thr, 4);
+                float4 a = make_float4(kx, ky, kz, 0.f);
+                const int32_t none = -1;
+                memcpy(&a.w, &none, 4);
+                r->mat_geo.push_back(make_float4(fcx, fcy, fcz, inv_r));
+                r->mat_emi.push_back(e);
+                r->mat_alb.push_back(a);
             } else {
-                s.kx[i] = s.ky[i] = s.kz[i] = 0.f;
+                RtmSceneF32Host& s = r->f32;
+                s.cx[i] = fcx; s.cy[i] = fcy; s.cz[i] = fcz;
+                s.m2cx[i] = -2.0f * fcx; s.m2cy[i] = -2.0f * fcy; s.m2cz[i] = -2.0f * fcz;
+                s.inv_r[i] = inv_r;
+                s.ex[i] = (float)em[3 * i]; s.ey[i] = (float)em[3 * i + 1]; s.ez[i] = (float)em[3 * i + 2];
+                s.kd[i] = kdf;
+                s.kd_thr[i] = thr;
+                s.kx[i] = kx; s.ky[i] = ky; s.kz[i] = kz;
             }
         }
     }
 
+    if (use_bvh) {
+        if (!rtm_bvh_build(n, sc->position, sc->radius, r->refd, r->bvh_host)) {
+            const int d = r->bvh_host.depth;
+            delete r;
+            return fail(RTM_E_UNSUPPORTED, "sphere hierarchy too deep (%d levels)", d);
+        }
+        if (f32_path)
+            for (int j = 0; j < r->bvh_host.n_big; ++j) memcpy(&r->mat_alb[r->bvh_host.big_id[j]].w, &j, 4);
+    }
+
     if (f32_path) {
+        // the packed pair test: the first 8 spheres (brute force) or the big list (hierarchy)
         RtmSceneF32Host& s = r->f32;
+        const int n_packed = use_bvh ? r->bvh_host.n_big : (n < 2 * RTM_MAX_PAIRS ? n : 2 * RTM_MAX_PAIRS);
         for (int j = 0; j < RTM_MAX_PAIRS; ++j) {
             float* f = reinterpret_cast<float*>(&s.pairs[j]);
             for (int h = 0; h < 2; ++h) {
-                const int i = 2 * j + h;
-                const bool real = i < n;
+                const int slot = 2 * j + h;
+                const bool real = slot < n_packed;
+                const int i = real ? (use_bvh ? r->bvh_host.big_id[slot] : slot) : 0;
+                float fcx = 0.f, fcy = 0.f, fcz = 0.f, K = 1e30f;
+                if (real) {
+                    fcx = (float)(cx[i] - r->refd[0]); fcy = (float)(cy[i] - r->refd[1]); fcz = (float)(cz[i] - r->refd[2]);
+                    // use the rounded centre consistently: K belongs to the sphere the FP32 kernel sees
+                    const double fx = fcx, fy = fcy, fz = fcz, rad = (double)sc->radius[i];
+                    K = (float)(fx * fx + fy * fy + fz * fz - rad * rad);
+                    if (!use_bvh) s.K[i] = K;
+                }
                 // dummy: centre at the reference point, -c' = -1e30 -> negative discriminant -> NaN -> never a hit
-                f[0 + h] = real ? s.cx[i] : 0.f;  f[2 + h] = real ? s.cy[i] : 0.f;  f[4 + h] = real ? s.cz[i] : 0.f;
-                f[6 + h] = real ? -s.m2cx[i] : 0.f; f[8 + h] = real ? -s.m2cy[i] : 0.f; f[10 + h] = real ? -s.m2cz[i] : 0.f;
-                f[12 + h] = real ? -s.K[i] : -1e30f;
+                f[0 + h] = fcx;  f[2 + h] = fcy;  f[4 + h] = fcz;
+                f[6 + h] = 2.0f * fcx; f[8 + h] = 2.0f * fcy; f[10 + h] = 2.0f * fcz;
+                f[12 + h] = -K;
                 f[14 + h] = 0.f;
             }
         }
+        if (!use_bvh)
+            for (int i = 2 * RTM_MAX_PAIRS; i < n; ++i) {
+                const double fx = s.cx[i], fy = s.cy[i], fz = s.cz[i], rad = (double)sc->radius[i];
+                s.K[i] = (float)(fx * fx + fy * fy + fz * fz - rad * rad);
+            }
     }
 
     // devices
@@ -439,6 +488,33 @@ int renderer_create(const rtm_scene_desc* sc, const rtm_options* opt_in, rtm_ren
             c.s64.n = n;
             c.s64.cx = c.d_scene64; c.s64.cy = c.s64.cx + n; c.s64.cz = c.s64.cy + n; c.s64.r2 = c.s64.cz + n;
             c.s64.kd = c.s64.r2 + n; c.s64.emission = c.s64.kd + n; c.s64.color = c.s64.emission + 3 * (size_t)n;
+            if (use_bvh) {
+                // one allocation, float4 units: nodes | leaf_geo | geo | emi | alb | leaf_id (int32, padded)
+                const RtmBvhHost& B = r->bvh_host;
+                const size_t n_nodes4 = B.nodes.size(), n_slots = B.leaf_geo.size(), n_mat = r->mat_geo.size();
+                const size_t total4 = n_nodes4 + n_slots + 3 * n_mat + (n_slots + 3) / 4 + 1;
+                CU(cudaMalloc(&c.d_bvh, total4 * sizeof(float4)));
+                float4* d = c.d_bvh;
+                auto put = [&](const void* src, size_t count4, size_t bytes) -> float4* {
+                    float4* at = d;
+                    if (bytes) cudaMemcpy(at, src, bytes, cudaMemcpyHostToDevice);
+                    d += count4;
+                    return at;
+                };
+                c.bvh.nodes = put(B.nodes.data(), n_nodes4, n_nodes4 * sizeof(float4));
+                c.bvh.leaf_geo = put(B.leaf_geo.data(), n_slots, n_slots * sizeof(float4));
+                c.mat.geo = put(r->mat_geo.data(), n_mat, n_mat * sizeof(float4));
+                c.mat.emi = put(r->mat_emi.data(), n_mat, n_mat * sizeof(float4));
+                c.mat.alb = put(r->mat_alb.data(), n_mat, n_mat * sizeof(float4));
+                c.bvh.leaf_id = (const int32_t*)put(B.leaf_id.data(), (n_slots + 3) / 4, n_slots * sizeof(int32_t));
+                CU(cudaGetLastError());
+                c.bvh.root = B.root;
+                c.bvh.n_big = B.n_big;
+                for (int j = 0; j < 8; ++j) c.bvh.big_id[j] = B.big_id[j];
+                c.s64.use_bvh = 1;
+                c.s64.bvh = c.bvh;
+                for (int k = 0; k < 3; ++k) c.s64.ref[k] = r->refd[k];
+            }
             if (opt.compat == RTM_COMPAT_ABC) CU(cudaMalloc(&c.records, r->n_sub * sizeof(float4)));
             CU(cudaMalloc(&c.accum, r->n_pix * sizeof(float4)));
             CU(cudaMemset(c.accum, 0, r->n_pix * sizeof(float4)));
@@ -613,7 +689,7 @@ int rtm_debug_closest_hit(rtm_renderer* r, int32_t mode, uint32_t n, const doubl
     if (!r || !org || !dir || !hit_out || !t_out || n == 0) return fail(RTM_E_INVALID, "bad argument");
     GpuCtx& c = r->gpus[0];
     CU(cudaSetDevice(c.device));
-    if (mode == 1 && r->n > RTM_MAX_CONST_SPHERES) return fail(RTM_E_UNSUPPORTED, "too many spheres for the FP32 test");
+    if (mode == 1 && !r->use_bvh && r->n > RTM_MAX_CONST_SPHERES) return fail(RTM_E_UNSUPPORTED, "too many spheres for the FP32 test");
     double *d_org = nullptr, *d_dir = nullptr, *d_t = nullptr;
     int32_t *d_oid = nullptr, *d_hit = nullptr;
     int rc = RTM_OK;
@@ -633,7 +709,8 @@ int rtm_debug_closest_hit(rtm_renderer* r, int32_t mode, uint32_t n, const doubl
         } else {
             if (r->f32.n != r->n) return fail(RTM_E_UNSUPPORTED, "handle was not created for the FP32 path");
             CU(rtm_upload_scene_f32(r->f32, c.stream));
-            rtm_launch_closest_hit_f32(r->n, r->refd, n, d_org, d_dir, d_oid, d_hit, d_t, c.stream);
+            if (r->use_bvh) rtm_launch_closest_hit_bvh_f32(c.bvh, c.mat, r->n, r->refd, n, d_org, d_dir, d_oid, d_hit, d_t, c.stream);
+            else rtm_launch_closest_hit_f32(r->n, r->refd, n, d_org, d_dir, d_oid, d_hit, d_t, c.stream);
         }
         CU(cudaGetLastError());
         CU(cudaStreamSynchronize(c.stream));
@@ -644,6 +721,22 @@ int rtm_debug_closest_hit(rtm_renderer* r, int32_t mode, uint32_t n, const doubl
     rc = body();
     cudaFree(d_org); cudaFree(d_dir); cudaFree(d_t); cudaFree(d_hit); cudaFree(d_oid);
     return rc;
+}
+
+int rtm_debug_bvh(const rtm_scene_desc* sc, int32_t* info, float* nodes_out, float* leaf_geo_out, int32_t* leaf_id_out) {
+    if (!sc || !info) return fail(RTM_E_INVALID, "null argument");
+    RtmBvhHost B;
+    const bool ok = rtm_bvh_build(sc->n_spheres, sc->position, sc->radius, sc->cam_origin, B);
+    info[0] = (int32_t)(B.nodes.size() / 4);
+    info[1] = (int32_t)B.leaf_id.size();
+    info[2] = B.root;
+    info[3] = B.depth;
+    info[4] = B.n_big;
+    for (int j = 0; j < 8; ++j) info[5 + j] = B.big_id[j];
+    if (nodes_out) memcpy(nodes_out, B.nodes.data(), B.nodes.size() * sizeof(float4));
+    if (leaf_geo_out) memcpy(leaf_geo_out, B.leaf_geo.data(), B.leaf_geo.size() * sizeof(float4));
+    if (leaf_id_out) memcpy(leaf_id_out, B.leaf_id.data(), B.leaf_id.size() * sizeof(int32_t));
+    return ok ? RTM_OK : fail(RTM_E_UNSUPPORTED, "sphere hierarchy too deep (%d levels)", B.depth);
 }
 
 int rtm_debug_fp32_peak(int32_t device, double* tflops_out, double* mhz_out) {

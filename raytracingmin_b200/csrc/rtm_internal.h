@@ -6,6 +6,7 @@
 
 #define RTM_MAX_CONST_SPHERES 256  // FP32 brute-force scene lives in __constant__ memory up to this size
 #define RTM_WARP 32
+#define RTM_BVH_STACK_DEV 64       // traversal stack entries per lane (bvh.h: the build caps the depth below this)
 
 // Camera frame of reference src/Renderer.cpp:202-208, precomputed on the host
 // in double without FMA: ax = camX*fovx, ay = camY*fovy, az = camZ.
@@ -16,9 +17,31 @@ struct RtmFrame {
     int32_t W, H, ss, S; // S = global "samples"
 };
 
+// Device view of the sphere hierarchy (bvh.h): nodes / leaf slots in global memory.
+struct RtmBvhDev {
+    const float4* nodes;      // 4 float4 per inner node
+    const float4* leaf_geo;   // per leaf slot: centre relative to the reference point, r^2 (float)
+    const int32_t* leaf_id;   // per leaf slot: original sphere index
+    int32_t root;             // child code of the root, RTM_BVH_NONE when empty
+    int32_t n_big;            // spheres kept out of the hierarchy, tested for every ray
+    int32_t big_id[8];        //   ascending original index
+};
+
+// Per-sphere records of the FP32 path in GLOBAL memory (hierarchy path, any N): the
+// same three float4 the brute-force kernel keeps in shared memory, plus the slot of
+// the sphere in the "big" list (or -1) in alb.w.
+struct RtmMatDev {
+    const float4* geo;  // cx cy cz 1/r
+    const float4* emi;  // emission rgb, roulette threshold (uint bits)
+    const float4* alb;  // color/kd rgb, big-list slot (int bits)
+};
+
 // Scene for the exact FP64 kernels: SoA in global memory (any N).
 struct RtmSceneF64 {
     int32_t n;
+    int32_t use_bvh;         // closest hit through `bvh` (same candidates arithmetic, same winner)
+    double ref[3];           // reference point the hierarchy's boxes are relative to
+    RtmBvhDev bvh;
     const double* cx;
     const double* cy;
     const double* cz;
@@ -65,6 +88,7 @@ struct RtmCounters {
     unsigned long long rays_traced;  // closest-hit queries executed
     unsigned long long tests;        // ray-sphere tests executed
     unsigned long long work_next;    // dynamic work cursor of the persistent megakernel
+    unsigned long long nodes;        // hierarchy nodes visited (hierarchy path only)
 };
 
 struct RtmPassParams {
@@ -83,7 +107,8 @@ struct RtmPassParams {
 
 // ---- launchers implemented by the kernel TUs (all asynchronous on `st`) ----
 void rtm_launch_primary_f64(const RtmSceneF64& sc, const RtmPassParams& p, int32_t* hits /*or null*/,
-                            float4* records /*or null*/, cudaStream_t st);
+                            float4* records /*or null*/, RtmCounters* counters /*hierarchy work, or null*/,
+                            cudaStream_t st);
 void rtm_launch_head_image(const RtmSceneF64& sc, const RtmPassParams& p, const int32_t* hits,
                            double* image64 /*[H][W][3]*/, float4* accum, cudaStream_t st);
 void rtm_launch_radiance_f64(const RtmSceneF64& sc, const RtmPassParams& p, float4* records,
@@ -94,11 +119,16 @@ void rtm_launch_closest_hit_f64(const RtmSceneF64& sc, uint32_t n, const double*
 cudaError_t rtm_upload_scene_f32(const RtmSceneF32Host& h, cudaStream_t st);
 void rtm_launch_radiance_mega(int32_t n_spheres, const RtmPassParams& p, float4* records, RtmCounters* counters,
                               int32_t sm_count, cudaStream_t st);
+void rtm_launch_radiance_bvh(const RtmBvhDev& bvh, const RtmMatDev& mat, const RtmPassParams& p, float4* records,
+                             RtmCounters* counters, int32_t sm_count, cudaStream_t st);
 void rtm_launch_accumulate(const RtmPassParams& p, const float4* records, float4* accum, cudaStream_t st);
 void rtm_launch_to_u8(const float4* accum, unsigned char* out, uint64_t n_pix, cudaStream_t st);
 void rtm_launch_closest_hit_f32(int32_t n_spheres, const double* refd, uint32_t n, const double* org,
                                 const double* dir, const int32_t* origin_id, int32_t* hit, double* t,
                                 cudaStream_t st);
+void rtm_launch_closest_hit_bvh_f32(const RtmBvhDev& bvh, const RtmMatDev& mat, int32_t n_spheres, const double* refd, uint32_t n,
+                                    const double* org, const double* dir, const int32_t* origin_id, int32_t* hit, double* t,
+                                    cudaStream_t st);
 void rtm_launch_philox(uint32_t n, uint32_t c1, uint32_t c2, uint32_t c3, uint32_t k0, uint32_t k1, uint32_t* out,
                        cudaStream_t st);
 void rtm_launch_fma_peak(float* sink, int32_t blocks, int32_t iters, cudaStream_t st);

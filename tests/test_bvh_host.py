@@ -1,0 +1,196 @@
+"""Host-side checks of the sphere hierarchy (raytracingmin_b200/csrc/bvh_build.cpp) — no GPU.
+
+The hierarchy only selects candidates; the winner must be the one the reference's O(N) loop
+(src/Renderer.cpp:58-73) picks.  Here: structural invariants of the built tree, and a Python
+emulation of the device traversal of kernels_exact.cu (same per-ray box inflation) checked
+against the oracle's brute-force closest hit on the 10 000-sphere scene.
+"""
+import os
+
+import numpy as np
+import pytest
+
+import oracle_lib as O
+import raytracingmin_b200 as rtm
+from raytracingmin_b200 import api
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+NONE = 0x7FFFFFFF
+
+
+def _children(node):
+    c = node[3].view(np.int32)
+    return int(c[0]), int(c[1])
+
+
+def _boxes(node):
+    b0 = (node[0][0], node[0][1], node[0][2], node[0][3], node[2][0], node[2][1])
+    b1 = (node[1][0], node[1][1], node[1][2], node[1][3], node[2][2], node[2][3])
+    return b0, b1
+
+
+def _leaf(code):
+    v = (~code) & 0xFFFFFFFF
+    return v >> 3, (v & 7) + 1
+
+
+def _collect(b, code, out):
+    if code < 0:
+        first, cnt = _leaf(code)
+        out.extend(range(first, first + cnt))
+        return
+    c0, c1 = _children(b["nodes"][code])
+    _collect(b, c0, out)
+    _collect(b, c1, out)
+
+
+@pytest.fixture(scope="module")
+def synth():
+    sc = rtm.load_scene(os.path.join(ROOT, "scenes", "synth10k.json"))
+    return sc, api.build_bvh(sc)
+
+
+def test_every_sphere_exactly_once(synth):
+    sc, b = synth
+    assert sorted(list(b["leaf_id"]) + b["big_id"]) == list(range(sc.n))
+    assert b["big_id"] == [0, 1, 2, 3, 4, 5, 6]           # the Cornell room of scenes/make_scenes.py
+    assert b["depth"] + 2 < 64
+
+
+def test_boxes_contain_their_spheres_and_rmin_is_a_lower_bound(synth):
+    sc, b = synth
+    ref = sc.cam_origin
+    rel = sc.position - ref
+    rad = sc.radius.astype(np.float64)
+    for ni in range(0, len(b["nodes"]), 37):              # every 37th node, full subtree each
+        node = b["nodes"][ni]
+        for code, box, rmin in zip(_children(node), _boxes(node), (node[3][2], node[3][3])):
+            slots = []
+            _collect(b, code, slots)
+            ids = b["leaf_id"][slots]
+            lo = (rel[ids] - rad[ids, None]).min(axis=0)
+            hi = (rel[ids] + rad[ids, None]).max(axis=0)
+            assert box[0] < lo[0] and box[2] < lo[1] and box[4] < lo[2]
+            assert box[1] > hi[0] and box[3] > hi[1] and box[5] > hi[2]
+            assert rmin <= rad[ids].min()
+    # leaf slots carry the float centre the FP32 kernels use and r^2
+    k = b["leaf_id"]
+    assert np.array_equal(b["leaf_geo"][:, :3], rel[k].astype(np.float32))
+    assert np.array_equal(b["leaf_geo"][:, 3], (rad[k] * rad[k]).astype(np.float32))
+
+
+def _sphere_test(c, r, o, d):
+    """src/SettingData.cpp:197-223 in numpy doubles (r*r in float, minValue 1e-5f)."""
+    p = c - o
+    bq = p[0] * d[0] + p[1] * d[1] + p[2] * d[2]
+    D4 = bq * bq - (p[0] * p[0] + p[1] * p[1] + p[2] * p[2]) + float(np.float32(r) * np.float32(r))
+    if D4 < 0.0:
+        return None
+    s = np.sqrt(D4)
+    t1, t2 = bq - s, bq + s
+    mv = float(np.float32(1e-5))
+    if t1 < mv and t2 < mv:
+        return None
+    return t1 if t1 > 0.001 else t2
+
+
+def _traverse(sc, b, o, d):
+    """kernels_exact.cu: closest_hit_bvh, statement by statement."""
+    dd = d[0] * d[0] + d[1] * d[1] + d[2] * d[2]
+    assert abs(dd - 1.0) <= 4e-7
+    best, bid, tested = np.finfo(np.float64).max, -1, 0
+
+    def consider(i):
+        nonlocal best, bid, tested
+        tested += 1
+        t = _sphere_test(sc.position[i], sc.radius[i], o, d)
+        if t is not None and t > 0.0 and (t < best or (t == best and i < bid)):
+            best, bid = t, i
+
+    for i in b["big_id"]:
+        consider(i)
+    ke = 4.5 * (abs(dd - 1.0) + 1e-14)
+    orel = o - sc.cam_origin
+    with np.errstate(divide="ignore"):
+        inv = 1.0 / d
+
+    def box(bx, rmin):
+        lo = np.array([bx[0], bx[2], bx[4]], np.float64)
+        hi = np.array([bx[1], bx[3], bx[5]], np.float64)
+        far = np.maximum(np.abs(lo - orel), np.abs(hi - orel))
+        infl = ke * float(far @ far) / float(rmin)
+        with np.errstate(invalid="ignore"):
+            t1, t2 = (lo - infl - orel) * inv, (hi + infl - orel) * inv
+        tmin = max(0.0, np.nanmax(np.fmin(t1, t2)))
+        tmax = min(best, np.nanmin(np.fmax(t1, t2)))
+        return tmin <= tmax, tmin
+
+    stack, node = [NONE], b["root"]
+    while node != NONE:
+        if node >= 0:
+            nd = b["nodes"][node]
+            c0, c1 = _children(nd)
+            b0, b1 = _boxes(nd)
+            h0, n0 = box(b0, nd[3][2])
+            h1, n1 = box(b1, nd[3][3])
+            if h0 and h1:
+                if n1 < n0:
+                    stack.append(c0)
+                    node = c1
+                else:
+                    stack.append(c1)
+                    node = c0
+            elif h0 or h1:
+                node = c0 if h0 else c1
+            else:
+                node = stack.pop()
+        else:
+            first, cnt = _leaf(node)
+            for k in range(first, first + cnt):
+                consider(int(b["leaf_id"][k]))
+            node = stack.pop()
+    return bid, best, tested
+
+
+def test_emulated_traversal_equals_brute_force(synth):
+    sc, b = synth
+    small = sc.with_dims(96, 54, 1, 1)
+    rng = np.random.default_rng(5)
+    n = 700
+    xs, ys = rng.integers(0, small.width, n), rng.integers(0, small.height, n)
+    d = O.oracle_camera_dirs(small, xs, ys, np.ones(n, np.int64), np.ones(n, np.int64))
+    org = np.tile(sc.cam_origin, (n, 1))
+    hit_o, t_o, _ = O.oracle_closest_hit(sc, org, d)
+    tested = 0
+    for i in range(n):
+        bid, best, k = _traverse(sc, b, org[i], d[i])
+        tested += k
+        assert bid == hit_o[i], (i, bid, hit_o[i])
+        if bid >= 0:
+            assert best == t_o[i]
+    assert tested / n < 200          # the point of the hierarchy: far fewer than 10 000 tests per ray
+    # secondary rays: start on the primary hit, random unit directions normalised the reference's way
+    p = org + d * t_o[:, None]
+    d2 = rng.normal(size=(n, 3))
+    m = np.sqrt((d2 * d2).sum(axis=1).astype(np.float32)).astype(np.float64)     # Ray.h:67-72
+    d2 = d2 / m[:, None]
+    hit2, t2, _ = O.oracle_closest_hit(sc, p, d2)
+    for i in range(0, n, 2):
+        bid, best, _ = _traverse(sc, b, p[i], d2[i])
+        assert bid == hit2[i], (i, bid, hit2[i])
+        if bid >= 0:
+            assert best == t2[i]
+
+
+def test_small_and_degenerate_inputs():
+    for seed, n, closed in [(1, 0, False), (2, 1, False), (3, 2, True), (4, 5, True), (5, 70, False)]:
+        sc = rtm.random_scene(seed, n, closed=closed)
+        b = api.build_bvh(sc)
+        assert sorted(list(b["leaf_id"]) + b["big_id"]) == list(range(sc.n))
+    # many identical spheres (what COMPAT_HEAD's position collapse produces): median splits must terminate
+    sc = rtm.random_scene(7, 300, closed=False)
+    sc.position[:] = sc.position[0]
+    sc.radius[:] = sc.radius[0]
+    b = api.build_bvh(sc.normalized())
+    assert sorted(list(b["leaf_id"]) + b["big_id"]) == list(range(sc.n))
+    assert b["depth"] < 40
