@@ -193,7 +193,7 @@ __device__ __forceinline__ double clamp01(double v) {
 
 // ---- K1: primary pass, one thread per sub-pixel ----------------------------
 __device__ __forceinline__ void primary_one(const RtmSceneF64& sc, const RtmPassParams& p, uint64_t q, int32_t* __restrict__ hits,
-                                            float4* __restrict__ records, BvhWork* work) {
+                                            float4* __restrict__ records, float* __restrict__ cps0, BvhWork* work) {
     int x, y, sx, sy;
     uint64_t qg;
     decode_sub(p, q, x, y, sx, sy, qg);
@@ -212,16 +212,23 @@ __device__ __forceinline__ void primary_one(const RtmSceneF64& sc, const RtmPass
             const uint32_t flip = (dot(n, d) < 0.0) ? 0u : RTM_REC_FLIP;   // Renderer.cpp:82-83
             rec = make_float4((float)(hp.x - p.refd[0]), (float)(hp.y - p.refd[1]), (float)(hp.z - p.refd[2]),
                               __uint_as_float((uint32_t)id | flip));
+            if (cps0) {
+                // what SettingData.cpp:198-200 will see for THIS sphere from the bounce origin hp:
+                // c' = |p_o|^2 - r^2, nonzero because d is unit only to float precision (Ray.h:67-72)
+                const d3 p_o = sub(sphere_center(sc, id), hp);
+                cps0[q] = (float)(dot(p_o, p_o) - __ldg(sc.r2 + id));
+            }
         }
         records[q] = rec;
     }
 }
 
 __global__ void __launch_bounds__(256) primary_f64_kernel(RtmSceneF64 sc, RtmPassParams p, int32_t* __restrict__ hits,
-                                                          float4* __restrict__ records, RtmCounters* __restrict__ counters) {
+                                                          float4* __restrict__ records, RtmCounters* __restrict__ counters,
+                                                          float* __restrict__ cps0) {
     const uint64_t q = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
     BvhWork work{0u, 0u};
-    if (q < p.n_sub) primary_one(sc, p, q, hits, records, sc.use_bvh ? &work : nullptr);
+    if (q < p.n_sub) primary_one(sc, p, q, hits, records, cps0, sc.use_bvh ? &work : nullptr);
     if (sc.use_bvh && counters) {   // hierarchy: tests / nodes actually executed, one atomic pair per warp
         unsigned long long t = work.tests, n = work.nodes;
         for (int off = 16; off > 0; off >>= 1) {
@@ -341,9 +348,9 @@ __global__ void closest_hit_f64_kernel(RtmSceneF64 sc, uint32_t n, const double*
 }  // namespace
 
 void rtm_launch_primary_f64(const RtmSceneF64& sc, const RtmPassParams& p, int32_t* hits, float4* records,
-                            RtmCounters* counters, cudaStream_t st) {
+                            RtmCounters* counters, float* cps0, cudaStream_t st) {
     const uint32_t blocks = (uint32_t)((p.n_sub + 255) / 256);
-    primary_f64_kernel<<<blocks, 256, 0, st>>>(sc, p, hits, records, counters);
+    primary_f64_kernel<<<blocks, 256, 0, st>>>(sc, p, hits, records, counters, cps0);
 }
 
 void rtm_launch_head_image(const RtmSceneF64& sc, const RtmPassParams& p, const int32_t* hits, double* image64,

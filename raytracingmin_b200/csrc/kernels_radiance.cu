@@ -264,9 +264,15 @@ __device__ __forceinline__ int trace_bvh_f32(const SelfMask& sm, const SharedBig
                     const int sid = __ldg(bvh.leaf_id + first + k);
                     const f3 p = mk(g.x - o.x, g.y - o.y, g.z - o.z);
                     const float b = dot(p, d);
+                    // discriminant as r^2 - |p - b d|^2: b^2 - (|p|^2 - r^2) cancels at |p|^2 ~ 400 and
+                    // leaves an error of 3e-4 against r^2 = 2.5e-3 for the smallest spheres
+                    const f3 l = mk(fmaf(-b, d.x, p.x), fmaf(-b, d.y, p.y), fmaf(-b, d.z, p.z));
+                    float D = g.w - dot(l, l);
                     float cp = dot(p, p) - g.w;
-                    cp = (sid == oid) ? 0.f : cp;                      // leaving this sphere's surface
-                    const float s = fast_sqrt(fmaf(b, b, -cp));        // NaN: the ray misses
+                    const bool self = (sid == oid);                    // leaving this sphere's surface
+                    cp = self ? 0.f : cp;
+                    D = self ? b * b : D;
+                    const float s = fast_sqrt(D);                      // NaN: the ray misses
                     const float tq = b + copysignf(s, b);
                     const float ta = tq - RTM_T_EPS, tb = fmaf(cp, fast_rcp(tq), -RTM_T_EPS);
                     const float c1 = (ta > 0.f) ? ta : FLT_MAX, c2 = (tb > 0.f) ? tb : FLT_MAX;
@@ -329,6 +335,32 @@ __device__ __forceinline__ f3 cosine_dir(f3 w, uint32_t u_phi, uint32_t u_z22) {
 
 __device__ __forceinline__ float clamp01f(float v) { return __saturatef(v); }
 
+// ---- the reference's self-intersection on small spheres ("ACNE") ---------------------
+// Ray.h:67-72 normalises with a FLOAT sqrt, so every direction has |d|^2 = 1 + eps,
+// eps ~ 1e-7.  SettingData.cpp:197-223 assumes a unit direction, so a hit reported at
+// distance t sits at |x - c|^2 = r^2 + t^2 eps: OFF the surface by t^2 eps / 2r, which for
+// r = 0.05, t = 15 is 2e-4.  When that point is inside the sphere (eps < 0), the next,
+// outward ray finds the far root t2 = |c'| / (|b| + sqrt(b^2 + |c'|)) of its own sphere
+// with c' = t^2 eps, b = -r cos(theta); it is accepted when t2 >= 1e-5 (:208-209), i.e. when
+//     -c' >= 2 tau r cos(theta) + tau^2,   tau = 1e-5f.
+// The path then continues from the same point with the normal flipped INWARD and stays
+// inside the sphere.  The r = 1e4 walls never qualify (cos(theta) < 1e-3); 0.05..0.3 spheres
+// do for about a fifth of the bounces and half of the primary hits, which darkens them
+// visibly in the reference's images — so the FP32 path carries c' as explicit lane state:
+// exact for primary hits (from the FP64 pass), and for bounce rays drawn from the
+// distribution the reference's arithmetic produces: eta = |v|^2 - 1 before normalisation
+// (std 5.3e-8, four summed bytes), x = fl32(1 + eta), m = sqrtf(x), eps = eta - 2(m - 1).
+// State: cpsn = c' / (2 tau r) (0 when the normal is flipped: an inward ray takes the
+// ordinary far root), test: cpsn + cos(theta) <= 0.
+#define RTM_ACNE_INV2TAU 5.0000001e4f   // 1 / (2 * (double)1e-5f)
+#define RTM_ACNE_2TAU 1.99999995e-5f
+__device__ __forceinline__ float ref_normalize_eps(uint32_t bits) {
+    const int S = (int)__dp4a(bits, 0x01010101u, 0u);
+    const float eta = (float)(S - 510) * 3.586e-10f;
+    const float m = __fsqrt_rn(1.0f + eta);
+    return eta - 2.0f * (m - 1.0f);
+}
+
 #define RTM_MEGA_THREADS 128
 #define RTM_MEGA_CHUNK 64u  // sub-pixels a warp reserves per global atomic
 
@@ -344,10 +376,11 @@ __device__ __forceinline__ float clamp01f(float v) { return __saturatef(v); }
 // RNG: one Philox2x32-10 call per hit, counter = (sub-pixel, sample<<9 | depth), key
 // from the seed: x -> roulette (32-bit compare against kd*2^32), y -> azimuth,
 // the low bits of x and y -> height.
-template <int N, bool BVH>
+template <int N, bool BVH, bool ACNE>
 __global__ void __launch_bounds__(RTM_MEGA_THREADS, BVH ? 4 : 5) radiance_mega_kernel(RtmPassParams p, float4* __restrict__ records,
                                                                                       RtmCounters* __restrict__ counters, int n_rt,
-                                                                                      RtmBvhDev bvh, RtmMatDev mat) {
+                                                                                      RtmBvhDev bvh, RtmMatDev mat,
+                                                                                      const float* __restrict__ cps0) {
     // brute force: N spheres (0 = runtime n_rt) with their records in shared memory;
     // hierarchy: N = slots of the packed big-sphere test (even, 0..8), records in global memory
     __shared__ SharedScene sh;
@@ -386,6 +419,7 @@ __global__ void __launch_bounds__(RTM_MEGA_THREADS, BVH ? 4 : 5) radiance_mega_k
     // path state
     f3 o = mk(0, 0, 0), w = mk(0, 0, 1), T = mk(1, 1, 1), L = mk(0, 0, 0);
     int id = 0, s = 0, depth = 0;
+    float cpsn = 0.f, Pcpsn = 0.f;   // ACNE: c' / (2 tau r) at the current origin / at the primary hit
 
     unsigned long long rays_ref = 0, traced = 0;
     const unsigned key_mask = p.key_mask;  // 0xFFFFFFF8 from the host: kept in a register for key_pack
@@ -439,6 +473,10 @@ __global__ void __launch_bounds__(RTM_MEGA_THREADS, BVH ? 4 : 5) radiance_mega_k
                     s = s_begin;
                     o = P; id = Pid; w = Pw;
                     T = mk(1, 1, 1); L = mk(e0.x, e0.y, e0.z); depth = 0;
+                    if (ACNE) {
+                        Pcpsn = (wbits & RTM_REC_FLIP) ? 0.f : cps0[ql] * g.w * RTM_ACNE_INV2TAU;
+                        cpsn = Pcpsn;
+                    }
                 }
             }
             const unsigned took = (__popc(need) < avail) ? __popc(need) : avail;
@@ -461,17 +499,38 @@ __global__ void __launch_bounds__(RTM_MEGA_THREADS, BVH ? 4 : 5) radiance_mega_k
                 const f3 d = cosine_dir(w, rnd.y, ((rnd.x & 0xFFFu) << 10) | (rnd.y & 0x3FFu));
                 float t;
                 int id2;
-                if (BVH) id2 = trace_bvh_f32<N / 2>(sh_mask, sh_big, bvh, id, __float_as_int(al.w), o, d, t, key_mask, n_tests, n_nodes);
+                bool selfhit = false;
+                float cosw = 0.f;
+                if (ACNE) {
+                    cosw = dot(w, d);
+                    selfhit = (cpsn + cosw <= 0.f);
+                }
+                if (ACNE && selfhit) {
+                    // SettingData.cpp:208-212: t1 <= 0.001 -> t2 of the sphere the ray stands (just) inside
+                    const float rr = fast_rcp(recs.geo(id).w);
+                    const float q = -cpsn * rr * RTM_ACNE_2TAU, bq = rr * cosw;
+                    t = q * fast_rcp(bq + fast_sqrt(fmaf(bq, bq, q)));
+                    id2 = id;
+                } else if (BVH) id2 = trace_bvh_f32<N / 2>(sh_mask, sh_big, bvh, id, __float_as_int(al.w), o, d, t, key_mask, n_tests, n_nodes);
                 else id2 = trace_f32<N>(sh_mask, n, id, o, d, t, key_mask);
                 ++traced;
                 if (id2 >= 0) {
                     o = mk(fmaf(d.x, t, o.x), fmaf(d.y, t, o.y), fmaf(d.z, t, o.z));  // Renderer.cpp:79
                     const float4 g = recs.geo(id2);
-                    const f3 nn = mk((o.x - g.x) * g.w, (o.y - g.y) * g.w, (o.z - g.z) * g.w);
+                    f3 nn = mk((o.x - g.x) * g.w, (o.y - g.y) * g.w, (o.z - g.z) * g.w);
+                    if (BVH && g.w > 1e-2f) {
+                        // small spheres: t carries an absolute error of ~1e-5 that is not small against
+                        // r = 0.05; put the hit back on the surface and make the normal unit
+                        const float inv = fast_rsqrt(dot(nn, nn));
+                        nn = mk(nn.x * inv, nn.y * inv, nn.z * inv);
+                        const float rr = fast_rcp(g.w);
+                        o = mk(fmaf(rr, nn.x, g.x), fmaf(rr, nn.y, g.y), fmaf(rr, nn.z, g.z));
+                    }
                     const bool flip = !(dot(nn, d) < 0.f);                            // :82-83
                     w = flip ? mk(-nn.x, -nn.y, -nn.z) : nn;
                     id = id2;
                     ++depth;
+                    if (ACNE) cpsn = flip ? 0.f : t * t * ref_normalize_eps(rnd.x ^ (rnd.y * 0x9E3779B9u)) * g.w * RTM_ACNE_INV2TAU;
                     const float4 e2 = recs.emi(id2);
                     L.x = fmaf(T.x, e2.x, L.x); L.y = fmaf(T.y, e2.y, L.y); L.z = fmaf(T.z, e2.z, L.z);
                     end = (__float_as_uint(e2.w) == 0u);   // kd == 0: the next roulette cannot continue
@@ -493,6 +552,7 @@ __global__ void __launch_bounds__(RTM_MEGA_THREADS, BVH ? 4 : 5) radiance_mega_k
                     const float4 e0 = recs.emi(Pid);
                     o = P; id = Pid; w = Pw;
                     T = mk(1, 1, 1); L = mk(e0.x, e0.y, e0.z); depth = 0;
+                    if (ACNE) cpsn = Pcpsn;
                 }
             }
         }
@@ -627,41 +687,48 @@ __global__ void __launch_bounds__(256) fma_peak_kernel(float* __restrict__ sink,
     if (r == 12345.678f) sink[0] = r;
 }
 
+template <int N, bool BVH, bool ACNE>
+void launch_mega2(const RtmPassParams& p, float4* records, RtmCounters* counters, int n_rt, int sm_count, cudaStream_t st,
+                  const RtmBvhDev& bvh, const RtmMatDev& mat, const float* cps0) {
+    int per_sm = 0;
+    cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, radiance_mega_kernel<N, BVH, ACNE>, RTM_MEGA_THREADS, 0);
+    if (per_sm < 1) per_sm = 1;
+    radiance_mega_kernel<N, BVH, ACNE><<<sm_count * per_sm, RTM_MEGA_THREADS, 0, st>>>(p, records, counters, n_rt, bvh, mat, cps0);
+}
+// cps0 != null selects the ACNE instantiation (see ref_normalize_eps)
 template <int N, bool BVH>
 void launch_mega(const RtmPassParams& p, float4* records, RtmCounters* counters, int n_rt, int sm_count, cudaStream_t st,
-                 const RtmBvhDev& bvh = RtmBvhDev{}, const RtmMatDev& mat = RtmMatDev{}) {
-    int per_sm = 0;
-    cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, radiance_mega_kernel<N, BVH>, RTM_MEGA_THREADS, 0);
-    if (per_sm < 1) per_sm = 1;
-    radiance_mega_kernel<N, BVH><<<sm_count * per_sm, RTM_MEGA_THREADS, 0, st>>>(p, records, counters, n_rt, bvh, mat);
+                 const float* cps0, const RtmBvhDev& bvh = RtmBvhDev{}, const RtmMatDev& mat = RtmMatDev{}) {
+    if (cps0) launch_mega2<N, BVH, true>(p, records, counters, n_rt, sm_count, st, bvh, mat, cps0);
+    else launch_mega2<N, BVH, false>(p, records, counters, n_rt, sm_count, st, bvh, mat, nullptr);
 }
 
 }  // namespace
 
 void rtm_launch_radiance_mega(int32_t n, const RtmPassParams& p, float4* records, RtmCounters* counters, int32_t sm_count,
-                              cudaStream_t st) {
+                              const float* cps0, cudaStream_t st) {
     switch (n) {
-        case 1: launch_mega<1, false>(p, records, counters, n, sm_count, st); break;
-        case 2: launch_mega<2, false>(p, records, counters, n, sm_count, st); break;
-        case 3: launch_mega<3, false>(p, records, counters, n, sm_count, st); break;
-        case 4: launch_mega<4, false>(p, records, counters, n, sm_count, st); break;
-        case 5: launch_mega<5, false>(p, records, counters, n, sm_count, st); break;
-        case 6: launch_mega<6, false>(p, records, counters, n, sm_count, st); break;
-        case 7: launch_mega<7, false>(p, records, counters, n, sm_count, st); break;
-        case 8: launch_mega<8, false>(p, records, counters, n, sm_count, st); break;
-        default: launch_mega<0, false>(p, records, counters, n, sm_count, st); break;
+        case 1: launch_mega<1, false>(p, records, counters, n, sm_count, st, cps0); break;
+        case 2: launch_mega<2, false>(p, records, counters, n, sm_count, st, cps0); break;
+        case 3: launch_mega<3, false>(p, records, counters, n, sm_count, st, cps0); break;
+        case 4: launch_mega<4, false>(p, records, counters, n, sm_count, st, cps0); break;
+        case 5: launch_mega<5, false>(p, records, counters, n, sm_count, st, cps0); break;
+        case 6: launch_mega<6, false>(p, records, counters, n, sm_count, st, cps0); break;
+        case 7: launch_mega<7, false>(p, records, counters, n, sm_count, st, cps0); break;
+        case 8: launch_mega<8, false>(p, records, counters, n, sm_count, st, cps0); break;
+        default: launch_mega<0, false>(p, records, counters, n, sm_count, st, cps0); break;
     }
 }
 
 // Hierarchy path: the packed test covers the (padded-to-even) list of big spheres.
 void rtm_launch_radiance_bvh(const RtmBvhDev& bvh, const RtmMatDev& mat, const RtmPassParams& p, float4* records,
-                             RtmCounters* counters, int32_t sm_count, cudaStream_t st) {
+                             RtmCounters* counters, int32_t sm_count, const float* cps0, cudaStream_t st) {
     switch ((bvh.n_big + 1) / 2) {
-        case 0: launch_mega<0, true>(p, records, counters, 0, sm_count, st, bvh, mat); break;
-        case 1: launch_mega<2, true>(p, records, counters, 0, sm_count, st, bvh, mat); break;
-        case 2: launch_mega<4, true>(p, records, counters, 0, sm_count, st, bvh, mat); break;
-        case 3: launch_mega<6, true>(p, records, counters, 0, sm_count, st, bvh, mat); break;
-        default: launch_mega<8, true>(p, records, counters, 0, sm_count, st, bvh, mat); break;
+        case 0: launch_mega<0, true>(p, records, counters, 0, sm_count, st, cps0, bvh, mat); break;
+        case 1: launch_mega<2, true>(p, records, counters, 0, sm_count, st, cps0, bvh, mat); break;
+        case 2: launch_mega<4, true>(p, records, counters, 0, sm_count, st, cps0, bvh, mat); break;
+        case 3: launch_mega<6, true>(p, records, counters, 0, sm_count, st, cps0, bvh, mat); break;
+        default: launch_mega<8, true>(p, records, counters, 0, sm_count, st, cps0, bvh, mat); break;
     }
 }
 

@@ -13,6 +13,7 @@
 #include <dlfcn.h>
 #include <nccl.h>  // types only; the library is dlopen'ed when n_gpus > 1
 
+#include <algorithm>
 #include <chrono>
 #include <cmath>
 #include <cstdarg>
@@ -114,6 +115,7 @@ struct GpuCtx {
     double* image64 = nullptr;
     unsigned char* u8 = nullptr;
     RtmCounters* counters = nullptr;
+    float* cps0 = nullptr;      // per sub-pixel c' at the primary hit (ACNE scenes only)
     float4* d_bvh = nullptr;    // one allocation: nodes | leaf_geo | geo | emi | alb | leaf_id
     RtmBvhDev bvh{};
     RtmMatDev mat{};
@@ -134,6 +136,7 @@ struct rtm_renderer {
     std::vector<GpuCtx> gpus;
     int32_t last_launches = 0;
     bool hits_valid = false;
+    bool acne = false;          // the FP32 path models the reference's self-intersection on small spheres
     bool use_bvh = false;       // closest hit through the hierarchy (bvh.h) instead of the O(N) loop
     RtmBvhHost bvh_host;
     std::vector<float4> mat_geo, mat_emi, mat_alb;
@@ -152,6 +155,7 @@ void free_ctx(GpuCtx& c) {
     if (c.u8) cudaFree(c.u8);
     if (c.counters) cudaFree(c.counters);
     if (c.d_bvh) cudaFree(c.d_bvh);
+    if (c.cps0) cudaFree(c.cps0);
     if (c.h_accum) cudaFreeHost(c.h_accum);
     if (c.ev0) cudaEventDestroy(c.ev0);
     if (c.ev1) cudaEventDestroy(c.ev1);
@@ -199,14 +203,14 @@ int enqueue_pass(rtm_renderer* r, GpuCtx& c, cudaStream_t st, bool want_hits, in
         int rc = ensure_hits(r, c);
         if (rc) return rc;
         if (!c.image64) CU(cudaMalloc(&c.image64, r->n_pix * 3 * sizeof(double)));
-        rtm_launch_primary_f64(c.s64, p, c.hits, nullptr, nullptr, st);
+        rtm_launch_primary_f64(c.s64, p, c.hits, nullptr, nullptr, nullptr, st);
         rtm_launch_head_image(c.s64, p, c.hits, c.image64, c.accum, st);
         *launches += 2;
     } else if (r->opt.precision == RTM_PRECISION_F64) {
         if (want_hits) {
             int rc = ensure_hits(r, c);
             if (rc) return rc;
-            rtm_launch_primary_f64(c.s64, p, c.hits, nullptr, nullptr, st);
+            rtm_launch_primary_f64(c.s64, p, c.hits, nullptr, nullptr, nullptr, st);
             *launches += 1;
         }
         rtm_launch_radiance_f64(c.s64, p, c.records, c.counters, st);
@@ -219,10 +223,10 @@ int enqueue_pass(rtm_renderer* r, GpuCtx& c, cudaStream_t st, bool want_hits, in
         }
         CU(rtm_upload_scene_f32(r->f32, st));
         CU(cudaEventRecord(c.ek[0], st));
-        rtm_launch_primary_f64(c.s64, p, want_hits ? c.hits : nullptr, c.records, c.counters, st);
+        rtm_launch_primary_f64(c.s64, p, want_hits ? c.hits : nullptr, c.records, c.counters, c.cps0, st);
         CU(cudaEventRecord(c.ek[1], st));
-        if (r->use_bvh) rtm_launch_radiance_bvh(c.bvh, c.mat, p, c.records, c.counters, c.sm_count, st);
-        else rtm_launch_radiance_mega(r->n, p, c.records, c.counters, c.sm_count, st);
+        if (r->use_bvh) rtm_launch_radiance_bvh(c.bvh, c.mat, p, c.records, c.counters, c.sm_count, c.cps0, st);
+        else rtm_launch_radiance_mega(r->n, p, c.records, c.counters, c.sm_count, c.cps0, st);
         CU(cudaEventRecord(c.ek[2], st));
         rtm_launch_accumulate(p, c.records, c.accum, st);
         CU(cudaEventRecord(c.ek[3], st));
@@ -423,6 +427,23 @@ int renderer_create(const rtm_scene_desc* sc, const rtm_options* opt_in, rtm_ren
         }
     }
 
+    if (f32_path) {
+        // ACNE (kernels_radiance.cu): the reference re-hits the sphere a ray leaves when
+        // t^2 |eps| >= 2 tau r cos(theta).  With t <= D (extent of the finite part of the scene seen from
+        // the camera), |eps| <= 1.8e-7, tau = 1e-5 this concerns directions with cos(theta) <= 9e-3 D^2 / r;
+        // cosine-weighted, that is a fraction (9e-3 D^2 / r)^2 of the bounces.  Modelled when any
+        // diffuse sphere reaches 1e-4 (the r = 1e4 walls of the Cornell scenes: 6e-7).
+        double D = 0.0;
+        for (int i = 0; i < n; ++i) {
+            if (sc->radius[i] >= 1000.f) continue;
+            const double dx = cx[i] - r->refd[0], dy = cy[i] - r->refd[1], dz = cz[i] - r->refd[2];
+            D = std::max(D, std::sqrt(dx * dx + dy * dy + dz * dz) + (double)sc->radius[i]);
+        }
+        if (D == 0.0) D = 30.0;
+        for (int i = 0; i < n; ++i)
+            if (kd[i] > 0.0 && 9e-3 * D * D / (double)sc->radius[i] > 1e-2) r->acne = true;
+    }
+
     if (use_bvh) {
         if (!rtm_bvh_build(n, sc->position, sc->radius, r->refd, r->bvh_host)) {
             const int d = r->bvh_host.depth;
@@ -515,6 +536,7 @@ int renderer_create(const rtm_scene_desc* sc, const rtm_options* opt_in, rtm_ren
                 c.s64.bvh = c.bvh;
                 for (int k = 0; k < 3; ++k) c.s64.ref[k] = r->refd[k];
             }
+            if (r->acne) CU(cudaMalloc(&c.cps0, r->n_sub * sizeof(float)));
             if (opt.compat == RTM_COMPAT_ABC) CU(cudaMalloc(&c.records, r->n_sub * sizeof(float4)));
             CU(cudaMalloc(&c.accum, r->n_pix * sizeof(float4)));
             CU(cudaMemset(c.accum, 0, r->n_pix * sizeof(float4)));

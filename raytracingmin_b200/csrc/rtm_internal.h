@@ -108,7 +108,7 @@ struct RtmPassParams {
 // ---- launchers implemented by the kernel TUs (all asynchronous on `st`) ----
 void rtm_launch_primary_f64(const RtmSceneF64& sc, const RtmPassParams& p, int32_t* hits /*or null*/,
                             float4* records /*or null*/, RtmCounters* counters /*hierarchy work, or null*/,
-                            cudaStream_t st);
+                            float* cps0 /*or null*/, cudaStream_t st);
 void rtm_launch_head_image(const RtmSceneF64& sc, const RtmPassParams& p, const int32_t* hits,
                            double* image64 /*[H][W][3]*/, float4* accum, cudaStream_t st);
 void rtm_launch_radiance_f64(const RtmSceneF64& sc, const RtmPassParams& p, float4* records,
@@ -117,10 +117,12 @@ void rtm_launch_closest_hit_f64(const RtmSceneF64& sc, uint32_t n, const double*
                                 int32_t* hit, double* t, cudaStream_t st);
 
 cudaError_t rtm_upload_scene_f32(const RtmSceneF32Host& h, cudaStream_t st);
+// cps0: per-sub-pixel c' = |c - P|^2 - r^2 at the primary hit from the FP64 pass, or null when the scene
+// has no sphere small enough for the reference's self-intersection to matter (kernels_radiance.cu: ACNE)
 void rtm_launch_radiance_mega(int32_t n_spheres, const RtmPassParams& p, float4* records, RtmCounters* counters,
-                              int32_t sm_count, cudaStream_t st);
+                              int32_t sm_count, const float* cps0, cudaStream_t st);
 void rtm_launch_radiance_bvh(const RtmBvhDev& bvh, const RtmMatDev& mat, const RtmPassParams& p, float4* records,
-                             RtmCounters* counters, int32_t sm_count, cudaStream_t st);
+                             RtmCounters* counters, int32_t sm_count, const float* cps0, cudaStream_t st);
 void rtm_launch_accumulate(const RtmPassParams& p, const float4* records, float4* accum, cudaStream_t st);
 void rtm_launch_to_u8(const float4* accum, unsigned char* out, uint64_t n_pix, cudaStream_t st);
 void rtm_launch_closest_hit_f32(int32_t n_spheres, const double* refd, uint32_t n, const double* org,
