@@ -217,77 +217,105 @@ struct SharedBig {
     int id[8];
 };
 
+#define RTM_BVH_NONE_DEV 0x7FFFFFFF
+__device__ __forceinline__ bool bvh_is_inner(int node) { return (unsigned)node < 0x7FFFFFFFu; }   // leaves are negative
+
+// Ray state of one lane inside the hierarchy.  best = candidate (root - eps), as in the packed test.
+struct BvhRay {
+    f3 inv, oi;      // 1/d and o/d
+    float best;
+    int hit;         // original sphere index of the current winner, -1 = none
+    int node;        // current node (child code), RTM_BVH_NONE_DEV when the traversal is over
+    int sp;
+};
+
+// the packed test over the big list, then position the lane on the root
 template <int NP>
-__device__ __forceinline__ int trace_bvh_f32(const SelfMask& sm, const SharedBig& big, const RtmBvhDev& bvh, int oid, int oslot,
-                                             f3 o, f3 d, float& t, unsigned key_mask, unsigned& n_tests, unsigned& n_nodes) {
-    float best = FLT_MAX;   // candidate (root - eps)
-    int id = -1;
+__device__ __forceinline__ void bvh_ray_begin(const SelfMask& sm, const SharedBig& big, const RtmBvhDev& bvh, int oslot, f3 o, f3 d,
+                                              unsigned key_mask, BvhRay& r, int* stack, unsigned& n_tests) {
+    r.best = FLT_MAX;
+    r.hit = -1;
     if (NP > 0) {
         const unsigned key = trace_pairs_f32<NP>(sm, oslot, o, d, key_mask);
         if (key < RTM_KEY_INF) {
-            best = __uint_as_float(key & ~7u);
-            id = big.id[key & 7u];
+            r.best = __uint_as_float(key & ~7u);
+            r.hit = big.id[key & 7u];
         }
         n_tests += 2 * NP;
     }
-    int node = bvh.root;
-    if (node != 0x7FFFFFFF) {
-        const f3 inv = mk(fast_rcp(d.x), fast_rcp(d.y), fast_rcp(d.z));
-        const f3 oi = mk(o.x * inv.x, o.y * inv.y, o.z * inv.z);
-        int stack[RTM_BVH_STACK_DEV];
-        int sp = 0;
-        stack[sp++] = 0x7FFFFFFF;
-        while (node != 0x7FFFFFFF) {
-            if (node >= 0) {
-                const float4* q = bvh.nodes + 4 * node;
-                const float4 q0 = __ldg(q), q1 = __ldg(q + 1), q2 = __ldg(q + 2), q3 = __ldg(q + 3);
-                float n0, n1;
-                const float tm = best + 2.f * RTM_T_EPS;
-                const bool h0 = box_test_f32(q0.x, q0.y, q0.z, q0.w, q2.x, q2.y, oi, inv, tm, n0);
-                const bool h1 = box_test_f32(q1.x, q1.y, q1.z, q1.w, q2.z, q2.w, oi, inv, tm, n1);
-                const int c0 = __float_as_int(q3.x), c1 = __float_as_int(q3.y);
-                ++n_nodes;
-                if (h0 && h1) {
-                    const bool swap = n1 < n0;
-                    stack[sp++] = swap ? c0 : c1;
-                    node = swap ? c1 : c0;
-                } else if (h0 || h1) {
-                    node = h0 ? c0 : c1;
-                } else {
-                    node = stack[--sp];
-                }
-            } else {
-                const unsigned code = ~(unsigned)node;
-                const unsigned first = code >> 3, cnt = (code & 7u) + 1u;
-                for (unsigned k = 0; k < cnt; ++k) {
-                    const float4 g = __ldg(bvh.leaf_geo + first + k);
-                    const int sid = __ldg(bvh.leaf_id + first + k);
-                    const f3 p = mk(g.x - o.x, g.y - o.y, g.z - o.z);
-                    const float b = dot(p, d);
-                    // discriminant as r^2 - |p - b d|^2: b^2 - (|p|^2 - r^2) cancels at |p|^2 ~ 400 and
-                    // leaves an error of 3e-4 against r^2 = 2.5e-3 for the smallest spheres
-                    const f3 l = mk(fmaf(-b, d.x, p.x), fmaf(-b, d.y, p.y), fmaf(-b, d.z, p.z));
-                    float D = g.w - dot(l, l);
-                    float cp = dot(p, p) - g.w;
-                    const bool self = (sid == oid);                    // leaving this sphere's surface
-                    cp = self ? 0.f : cp;
-                    D = self ? b * b : D;
-                    const float s = fast_sqrt(D);                      // NaN: the ray misses
-                    const float tq = b + copysignf(s, b);
-                    const float ta = tq - RTM_T_EPS, tb = fmaf(cp, fast_rcp(tq), -RTM_T_EPS);
-                    const float c1 = (ta > 0.f) ? ta : FLT_MAX, c2 = (tb > 0.f) ? tb : FLT_MAX;
-                    const float c = fminf(c1, c2);
-                    const bool ok = (c < best) || (c == best && sid < id);
-                    best = ok ? c : best;
-                    id = ok ? sid : id;
-                }
-                n_tests += cnt;
-                node = stack[--sp];
-            }
-        }
+    r.inv = mk(fast_rcp(d.x), fast_rcp(d.y), fast_rcp(d.z));
+    r.oi = mk(o.x * r.inv.x, o.y * r.inv.y, o.z * r.inv.z);
+    r.node = bvh.root;
+    r.sp = 0;
+    stack[r.sp++] = RTM_BVH_NONE_DEV;
+}
+
+// one inner node: test both children, descend into the nearer one, push the other
+__device__ __forceinline__ void bvh_inner_step(const RtmBvhDev& bvh, BvhRay& r, int* stack) {
+    const float4* q = bvh.nodes + 4 * r.node;
+    const float4 q0 = __ldg(q), q1 = __ldg(q + 1), q2 = __ldg(q + 2), q3 = __ldg(q + 3);
+    float n0, n1;
+    const float tm = r.best + 2.f * RTM_T_EPS;
+    const bool h0 = box_test_f32(q0.x, q0.y, q0.z, q0.w, q2.x, q2.y, r.oi, r.inv, tm, n0);
+    const bool h1 = box_test_f32(q1.x, q1.y, q1.z, q1.w, q2.z, q2.w, r.oi, r.inv, tm, n1);
+    const int c0 = __float_as_int(q3.x), c1 = __float_as_int(q3.y);
+    if (h0 && h1) {
+        const bool swap = n1 < n0;
+        stack[r.sp++] = swap ? c0 : c1;
+        r.node = swap ? c1 : c0;
+    } else if (h0 || h1) {
+        r.node = h0 ? c0 : c1;
+    } else {
+        r.node = stack[--r.sp];
     }
-    t = best + RTM_T_EPS;
-    return id;
+}
+
+// one leaf: 1..4 spheres in the direct form, then pop
+__device__ __forceinline__ void bvh_leaf_step(const RtmBvhDev& bvh, int oid, f3 o, f3 d, BvhRay& r, int* stack, unsigned& n_tests) {
+    const unsigned code = ~(unsigned)r.node;
+    const unsigned first = code >> 3, cnt = (code & 7u) + 1u;
+    for (unsigned k = 0; k < cnt; ++k) {
+        const float4 g = __ldg(bvh.leaf_geo + first + k);
+        const int sid = __ldg(bvh.leaf_id + first + k);
+        const f3 p = mk(g.x - o.x, g.y - o.y, g.z - o.z);
+        const float b = dot(p, d);
+        // discriminant as r^2 - |p - b d|^2: b^2 - (|p|^2 - r^2) cancels at |p|^2 ~ 400 and
+        // leaves an error of 3e-4 against r^2 = 2.5e-3 for the smallest spheres
+        const f3 l = mk(fmaf(-b, d.x, p.x), fmaf(-b, d.y, p.y), fmaf(-b, d.z, p.z));
+        float D = g.w - dot(l, l);
+        float cp = dot(p, p) - g.w;
+        const bool self = (sid == oid);                    // leaving this sphere's surface
+        cp = self ? 0.f : cp;
+        D = self ? b * b : D;
+        const float s = fast_sqrt(D);                      // NaN: the ray misses
+        const float tq = b + copysignf(s, b);
+        const float ta = tq - RTM_T_EPS, tb = fmaf(cp, fast_rcp(tq), -RTM_T_EPS);
+        const float c1 = (ta > 0.f) ? ta : FLT_MAX, c2 = (tb > 0.f) ? tb : FLT_MAX;
+        const float c = fminf(c1, c2);
+        const bool ok = (c < r.best) || (c == r.best && sid < r.hit);
+        r.best = ok ? c : r.best;
+        r.hit = ok ? sid : r.hit;
+    }
+    n_tests += cnt;
+    r.node = stack[--r.sp];
+}
+
+// whole query (test hook; the render kernel interleaves the same steps across its lanes)
+template <int NP>
+__device__ __forceinline__ int trace_bvh_f32(const SelfMask& sm, const SharedBig& big, const RtmBvhDev& bvh, int oid, int oslot,
+                                             f3 o, f3 d, float& t, unsigned key_mask, unsigned& n_tests, unsigned& n_nodes) {
+    BvhRay r;
+    int stack[RTM_BVH_STACK_DEV];
+    bvh_ray_begin<NP>(sm, big, bvh, oslot, o, d, key_mask, r, stack, n_tests);
+    while (r.node != RTM_BVH_NONE_DEV) {
+        while (bvh_is_inner(r.node)) {
+            bvh_inner_step(bvh, r, stack);
+            ++n_nodes;
+        }
+        if (r.node < 0) bvh_leaf_step(bvh, oid, o, d, r, stack, n_tests);
+    }
+    t = r.best + RTM_T_EPS;
+    return r.hit;
 }
 
 // Per-sphere data addressed with a per-lane index (the hit id): shared memory, three
@@ -575,6 +603,233 @@ __global__ void __launch_bounds__(RTM_MEGA_THREADS, BVH ? 4 : 5) radiance_mega_k
     }
 }
 
+// ---- the radiance kernel of the hierarchy path -------------------------------------------
+// Same estimator, same lane-owns-a-sub-pixel work distribution as radiance_mega_kernel, but a
+// closest-hit query now costs ~25 node visits + ~11 sphere tests with a large spread, so "one
+// loop iteration = one bounce" would leave a warp waiting for its longest traversal with the
+// shading code interleaved at 1/32 occupancy (measured: 6.3 of 32 lanes active on average).
+// Here a lane is in one of two phases and the warp runs them as separate, coherent blocks:
+//   S (shade)  standing on a hit: apply a finished ray, roulette, sample the bounce, start the
+//              next ray (or close the sample / the sub-pixel);
+//   T (trace)  walk the hierarchy, while-while: all lanes step through inner nodes until each
+//              holds a leaf, then all test their leaf's spheres.
+// The T block keeps stepping until at least RTM_BVH_S_THRESH lanes have finished their rays;
+// only then is the S block run (for those lanes together), so S code runs at >= 25 % and T code
+// at >= 75 % lane occupancy (Aila & Laine's persistent threads with a refill threshold).
+#define RTM_BVH_S_THRESH 8
+
+template <int NP, bool ACNE>
+__global__ void __launch_bounds__(RTM_MEGA_THREADS, 4) radiance_bvh_kernel(RtmPassParams p, float4* __restrict__ records,
+                                                                           RtmCounters* __restrict__ counters, RtmBvhDev bvh,
+                                                                           RtmMatDev mat, const float* __restrict__ cps0) {
+    __shared__ SelfMask sh_mask;
+    __shared__ SharedBig sh_big;
+    init_selfmask(sh_mask);
+    if (threadIdx.x < 8) sh_big.id[threadIdx.x] = (threadIdx.x < (unsigned)bvh.n_big) ? bvh.big_id[threadIdx.x] : 0;
+    __syncthreads();
+
+    const unsigned lane = threadIdx.x & 31u;
+    const unsigned lt_mask = (1u << lane) - 1u;
+    const unsigned n_sub = (unsigned)p.n_sub;
+    const int s_begin = p.s_begin, s_end = p.s_end;
+    const float inv_norm = p.inv_norm;
+    const unsigned sub_begin = (unsigned)p.sub_begin, sub_count = (unsigned)p.sub_count;
+    const unsigned grid = (unsigned)(p.frame.ss * p.frame.ss);
+    const bool full_grid = (sub_count == grid);
+    const unsigned key_mask = p.key_mask;
+
+    unsigned w_next = 0, w_end = 0;
+    bool have = false, done = false, tracing = false, pending = false;
+    unsigned q = 0, ql = 0;
+    f3 P = mk(0, 0, 0), Pw = mk(0, 0, 1);
+    int Pid = 0;
+    f3 acc = mk(0, 0, 0);
+    f3 o = mk(0, 0, 0), w = mk(0, 0, 1), T = mk(1, 1, 1), L = mk(0, 0, 0), d = mk(0, 0, 1);
+    int id = 0, s = 0, depth = 0;
+    float cpsn = 0.f, Pcpsn = 0.f;
+    uint32_t eps_bits = 0;
+    BvhRay ray;
+    ray.node = RTM_BVH_NONE_DEV;
+    int stack[RTM_BVH_STACK_DEV];
+    unsigned long long rays_ref = 0, traced = 0;
+    unsigned n_tests = 0, n_nodes = 0;
+
+    for (;;) {
+        // ---- refill (warp-uniform): lanes without a sub-pixel take the next ones of the warp's chunk
+        unsigned need = __ballot_sync(0xffffffffu, !have && !done);
+        while (need) {
+            if (w_next == w_end) {
+                unsigned long long start = 0;
+                if (lane == 0) start = atomicAdd(&counters->work_next, (unsigned long long)RTM_MEGA_CHUNK);
+                start = __shfl_sync(0xffffffffu, start, 0);
+                if (start >= (unsigned long long)n_sub) {
+                    if (!have) done = true;
+                    break;
+                }
+                w_next = (unsigned)start;
+                w_end = (start + RTM_MEGA_CHUNK < (unsigned long long)n_sub) ? (unsigned)start + RTM_MEGA_CHUNK : n_sub;
+            }
+            const unsigned avail = w_end - w_next;
+            const unsigned rank = __popc(need & lt_mask);
+            const bool mine = ((need >> lane) & 1u) && rank < avail;
+            if (mine) {
+                ql = w_next + rank;
+                q = full_grid ? ql : (ql / sub_count) * grid + sub_begin + (ql % sub_count);
+                const float4 rec = records[ql];
+                const unsigned wbits = __float_as_uint(rec.w);
+                const unsigned ns = (unsigned)(s_end - s_begin);
+                const bool miss = (wbits == RTM_REC_MISS);
+                Pid = miss ? 0 : (int)(wbits & RTM_REC_IDMASK);
+                const float4 e0 = __ldg(mat.emi + Pid);
+                if (miss || __float_as_uint(e0.w) == 0u) {
+                    float4 out = make_float4(0.f, 0.f, 0.f, 0.f);
+                    if (!miss) {
+                        out.x = clamp01f(e0.x * inv_norm) * (float)ns;
+                        out.y = clamp01f(e0.y * inv_norm) * (float)ns;
+                        out.z = clamp01f(e0.z * inv_norm) * (float)ns;
+                    }
+                    records[ql] = out;
+                    rays_ref += ns;
+                } else {
+                    have = true;
+                    P = mk(rec.x, rec.y, rec.z);
+                    const float4 g = __ldg(mat.geo + Pid);
+                    const float ir = (wbits & RTM_REC_FLIP) ? -g.w : g.w;
+                    Pw = mk((P.x - g.x) * ir, (P.y - g.y) * ir, (P.z - g.z) * ir);
+                    acc = mk(0, 0, 0);
+                    s = s_begin;
+                    o = P; id = Pid; w = Pw;
+                    T = mk(1, 1, 1); L = mk(e0.x, e0.y, e0.z); depth = 0;
+                    if (ACNE) {
+                        Pcpsn = (wbits & RTM_REC_FLIP) ? 0.f : cps0[ql] * g.w * RTM_ACNE_INV2TAU;
+                        cpsn = Pcpsn;
+                    }
+                }
+            }
+            const unsigned took = (__popc(need) < avail) ? __popc(need) : avail;
+            w_next += took;
+            need = __ballot_sync(0xffffffffu, !have && !done && !mine);
+        }
+        const unsigned tr = __ballot_sync(0xffffffffu, tracing);
+        const unsigned sready = __ballot_sync(0xffffffffu, have && !tracing);
+        if ((tr | sready) == 0u) {
+            if (__all_sync(0xffffffffu, done)) break;
+            continue;
+        }
+
+        // ---- S block
+        if ((tr == 0u || __popc(sready) >= RTM_BVH_S_THRESH) && have && !tracing) {
+            // a finished ray is applied to the path; returns true when the path ends there
+            auto apply_hit = [&](int id2, float t) -> bool {
+                if (id2 < 0) return true;                                            // miss: Renderer.cpp:116
+                o = mk(fmaf(d.x, t, o.x), fmaf(d.y, t, o.y), fmaf(d.z, t, o.z));     // :79
+                const float4 g = __ldg(mat.geo + id2);
+                f3 nn = mk((o.x - g.x) * g.w, (o.y - g.y) * g.w, (o.z - g.z) * g.w);
+                if (g.w > 1e-2f) {
+                    // small spheres: t carries an absolute error of ~1e-5 that is not small against
+                    // r = 0.05; put the hit back on the surface and make the normal unit
+                    const float inv = fast_rsqrt(dot(nn, nn));
+                    nn = mk(nn.x * inv, nn.y * inv, nn.z * inv);
+                    const float rr = fast_rcp(g.w);
+                    o = mk(fmaf(rr, nn.x, g.x), fmaf(rr, nn.y, g.y), fmaf(rr, nn.z, g.z));
+                }
+                const bool flip = !(dot(nn, d) < 0.f);                               // :82-83
+                w = flip ? mk(-nn.x, -nn.y, -nn.z) : nn;
+                id = id2;
+                ++depth;
+                if (ACNE) cpsn = flip ? 0.f : t * t * ref_normalize_eps(eps_bits) * g.w * RTM_ACNE_INV2TAU;
+                const float4 e2 = __ldg(mat.emi + id2);
+                L.x = fmaf(T.x, e2.x, L.x); L.y = fmaf(T.y, e2.y, L.y); L.z = fmaf(T.z, e2.z, L.z);
+                return __float_as_uint(e2.w) == 0u;                                  // kd == 0: the next roulette cannot continue
+            };
+            bool end = false;
+            if (pending) {
+                pending = false;
+                end = apply_hit(ray.hit, ray.best + RTM_T_EPS);
+            }
+            for (;;) {
+                if (!end) {
+                    const uint2 rnd = rtm_philox2x32_10(make_uint2(q, ((unsigned)s << 9) | (unsigned)depth), p.rk);
+                    const float4 em = __ldg(mat.emi + id);
+                    end = !((rnd.x < __float_as_uint(em.w)) && (depth + 1 < p.max_depth));   // Renderer.cpp:78
+                    if (!end) {
+                        const float4 al = __ldg(mat.alb + id);
+                        T.x *= al.x; T.y *= al.y; T.z *= al.z;                               // colorKD
+                        d = cosine_dir(w, rnd.y, ((rnd.x & 0xFFFu) << 10) | (rnd.y & 0x3FFu));
+                        eps_bits = rnd.x ^ (rnd.y * 0x9E3779B9u);
+                        ++traced;
+                        if (ACNE) {
+                            const float cosw = dot(w, d);
+                            if (cpsn + cosw <= 0.f) {
+                                // SettingData.cpp:208-212: the far root of the sphere the ray stands (just) inside
+                                const float rr = fast_rcp(__ldg(mat.geo + id).w);
+                                const float qq = -cpsn * rr * RTM_ACNE_2TAU, bq = rr * cosw;
+                                end = apply_hit(id, qq * fast_rcp(bq + fast_sqrt(fmaf(bq, bq, qq))));
+                                continue;
+                            }
+                        }
+                        bvh_ray_begin<NP>(sh_mask, sh_big, bvh, __float_as_int(al.w), o, d, key_mask, ray, stack, n_tests);
+                        if (ray.node == RTM_BVH_NONE_DEV) {
+                            end = apply_hit(ray.hit, ray.best + RTM_T_EPS);
+                            continue;
+                        }
+                        tracing = true;
+                        break;
+                    }
+                }
+                // the sample is complete: Renderer.cpp:240-242
+                acc.x += clamp01f(L.x * inv_norm);
+                acc.y += clamp01f(L.y * inv_norm);
+                acc.z += clamp01f(L.z * inv_norm);
+                ++s;
+                if (s == s_end) {
+                    records[ql] = make_float4(acc.x, acc.y, acc.z, 0.f);
+                    rays_ref += (unsigned)(s_end - s_begin);
+                    have = false;
+                    break;
+                }
+                const float4 e0 = __ldg(mat.emi + Pid);
+                o = P; id = Pid; w = Pw;
+                T = mk(1, 1, 1); L = mk(e0.x, e0.y, e0.z); depth = 0;
+                if (ACNE) cpsn = Pcpsn;
+                end = false;
+            }
+        }
+
+        // ---- T block: while-while until enough lanes are ready for the S block
+        unsigned still = __ballot_sync(0xffffffffu, tracing);
+        while (still) {
+            while (tracing && bvh_is_inner(ray.node)) {
+                bvh_inner_step(bvh, ray, stack);
+                ++n_nodes;
+            }
+            if (tracing && ray.node < 0) bvh_leaf_step(bvh, id, o, d, ray, stack, n_tests);
+            if (tracing && ray.node == RTM_BVH_NONE_DEV) {
+                tracing = false;
+                pending = true;
+            }
+            still = __ballot_sync(0xffffffffu, tracing);
+            const unsigned ready = __ballot_sync(0xffffffffu, !tracing && !done);
+            if (__popc(ready) >= RTM_BVH_S_THRESH) break;
+        }
+    }
+
+    rays_ref += traced;
+    unsigned long long tests = n_tests, nodes = n_nodes;
+    for (int off = 16; off > 0; off >>= 1) {
+        rays_ref += __shfl_down_sync(0xffffffffu, rays_ref, off);
+        traced += __shfl_down_sync(0xffffffffu, traced, off);
+        tests += __shfl_down_sync(0xffffffffu, tests, off);
+        nodes += __shfl_down_sync(0xffffffffu, nodes, off);
+    }
+    if (lane == 0) {
+        atomicAdd(&counters->rays_ref, rays_ref);
+        atomicAdd(&counters->rays_traced, traced);
+        atomicAdd(&counters->tests, tests);
+        atomicAdd(&counters->nodes, nodes);
+    }
+}
+
 // ---- accumulate: sub-pixel sums -> pixel, coalesced float4 in and out ---------
 // records float4[n_pix][g] (g = ss*ss) -> accum float4[n_pix].  For power-of-two
 // g <= 32 one lane per record and a butterfly over each group of g lanes.
@@ -721,14 +976,31 @@ void rtm_launch_radiance_mega(int32_t n, const RtmPassParams& p, float4* records
 }
 
 // Hierarchy path: the packed test covers the (padded-to-even) list of big spheres.
+namespace {
+template <int NP>
+void launch_bvh(const RtmBvhDev& bvh, const RtmMatDev& mat, const RtmPassParams& p, float4* records, RtmCounters* counters,
+                int sm_count, const float* cps0, cudaStream_t st) {
+    int per_sm = 0;
+    if (cps0) {
+        cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, radiance_bvh_kernel<NP, true>, RTM_MEGA_THREADS, 0);
+        if (per_sm < 1) per_sm = 1;
+        radiance_bvh_kernel<NP, true><<<sm_count * per_sm, RTM_MEGA_THREADS, 0, st>>>(p, records, counters, bvh, mat, cps0);
+    } else {
+        cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, radiance_bvh_kernel<NP, false>, RTM_MEGA_THREADS, 0);
+        if (per_sm < 1) per_sm = 1;
+        radiance_bvh_kernel<NP, false><<<sm_count * per_sm, RTM_MEGA_THREADS, 0, st>>>(p, records, counters, bvh, mat, nullptr);
+    }
+}
+}  // namespace
+
 void rtm_launch_radiance_bvh(const RtmBvhDev& bvh, const RtmMatDev& mat, const RtmPassParams& p, float4* records,
                              RtmCounters* counters, int32_t sm_count, const float* cps0, cudaStream_t st) {
     switch ((bvh.n_big + 1) / 2) {
-        case 0: launch_mega<0, true>(p, records, counters, 0, sm_count, st, cps0, bvh, mat); break;
-        case 1: launch_mega<2, true>(p, records, counters, 0, sm_count, st, cps0, bvh, mat); break;
-        case 2: launch_mega<4, true>(p, records, counters, 0, sm_count, st, cps0, bvh, mat); break;
-        case 3: launch_mega<6, true>(p, records, counters, 0, sm_count, st, cps0, bvh, mat); break;
-        default: launch_mega<8, true>(p, records, counters, 0, sm_count, st, cps0, bvh, mat); break;
+        case 0: launch_bvh<0>(bvh, mat, p, records, counters, sm_count, cps0, st); break;
+        case 1: launch_bvh<1>(bvh, mat, p, records, counters, sm_count, cps0, st); break;
+        case 2: launch_bvh<2>(bvh, mat, p, records, counters, sm_count, cps0, st); break;
+        case 3: launch_bvh<3>(bvh, mat, p, records, counters, sm_count, cps0, st); break;
+        default: launch_bvh<4>(bvh, mat, p, records, counters, sm_count, cps0, st); break;
     }
 }
 
