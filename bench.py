@@ -201,7 +201,7 @@ def run_gpu_arm(args):
 
     # device-resident handle: the library writes its partial framebuffer straight into a
     # torch tensor (the NCCL send buffer); no host sync between the last kernel and the reduce.
-    r = rtm.Renderer(sc, device=local, seed=0x5EED, **plan)
+    r = rtm.Renderer(sc, device=local, seed=0x5EED, variant=args.variant, **plan)
     accum = torch.zeros((sc.height, sc.width, 4), dtype=torch.float32, device=dev)
     r.set_accum_buffer(accum.data_ptr())
     stream = torch.cuda.current_stream()
@@ -297,6 +297,7 @@ def run_gpu_arm(args):
             "data": "synthetic",
             "config": {"workload": wl["name"], "scene": wl["scene"], "width": sc.width, "height": sc.height,
                        "samples": sc.samples, "superSamples": sc.superSamples, "spp": sc.spp, "n_spheres": sc.n,
+                       "variant": args.variant,
                        "closest_hit": "brute force (packed pairs)" if sc.n <= 64 else
                                       f"hierarchy: {st.sphere_tests / max(1, st.rays_traced):.1f} sphere tests + "
                                       f"{st.bvh_nodes / max(1, st.rays_traced):.1f} nodes per traced ray",
@@ -313,7 +314,8 @@ def run_gpu_arm(args):
             "kernel_ms": {"primary_f64": kms[0], "radiance_mega": kms[1], "accumulate": kms[2]},
             "roofline": {"bound": "fp32", "achieved": achieved, "peak": fp32_peak, "unit": "TFLOP/s",
                          "frac": achieved / fp32_peak if fp32_peak else None, "traffic": None,
-                         "kernel": "radiance_mega_kernel",
+                         "kernel": ("radiance_mega_kernel" if sc.n <= 64 else "radiance_bvh_kernel") if args.variant == "mega"
+                                   else "wf_shade_kernel + wf_extend_*_kernel (all waves)",
                          "peak_source": f"FP32 FMA-chain microbenchmark run live on this GPU (implied {implied_mhz:.0f} MHz); "
                                         "MEASURED_PEAKS.json holds no FP32 figure",
                          "flops_per_launch": f_kernel, "whole_pass_tflops": f_total / (ms_step * 1e-3) / 1e12,
@@ -338,6 +340,8 @@ def main():
     ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
     ap.add_argument("--workload", default="c4", choices=sorted(WORKLOADS))
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--variant", default="mega", choices=["mega", "wavefront"],
+                    help="kernel organisation of the FP32 bounce loop (DESIGN.md: megakernel vs wavefront)")
     args = ap.parse_args()
     if args.impl == "reference":
         return run_reference_arm(args)

@@ -616,10 +616,18 @@ __global__ void __launch_bounds__(RTM_MEGA_THREADS, BVH ? 4 : 5) radiance_mega_k
 // The T block keeps stepping until at least RTM_BVH_S_THRESH lanes have finished their rays;
 // only then is the S block run (for those lanes together), so S code runs at >= 25 % and T code
 // at >= 75 % lane occupancy (Aila & Laine's persistent threads with a refill threshold).
-#define RTM_BVH_S_THRESH 8
+#ifndef RTM_BVH_S_THRESH
+#define RTM_BVH_S_THRESH 16
+#endif
+#ifndef RTM_BVH_BURST
+#define RTM_BVH_BURST 8
+#endif
+#ifndef RTM_BVH_MINBLOCKS
+#define RTM_BVH_MINBLOCKS 6
+#endif
 
 template <int NP, bool ACNE>
-__global__ void __launch_bounds__(RTM_MEGA_THREADS, 4) radiance_bvh_kernel(RtmPassParams p, float4* __restrict__ records,
+__global__ void __launch_bounds__(RTM_MEGA_THREADS, RTM_BVH_MINBLOCKS) radiance_bvh_kernel(RtmPassParams p, float4* __restrict__ records,
                                                                            RtmCounters* __restrict__ counters, RtmBvhDev bvh,
                                                                            RtmMatDev mat, const float* __restrict__ cps0) {
     __shared__ SelfMask sh_mask;
@@ -799,7 +807,10 @@ __global__ void __launch_bounds__(RTM_MEGA_THREADS, 4) radiance_bvh_kernel(RtmPa
         // ---- T block: while-while until enough lanes are ready for the S block
         unsigned still = __ballot_sync(0xffffffffu, tracing);
         while (still) {
-            while (tracing && bvh_is_inner(ray.node)) {
+            // at most RTM_BVH_BURST inner nodes per round: a lane on its long first descent must not
+            // keep the lanes that hop between neighbouring leaves (2-3 nodes apart) waiting
+#pragma unroll 1
+            for (int k = 0; k < RTM_BVH_BURST && tracing && bvh_is_inner(ray.node); ++k) {
                 bvh_inner_step(bvh, ray, stack);
                 ++n_nodes;
             }
@@ -972,6 +983,54 @@ void rtm_launch_radiance_mega(int32_t n, const RtmPassParams& p, float4* records
         case 7: launch_mega<7, false>(p, records, counters, n, sm_count, st, cps0); break;
         case 8: launch_mega<8, false>(p, records, counters, n, sm_count, st, cps0); break;
         default: launch_mega<0, false>(p, records, counters, n, sm_count, st, cps0); break;
+    }
+}
+
+// ---- wavefront variant -------------------------------------------------------------------
+namespace {
+#include "kernels_wavefront.cuh"
+
+template <int N, bool BVH>
+void launch_wf_shade(const RtmBvhDev& bvh, const RtmMatDev& mat, const RtmPassParams& p, float4* records, RtmCounters* counters,
+                     int n_rt, const float* cps0, const RtmWaveDev& wv, int wave, cudaStream_t st) {
+    const unsigned g = (unsigned)((wv.n_slots + 127) / 128);
+    if (cps0) wf_shade_kernel<N, BVH, true><<<g, 128, 0, st>>>(p, records, counters, n_rt, bvh, mat, cps0, wv, wave);
+    else wf_shade_kernel<N, BVH, false><<<g, 128, 0, st>>>(p, records, counters, n_rt, bvh, mat, nullptr, wv, wave);
+}
+}  // namespace
+
+void rtm_launch_wf_shade(int32_t n, bool use_bvh, const RtmBvhDev& bvh, const RtmMatDev& mat, const RtmPassParams& p,
+                         float4* records, RtmCounters* counters, const float* cps0, const RtmWaveDev& wv, int32_t wave,
+                         cudaStream_t st) {
+    if (use_bvh) {
+        switch ((bvh.n_big + 1) / 2) {
+            case 0: launch_wf_shade<0, true>(bvh, mat, p, records, counters, 0, cps0, wv, wave, st); break;
+            case 1: launch_wf_shade<2, true>(bvh, mat, p, records, counters, 0, cps0, wv, wave, st); break;
+            case 2: launch_wf_shade<4, true>(bvh, mat, p, records, counters, 0, cps0, wv, wave, st); break;
+            case 3: launch_wf_shade<6, true>(bvh, mat, p, records, counters, 0, cps0, wv, wave, st); break;
+            default: launch_wf_shade<8, true>(bvh, mat, p, records, counters, 0, cps0, wv, wave, st); break;
+        }
+        return;
+    }
+    // brute force: the shade kernel only needs the per-sphere records (shared memory, any n <= 256)
+    launch_wf_shade<0, false>(bvh, mat, p, records, counters, n, cps0, wv, wave, st);
+}
+
+void rtm_launch_wf_extend(int32_t n, bool use_bvh, const RtmBvhDev& bvh, const RtmWaveDev& wv, int32_t wave, RtmCounters* counters,
+                          int32_t sm_count, cudaStream_t st) {
+    if (use_bvh) {
+        int per_sm = 0;
+        cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, wf_extend_bvh_kernel, 128, 0);
+        if (per_sm < 1) per_sm = 1;
+        wf_extend_bvh_kernel<<<sm_count * per_sm, 128, 0, st>>>(bvh, wv, wave, counters);
+        return;
+    }
+    const unsigned g = (unsigned)((wv.n_slots + 127) / 128);
+    switch (n) {
+#define RTM_CASE(K) case K: wf_extend_brute_kernel<K><<<g, 128, 0, st>>>(wv, wave, n, 0xFFFFFFF8u, counters); break
+        RTM_CASE(1); RTM_CASE(2); RTM_CASE(3); RTM_CASE(4); RTM_CASE(5); RTM_CASE(6); RTM_CASE(7); RTM_CASE(8);
+#undef RTM_CASE
+        default: wf_extend_brute_kernel<0><<<g, 128, 0, st>>>(wv, wave, n, 0xFFFFFFF8u, counters); break;
     }
 }
 

@@ -116,6 +116,10 @@ struct GpuCtx {
     unsigned char* u8 = nullptr;
     RtmCounters* counters = nullptr;
     float* cps0 = nullptr;      // per sub-pixel c' at the primary hit (ACNE scenes only)
+    float4* d_wave = nullptr;   // wavefront variant: one allocation behind `wv`
+    RtmWaveDev wv{};
+    unsigned* h_live = nullptr; // pinned: wv.ctrl[3] read back between batches of waves
+    int32_t waves = 0;          // waves of the last wavefront pass
     float4* d_bvh = nullptr;    // one allocation: nodes | leaf_geo | geo | emi | alb | leaf_id
     RtmBvhDev bvh{};
     RtmMatDev mat{};
@@ -156,6 +160,8 @@ void free_ctx(GpuCtx& c) {
     if (c.counters) cudaFree(c.counters);
     if (c.d_bvh) cudaFree(c.d_bvh);
     if (c.cps0) cudaFree(c.cps0);
+    if (c.d_wave) cudaFree(c.d_wave);
+    if (c.h_live) cudaFreeHost(c.h_live);
     if (c.h_accum) cudaFreeHost(c.h_accum);
     if (c.ev0) cudaEventDestroy(c.ev0);
     if (c.ev1) cudaEventDestroy(c.ev1);
@@ -225,7 +231,23 @@ int enqueue_pass(rtm_renderer* r, GpuCtx& c, cudaStream_t st, bool want_hits, in
         CU(cudaEventRecord(c.ek[0], st));
         rtm_launch_primary_f64(c.s64, p, want_hits ? c.hits : nullptr, c.records, c.counters, c.cps0, st);
         CU(cudaEventRecord(c.ek[1], st));
-        if (r->use_bvh) rtm_launch_radiance_bvh(c.bvh, c.mat, p, c.records, c.counters, c.sm_count, c.cps0, st);
+        if (r->opt.variant == RTM_VARIANT_WAVEFRONT) {
+            // waves until a shade kernel queues no ray; the host looks at the device flag every 32 waves
+            // (the only host synchronisations of the pass: this variant is not fully asynchronous)
+            CU(cudaMemsetAsync(c.wv.ctrl, 0, 4 * sizeof(unsigned), st));
+            int wave = 0;
+            for (;;) {
+                for (int k = 0; k < 32; ++k, ++wave) {
+                    rtm_launch_wf_shade(r->n, r->use_bvh, c.bvh, c.mat, p, c.records, c.counters, c.cps0, c.wv, wave, st);
+                    rtm_launch_wf_extend(r->n, r->use_bvh, c.bvh, c.wv, wave, c.counters, c.sm_count, st);
+                }
+                *launches += 64;
+                CU(cudaMemcpyAsync(c.h_live, c.wv.ctrl + 3, sizeof(unsigned), cudaMemcpyDeviceToHost, st));
+                CU(cudaStreamSynchronize(st));
+                if (*c.h_live != (unsigned)wave) break;   // the last wave of the batch queued nothing
+            }
+            c.waves = wave;
+        } else if (r->use_bvh) rtm_launch_radiance_bvh(c.bvh, c.mat, p, c.records, c.counters, c.sm_count, c.cps0, st);
         else rtm_launch_radiance_mega(r->n, p, c.records, c.counters, c.sm_count, c.cps0, st);
         CU(cudaEventRecord(c.ek[2], st));
         rtm_launch_accumulate(p, c.records, c.accum, st);
@@ -327,8 +349,10 @@ int renderer_create(const rtm_scene_desc* sc, const rtm_options* opt_in, rtm_ren
     const bool full_grid = (opt.sub_end - opt.sub_begin) == sc->superSamples * sc->superSamples;
     if (!full_grid && (opt.compat == RTM_COMPAT_HEAD || opt.n_gpus > 1))
         return fail(RTM_E_UNSUPPORTED, "sub-pixel slices need COMPAT_ABC and one GPU per handle");
-    if (opt.variant != RTM_VARIANT_MEGA) return fail(RTM_E_UNSUPPORTED, "variant %d not built", opt.variant);
+    if (opt.variant != RTM_VARIANT_MEGA && opt.variant != RTM_VARIANT_WAVEFRONT) return fail(RTM_E_INVALID, "bad variant %d", opt.variant);
     const bool f32_path = (opt.compat == RTM_COMPAT_ABC && opt.precision == RTM_PRECISION_F32);
+    if (opt.variant == RTM_VARIANT_WAVEFRONT && (!f32_path || opt.n_gpus > 1))
+        return fail(RTM_E_UNSUPPORTED, "the wavefront variant exists for COMPAT_ABC + PRECISION_F32 with one GPU per handle");
     if (opt.accel != RTM_ACCEL_AUTO && opt.accel != RTM_ACCEL_BRUTE && opt.accel != RTM_ACCEL_BVH)
         return fail(RTM_E_INVALID, "bad accel %d", opt.accel);
     const bool use_bvh = opt.accel == RTM_ACCEL_BVH || (opt.accel == RTM_ACCEL_AUTO && sc->n_spheres > 64);
@@ -537,6 +561,25 @@ int renderer_create(const rtm_scene_desc* sc, const rtm_options* opt_in, rtm_ren
                 for (int k = 0; k < 3; ++k) c.s64.ref[k] = r->refd[k];
             }
             if (r->acne) CU(cudaMalloc(&c.cps0, r->n_sub * sizeof(float)));
+            if (opt.variant == RTM_VARIANT_WAVEFRONT) {
+                // path slots: 8 resident warps' worth per SM partition x 4, at most one per sub-pixel
+                uint64_t slots = (uint64_t)c.sm_count * 2048ull * 4ull;
+                if (slots > r->n_sub) slots = r->n_sub;
+                slots = (slots + 127) / 128 * 128;
+                const size_t per_slot4 = 8;   // a0..a6, ray
+                const size_t total4 = slots * per_slot4 + slots / 2 /*hit: float2*/ + 2 * (slots / 4) /*queues*/ + 4;
+                CU(cudaMalloc(&c.d_wave, total4 * sizeof(float4)));
+                float4* d = c.d_wave;
+                RtmWaveDev& w = c.wv;
+                w.a0 = d; d += slots; w.a1 = d; d += slots; w.a2 = d; d += slots; w.a3 = d; d += slots;
+                w.a4 = d; d += slots; w.a5 = d; d += slots; w.a6 = d; d += slots; w.ray = d; d += slots;
+                w.hit = (float2*)d; d += slots / 2;
+                w.queue[0] = (int32_t*)d; d += slots / 4;
+                w.queue[1] = (int32_t*)d; d += slots / 4;
+                w.ctrl = (unsigned*)d;
+                w.n_slots = (int32_t)slots;
+                CU(cudaMallocHost(&c.h_live, sizeof(unsigned)));
+            }
             if (opt.compat == RTM_COMPAT_ABC) CU(cudaMalloc(&c.records, r->n_sub * sizeof(float4)));
             CU(cudaMalloc(&c.accum, r->n_pix * sizeof(float4)));
             CU(cudaMemset(c.accum, 0, r->n_pix * sizeof(float4)));

@@ -105,6 +105,24 @@ struct RtmPassParams {
     int32_t sub_begin, sub_count;  // slice of the ss*ss sub-pixel grid
 };
 
+// Wavefront variant (RTM_VARIANT_WAVEFRONT): path state of `n_slots` concurrent sub-pixels in
+// global memory, one wave = shade kernel (apply hit, roulette, sample, emit ray) + extend kernel
+// (closest hit for every queued ray).  All arrays are per slot.
+struct RtmWaveDev {
+    float4* a0;        // o.xyz, id
+    float4* a1;        // w.xyz (oriented normal), cpsn
+    float4* a2;        // T.xyz, s << 10 | depth
+    float4* a3;        // L.xyz, flags (0 empty, 1 sub-pixel in flight, 2 + ray pending)
+    float4* a4;        // acc.xyz, ql
+    float4* a5;        // P.xyz, Pid             (constant while the slot holds a sub-pixel)
+    float4* a6;        // Pw.xyz, Pcpsn
+    float4* ray;       // d.xyz, -
+    float2* hit;       // t, hit id (shade seeds it with the big-sphere result on the hierarchy path)
+    int32_t* queue[2]; // slots with a pending ray, per wave parity
+    unsigned* ctrl;    // [0],[1] queue lengths per parity; [2] extend's fetch cursor; [3] 1 + last wave that queued a ray
+    int32_t n_slots;
+};
+
 // ---- launchers implemented by the kernel TUs (all asynchronous on `st`) ----
 void rtm_launch_primary_f64(const RtmSceneF64& sc, const RtmPassParams& p, int32_t* hits /*or null*/,
                             float4* records /*or null*/, RtmCounters* counters /*hierarchy work, or null*/,
@@ -123,6 +141,12 @@ void rtm_launch_radiance_mega(int32_t n_spheres, const RtmPassParams& p, float4*
                               int32_t sm_count, const float* cps0, cudaStream_t st);
 void rtm_launch_radiance_bvh(const RtmBvhDev& bvh, const RtmMatDev& mat, const RtmPassParams& p, float4* records,
                              RtmCounters* counters, int32_t sm_count, const float* cps0, cudaStream_t st);
+// one wave of the wavefront variant; `wave` counts from 0 (its parity selects the queue)
+void rtm_launch_wf_shade(int32_t n_spheres, bool use_bvh, const RtmBvhDev& bvh, const RtmMatDev& mat, const RtmPassParams& p,
+                         float4* records, RtmCounters* counters, const float* cps0, const RtmWaveDev& wv, int32_t wave,
+                         cudaStream_t st);
+void rtm_launch_wf_extend(int32_t n_spheres, bool use_bvh, const RtmBvhDev& bvh, const RtmWaveDev& wv, int32_t wave,
+                          RtmCounters* counters, int32_t sm_count, cudaStream_t st);
 void rtm_launch_accumulate(const RtmPassParams& p, const float4* records, float4* accum, cudaStream_t st);
 void rtm_launch_to_u8(const float4* accum, unsigned char* out, uint64_t n_pix, cudaStream_t st);
 void rtm_launch_closest_hit_f32(int32_t n_spheres, const double* refd, uint32_t n, const double* org,

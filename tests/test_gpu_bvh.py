@@ -183,3 +183,30 @@ def test_bvh_deterministic_and_slices_add_up(synth):
         rays += res.stats.rays
     assert rays == full.stats.rays
     assert np.allclose(parts, full.image, rtol=2e-6, atol=1e-7)
+
+
+# ---------------- wavefront variant (same estimator, state in global memory) ----------------
+@pytest.mark.parametrize("which", ["cornell", "random200_brute", "random200_bvh", "synth10k"])
+def test_wavefront_matches_megakernel(scene_path, synth, which):
+    if which == "cornell":
+        sc, kw = rtm.load_scene(scene_path("cornellBox"), "abc").with_dims(96, 50, 8, 2), {}
+    elif which == "synth10k":
+        sc, kw = synth.with_dims(96, 54, 16, 1), {}
+    else:
+        sc = rtm.random_scene(21, 200, width=64, height=36, samples=32, superSamples=1)
+        kw = dict(accel="brute" if which.endswith("brute") else "bvh")
+    with rtm.Renderer(sc, seed=9, **kw) as r:
+        a = r.render(want_hits=True)
+    with rtm.Renderer(sc, seed=9, variant="wavefront", **kw) as r:
+        b = r.render(want_hits=True)
+        b2 = r.render()
+    assert np.array_equal(a.hits, b.hits)
+    assert np.array_equal(b.image, b2.image)                       # deterministic
+    assert b.stats.samples == a.stats.samples
+    # same RNG keys and the same formulas: the paths coincide except where a rounding difference between
+    # the two compilations flips a roulette/closest-hit decision
+    assert abs(b.stats.rays - a.stats.rays) <= 2e-3 * a.stats.rays, (a.stats.rays, b.stats.rays)
+    ia, ib = a.image.astype(np.float64), b.image.astype(np.float64)
+    assert abs(ia.mean() - ib.mean()) <= 5e-3 * ia.mean()
+    same = np.isclose(ia, ib, rtol=1e-4, atol=1e-6).all(axis=-1).mean()
+    assert same > 0.9, same
