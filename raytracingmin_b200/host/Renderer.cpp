@@ -29,6 +29,7 @@ void Renderer::Render(std::string fileName) {
     opt.device = options.device; opt.n_gpus = options.n_gpus;
     opt.compat = (options.compat == Compat::Head) ? RTM_COMPAT_HEAD : RTM_COMPAT_ABC;
     opt.precision = options.precision; opt.max_depth = options.max_depth; opt.seed = options.seed;
+    opt.accel = options.accel; opt.variant = options.variant;
 
     rtm_renderer* r = nullptr;
     if (renderer_create(&sc, &opt, &r) != RTM_OK) throw std::runtime_error(std::string("renderer_create: ") + renderer_last_error());
@@ -51,6 +52,7 @@ void Renderer::Render(std::string fileName) {
     if (!options.quiet) std::cout << data.height << " / " << data.height << std::endl;
     stats.samples = st.samples; stats.rays = st.rays; stats.device_ms = st.device_ms; stats.e2e_ms = st.e2e_ms;
     stats.kernel_launches = st.kernel_launches; stats.n_gpus = st.n_gpus;
+    stats.sphere_tests = st.sphere_tests; stats.bvh_nodes = st.bvh_nodes;
 
     // src/Renderer.cpp:256-257: JPEG quality 60 and BMP, same names
     if (!imgw::write_jpg(fileName + ".jpg", image8.data(), data.width, data.height, 60))

@@ -16,13 +16,15 @@ struct RenderOptions {           // everything the reference does not have; defa
     int device = 0, n_gpus = 1;
     int precision = 0;           // RTM_PRECISION_F32
     int max_depth = 0;
+    int accel = 0;               // RTM_ACCEL_AUTO: brute force up to 64 spheres, the hierarchy beyond
+    int variant = 0;             // RTM_VARIANT_MEGA (1 = wavefront, kept for comparison)
     uint64_t seed = 0x5EED;
     bool want_hits = false;      // keep the primary-hit map (int32[H][W][ss][ss])
     bool quiet = false;
 };
 
 struct RenderStats {
-    uint64_t samples = 0, rays = 0;
+    uint64_t samples = 0, rays = 0, sphere_tests = 0, bvh_nodes = 0;
     double device_ms = 0, e2e_ms = 0;
     int kernel_launches = 0, n_gpus = 0;
 };

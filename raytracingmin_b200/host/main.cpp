@@ -36,6 +36,7 @@ void usage() {
               << "-sampleJson : write the sample scene file settingData.json and exit\n"
               << "-json <file> : scene file to render (default settingData.json)\n"
               << "--compat=abc|head  --gpus=N  --device=N  --seed=N  --precision=f32|f64  --max-depth=N\n"
+              << "--accel=auto|brute|bvh  --variant=mega|wavefront\n"
               << "--width=N --height=N --samples=N --superSamples=N : override the file's settings\n"
               << "--out=<name> : output base name (default result)  --dump-hits=<file>  --stats  --quiet\n";
 }
@@ -64,6 +65,8 @@ int main(int argc, char* argv[]) {
         else if (opt_value(a, "--seed", v)) ro.seed = std::strtoull(v.c_str(), nullptr, 0);
         else if (opt_value(a, "--precision", v)) ro.precision = (v == "f64") ? 1 : 0;
         else if (opt_value(a, "--max-depth", v)) ro.max_depth = std::atoi(v.c_str());
+        else if (opt_value(a, "--accel", v)) ro.accel = (v == "brute") ? 1 : (v == "bvh") ? 2 : 0;
+        else if (opt_value(a, "--variant", v)) ro.variant = (v == "wavefront") ? 1 : 0;
         else if (opt_value(a, "--width", v)) ow = std::atoi(v.c_str());
         else if (opt_value(a, "--height", v)) oh = std::atoi(v.c_str());
         else if (opt_value(a, "--samples", v)) os = std::atoi(v.c_str());
@@ -93,9 +96,10 @@ int main(int argc, char* argv[]) {
         if (stats) {
             const auto& s = renderer.stats;
             std::printf("{\"samples\": %llu, \"rays\": %llu, \"device_ms\": %.3f, \"e2e_ms\": %.3f, \"mrays_per_s\": %.1f, "
-                        "\"msamples_per_s\": %.1f, \"kernel_launches\": %d, \"n_gpus\": %d}\n",
+                        "\"msamples_per_s\": %.1f, \"kernel_launches\": %d, \"n_gpus\": %d, \"sphere_tests\": %llu, \"bvh_nodes\": %llu}\n",
                         (unsigned long long)s.samples, (unsigned long long)s.rays, s.device_ms, s.e2e_ms,
-                        s.rays / (s.device_ms * 1e3), s.samples / (s.device_ms * 1e3), s.kernel_launches, s.n_gpus);
+                        s.rays / (s.device_ms * 1e3), s.samples / (s.device_ms * 1e3), s.kernel_launches, s.n_gpus,
+                        (unsigned long long)s.sphere_tests, (unsigned long long)s.bvh_nodes);
         }
     } catch (const std::exception& e) {
         std::cerr << "error: " << e.what() << std::endl;
