@@ -188,9 +188,12 @@ class Renderer:
         return d
 
     # -- the drop-in call: host buffers in, host buffers out
-    def render(self, want_image: bool = True, want_hits: bool = False) -> RenderResult:
+    def render(self, want_image: bool = True, want_hits: bool = False, image_out: Optional[np.ndarray] = None) -> RenderResult:
+        """renderer_render: host buffers out.  `image_out` (float32 [H][W][3], C-contiguous) is reused when given."""
         sc = self.scene
-        img = np.empty((sc.height, sc.width, 3), np.float32) if want_image else None
+        if image_out is not None:
+            assert image_out.dtype == np.float32 and image_out.shape == (sc.height, sc.width, 3) and image_out.flags.c_contiguous
+        img = (image_out if image_out is not None else np.empty((sc.height, sc.width, 3), np.float32)) if want_image else None
         hits = np.empty((sc.height, sc.width, sc.superSamples, sc.superSamples), np.int32) if want_hits else None
         st = _Stats()
         _check(self._lib, self._lib.renderer_render(

@@ -882,6 +882,15 @@ __global__ void __launch_bounds__(256) to_u8_kernel(const float4* __restrict__ a
     }
 }
 
+// ---- float4[H][W] {r,g,b,0} -> float[H][W][3], the layout of renderer_render's rgb_out ----
+__global__ void __launch_bounds__(256) pack_rgb_kernel(const float4* __restrict__ accum, float* __restrict__ out,
+                                                       unsigned long long n_pix) {
+    const unsigned long long pix = (unsigned long long)blockIdx.x * blockDim.x + threadIdx.x;
+    if (pix >= n_pix) return;
+    const float4 v = accum[pix];
+    out[3 * pix] = v.x; out[3 * pix + 1] = v.y; out[3 * pix + 2] = v.z;
+}
+
 // ---- test hooks ---------------------------------------------------------------
 __global__ void closest_hit_f32_kernel(int n_sph, unsigned key_mask, double rx, double ry, double rz, uint32_t n, const double* __restrict__ org,
                                        const double* __restrict__ dir, const int32_t* __restrict__ origin_id,
@@ -1071,6 +1080,10 @@ void rtm_launch_accumulate(const RtmPassParams& p, const float4* records, float4
     } else {
         accumulate_generic_kernel<<<(unsigned)((n_pix + 255) / 256), 256, 0, st>>>(records, accum, n_pix, g);
     }
+}
+
+void rtm_launch_pack_rgb(const float4* accum, float* out, uint64_t n_pix, cudaStream_t st) {
+    pack_rgb_kernel<<<(unsigned)((n_pix + 255) / 256), 256, 0, st>>>(accum, out, n_pix);
 }
 
 void rtm_launch_to_u8(const float4* accum, unsigned char* out, uint64_t n_pix, cudaStream_t st) {

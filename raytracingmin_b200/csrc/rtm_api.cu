@@ -123,7 +123,7 @@ struct GpuCtx {
     float4* d_bvh = nullptr;    // one allocation: nodes | leaf_geo | geo | emi | alb | leaf_id
     RtmBvhDev bvh{};
     RtmMatDev mat{};
-    float4* h_accum = nullptr;  // pinned staging
+    float* d_rgb = nullptr;     // float[H][W][3] staging for renderer_render's rgb_out
     int32_t s_begin = 0, s_end = 0;
     ncclComm_t comm = nullptr;
 };
@@ -162,7 +162,7 @@ void free_ctx(GpuCtx& c) {
     if (c.cps0) cudaFree(c.cps0);
     if (c.d_wave) cudaFree(c.d_wave);
     if (c.h_live) cudaFreeHost(c.h_live);
-    if (c.h_accum) cudaFreeHost(c.h_accum);
+    if (c.d_rgb) cudaFree(c.d_rgb);
     if (c.ev0) cudaEventDestroy(c.ev0);
     if (c.ev1) cudaEventDestroy(c.ev1);
     for (auto& e : c.ek) if (e) cudaEventDestroy(e);
@@ -683,8 +683,11 @@ int renderer_render(rtm_renderer* r, float* rgb_out, int32_t* hit_out, rtm_stats
     GpuCtx& c0 = r->gpus[0];
     CU(cudaSetDevice(c0.device));
     if (rgb_out) {
-        if (!c0.h_accum) CU(cudaMallocHost(&c0.h_accum, r->n_pix * sizeof(float4)));
-        CU(cudaMemcpyAsync(c0.h_accum, c0.accum, r->n_pix * sizeof(float4), cudaMemcpyDeviceToHost, c0.stream));
+        // repacked on the device, then ONE copy of 12 B/pixel straight into the caller's buffer
+        if (!c0.d_rgb) CU(cudaMalloc(&c0.d_rgb, r->n_pix * 3 * sizeof(float)));
+        rtm_launch_pack_rgb(c0.accum, c0.d_rgb, r->n_pix, c0.stream);
+        CU(cudaGetLastError());
+        CU(cudaMemcpyAsync(rgb_out, c0.d_rgb, r->n_pix * 3 * sizeof(float), cudaMemcpyDeviceToHost, c0.stream));
     }
     if (hit_out) CU(cudaMemcpyAsync(hit_out, c0.hits, r->n_sub * sizeof(int32_t), cudaMemcpyDeviceToHost, c0.stream));
     double dev_ms = 0;
@@ -695,12 +698,6 @@ int renderer_render(rtm_renderer* r, float* rgb_out, int32_t* hit_out, rtm_stats
         float ms = 0;
         CU(cudaEventElapsedTime(&ms, c.ev0, c.ev1));
         if (ms > dev_ms) dev_ms = ms;
-    }
-    if (rgb_out) {
-        const float4* a = c0.h_accum;
-        for (uint64_t i = 0; i < r->n_pix; ++i) {
-            rgb_out[3 * i] = a[i].x; rgb_out[3 * i + 1] = a[i].y; rgb_out[3 * i + 2] = a[i].z;
-        }
     }
     r->last_launches = launches;
     r->hits_valid = (hit_out != nullptr) || r->opt.compat == RTM_COMPAT_HEAD;
