@@ -183,6 +183,10 @@ int rtm_debug_philox(int32_t device, uint32_t n, uint32_t c1, uint32_t c2, uint3
 int rtm_debug_closest_hit(rtm_renderer* r, int32_t mode, uint32_t n, const double* org, const double* dir,
                           const int32_t* origin_id, int32_t* hit_out, double* t_out);
 
+/* The FP32 path's model of the reference's Normalize() error (ACNE): out[i] = eps drawn
+ * from the 32 random bits bits[i]. */
+int rtm_debug_acne_eps(int32_t device, uint32_t n, const uint32_t* bits, float* eps_out);
+
 /* The sphere hierarchy renderer_create would build for `scene` (host only, no GPU needed).
  * info[13] = {inner nodes, leaf slots, root code, depth, n_big, big_id[8]}.  Call once with the
  * three arrays NULL to size them: nodes_out float[16*nodes] (4 float4 per node: child boxes,

@@ -940,6 +940,11 @@ __global__ void closest_hit_bvh_f32_kernel(RtmBvhDev bvh, RtmMatDev mat, unsigne
     tout[i] = (double)t;
 }
 
+__global__ void acne_eps_kernel(uint32_t n, const uint32_t* __restrict__ bits, float* __restrict__ out) {
+    const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i < n) out[i] = ref_normalize_eps(bits[i]);
+}
+
 __global__ void philox_kernel(uint32_t n, uint32_t c1, uint32_t c2, uint32_t c3, uint32_t k0, uint32_t k1, uint32_t* __restrict__ out) {
     const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
     if (i >= n) return;
@@ -1108,6 +1113,10 @@ void rtm_launch_closest_hit_bvh_f32(const RtmBvhDev& bvh, const RtmMatDev& mat, 
         default: RTM_CASE(4); break;
 #undef RTM_CASE
     }
+}
+
+void rtm_launch_acne_eps(uint32_t n, const uint32_t* bits, float* out, cudaStream_t st) {
+    acne_eps_kernel<<<(n + 127) / 128, 128, 0, st>>>(n, bits, out);
 }
 
 void rtm_launch_philox(uint32_t n, uint32_t c1, uint32_t c2, uint32_t c3, uint32_t k0, uint32_t k1, uint32_t* out, cudaStream_t st) {

@@ -785,6 +785,23 @@ int rtm_debug_closest_hit(rtm_renderer* r, int32_t mode, uint32_t n, const doubl
     return rc;
 }
 
+int rtm_debug_acne_eps(int32_t device, uint32_t n, const uint32_t* bits, float* out) {
+    if (!bits || !out || n == 0) return fail(RTM_E_INVALID, "bad argument");
+    CU(cudaSetDevice(device));
+    uint32_t* d_bits = nullptr;
+    float* d_out = nullptr;
+    CU(cudaMalloc(&d_bits, (size_t)n * 4));
+    cudaError_t e = cudaMalloc(&d_out, (size_t)n * 4);
+    if (e == cudaSuccess) e = cudaMemcpy(d_bits, bits, (size_t)n * 4, cudaMemcpyHostToDevice);
+    if (e == cudaSuccess) {
+        rtm_launch_acne_eps(n, d_bits, d_out, nullptr);
+        e = cudaMemcpy(out, d_out, (size_t)n * 4, cudaMemcpyDeviceToHost);
+    }
+    cudaFree(d_bits); cudaFree(d_out);
+    CU(e);
+    return RTM_OK;
+}
+
 int rtm_debug_bvh(const rtm_scene_desc* sc, int32_t* info, float* nodes_out, float* leaf_geo_out, int32_t* leaf_id_out) {
     if (!sc || !info) return fail(RTM_E_INVALID, "null argument");
     RtmBvhHost B;

@@ -156,6 +156,7 @@ void rtm_launch_closest_hit_f32(int32_t n_spheres, const double* refd, uint32_t 
 void rtm_launch_closest_hit_bvh_f32(const RtmBvhDev& bvh, const RtmMatDev& mat, int32_t n_spheres, const double* refd, uint32_t n,
                                     const double* org, const double* dir, const int32_t* origin_id, int32_t* hit, double* t,
                                     cudaStream_t st);
+void rtm_launch_acne_eps(uint32_t n, const uint32_t* bits, float* out, cudaStream_t st);
 void rtm_launch_philox(uint32_t n, uint32_t c1, uint32_t c2, uint32_t c3, uint32_t k0, uint32_t k1, uint32_t* out,
                        cudaStream_t st);
 void rtm_launch_fma_peak(float* sink, int32_t blocks, int32_t iters, cudaStream_t st);
