@@ -133,7 +133,9 @@ template <int NP>
 __device__ __forceinline__ unsigned trace_pairs_f32(const SelfMask& sm, int oid, f3 o, f3 d, unsigned key_mask) {
     const float noo = -dot(o, o), ndO = -dot(d, o);
     const u64 dx = pk(d.x, d.x), dy = pk(d.y, d.y), dz = pk(d.z, d.z);
-    const u64 ox = pk(o.x, o.x), oy = pk(o.y, o.y), oz = pk(o.z, o.z);
+    // o.(2c) is formed as (2o).c — bit-identical (power-of-two scaling) and the pair needs 4 constants, not 7
+    const float o2x = o.x + o.x, o2y = o.y + o.y, o2z = o.z + o.z;
+    const u64 ox = pk(o2x, o2x), oy = pk(o2y, o2y), oz = pk(o2z, o2z);
     const u64 noo2 = pk(noo, noo), ndO2 = pk(ndO, ndO), neps2 = pk(-RTM_T_EPS, -RTM_T_EPS);
     unsigned best = RTM_KEY_INF;
     const float4 m0 = sm.row[oid + 1][0], m1 = sm.row[oid + 1][1];
@@ -142,7 +144,7 @@ __device__ __forceinline__ unsigned trace_pairs_f32(const SelfMask& sm, int oid,
     for (int j = 0; j < NP; ++j) {
         const RtmPairF32& c = c_scene.pairs[j];
         const u64 b2 = fma2(dx, pk(c.cx), fma2(dy, pk(c.cy), fma2(dz, pk(c.cz), ndO2)));                   // (c-o).d
-        const u64 ncp2 = fma2(ox, pk(c.p2x), fma2(oy, pk(c.p2y), fma2(oz, pk(c.p2z), add2(noo2, pk(c.nK)))));  // r^2 - |c-o|^2
+        const u64 ncp2 = fma2(ox, pk(c.cx), fma2(oy, pk(c.cy), fma2(oz, pk(c.cz), add2(noo2, pk(c.nK)))));     // r^2 - |c-o|^2
         const u64 ncp = mul2(ncp2, mask[j]);   // leaving this sphere's surface: c' = 0 exactly
         float b0, b1;
         unpk(b2, b0, b1);
@@ -203,12 +205,12 @@ __device__ __forceinline__ int trace_f32(const SelfMask& sm, int n_rt, int oid, 
 __device__ __forceinline__ bool box_test_f32(float lx, float hx, float ly, float hy, float lz, float hz, f3 oi, f3 inv,
                                              float tmax_in, float& tnear) {
     // (plane - o) / d as one FMA per plane; NaN (0 * inf) drops out of fminf/fmaxf: that slab is ignored
-    float t1 = fmaf(lx, inv.x, -oi.x), t2 = fmaf(hx, inv.x, -oi.x);
-    float tmin = fmaxf(0.f, fminf(t1, t2)), tmax = fminf(tmax_in, fmaxf(t1, t2));
-    t1 = fmaf(ly, inv.y, -oi.y); t2 = fmaf(hy, inv.y, -oi.y);
-    tmin = fmaxf(tmin, fminf(t1, t2)); tmax = fminf(tmax, fmaxf(t1, t2));
-    t1 = fmaf(lz, inv.z, -oi.z); t2 = fmaf(hz, inv.z, -oi.z);
-    tmin = fmaxf(tmin, fminf(t1, t2)); tmax = fminf(tmax, fmaxf(t1, t2));
+    const float ax = fmaf(lx, inv.x, -oi.x), bx = fmaf(hx, inv.x, -oi.x);
+    const float ay = fmaf(ly, inv.y, -oi.y), by = fmaf(hy, inv.y, -oi.y);
+    const float az = fmaf(lz, inv.z, -oi.z), bz = fmaf(hz, inv.z, -oi.z);
+    // nested so that the compiler can form 3-input FMNMX3
+    const float tmin = fmaxf(fmaxf(fminf(ax, bx), fminf(ay, by)), fmaxf(fminf(az, bz), 0.f));
+    const float tmax = fminf(fminf(fmaxf(ax, bx), fmaxf(ay, by)), fminf(fmaxf(az, bz), tmax_in));
     tnear = tmin;
     return tmin <= tmax;
 }
@@ -755,6 +757,8 @@ __global__ void __launch_bounds__(RTM_MEGA_THREADS, RTM_BVH_MINBLOCKS) radiance_
                 pending = false;
                 end = apply_hit(ray.hit, ray.best + RTM_T_EPS);
             }
+            for (;;) {   // usually one round; another one only with an empty hierarchy
+            int oslot = -2;   // >= -1: a bounce direction is ready, start the ray after the loop
             for (;;) {
                 if (!end) {
                     const uint2 rnd = rtm_philox2x32_10(make_uint2(q, ((unsigned)s << 9) | (unsigned)depth), p.rk);
@@ -776,12 +780,7 @@ __global__ void __launch_bounds__(RTM_MEGA_THREADS, RTM_BVH_MINBLOCKS) radiance_
                                 continue;
                             }
                         }
-                        bvh_ray_begin<NP>(sh_mask, sh_big, bvh, __float_as_int(al.w), o, d, key_mask, ray, stack, n_tests);
-                        if (ray.node == RTM_BVH_NONE_DEV) {
-                            end = apply_hit(ray.hit, ray.best + RTM_T_EPS);
-                            continue;
-                        }
-                        tracing = true;
+                        oslot = __float_as_int(al.w);
                         break;
                     }
                 }
@@ -801,6 +800,16 @@ __global__ void __launch_bounds__(RTM_MEGA_THREADS, RTM_BVH_MINBLOCKS) radiance_
                 T = mk(1, 1, 1); L = mk(e0.x, e0.y, e0.z); depth = 0;
                 if (ACNE) cpsn = Pcpsn;
                 end = false;
+            }
+            if (oslot < -1) break;   // the sub-pixel is finished
+            // the packed big-sphere test (~140 instructions) runs once, for all lanes that start a ray, instead of
+            // once per roulette round with whichever lanes happened to continue in that round
+            bvh_ray_begin<NP>(sh_mask, sh_big, bvh, oslot, o, d, key_mask, ray, stack, n_tests);
+            if (ray.node != RTM_BVH_NONE_DEV) {
+                tracing = true;
+                break;
+            }
+            end = apply_hit(ray.hit, ray.best + RTM_T_EPS);
             }
         }
 
