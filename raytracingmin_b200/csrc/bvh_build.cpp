@@ -217,5 +217,40 @@ bool rtm_bvh_build(int32_t n, const double* position, const float* radius, const
     const Builder::Sub root = bl.build(0, (int)bl.prims.size(), 0);
     out.root = root.code;
     out.depth = bl.max_depth;
+    if (root.code >= 0) {
+        // renumber the inner nodes breadth-first: node 0 is the root and the first 2^k - 1 indices are the top
+        // k levels (neighbouring cache lines for the part of the tree every ray walks; a shared-memory copy of
+        // these levels was measured and was slower than L1: profiles/r01)
+        const size_t n_nodes = out.nodes.size() / 4;
+        std::vector<int32_t> order, new_id(n_nodes, -1);
+        order.reserve(n_nodes);
+        order.push_back(root.code);
+        new_id[root.code] = 0;
+        for (size_t k = 0; k < order.size(); ++k) {
+            const float4 c = out.nodes[4 * (size_t)order[k] + 3];
+            int32_t ch[2];
+            memcpy(&ch[0], &c.x, 4);
+            memcpy(&ch[1], &c.y, 4);
+            for (int j = 0; j < 2; ++j)
+                if (ch[j] >= 0) {
+                    new_id[ch[j]] = (int32_t)order.size();
+                    order.push_back(ch[j]);
+                }
+        }
+        std::vector<float4> nn(out.nodes.size());
+        for (size_t k = 0; k < order.size(); ++k) {
+            for (int j = 0; j < 4; ++j) nn[4 * k + j] = out.nodes[4 * (size_t)order[k] + j];
+            float4& c = nn[4 * k + 3];
+            int32_t ch[2];
+            memcpy(&ch[0], &c.x, 4);
+            memcpy(&ch[1], &c.y, 4);
+            for (int j = 0; j < 2; ++j)
+                if (ch[j] >= 0) ch[j] = new_id[ch[j]];
+            memcpy(&c.x, &ch[0], 4);
+            memcpy(&c.y, &ch[1], 4);
+        }
+        out.nodes.swap(nn);
+        out.root = 0;
+    }
     return bl.max_depth + 2 < RTM_BVH_STACK;
 }

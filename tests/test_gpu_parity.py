@@ -68,6 +68,26 @@ def test_hits_cornell_default_size_bit_exact(scene_path, level):
         assert np.array_equal(got, want), f"{int((got != want).sum())} of {want.size} differ"
 
 
+def test_hits_c4_full_size_bit_exact(scene_path):
+    """BASELINE config 4 at its full size: Cornell 3840x2160, ss=4 -> 132.7 M sub-pixels, every index equal
+    to the oracle's (compared as uint8 to keep the host copies at 133 MB each)."""
+    sc = rtm.load_scene(scene_path("cornellBox"), "abc").with_dims(3840, 2160, 1, 4)
+    want = O.oracle_primary_hits(sc).astype(np.int8)
+    with rtm.Renderer(sc) as r:
+        got = r.render(want_image=False, want_hits=True).hits.astype(np.int8)
+    assert got.shape == (2160, 3840, 4, 4)
+    assert np.array_equal(got, want), f"{int((got != want).sum())} of {want.size} differ"
+
+
+def test_hits_c3_full_size_bit_exact(scene_path):
+    """BASELINE config 3: simpleSetting2 at 1920x1080 (every primary ray starts on object 4's surface)."""
+    sc = rtm.load_scene(scene_path("simple2"), "abc").with_dims(1920, 1080, 1, 1)
+    want = O.oracle_primary_hits(sc)
+    with rtm.Renderer(sc) as r:
+        got = r.render(want_image=False, want_hits=True).hits
+    assert np.array_equal(got, want)
+
+
 @pytest.mark.parametrize("seed,n,ss", [(3, 0, 1), (5, 1, 3), (7, 12, 2), (9, 60, 1), (11, 200, 2)])
 def test_hits_random_scenes(seed, n, ss):
     """ragged sizes (odd width/height, ss=3), empty scene, > 8 spheres (runtime-N kernel)."""
