@@ -205,10 +205,32 @@ def run_gpu_arm(args):
     accum = torch.zeros((sc.height, sc.width, 4), dtype=torch.float32, device=dev)
     r.set_accum_buffer(accum.data_ptr())
     stream = torch.cuda.current_stream()
+    frame_bytes = n_pix * 16
+    peer = world > 1 and args.reduce == "peer"
+    if peer:
+        # peer-memory gather (include/rtm_b200.h): rank 0 exports 2 x world framebuffer slots (double-buffered per
+        # step), every rank's accumulate kernel stores its partial framebuffer straight into its slot in rank 0's HBM
+        # over NVLink, a one-element all_reduce orders the streams, rank 0 sums the slots with one kernel.
+        objs = [r.peer_export(2 * world) if rank == 0 else None]
+        dist.broadcast_object_list(objs, src=0)
+        base = objs[0][1] if rank == 0 else r.peer_open(objs[0][0])
+        flag = torch.zeros(1, dtype=torch.float32, device=dev)
+        step_no = [0]
 
-    def step():
+    def step_nccl():
         r.render_async(stream.cuda_stream)
         reduce_partials(accum, dst=0)
+
+    def step_peer():
+        half = (step_no[0] & 1) * world
+        step_no[0] += 1
+        r.set_accum_buffer(base + (half + rank) * frame_bytes)
+        r.render_async(stream.cuda_stream)
+        dist.all_reduce(flag)          # stream-ordered: returns on a rank after every rank's stores were issued
+        if rank == 0:
+            r.sum_partials(base + half * frame_bytes, world, accum.data_ptr(), stream.cuda_stream)
+
+    step = step_peer if peer else step_nccl
 
     def fence():
         torch.cuda.synchronize()
@@ -281,6 +303,17 @@ def run_gpu_arm(args):
     e2e_s = float(te.item())
     h2d = rtm_scene_bytes(sc)
 
+    reduce_check = None
+    if peer:
+        # untimed: the same pass through the NCCL sum-reduce must give the same image (up to summation order)
+        got = accum.clone()
+        r.set_accum_buffer(accum.data_ptr())
+        step_nccl()
+        fence()
+        if rank == 0:
+            reduce_check = float((got - accum).abs().max().item())
+        accum.copy_(got)
+
     line = None
     if rank == 0:
         fp32_peak, implied_mhz = api.fp32_peak_tflops(local)
@@ -313,7 +346,10 @@ def run_gpu_arm(args):
                                       f"hierarchy: {st.sphere_tests / max(1, st.rays_traced):.1f} sphere tests + "
                                       f"{st.bvh_nodes / max(1, st.rays_traced):.1f} nodes per traced ray",
                        "partition": (("sub-pixel grid" if plan["sub_end"] - plan["sub_begin"] < sc.superSamples ** 2 else "samples loop")
-                                     + f" sliced over {world} rank(s)" + (", one NCCL sum-reduce to rank 0" if world > 1 else "")),
+                                     + f" sliced over {world} rank(s)"
+                                     + ((", partial framebuffers stored into rank 0's HBM over NVLink by the accumulate kernel "
+                                         "+ one sum kernel (peer-memory gather)") if peer else
+                                        (", one NCCL sum-reduce to rank 0" if world > 1 else ""))),
                        "l2": f"inputs larger than L2: the {n_sub * 16 / 1e9:.2f} GB sub-pixel record buffer is rewritten and re-read every step"
                              if n_sub * 16 > 126e6 else "working set below L2 (plumbing workload)",
                        "semantics": "L-ABC (SURVEY.md §0.1), FP64 bit-exact primary pass + FP32 bounces, Philox2x32-10"},
@@ -321,7 +357,7 @@ def run_gpu_arm(args):
             "rays_per_sample": rays_all / samples_all,
             "e2e": {"value": rays_all / e2e_s / 1e6, "unit": "Mrays/s", "h2d_bytes_per_step": h2d,
                     "d2h_bytes_per_step": d2h, "ms_per_step": e2e_s * 1e3, "steps": e2e_steps},
-            "gpu_launches": 3 * args.steps,
+            "gpu_launches": (3 + (1 if peer else 0)) * args.steps,
             "kernel_ms": {"primary_f64": kms[0], "radiance_mega": kms[1], "accumulate": kms[2]},
             "roofline": {"bound": "fp32", "achieved": achieved, "peak": fp32_peak, "unit": "TFLOP/s",
                          "frac": achieved / fp32_peak if fp32_peak else None,
@@ -337,6 +373,8 @@ def run_gpu_arm(args):
                          "framebuffer_store_GBs": fb_gbs, "hbm_peak_GBs": peaks.get("hbm_gbs")},
             "clocks": clocks,
         }
+        if reduce_check is not None:
+            line["reduce_check_max_abs_diff_vs_nccl"] = reduce_check
     if world > 1:
         dist.barrier()
     return line, (r, sc, wl)
@@ -374,6 +412,8 @@ def main():
     ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
     ap.add_argument("--workload", default="c4", choices=sorted(WORKLOADS))
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--reduce", default="nccl", choices=["peer", "nccl"],
+                    help="N > 1: how the partial framebuffers reach rank 0 (peer-memory gather kernel path, or ncclReduce)")
     ap.add_argument("--variant", default="mega", choices=["mega", "wavefront"],
                     help="kernel organisation of the FP32 bounce loop (DESIGN.md: megakernel vs wavefront)")
     args = ap.parse_args()

@@ -160,6 +160,15 @@ void* renderer_device_hits(rtm_renderer* r);
  * buffer): float4[H][W] device memory on the handle's device. */
 int renderer_set_accum_buffer(rtm_renderer* r, void* device_float4);
 
+/* Peer-memory gather for one-process-per-GPU runs (replaces the NCCL reduce of the partial framebuffers):
+ *   root:  renderer_peer_export(r, G, handle, &base)   allocates float4[G][H][W] on the root GPU, CUDA IPC handle (64 B)
+ *   rank:  renderer_peer_open(r, handle, &base)        maps it; renderer_set_accum_buffer(r, base + g*H*W*16) makes the
+ *          rank's LAST kernel store its partial framebuffer straight into the root's HBM over NVLink
+ *   root:  after a cross-rank barrier on the stream, renderer_sum_partials(r, base, G, out, stream): out = sum of slots */
+int renderer_peer_export(rtm_renderer* r, int32_t n_slots, void* handle64, void** device_ptr);
+int renderer_peer_open(rtm_renderer* r, const void* handle64, void** device_ptr);
+int renderer_sum_partials(rtm_renderer* r, const void* partials, int32_t n_slots, void* out_float4, void* stream);
+
 /* COMPAT_HEAD only: the double image double[H][W][3], bit-exact against the reference. */
 int renderer_read_image_f64(rtm_renderer* r, double* image_out);
 

@@ -82,7 +82,7 @@ class RenderResult:
 EXPORTS = [
     "renderer_abi_version", "renderer_default_options", "renderer_create", "renderer_render",
     "renderer_render_async", "renderer_read_stats", "renderer_read_kernel_ms", "renderer_device_accum", "renderer_device_hits",
-    "renderer_set_accum_buffer", "renderer_read_image_f64", "renderer_read_u8", "renderer_destroy",
+    "renderer_set_accum_buffer", "renderer_peer_export", "renderer_peer_open", "renderer_sum_partials", "renderer_read_image_f64", "renderer_read_u8", "renderer_destroy",
     "renderer_last_error", "rtm_debug_philox", "rtm_debug_closest_hit", "rtm_debug_fp32_peak", "rtm_debug_bvh", "rtm_debug_acne_eps",
 ]
 
@@ -118,6 +118,9 @@ def load_library():
     lib.renderer_device_hits.argtypes = [vp]
     lib.renderer_device_hits.restype = vp
     lib.renderer_set_accum_buffer.argtypes = [vp, vp]
+    lib.renderer_peer_export.argtypes = [vp, C.c_int32, vp, P(vp)]
+    lib.renderer_peer_open.argtypes = [vp, vp, P(vp)]
+    lib.renderer_sum_partials.argtypes = [vp, vp, C.c_int32, vp, vp]
     lib.renderer_read_image_f64.argtypes = [vp, vp]
     lib.renderer_read_u8.argtypes = [vp, vp]
     lib.renderer_destroy.argtypes = [vp]
@@ -221,6 +224,23 @@ class Renderer:
 
     def set_accum_buffer(self, device_ptr: int) -> None:
         _check(self._lib, self._lib.renderer_set_accum_buffer(self._h, C.c_void_p(device_ptr)))
+
+    # -- peer-memory gather (one process per GPU), see include/rtm_b200.h
+    def peer_export(self, n_slots: int):
+        h = (C.c_char * 64)()
+        p = C.c_void_p()
+        _check(self._lib, self._lib.renderer_peer_export(self._h, n_slots, h, C.byref(p)))
+        return bytes(h.raw), int(p.value)
+
+    def peer_open(self, handle: bytes) -> int:
+        h = (C.c_char * 64).from_buffer_copy(handle)
+        p = C.c_void_p()
+        _check(self._lib, self._lib.renderer_peer_open(self._h, h, C.byref(p)))
+        return int(p.value)
+
+    def sum_partials(self, partials_ptr: int, n_slots: int, out_ptr: int, stream: int = 0) -> None:
+        _check(self._lib, self._lib.renderer_sum_partials(self._h, C.c_void_p(partials_ptr), n_slots, C.c_void_p(out_ptr),
+                                                          C.c_void_p(stream)))
 
     def read_image_f64(self) -> np.ndarray:
         sc = self.scene

@@ -891,6 +891,21 @@ __global__ void __launch_bounds__(256) to_u8_kernel(const float4* __restrict__ a
     }
 }
 
+// ---- sum of G partial framebuffers that the ranks' accumulate kernels stored into THIS GPU's memory over
+// NVLink (peer stores): out[pix] = sum_g partials[g][pix], fixed order g = 0..G-1 (deterministic) --------------
+__global__ void __launch_bounds__(256) sum_partials_kernel(const float4* __restrict__ partials, float4* __restrict__ out,
+                                                           unsigned long long n_pix, int G) {
+    const unsigned long long pix = (unsigned long long)blockIdx.x * blockDim.x + threadIdx.x;
+    if (pix >= n_pix) return;
+    float4 a = partials[pix];
+    for (int g = 1; g < G; ++g) {
+        const float4 v = partials[(unsigned long long)g * n_pix + pix];
+        a.x += v.x; a.y += v.y; a.z += v.z;
+    }
+    a.w = 0.f;
+    out[pix] = a;
+}
+
 // ---- float4[H][W] {r,g,b,0} -> float[H][W][3], the layout of renderer_render's rgb_out ----
 __global__ void __launch_bounds__(256) pack_rgb_kernel(const float4* __restrict__ accum, float* __restrict__ out,
                                                        unsigned long long n_pix) {
@@ -1094,6 +1109,10 @@ void rtm_launch_accumulate(const RtmPassParams& p, const float4* records, float4
     } else {
         accumulate_generic_kernel<<<(unsigned)((n_pix + 255) / 256), 256, 0, st>>>(records, accum, n_pix, g);
     }
+}
+
+void rtm_launch_sum_partials(const float4* partials, float4* out, uint64_t n_pix, int32_t G, cudaStream_t st) {
+    sum_partials_kernel<<<(unsigned)((n_pix + 255) / 256), 256, 0, st>>>(partials, out, n_pix, G);
 }
 
 void rtm_launch_pack_rgb(const float4* accum, float* out, uint64_t n_pix, cudaStream_t st) {

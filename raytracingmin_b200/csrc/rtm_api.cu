@@ -124,6 +124,8 @@ struct GpuCtx {
     RtmBvhDev bvh{};
     RtmMatDev mat{};
     float* d_rgb = nullptr;     // float[H][W][3] staging for renderer_render's rgb_out
+    float4* peer_stage = nullptr;   // exported gather buffer: G partial framebuffers written by peer GPUs
+    void* peer_opened = nullptr;    // a peer's gather buffer opened through CUDA IPC
     int32_t s_begin = 0, s_end = 0;
     ncclComm_t comm = nullptr;
 };
@@ -163,6 +165,8 @@ void free_ctx(GpuCtx& c) {
     if (c.d_wave) cudaFree(c.d_wave);
     if (c.h_live) cudaFreeHost(c.h_live);
     if (c.d_rgb) cudaFree(c.d_rgb);
+    if (c.peer_opened) cudaIpcCloseMemHandle(c.peer_opened);
+    if (c.peer_stage) cudaFree(c.peer_stage);
     if (c.ev0) cudaEventDestroy(c.ev0);
     if (c.ev1) cudaEventDestroy(c.ev1);
     for (auto& e : c.ek) if (e) cudaEventDestroy(e);
@@ -648,6 +652,46 @@ int renderer_set_accum_buffer(rtm_renderer* r, void* p) {
     if (c.accum && c.accum_owned) CU(cudaFree(c.accum));
     c.accum = (float4*)p;
     c.accum_owned = false;
+    return RTM_OK;
+}
+
+// ---- peer-memory gather (one process per GPU): the root exports G framebuffer slots, every rank points its
+// accumulate kernel at its slot (coalesced 16 B stores over NVLink), the root sums the slots.
+int renderer_peer_export(rtm_renderer* r, int32_t n_slots, void* handle64, void** device_ptr) {
+    if (!r || !handle64 || !device_ptr || n_slots < 1) return fail(RTM_E_INVALID, "bad argument");
+    if (r->gpus.size() != 1) return fail(RTM_E_UNSUPPORTED, "one GPU per handle");
+    GpuCtx& c = r->gpus[0];
+    CU(cudaSetDevice(c.device));
+    if (c.peer_stage) { CU(cudaFree(c.peer_stage)); c.peer_stage = nullptr; }
+    CU(cudaMalloc(&c.peer_stage, (size_t)n_slots * r->n_pix * sizeof(float4)));
+    CU(cudaMemset(c.peer_stage, 0, (size_t)n_slots * r->n_pix * sizeof(float4)));
+    static_assert(sizeof(cudaIpcMemHandle_t) == 64, "IPC handle size");
+    cudaIpcMemHandle_t h;
+    CU(cudaIpcGetMemHandle(&h, c.peer_stage));
+    memcpy(handle64, &h, 64);
+    *device_ptr = c.peer_stage;
+    return RTM_OK;
+}
+
+int renderer_peer_open(rtm_renderer* r, const void* handle64, void** device_ptr) {
+    if (!r || !handle64 || !device_ptr) return fail(RTM_E_INVALID, "null argument");
+    if (r->gpus.size() != 1) return fail(RTM_E_UNSUPPORTED, "one GPU per handle");
+    GpuCtx& c = r->gpus[0];
+    CU(cudaSetDevice(c.device));
+    if (c.peer_opened) { CU(cudaIpcCloseMemHandle(c.peer_opened)); c.peer_opened = nullptr; }
+    cudaIpcMemHandle_t h;
+    memcpy(&h, handle64, 64);
+    CU(cudaIpcOpenMemHandle(&c.peer_opened, h, cudaIpcMemLazyEnablePeerAccess));
+    *device_ptr = c.peer_opened;
+    return RTM_OK;
+}
+
+int renderer_sum_partials(rtm_renderer* r, const void* partials, int32_t n_slots, void* out_float4, void* stream) {
+    if (!r || !partials || !out_float4 || n_slots < 1) return fail(RTM_E_INVALID, "bad argument");
+    GpuCtx& c = r->gpus[0];
+    CU(cudaSetDevice(c.device));
+    rtm_launch_sum_partials((const float4*)partials, (float4*)out_float4, r->n_pix, n_slots, (cudaStream_t)stream);
+    CU(cudaGetLastError());
     return RTM_OK;
 }
 

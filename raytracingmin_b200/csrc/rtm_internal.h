@@ -148,6 +148,7 @@ void rtm_launch_wf_shade(int32_t n_spheres, bool use_bvh, const RtmBvhDev& bvh, 
 void rtm_launch_wf_extend(int32_t n_spheres, bool use_bvh, const RtmBvhDev& bvh, const RtmWaveDev& wv, int32_t wave,
                           RtmCounters* counters, int32_t sm_count, cudaStream_t st);
 void rtm_launch_accumulate(const RtmPassParams& p, const float4* records, float4* accum, cudaStream_t st);
+void rtm_launch_sum_partials(const float4* partials /*[G][n_pix]*/, float4* out, uint64_t n_pix, int32_t G, cudaStream_t st);
 void rtm_launch_pack_rgb(const float4* accum, float* out /*[n_pix][3]*/, uint64_t n_pix, cudaStream_t st);
 void rtm_launch_to_u8(const float4* accum, unsigned char* out, uint64_t n_pix, cudaStream_t st);
 void rtm_launch_closest_hit_f32(int32_t n_spheres, const double* refd, uint32_t n, const double* org,
