@@ -352,7 +352,7 @@ def run_gpu_arm(args):
                                         (", one NCCL sum-reduce to rank 0" if world > 1 else ""))),
                        "l2": f"inputs larger than L2: the {n_sub * 16 / 1e9:.2f} GB sub-pixel record buffer is rewritten and re-read every step"
                              if n_sub * 16 > 126e6 else "working set below L2 (plumbing workload)",
-                       "semantics": "L-ABC (SURVEY.md §0.1), FP64 bit-exact primary pass + FP32 bounces, Philox2x32-10"},
+                       "semantics": "L-ABC (SURVEY.md §0.1), FP64 bit-exact primary pass + FP32 bounces, counter-based pcg3d hash per (sub-pixel, sample, depth)"},
             "msamples_per_s": samples_all / (ms_step * 1e-3) / 1e6,
             "rays_per_sample": rays_all / samples_all,
             "e2e": {"value": rays_all / e2e_s / 1e6, "unit": "Mrays/s", "h2d_bytes_per_step": h2d,

@@ -101,7 +101,7 @@ typedef struct rtm_options {
     int32_t sample_begin;  /* slice [sample_begin, sample_end) of the "samples" loop */
     int32_t sample_end;    /*   (src/Renderer.cpp:226) this handle renders; 0,0 = all.  The divisor
                               of :240 stays the GLOBAL samples count, so slices add up exactly. */
-    uint64_t seed;         /* Philox key; the image is a pure function of (scene, seed) */
+    uint64_t seed;         /* RNG key; the image is a pure function of (scene, seed) */
     int32_t sub_begin;     /* slice [sub_begin, sub_end) of the superSamples^2 sub-pixel grid */
     int32_t sub_end;       /*   (src/Renderer.cpp:224-225, index (sx-1)*ss + (sy-1)) this handle renders;
                               0,0 = all.  The preferred multi-GPU partition when ss^2 divides by the GPU

@@ -403,7 +403,7 @@ __device__ __forceinline__ float ref_normalize_eps(uint32_t bits) {
 // roulette kills it (Renderer.cpp:112), the bounce ray misses (:116), the depth cap is
 // reached, or it lands on a surface with kd == 0 (the roulette there can never continue,
 // so the sample is closed in the same iteration instead of spending another one).
-// RNG: one Philox2x32-10 call per hit, counter = (sub-pixel, sample<<9 | depth), key
+// RNG: one rtm_bounce_rng call per hit (pcg3d hash, philox.cuh), counter = (sub-pixel, sample<<9 | depth), key
 // from the seed: x -> roulette (32-bit compare against kd*2^32), y -> azimuth,
 // the low bits of x and y -> height.
 template <int N, bool BVH, bool ACNE>
@@ -519,7 +519,7 @@ __global__ void __launch_bounds__(RTM_MEGA_THREADS, BVH ? 4 : 5) radiance_mega_k
         }
 
         if (have) {
-            const uint2 rnd = rtm_philox2x32_10(make_uint2(q, ((unsigned)s << 9) | (unsigned)depth), p.rk);
+            const uint2 rnd = rtm_bounce_rng(make_uint2(q, ((unsigned)s << 9) | (unsigned)depth), p.rk);
             const float4 em = recs.emi(id);
             // Russian roulette, Renderer.cpp:78
             bool end = !((rnd.x < __float_as_uint(em.w)) && (depth + 1 < p.max_depth));
@@ -761,7 +761,7 @@ __global__ void __launch_bounds__(RTM_MEGA_THREADS, RTM_BVH_MINBLOCKS) radiance_
             int oslot = -2;   // >= -1: a bounce direction is ready, start the ray after the loop
             for (;;) {
                 if (!end) {
-                    const uint2 rnd = rtm_philox2x32_10(make_uint2(q, ((unsigned)s << 9) | (unsigned)depth), p.rk);
+                    const uint2 rnd = rtm_bounce_rng(make_uint2(q, ((unsigned)s << 9) | (unsigned)depth), p.rk);
                     const float4 em = __ldg(mat.emi + id);
                     end = !((rnd.x < __float_as_uint(em.w)) && (depth + 1 < p.max_depth));   // Renderer.cpp:78
                     if (!end) {

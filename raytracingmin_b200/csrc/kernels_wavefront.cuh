@@ -159,7 +159,7 @@ __global__ void __launch_bounds__(128) wf_shade_kernel(RtmPassParams p, float4* 
                 end = false;
             }
             if (!end) {
-                const uint2 rnd = rtm_philox2x32_10(make_uint2(q, ((unsigned)s << 9) | (unsigned)depth), p.rk);
+                const uint2 rnd = rtm_bounce_rng(make_uint2(q, ((unsigned)s << 9) | (unsigned)depth), p.rk);
                 const float4 em = recs.emi(id);
                 end = !((rnd.x < __float_as_uint(em.w)) && (depth + 1 < p.max_depth));   // Renderer.cpp:78
                 if (!end) {

@@ -97,7 +97,7 @@ struct RtmPassParams {
     int32_t max_depth;
     uint32_t seed_lo, seed_hi;
     uint32_t key_mask;        // 0xFFFFFFF8, passed in so that it lives in a register (see key_pack)
-    uint32_t rk[10];          // Philox2x32 round keys: fold(seed) + r*0x9E3779B9
+    uint32_t rk[10];          // rk[0] = fold(seed): key of the bounce hash; rk[r] = rk[0] + r*0x9E3779B9 (Philox2x32 round keys, -DRTM_RNG_PHILOX)
     float inv_norm;           // 1/(ss*ss*S) for the FP32 path
     float ref[3];             // reference point (as float, informational)
     double refd[3];           // reference point

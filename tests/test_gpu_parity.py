@@ -223,7 +223,9 @@ def test_radiance_f32_converges_to_oracle(scene_path):
 
 @pytest.mark.parametrize("name", ["settingData", "simple1", "simple2"])
 def test_radiance_other_scenes_mean_and_rays(scene_path, name):
-    sc = rtm.load_scene(scene_path(name), "abc").with_dims(64, 34, 512, 1)
+    # 4096 spp on both sides: at 512 spp the image mean of these scenes (rare, bright emitter hits) has a
+    # seed-to-seed standard deviation of 1.4 %, too close to the 3 % tolerance below
+    sc = rtm.load_scene(scene_path(name), "abc").with_dims(64, 34, 4096, 1)
     ref, rays_o, samples_o = O.oracle_render(sc, O.LEVEL_ABC, 31)
     for precision in ("f32", "f64"):
         with rtm.Renderer(sc, precision=precision) as r:
