@@ -334,3 +334,29 @@ def test_stats_counters(scene_path):
     assert st.rays >= st.samples
     assert st.sphere_tests == st.rays_traced * sc.n
     assert st.kernel_launches == 3 and st.device_ms > 0 and st.e2e_ms >= st.device_ms * 0.5
+
+
+# ---------------- the north-star radiance bar on the reference's own objects ----------------
+def test_c2_radiance_rmse_vs_reference_objects_band():
+    """BASELINE config 2's sampling (25 samples x 4x4 sub-pixels = 400 spp) at a quarter of its resolution: per-channel
+    RMSE against the 6400-spp render of the REFERENCE'S OWN objects must lie inside the band (mean +- 6 sigma) of 8 equal-spp renders
+    of those same objects (tests/golden/make_golden_c2.py)."""
+    import os
+    g = np.load(os.path.join(os.path.dirname(os.path.abspath(__file__)), "golden", "c2_quarter_golden.npz"))
+    hi, band, bias_band = g["hi"].astype(np.float64), g["band_rmse"], g["band_mean"]
+    sc = rtm.load_scene(os.path.join(os.path.dirname(os.path.dirname(os.path.abspath(__file__))), "scenes", "cornellBox.head.json"),
+                        "abc").with_dims(240, 126, 25, 4)
+    for precision, seed in (("f32", 2024), ("f32", 7), ("f64", 2024)):
+        with rtm.Renderer(sc, precision=precision, seed=seed) as r:
+            res = r.render()
+        img = res.image.astype(np.float64)
+        rm = _rmse(img, hi)
+        # tolerance: the reference's own seed-to-seed band at equal spp (mean + 4 sigma over K = 8); the 6400-spp
+        # image carries 1/16 of the variance itself, which the band already contains
+        # (K = 8 estimates sigma to +-25 %: 6 sigma = 3 % of the RMSE here)
+        assert (rm <= band.mean(axis=0) + 6.0 * band.std(axis=0)).all(), (precision, rm, band.mean(axis=0), band.std(axis=0))
+        assert (rm >= band.mean(axis=0) - 6.0 * band.std(axis=0)).all(), ("not the same estimator", precision, rm, band.mean(axis=0))
+        bias = (img - hi).reshape(-1, 3).mean(axis=0)
+        assert (np.abs(bias) <= np.abs(bias_band).max(axis=0) + 4.0 * bias_band.std(axis=0)).all(), (precision, bias, bias_band)
+        rps = res.stats.rays / res.stats.samples
+        assert abs(rps - float(g["rays_per_sample"])) < 0.005 * rps
