@@ -12,6 +12,7 @@
 #include <fstream>
 #include <iostream>
 #include <string>
+#include <vector>
 #include <sys/stat.h>
 
 #include "Renderer.h"
@@ -38,13 +39,14 @@ void usage() {
               << "--compat=abc|head  --gpus=N  --device=N  --seed=N  --precision=f32|f64  --max-depth=N\n"
               << "--accel=auto|brute|bvh  --variant=mega|wavefront\n"
               << "--width=N --height=N --samples=N --superSamples=N : override the file's settings\n"
-              << "--out=<name> : output base name (default result)  --dump-hits=<file>  --stats  --quiet\n";
+              << "--out=<name> : output base name (default result)  --dump-hits=<file>  --stats  --quiet\n"
+              << "--dump-pfm=<file> : the linear image before the 8-bit conversion (float RGB, Portable Float Map)\n";
 }
 
 }  // namespace
 
 int main(int argc, char* argv[]) {
-    std::string jsonFile = "settingData.json", outName = "result", dumpHits, v;
+    std::string jsonFile = "settingData.json", outName = "result", dumpHits, dumpPfm, v;
     png::RenderOptions ro;
     int ow = 0, oh = 0, os = 0, oss = 0;
     bool stats = false;
@@ -73,6 +75,7 @@ int main(int argc, char* argv[]) {
         else if (opt_value(a, "--superSamples", v)) oss = std::atoi(v.c_str());
         else if (opt_value(a, "--out", v)) outName = v;
         else if (opt_value(a, "--dump-hits", v)) { dumpHits = v; ro.want_hits = true; }
+        else if (opt_value(a, "--dump-pfm", v)) dumpPfm = v;
         else if (a == "--stats") stats = true;
         else if (a == "--quiet") ro.quiet = true;
     }
@@ -89,6 +92,17 @@ int main(int argc, char* argv[]) {
         if (oss > 0) loadData.data.superSamples = oss;
         png::Renderer renderer(loadData.data, ro);
         renderer.Render(outName);
+        if (!dumpPfm.empty()) {
+            // what the RMSE tooling compares ("linear float images before 8-bit conversion"; the
+            // JPEG is lossy, the BMP quantised and clipped at 1.0).  PFM: rows bottom-to-top, negative scale = little endian.
+            std::ofstream f(dumpPfm, std::ios::binary);
+            f << "PF\n" << loadData.data.width << " " << loadData.data.height << "\n-1.0\n";
+            std::vector<float> row((size_t)loadData.data.width * 3);
+            for (int y = loadData.data.height - 1; y >= 0; --y) {
+                for (size_t i = 0; i < row.size(); ++i) row[i] = (float)renderer.image[(size_t)y * row.size() + i];
+                f.write(reinterpret_cast<const char*>(row.data()), (std::streamsize)(row.size() * sizeof(float)));
+            }
+        }
         if (!dumpHits.empty()) {
             std::ofstream f(dumpHits, std::ios::binary);
             f.write(reinterpret_cast<const char*>(renderer.hits.data()), (std::streamsize)(renderer.hits.size() * sizeof(int32_t)));

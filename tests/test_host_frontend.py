@@ -147,7 +147,8 @@ def test_cli_renders_result_files(hostlib, tmp_path, scene_path):
     import raytracingmin_b200 as rtm
     hits = tmp_path / "hits.bin"
     r = subprocess.run([CLI, "-json", scene_path("cornellBox"), "--width=96", "--height=50", "--samples=4", "--superSamples=2",
-                        "--stats", f"--dump-hits={hits}"], capture_output=True, text=True, cwd=tmp_path)
+                        "--stats", f"--dump-hits={hits}", f"--dump-pfm={tmp_path / 'linear.pfm'}"],
+                       capture_output=True, text=True, cwd=tmp_path)
     assert r.returncode == 0, r.stderr
     bmp = np.asarray(Image.open(tmp_path / "result.bmp").convert("RGB"))
     assert Image.open(tmp_path / "result.jpg").size == (96, 50)
@@ -157,5 +158,9 @@ def test_cli_renders_result_files(hostlib, tmp_path, scene_path):
         u8 = rr.read_u8()
     assert np.array_equal(bmp, u8)                                   # same seed, same image, bit for bit
     assert np.array_equal(np.fromfile(hits, np.int32).reshape(res.hits.shape), res.hits)
+    with open(tmp_path / "linear.pfm", "rb") as f:                   # the linear image, before the 8-bit conversion
+        assert f.readline() == b"PF\n" and f.readline() == b"96 50\n" and f.readline() == b"-1.0\n"
+        pfm = np.frombuffer(f.read(), "<f4").reshape(50, 96, 3)[::-1]
+    assert np.array_equal(pfm, res.image)
     st = json.loads(r.stdout.strip().splitlines()[-1])
     assert st["samples"] == 96 * 50 * 16 and st["rays"] == res.stats.rays
