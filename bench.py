@@ -40,6 +40,11 @@ WORKLOADS = {
                name="simpleSetting1 960x504 x 100 spp (file defaults)"),
     "c5": dict(scene="synth10k", file="synth10k.json", width=1920, height=1080, samples=256, superSamples=1,
                name="synthetic 10k spheres 1920x1080 x 256 spp (closest hit through the hierarchy)"),
+    # PlaneObject extension: the Cornell box with squares instead of r = 1e4 wall spheres
+    "c2p": dict(scene="cornellBoxPlanes", file="cornellBoxPlanes.json", width=960, height=504, samples=25, superSamples=4,
+                name="planar cornellBox (3 spheres + 6 planes, extension) 960x504 x 400 spp"),
+    "c4p": dict(scene="cornellBoxPlanes", file="cornellBoxPlanes.json", width=3840, height=2160, samples=64, superSamples=4,
+                name="planar cornellBox (3 spheres + 6 planes, extension) 3840x2160 x 1024 spp"),
     "tiny": dict(scene="cornellBox", width=192, height=108, samples=8, superSamples=2,
                  name="cornellBox 192x108 x 32 spp (plumbing check only)"),
 }
@@ -115,7 +120,7 @@ def cpu_render_sample(sc, wl, target_seconds: float):
     cores = os.cpu_count() or 1
     w, h = max(16, sc.width // 8), max(9, sc.height // 8)
     small = sc.with_dims(w, h, 1, sc.superSamples)
-    use_ref = O.ref_available("abc")
+    use_ref = O.ref_available("abc") and sc.n_planes == 0   # the reference's objects cannot hold a plane
 
     def run(S):
         s2 = small.with_dims(samples=S)
@@ -341,6 +346,8 @@ def run_gpu_arm(args):
             "data": "synthetic",
             "config": {"workload": wl["name"], "scene": wl["scene"], "width": sc.width, "height": sc.height,
                        "samples": sc.samples, "superSamples": sc.superSamples, "spp": sc.spp, "n_spheres": sc.n,
+                       **({"n_planes": sc.n_planes, "flops_note": "plane tests are not counted (the 17-flop figure is the sphere test's)"}
+                          if sc.n_planes else {}),
                        "variant": args.variant,
                        "closest_hit": "brute force (packed pairs)" if sc.n <= 64 else
                                       f"hierarchy: {st.sphere_tests / max(1, st.rays_traced):.1f} sphere tests + "

@@ -30,7 +30,7 @@
 extern "C" {
 #endif
 
-#define RTM_ABI_VERSION 2
+#define RTM_ABI_VERSION 3
 
 enum {
     RTM_OK = 0,
@@ -85,6 +85,20 @@ typedef struct rtm_scene_desc {
     const float* radius;            /* [n]    SphereObject::m_size (FLOAT, src/SettingData.h:31) */
     const double* color;            /* [n][3] Material::color */
     const double* emission;         /* [n][3] Material::emission */
+    /* EXTENSION (ABI 3): PlaneObject, "00 objectType" 2 — declared by the reference
+     * (src/SettingData.h:33-42) but never parsed and never intersected (src/SettingData.cpp:243-246
+     * falls off the end), so there is no reference behaviour to match; DESIGN.md §10 defines it as a
+     * finite square.  Arrays are the ctor arguments of src/SettingData.cpp:235.  Planes take the
+     * object ids n_spheres .. n_spheres+n_planes-1 (hit map, tie rule).  COMPAT_ABC only; the FP32
+     * path takes them in the brute-force megakernel (n_spheres + n_planes <= 256, n_planes <= 16).
+     * n_planes = 0 (and NULL arrays) = the reference's scenes. */
+    int32_t n_planes;
+    const double* plane_position;   /* [m][3] */
+    const double* plane_up;         /* [m][3] */
+    const double* plane_target;     /* [m][3] */
+    const double* plane_width;      /* [m]    */
+    const double* plane_color;      /* [m][3] */
+    const double* plane_emission;   /* [m][3] */
 } rtm_scene_desc;
 
 typedef struct rtm_options {

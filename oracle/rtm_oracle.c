@@ -68,6 +68,65 @@ int rtmo_intersect_sphere(const double* center3, float radius, const double* org
     return hit;
 }
 
+/* ---- plane: EXTENSION -----------------------------------------
+ * The reference declares PlaneObject (src/SettingData.h:33-42) but its Intersect only
+ * rejects parallel rays and then falls off the end (src/SettingData.cpp:243-246): there is
+ * nothing to be in parity with.  Defined here as a finite square, keeping what the
+ * reference does define:
+ *   ctor (src/SettingData.cpp:235-242): normal = Normalize(target - position) (float-sqrt
+ *        Normalize), right = Normalize(Cross(normal, up)) * 0.5 * width;
+ *   added: upp = Cross(right, normal) (half-extent vector of the other side),
+ *        rr = Dot(right,right), uu = Dot(upp,upp);
+ *   Intersect: reject |Dot(normal,dir)| < FLT_EPSILON (:244-245); t = Dot(normal, position
+ *        - org) / Dot(normal, dir); accept t > 0.001 (the sphere's near threshold, :209) with
+ *        q = org + dir*t - position, |Dot(q,right)| <= rr and |Dot(q,upp)| <= uu;
+ *        out_normal = normal (PathTracing orients it, src/Renderer.cpp:82-83). */
+typedef struct { v3 position, normal, right, upp; double rr, uu; } plane_t;
+
+static plane_t make_plane(v3 position, v3 up, v3 target, double width) {
+    plane_t p;
+    p.position = position;
+    p.normal = normalize3(v3_sub(target, position));
+    p.right = v3_scale(v3_scale(normalize3(cross3(p.normal, up)), 0.5), width);
+    p.upp = cross3(p.right, p.normal);
+    p.rr = dot3(p.right, p.right);
+    p.uu = dot3(p.upp, p.upp);
+    return p;
+}
+
+static int intersect_plane(const plane_t* p, v3 org, v3 dir, double* out_dis, v3* out_normal) {
+    const double dn = dot3(p->normal, dir);
+    if (fabs(dn) < FLT_EPSILON) return 0;
+    const double t = dot3(p->normal, v3_sub(p->position, org)) / dn;
+    if (!(t > 0.001)) return 0;
+    const v3 q = v3_sub(v3_add(org, v3_scale(dir, t)), p->position);
+    if (fabs(dot3(q, p->right)) > p->rr || fabs(dot3(q, p->upp)) > p->uu) return 0;
+    *out_dis = t;
+    *out_normal = p->normal;
+    return 1;
+}
+
+static plane_t scene_plane(const rtmo_scene* s, int j) {
+    return make_plane(v3_load(s->pl_position + 3 * j), v3_load(s->pl_up + 3 * j), v3_load(s->pl_target + 3 * j), s->pl_width[j]);
+}
+
+void rtmo_plane_frame(const double* position3, const double* up3, const double* target3, double width, double* out11) {
+    const plane_t p = make_plane(v3_load(position3), v3_load(up3), v3_load(target3), width);
+    v3_store(out11, p.normal); v3_store(out11 + 3, p.right); v3_store(out11 + 6, p.upp);
+    out11[9] = p.rr; out11[10] = p.uu;
+}
+
+int rtmo_intersect_plane(const double* position3, const double* up3, const double* target3, double width,
+                         const double* org3, const double* dir3, double* t_out, double* normal3) {
+    const plane_t p = make_plane(v3_load(position3), v3_load(up3), v3_load(target3), width);
+    double t = 0.0;
+    v3 n = {0, 0, 0};
+    const int hit = intersect_plane(&p, v3_load(org3), v3_load(dir3), &t, &n);
+    *t_out = t;
+    if (hit && normal3) v3_store(normal3, n);
+    return hit;
+}
+
 /* ---- camera (src/Renderer.cpp:202-208, 227-232) --------------------------- */
 typedef struct { v3 camX, camY, camZ; double fovx, fovy; } frame_t;
 
@@ -118,6 +177,16 @@ static int closest_hit(const rtmo_scene* s, v3 org, v3 dir, double* dis_out, v3*
             dis = tmp_dis;
             normal = tmp_normal;
             hitObject = i;
+        }
+    }
+    for (int j = 0; j < s->n_planes; ++j) { /* extension: planes follow the spheres in the object list */
+        double tmp_dis;
+        v3 tmp_normal;
+        const plane_t p = scene_plane(s, j);
+        if (intersect_plane(&p, org, dir, &tmp_dis, &tmp_normal) && tmp_dis < dis && tmp_dis > 0) {
+            dis = tmp_dis;
+            normal = tmp_normal;
+            hitObject = s->n + j;
         }
     }
     if (dis_out) *dis_out = dis;
@@ -197,8 +266,9 @@ static v3 path_trace(const rtmo_scene* s, int level, v3 org, v3 dir, mt19937_t* 
     c->rays++;
     const int hitObject = closest_hit(s, org, dir, &dis, &normal);
     if (hitObject == -1 || !(dis > 0)) return v3_make(0, 0, 0);
-    const v3 color = v3_load(s->color + 3 * hitObject);
-    const v3 emission = v3_load(s->emission + 3 * hitObject);
+    const int isPlane = hitObject >= s->n;
+    const v3 color = isPlane ? v3_load(s->pl_color + 3 * (hitObject - s->n)) : v3_load(s->color + 3 * hitObject);
+    const v3 emission = isPlane ? v3_load(s->pl_emission + 3 * (hitObject - s->n)) : v3_load(s->emission + 3 * hitObject);
     const float kd = material_kd(color);
     if (!(mt_uniform01(rng) <= kd)) return emission; /* :78, :112 */
     const v3 colorKD = v3_div(color, (double)kd);      /* SettingData.h:11-13 */
@@ -284,7 +354,8 @@ int rtmo_render_head_exact(const rtmo_scene* s, double* image) {
             for (int sx = 1; sx <= s->superSamples; ++sx)
                 for (int sy = 1; sy <= s->superSamples; ++sy) {
                     const int h = closest_hit(s, org, camera_dir(s, &f, x, y, sx, sy), NULL, NULL);
-                    v3 cal = (h < 0) ? v3_make(0, 0, 0) : v3_load(s->emission + 3 * h);
+                    v3 cal = (h < 0) ? v3_make(0, 0, 0)
+                                     : (h >= s->n) ? v3_load(s->pl_emission + 3 * (h - s->n)) : v3_load(s->emission + 3 * h);
                     cal = v3_div(v3_div(v3_div(cal, s->superSamples), s->superSamples), s->samples);
                     cal = v3_make(clamp01(cal.x), clamp01(cal.y), clamp01(cal.z));
                     for (int smp = 0; smp < s->samples; ++smp) acc = v3_add(acc, cal);

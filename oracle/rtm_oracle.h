@@ -31,7 +31,23 @@ typedef struct rtmo_scene {
     const float* radius;     /* [n]     SphereObject::m_size     (FLOAT, src/SettingData.h:31) */
     const double* color;     /* [n][3]  Material::color */
     const double* emission;  /* [n][3]  Material::emission */
+    /* EXTENSION (no reference semantics to pin): PlaneObject, objectType 2.
+     * Object indices n .. n+n_planes-1; ctor arguments of src/SettingData.cpp:235. */
+    int32_t n_planes;
+    const double* pl_position;  /* [m][3] */
+    const double* pl_up;        /* [m][3] */
+    const double* pl_target;    /* [m][3] */
+    const double* pl_width;     /* [m]    */
+    const double* pl_color;     /* [m][3] */
+    const double* pl_emission;  /* [m][3] */
 } rtmo_scene;
+
+/* Derived plane frame: normal[3], right[3], upp[3], rr, uu (11 doubles), see rtm_oracle.c. */
+void rtmo_plane_frame(const double* position3, const double* up3, const double* target3, double width, double* out11);
+
+/* The extension's finite-square test; returns 1 on hit. */
+int rtmo_intersect_plane(const double* position3, const double* up3, const double* target3, double width,
+                         const double* org3, const double* dir3, double* t_out, double* normal3);
 
 /* src/SettingData.cpp:197-226; returns 1 on hit. normal3 written only on hit. */
 int rtmo_intersect_sphere(const double* center3, float radius, const double* org3, const double* dir3,

@@ -39,6 +39,10 @@ class _SceneDesc(C.Structure):
         ("fov", C.c_float), ("n_spheres", C.c_int32),
         ("position", C.POINTER(C.c_double)), ("radius", C.POINTER(C.c_float)),
         ("color", C.POINTER(C.c_double)), ("emission", C.POINTER(C.c_double)),
+        # ABI 3: PlaneObject extension
+        ("n_planes", C.c_int32),
+        ("plane_position", C.POINTER(C.c_double)), ("plane_up", C.POINTER(C.c_double)), ("plane_target", C.POINTER(C.c_double)),
+        ("plane_width", C.POINTER(C.c_double)), ("plane_color", C.POINTER(C.c_double)), ("plane_emission", C.POINTER(C.c_double)),
     ]
 
 
@@ -154,17 +158,7 @@ class Renderer:
         self._h = C.c_void_p()
         sc = scene.normalized()
         self.scene = sc
-        d = _SceneDesc()
-        d.width, d.height, d.samples, d.superSamples = sc.width, sc.height, sc.samples, sc.superSamples
-        d.cam_origin[:] = list(sc.cam_origin)
-        d.cam_target[:] = list(sc.cam_target)
-        d.cam_up[:] = list(sc.cam_up)
-        d.fov = sc.fov
-        d.n_spheres = sc.n
-        d.position = sc.position.ctypes.data_as(C.POINTER(C.c_double))
-        d.radius = sc.radius.ctypes.data_as(C.POINTER(C.c_float))
-        d.color = sc.color.ctypes.data_as(C.POINTER(C.c_double))
-        d.emission = sc.emission.ctypes.data_as(C.POINTER(C.c_double))
+        d = self._desc(sc)
         o = _Options()
         self._lib.renderer_default_options(C.byref(o))
         o.device, o.n_gpus = device, n_gpus
@@ -189,6 +183,12 @@ class Renderer:
         d.radius = sc.radius.ctypes.data_as(C.POINTER(C.c_float))
         d.color = sc.color.ctypes.data_as(C.POINTER(C.c_double))
         d.emission = sc.emission.ctypes.data_as(C.POINTER(C.c_double))
+        d.n_planes = sc.n_planes
+        if sc.n_planes:
+            dp = C.POINTER(C.c_double)
+            d.plane_position, d.plane_up = sc.pl_position.ctypes.data_as(dp), sc.pl_up.ctypes.data_as(dp)
+            d.plane_target, d.plane_width = sc.pl_target.ctypes.data_as(dp), sc.pl_width.ctypes.data_as(dp)
+            d.plane_color, d.plane_emission = sc.pl_color.ctypes.data_as(dp), sc.pl_emission.ctypes.data_as(dp)
         return d
 
     # -- the drop-in call: host buffers in, host buffers out

@@ -49,6 +49,35 @@ __device__ __forceinline__ bool sphere_test(d3 c, double r2, d3 o, d3 d, double&
     return true;
 }
 
+// PlaneObject EXTENSION (no reference semantics: SettingData.cpp:243-246 only rejects parallel
+// rays and falls off the end).  Finite square, operation for operation the definition in DESIGN.md §10:
+// intersect_plane: t = n.(position - o) / n.d, accepted for t > 0.001 inside |q.right| <= rr,
+// |q.upp| <= uu.  The frame (normal, right, upp, rr, uu) is derived on the host.
+__device__ __forceinline__ bool plane_test(const double* __restrict__ pl, d3 o, d3 d, double& t) {
+    const d3 n = mk(__ldg(pl + 0), __ldg(pl + 1), __ldg(pl + 2));
+    const double dn = dot(n, d);
+    if (fabs(dn) < (double)FLT_EPSILON) return false;   // SettingData.cpp:244-245
+    const d3 pos = mk(__ldg(pl + 3), __ldg(pl + 4), __ldg(pl + 5));
+    const double tt = dot(n, sub(pos, o)) / dn;
+    if (!(tt > 0.001)) return false;
+    const d3 q = sub(add(o, scale(d, tt)), pos);
+    if (fabs(dot(q, mk(__ldg(pl + 6), __ldg(pl + 7), __ldg(pl + 8)))) > __ldg(pl + 12)) return false;
+    if (fabs(dot(q, mk(__ldg(pl + 9), __ldg(pl + 10), __ldg(pl + 11)))) > __ldg(pl + 13)) return false;
+    t = tt;
+    return true;
+}
+
+// planes follow the spheres in the object list: strict `<` keeps a sphere on an exact tie
+__device__ __forceinline__ void consider_planes(const RtmSceneF64& sc, d3 o, d3 d, double& best, int& id) {
+    for (int j = 0; j < sc.n_planes; ++j) {
+        double t;
+        if (plane_test(sc.planes + 16 * j, o, d, t) && t < best && t > 0.0) {
+            best = t;
+            id = sc.n + j;
+        }
+    }
+}
+
 // Renderer.cpp:58-73: strict `<` keeps the lowest index on exact ties; `t > 0`.
 __device__ __forceinline__ int closest_hit_brute(const RtmSceneF64& sc, d3 o, d3 d, double& best) {
     int id = -1;
@@ -61,6 +90,7 @@ __device__ __forceinline__ int closest_hit_brute(const RtmSceneF64& sc, d3 o, d3
             id = i;
         }
     }
+    consider_planes(sc, o, d, best, id);
     return id;
 }
 
@@ -116,7 +146,10 @@ __device__ int closest_hit_bvh(const RtmSceneF64& sc, d3 o, d3 d, double& best, 
     best = DBL_MAX;
     for (int j = 0; j < sc.bvh.n_big; ++j) consider(sc, sc.bvh.big_id[j], o, d, best, id);
     int node = sc.bvh.root;
-    if (node == 0x7FFFFFFF) return id;
+    if (node == 0x7FFFFFFF) {
+        consider_planes(sc, o, d, best, id);
+        return id;
+    }
     const double ke = 4.5 * (fabs(dd - 1.0) + 1e-14);
     const d3 orel = mk(o.x - sc.ref[0], o.y - sc.ref[1], o.z - sc.ref[2]);
     const d3 inv = mk(1.0 / d.x, 1.0 / d.y, 1.0 / d.z);
@@ -149,6 +182,7 @@ __device__ int closest_hit_bvh(const RtmSceneF64& sc, d3 o, d3 d, double& best, 
             node = stack[--sp];
         }
     }
+    consider_planes(sc, o, d, best, id);
     return id;
 }
 
@@ -158,6 +192,15 @@ __device__ __forceinline__ int closest_hit(const RtmSceneF64& sc, d3 o, d3 d, do
 
 __device__ __forceinline__ d3 sphere_center(const RtmSceneF64& sc, int i) {
     return mk(__ldg(sc.cx + i), __ldg(sc.cy + i), __ldg(sc.cz + i));
+}
+
+// the normal Intersect hands back: SettingData.cpp:214-215 for a sphere, the plane's own normal (extension)
+__device__ __forceinline__ d3 hit_normal(const RtmSceneF64& sc, int id, d3 o, d3 d, double t) {
+    if (id >= sc.n) {
+        const double* pl = sc.planes + 16 * (id - sc.n);
+        return mk(__ldg(pl + 0), __ldg(pl + 1), __ldg(pl + 2));
+    }
+    return normalize(sub(add(o, scale(d, t)), sphere_center(sc, id)));
 }
 
 // Renderer.cpp:227-232.  `rate` is float, rate*sx is a float product, the
@@ -208,11 +251,12 @@ __device__ __forceinline__ void primary_one(const RtmSceneF64& sc, const RtmPass
             rec = make_float4(0.f, 0.f, 0.f, __uint_as_float(RTM_REC_MISS));
         } else {
             const d3 hp = add(scale(d, t), o);                          // Renderer.cpp:79
-            const d3 n = normalize(sub(add(o, scale(d, t)), sphere_center(sc, id)));  // SettingData.cpp:214-215
+            const d3 n = hit_normal(sc, id, o, d, t);
             const uint32_t flip = (dot(n, d) < 0.0) ? 0u : RTM_REC_FLIP;   // Renderer.cpp:82-83
             rec = make_float4((float)(hp.x - p.refd[0]), (float)(hp.y - p.refd[1]), (float)(hp.z - p.refd[2]),
                               __uint_as_float((uint32_t)id | flip));
-            if (cps0) {
+            if (cps0 && id >= sc.n) cps0[q] = 0.f;
+            else if (cps0) {
                 // what SettingData.cpp:198-200 will see for THIS sphere from the bounce origin hp:
                 // c' = |p_o|^2 - r^2, nonzero because d is unit only to float precision (Ray.h:67-72)
                 const d3 p_o = sub(sphere_center(sc, id), hp);
@@ -301,7 +345,7 @@ __global__ void __launch_bounds__(128) radiance_f64_kernel(RtmSceneF64 sc, RtmPa
                 const d3 col = mk(__ldg(sc.color + 3 * id), __ldg(sc.color + 3 * id + 1), __ldg(sc.color + 3 * id + 2));
                 T = mul(T, divs(col, kd));                   // colorKD(), SettingData.h:11-13
                 const d3 hp = add(scale(d, t), o);           // :79
-                const d3 n = normalize(sub(add(o, scale(d, t)), sphere_center(sc, id)));
+                const d3 n = hit_normal(sc, id, o, d, t);
                 const d3 w = (dot(n, d) < 0.0) ? n : scale(n, -1.0);  // :82-83,87
                 const double r1 = 2 * PI * rtm_u01_f64_32(r.z);       // :88
                 const double r2 = rtm_u01_f64_32(r.w);                // :89

@@ -196,6 +196,28 @@ __device__ __forceinline__ int trace_f32(const SelfMask& sm, int n_rt, int oid, 
     return trace_loop_f32(n_rt, oid, o, d, t);
 }
 
+// ---- PlaneObject extension ---------------------------------------
+// Finite squares from constant memory (uniform index: one broadcast per constant), tested after the
+// spheres; (t, id) are updated in place, `t < best` keeps a sphere on an exact tie.  The plane a ray
+// leaves is skipped by id (the FP64 definition rejects it through t > 1e-3: t is 0 there).
+__device__ __forceinline__ void trace_planes_f32(int n_sph, int n_pl, int oid, f3 o, f3 d, float& t, int& id) {
+    for (int j = 0; j < n_pl; ++j) {
+        const RtmPlaneF32& pl = c_scene.planes[j];
+        const float dn = fmaf(pl.nx, d.x, fmaf(pl.ny, d.y, pl.nz * d.z));
+        const float num = pl.d0 - fmaf(pl.nx, o.x, fmaf(pl.ny, o.y, pl.nz * o.z));
+        const float tt = num * fast_rcp(dn);
+        if (n_sph + j != oid && fabsf(dn) >= FLT_EPSILON && tt > RTM_T_EPS && tt < t) {
+            const f3 q = mk(fmaf(d.x, tt, o.x) - pl.px, fmaf(d.y, tt, o.y) - pl.py, fmaf(d.z, tt, o.z) - pl.pz);
+            const float a = fmaf(q.x, pl.rx, fmaf(q.y, pl.ry, q.z * pl.rz));
+            const float b = fmaf(q.x, pl.ux, fmaf(q.y, pl.uy, q.z * pl.uz));
+            if (fabsf(a) <= 1.f && fabsf(b) <= 1.f) {
+                t = tt;
+                id = n_sph + j;
+            }
+        }
+    }
+}
+
 // ---- closest hit through the hierarchy (bvh.h), FP32 ------------------------------
 // Up to 8 "big" spheres (the r = 1e4 walls) go through the packed pair test above with the
 // cancellation-free K form; everything else sits in a two-child hierarchy walked per lane
@@ -406,11 +428,12 @@ __device__ __forceinline__ float ref_normalize_eps(uint32_t bits) {
 // RNG: one rtm_bounce_rng call per hit (pcg3d hash, philox.cuh), counter = (sub-pixel, sample<<9 | depth), key
 // from the seed: x -> roulette (32-bit compare against kd*2^32), y -> azimuth,
 // the low bits of x and y -> height.
-template <int N, bool BVH, bool ACNE>
+// PL: the scene also holds n_pl planes (extension); their records sit behind the spheres', ids n .. n+n_pl-1.
+template <int N, bool BVH, bool ACNE, bool PL>
 __global__ void __launch_bounds__(RTM_MEGA_THREADS, BVH ? 4 : 5) radiance_mega_kernel(RtmPassParams p, float4* __restrict__ records,
                                                                                       RtmCounters* __restrict__ counters, int n_rt,
                                                                                       RtmBvhDev bvh, RtmMatDev mat,
-                                                                                      const float* __restrict__ cps0) {
+                                                                                      const float* __restrict__ cps0, int n_pl) {
     // brute force: N spheres (0 = runtime n_rt) with their records in shared memory;
     // hierarchy: N = slots of the packed big-sphere test (even, 0..8), records in global memory
     __shared__ SharedScene sh;
@@ -422,7 +445,7 @@ __global__ void __launch_bounds__(RTM_MEGA_THREADS, BVH ? 4 : 5) radiance_mega_k
         if (threadIdx.x < 8) sh_big.id[threadIdx.x] = (threadIdx.x < (unsigned)bvh.n_big) ? bvh.big_id[threadIdx.x] : 0;
         __syncthreads();
     } else {
-        load_shared_scene(sh, n);
+        load_shared_scene(sh, PL ? n + n_pl : n);
     }
     SceneRecs<BVH> recs;
     recs.sh = &sh;
@@ -499,6 +522,7 @@ __global__ void __launch_bounds__(RTM_MEGA_THREADS, BVH ? 4 : 5) radiance_mega_k
                     const float4 g = recs.geo(Pid);
                     const float ir = (wbits & RTM_REC_FLIP) ? -g.w : g.w;
                     Pw = mk((P.x - g.x) * ir, (P.y - g.y) * ir, (P.z - g.z) * ir);
+                    if (PL && Pid >= n) Pw = (wbits & RTM_REC_FLIP) ? mk(-g.x, -g.y, -g.z) : mk(g.x, g.y, g.z);
                     acc = mk(0, 0, 0);
                     s = s_begin;
                     o = P; id = Pid; w = Pw;
@@ -533,7 +557,7 @@ __global__ void __launch_bounds__(RTM_MEGA_THREADS, BVH ? 4 : 5) radiance_mega_k
                 float cosw = 0.f;
                 if (ACNE) {
                     cosw = dot(w, d);
-                    selfhit = (cpsn + cosw <= 0.f);
+                    selfhit = (cpsn + cosw <= 0.f) && !(PL && id >= n);
                 }
                 if (ACNE && selfhit) {
                     // SettingData.cpp:208-212: t1 <= 0.001 -> t2 of the sphere the ray stands (just) inside
@@ -542,12 +566,17 @@ __global__ void __launch_bounds__(RTM_MEGA_THREADS, BVH ? 4 : 5) radiance_mega_k
                     t = q * fast_rcp(bq + fast_sqrt(fmaf(bq, bq, q)));
                     id2 = id;
                 } else if (BVH) id2 = trace_bvh_f32<N / 2>(sh_mask, sh_big, bvh, id, __float_as_int(al.w), o, d, t, key_mask, n_tests, n_nodes);
-                else id2 = trace_f32<N>(sh_mask, n, id, o, d, t, key_mask);
+                else {
+                    // a ray leaving a plane has no origin sphere (the self mask only has rows for spheres)
+                    id2 = trace_f32<N>(sh_mask, n, (PL && id >= n) ? -1 : id, o, d, t, key_mask);
+                    if (PL) trace_planes_f32(n, n_pl, id, o, d, t, id2);
+                }
                 ++traced;
                 if (id2 >= 0) {
                     o = mk(fmaf(d.x, t, o.x), fmaf(d.y, t, o.y), fmaf(d.z, t, o.z));  // Renderer.cpp:79
                     const float4 g = recs.geo(id2);
                     f3 nn = mk((o.x - g.x) * g.w, (o.y - g.y) * g.w, (o.z - g.z) * g.w);
+                    if (PL && id2 >= n) nn = mk(g.x, g.y, g.z);
                     if (BVH && g.w > 1e-2f) {
                         // small spheres: t carries an absolute error of ~1e-5 that is not small against
                         // r = 0.05; put the hit back on the surface and make the normal unit
@@ -916,7 +945,7 @@ __global__ void __launch_bounds__(256) pack_rgb_kernel(const float4* __restrict_
 }
 
 // ---- test hooks ---------------------------------------------------------------
-__global__ void closest_hit_f32_kernel(int n_sph, unsigned key_mask, double rx, double ry, double rz, uint32_t n, const double* __restrict__ org,
+__global__ void closest_hit_f32_kernel(int n_sph, int n_pl, unsigned key_mask, double rx, double ry, double rz, uint32_t n, const double* __restrict__ org,
                                        const double* __restrict__ dir, const int32_t* __restrict__ origin_id,
                                        int32_t* __restrict__ hit, double* __restrict__ tout) {
     __shared__ SelfMask sh_mask;
@@ -927,8 +956,9 @@ __global__ void closest_hit_f32_kernel(int n_sph, unsigned key_mask, double rx, 
     const f3 o = mk((float)(org[3 * i] - rx), (float)(org[3 * i + 1] - ry), (float)(org[3 * i + 2] - rz));
     const f3 d = mk((float)dir[3 * i], (float)dir[3 * i + 1], (float)dir[3 * i + 2]);
     float t;
-    int oid = origin_id ? origin_id[i] : -1;
-    if (oid < -1 || oid >= n_sph) oid = -1;
+    int oid_all = origin_id ? origin_id[i] : -1;
+    if (oid_all < -1 || oid_all >= n_sph + n_pl) oid_all = -1;
+    const int oid = (oid_all >= n_sph) ? -1 : oid_all;
     int id;
     // same code paths as the megakernel: packed pairs up to 8 spheres, the loop beyond
     if (n_sph >= 1 && n_sph <= 2) id = trace_f32<2>(sh_mask, n_sph, oid, o, d, t, key_mask);
@@ -936,6 +966,7 @@ __global__ void closest_hit_f32_kernel(int n_sph, unsigned key_mask, double rx, 
     else if (n_sph <= 6 && n_sph >= 5) id = trace_f32<6>(sh_mask, n_sph, oid, o, d, t, key_mask);
     else if (n_sph <= 8 && n_sph >= 7) id = trace_f32<8>(sh_mask, n_sph, oid, o, d, t, key_mask);
     else id = trace_f32<0>(sh_mask, n_sph, oid, o, d, t, key_mask);
+    trace_planes_f32(n_sph, n_pl, oid_all, o, d, t, id);
     hit[i] = id;
     tout[i] = (double)t;
 }
@@ -991,36 +1022,41 @@ __global__ void __launch_bounds__(256) fma_peak_kernel(float* __restrict__ sink,
     if (r == 12345.678f) sink[0] = r;
 }
 
-template <int N, bool BVH, bool ACNE>
-void launch_mega2(const RtmPassParams& p, float4* records, RtmCounters* counters, int n_rt, int sm_count, cudaStream_t st,
+template <int N, bool BVH, bool ACNE, bool PL>
+void launch_mega2(const RtmPassParams& p, float4* records, RtmCounters* counters, int n_rt, int n_pl, int sm_count, cudaStream_t st,
                   const RtmBvhDev& bvh, const RtmMatDev& mat, const float* cps0) {
     int per_sm = 0;
-    cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, radiance_mega_kernel<N, BVH, ACNE>, RTM_MEGA_THREADS, 0);
+    cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, radiance_mega_kernel<N, BVH, ACNE, PL>, RTM_MEGA_THREADS, 0);
     if (per_sm < 1) per_sm = 1;
-    radiance_mega_kernel<N, BVH, ACNE><<<sm_count * per_sm, RTM_MEGA_THREADS, 0, st>>>(p, records, counters, n_rt, bvh, mat, cps0);
+    radiance_mega_kernel<N, BVH, ACNE, PL><<<sm_count * per_sm, RTM_MEGA_THREADS, 0, st>>>(p, records, counters, n_rt, bvh, mat, cps0, n_pl);
 }
-// cps0 != null selects the ACNE instantiation (see ref_normalize_eps)
+// cps0 != null selects the ACNE instantiation (see ref_normalize_eps), n_pl > 0 the one with the plane loop
 template <int N, bool BVH>
-void launch_mega(const RtmPassParams& p, float4* records, RtmCounters* counters, int n_rt, int sm_count, cudaStream_t st,
+void launch_mega(const RtmPassParams& p, float4* records, RtmCounters* counters, int n_rt, int n_pl, int sm_count, cudaStream_t st,
                  const float* cps0, const RtmBvhDev& bvh = RtmBvhDev{}, const RtmMatDev& mat = RtmMatDev{}) {
-    if (cps0) launch_mega2<N, BVH, true>(p, records, counters, n_rt, sm_count, st, bvh, mat, cps0);
-    else launch_mega2<N, BVH, false>(p, records, counters, n_rt, sm_count, st, bvh, mat, nullptr);
+    if (n_pl > 0) {
+        if (cps0) launch_mega2<N, BVH, true, true>(p, records, counters, n_rt, n_pl, sm_count, st, bvh, mat, cps0);
+        else launch_mega2<N, BVH, false, true>(p, records, counters, n_rt, n_pl, sm_count, st, bvh, mat, nullptr);
+    } else {
+        if (cps0) launch_mega2<N, BVH, true, false>(p, records, counters, n_rt, 0, sm_count, st, bvh, mat, cps0);
+        else launch_mega2<N, BVH, false, false>(p, records, counters, n_rt, 0, sm_count, st, bvh, mat, nullptr);
+    }
 }
 
 }  // namespace
 
-void rtm_launch_radiance_mega(int32_t n, const RtmPassParams& p, float4* records, RtmCounters* counters, int32_t sm_count,
-                              const float* cps0, cudaStream_t st) {
+void rtm_launch_radiance_mega(int32_t n, int32_t n_pl, const RtmPassParams& p, float4* records, RtmCounters* counters,
+                              int32_t sm_count, const float* cps0, cudaStream_t st) {
     switch (n) {
-        case 1: launch_mega<1, false>(p, records, counters, n, sm_count, st, cps0); break;
-        case 2: launch_mega<2, false>(p, records, counters, n, sm_count, st, cps0); break;
-        case 3: launch_mega<3, false>(p, records, counters, n, sm_count, st, cps0); break;
-        case 4: launch_mega<4, false>(p, records, counters, n, sm_count, st, cps0); break;
-        case 5: launch_mega<5, false>(p, records, counters, n, sm_count, st, cps0); break;
-        case 6: launch_mega<6, false>(p, records, counters, n, sm_count, st, cps0); break;
-        case 7: launch_mega<7, false>(p, records, counters, n, sm_count, st, cps0); break;
-        case 8: launch_mega<8, false>(p, records, counters, n, sm_count, st, cps0); break;
-        default: launch_mega<0, false>(p, records, counters, n, sm_count, st, cps0); break;
+        case 1: launch_mega<1, false>(p, records, counters, n, n_pl, sm_count, st, cps0); break;
+        case 2: launch_mega<2, false>(p, records, counters, n, n_pl, sm_count, st, cps0); break;
+        case 3: launch_mega<3, false>(p, records, counters, n, n_pl, sm_count, st, cps0); break;
+        case 4: launch_mega<4, false>(p, records, counters, n, n_pl, sm_count, st, cps0); break;
+        case 5: launch_mega<5, false>(p, records, counters, n, n_pl, sm_count, st, cps0); break;
+        case 6: launch_mega<6, false>(p, records, counters, n, n_pl, sm_count, st, cps0); break;
+        case 7: launch_mega<7, false>(p, records, counters, n, n_pl, sm_count, st, cps0); break;
+        case 8: launch_mega<8, false>(p, records, counters, n, n_pl, sm_count, st, cps0); break;
+        default: launch_mega<0, false>(p, records, counters, n, n_pl, sm_count, st, cps0); break;
     }
 }
 
@@ -1123,9 +1159,9 @@ void rtm_launch_to_u8(const float4* accum, unsigned char* out, uint64_t n_pix, c
     to_u8_kernel<<<(unsigned)((n_pix + 255) / 256), 256, 0, st>>>(accum, out, n_pix);
 }
 
-void rtm_launch_closest_hit_f32(int32_t n_spheres, const double* refd, uint32_t n, const double* org, const double* dir,
+void rtm_launch_closest_hit_f32(int32_t n_spheres, int32_t n_planes, const double* refd, uint32_t n, const double* org, const double* dir,
                                 const int32_t* origin_id, int32_t* hit, double* t, cudaStream_t st) {
-    closest_hit_f32_kernel<<<(n + 127) / 128, 128, 0, st>>>(n_spheres, 0xFFFFFFF8u, refd[0], refd[1], refd[2], n, org, dir, origin_id, hit, t);
+    closest_hit_f32_kernel<<<(n + 127) / 128, 128, 0, st>>>(n_spheres, n_planes, 0xFFFFFFF8u, refd[0], refd[1], refd[2], n, org, dir, origin_id, hit, t);
 }
 
 void rtm_launch_closest_hit_bvh_f32(const RtmBvhDev& bvh, const RtmMatDev& mat, int32_t n_spheres, const double* refd, uint32_t n,

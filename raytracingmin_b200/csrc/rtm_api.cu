@@ -93,6 +93,7 @@ struct v3 {
 v3 vsub(v3 a, v3 b) { return {a.x - b.x, a.y - b.y, a.z - b.z}; }
 v3 vneg(v3 a) { return {-a.x, -a.y, -a.z}; }
 v3 vscale(v3 a, double s) { return {a.x * s, a.y * s, a.z * s}; }
+double vdot(v3 a, v3 b) { return a.x * b.x + a.y * b.y + a.z * b.z; }  // Ray.h:61-63
 v3 vcross(v3 a, v3 b) { return {a.y * b.z - a.z * b.y, -a.x * b.z + a.z * b.x, a.x * b.y - a.y * b.x}; }  // Ray.h:64-66
 v3 vnormalize(v3 a) {                                                                                        // Ray.h:67-72
     const double m = (double)sqrtf((float)(a.x * a.x + a.y * a.y + a.z * a.z));
@@ -134,7 +135,7 @@ struct GpuCtx {
 
 struct rtm_renderer {
     rtm_options opt{};
-    int32_t W = 0, H = 0, S = 0, ss = 0, n = 0;
+    int32_t W = 0, H = 0, S = 0, ss = 0, n = 0, n_planes = 0;
     uint64_t n_pix = 0, n_sub = 0;
     RtmFrame frame{};
     RtmSceneF32Host f32{};
@@ -252,7 +253,7 @@ int enqueue_pass(rtm_renderer* r, GpuCtx& c, cudaStream_t st, bool want_hits, in
             }
             c.waves = wave;
         } else if (r->use_bvh) rtm_launch_radiance_bvh(c.bvh, c.mat, p, c.records, c.counters, c.sm_count, c.cps0, st);
-        else rtm_launch_radiance_mega(r->n, p, c.records, c.counters, c.sm_count, c.cps0, st);
+        else rtm_launch_radiance_mega(r->n, r->n_planes, p, c.records, c.counters, c.sm_count, c.cps0, st);
         CU(cudaEventRecord(c.ek[2], st));
         rtm_launch_accumulate(p, c.records, c.accum, st);
         CU(cudaEventRecord(c.ek[3], st));
@@ -334,6 +335,10 @@ int renderer_create(const rtm_scene_desc* sc, const rtm_options* opt_in, rtm_ren
     if (sc->n_spheres < 0 || (sc->n_spheres > 0 && (!sc->position || !sc->radius || !sc->color || !sc->emission)))
         return fail(RTM_E_INVALID, "scene arrays missing for %d spheres", sc->n_spheres);
     if (sc->n_spheres > (int32_t)RTM_REC_IDMASK) return fail(RTM_E_INVALID, "too many spheres");
+    const int m = sc->n_planes;
+    if (m < 0 || (m > 0 && (!sc->plane_position || !sc->plane_up || !sc->plane_target || !sc->plane_width || !sc->plane_color ||
+                            !sc->plane_emission)))
+        return fail(RTM_E_INVALID, "scene arrays missing for %d planes", m);
     if (opt.n_gpus < 1) opt.n_gpus = 1;
     if (opt.max_depth <= 0) opt.max_depth = 256;
     if (opt.compat != RTM_COMPAT_HEAD && opt.compat != RTM_COMPAT_ABC) return fail(RTM_E_INVALID, "bad compat %d", opt.compat);
@@ -360,9 +365,13 @@ int renderer_create(const rtm_scene_desc* sc, const rtm_options* opt_in, rtm_ren
     if (opt.accel != RTM_ACCEL_AUTO && opt.accel != RTM_ACCEL_BRUTE && opt.accel != RTM_ACCEL_BVH)
         return fail(RTM_E_INVALID, "bad accel %d", opt.accel);
     const bool use_bvh = opt.accel == RTM_ACCEL_BVH || (opt.accel == RTM_ACCEL_AUTO && sc->n_spheres > 64);
-    if (f32_path && !use_bvh && sc->n_spheres > RTM_MAX_CONST_SPHERES)
-        return fail(RTM_E_UNSUPPORTED, "FP32 brute-force path holds at most %d spheres (use RTM_ACCEL_BVH / AUTO)",
+    if (f32_path && !use_bvh && sc->n_spheres + m > RTM_MAX_CONST_SPHERES)
+        return fail(RTM_E_UNSUPPORTED, "FP32 brute-force path holds at most %d objects (use RTM_ACCEL_BVH / AUTO)",
                     RTM_MAX_CONST_SPHERES);
+    if (m > 0 && opt.compat != RTM_COMPAT_ABC) return fail(RTM_E_UNSUPPORTED, "planes are an extension of COMPAT_ABC");
+    if (m > 0 && f32_path && (use_bvh || opt.variant != RTM_VARIANT_MEGA || m > RTM_MAX_PLANES))
+        return fail(RTM_E_UNSUPPORTED, "FP32 path: planes go through the brute-force megakernel (<= 64 spheres or RTM_ACCEL_BRUTE, "
+                    "<= %d planes); use RTM_PRECISION_F64 otherwise", RTM_MAX_PLANES);
 
     int ndev = 0;
     cudaError_t ce = cudaGetDeviceCount(&ndev);
@@ -376,6 +385,7 @@ int renderer_create(const rtm_scene_desc* sc, const rtm_options* opt_in, rtm_ren
     rtm_renderer* r = new rtm_renderer();
     r->opt = opt;
     r->W = sc->width; r->H = sc->height; r->S = sc->samples; r->ss = sc->superSamples; r->n = sc->n_spheres;
+    r->n_planes = m;
     r->use_bvh = use_bvh;
     r->n_pix = (uint64_t)r->W * r->H;
     r->n_sub = r->n_pix * (uint64_t)(opt.sub_end - opt.sub_begin);   // sub-pixels this handle renders
@@ -403,15 +413,19 @@ int renderer_create(const rtm_scene_desc* sc, const rtm_options* opt_in, rtm_ren
 
     // scene arrays
     const int n = r->n;
-    std::vector<double> h64((size_t)n * 11 + 1);
+    // cx cy cz r2 [n] | kd [n+m] | emission [3(n+m)] | color [3(n+m)] | planes [16 m]
+    const size_t nm = (size_t)n + (size_t)m;
+    std::vector<double> h64((size_t)n * 4 + nm * 7 + (size_t)m * 16 + 1);
     double* cx = h64.data();
     double* cy = cx + n;
     double* cz = cy + n;
     double* r2 = cz + n;
     double* kd = r2 + n;
-    double* em = kd + n;
-    double* col = em + 3 * (size_t)n;
+    double* em = kd + nm;
+    double* col = em + 3 * nm;
+    double* planes = col + 3 * nm;
     r->f32.n = n;
+    r->f32.n_planes = m;
     for (int i = 0; i < n; ++i) {
         cx[i] = sc->position[3 * i]; cy[i] = sc->position[3 * i + 1]; cz[i] = sc->position[3 * i + 2];
         const float rad = sc->radius[i];
@@ -452,6 +466,55 @@ int renderer_create(const rtm_scene_desc* sc, const rtm_options* opt_in, rtm_ren
                 s.kd_thr[i] = thr;
                 s.kx[i] = kx; s.ky[i] = ky; s.kz[i] = kz;
             }
+        }
+    }
+
+    // PlaneObject extension: frame as the ctor of src/SettingData.cpp:235-242 derives it (float-sqrt Normalize),
+    // operation order fixed by DESIGN.md §10 (the tests compare the hit maps bit for bit)
+    for (int j = 0; j < m; ++j) {
+        const v3 position{sc->plane_position[3 * j], sc->plane_position[3 * j + 1], sc->plane_position[3 * j + 2]};
+        const v3 up{sc->plane_up[3 * j], sc->plane_up[3 * j + 1], sc->plane_up[3 * j + 2]};
+        const v3 target{sc->plane_target[3 * j], sc->plane_target[3 * j + 1], sc->plane_target[3 * j + 2]};
+        const v3 normal = vnormalize(vsub(target, position));
+        const v3 right = vscale(vscale(vnormalize(vcross(normal, up)), 0.5), sc->plane_width[j]);
+        const v3 upp = vcross(right, normal);
+        const double rr = vdot(right, right), uu = vdot(upp, upp);
+        if (!(rr > 0.0) || !(uu > 0.0) || !std::isfinite(rr) || !std::isfinite(uu) || !std::isfinite(vdot(normal, normal))) {
+            delete r;
+            return fail(RTM_E_INVALID, "plane %d is degenerate (target == position, up parallel to the normal, or width <= 0)", j);
+        }
+        double* pl = planes + 16 * (size_t)j;
+        pl[0] = normal.x; pl[1] = normal.y; pl[2] = normal.z;
+        pl[3] = position.x; pl[4] = position.y; pl[5] = position.z;
+        pl[6] = right.x; pl[7] = right.y; pl[8] = right.z;
+        pl[9] = upp.x; pl[10] = upp.y; pl[11] = upp.z;
+        pl[12] = rr; pl[13] = uu; pl[14] = pl[15] = 0.0;
+        const size_t i = (size_t)n + j;
+        const double c0 = sc->plane_color[3 * j], c1 = sc->plane_color[3 * j + 1], c2 = sc->plane_color[3 * j + 2];
+        const double m01 = (c0 < c1) ? c1 : c0;
+        const float kdf = (float)((m01 < c2) ? c2 : m01);  // SettingData.h:14-16
+        kd[i] = (double)kdf;
+        for (int k = 0; k < 3; ++k) {
+            em[3 * i + k] = sc->plane_emission[3 * j + k];
+            col[3 * i + k] = sc->plane_color[3 * j + k];
+        }
+        if (f32_path) {
+            RtmSceneF32Host& s = r->f32;
+            const double th = (double)kdf * 4294967296.0;
+            s.kd_thr[i] = (th >= 4294967295.0) ? 0xFFFFFFFFu : (th <= 0.0 ? 0u : (uint32_t)th);
+            s.kd[i] = kdf;
+            s.cx[i] = (float)normal.x; s.cy[i] = (float)normal.y; s.cz[i] = (float)normal.z;   // geo of a plane: its normal, 1/r = 0
+            s.inv_r[i] = 0.f;
+            s.ex[i] = (float)em[3 * i]; s.ey[i] = (float)em[3 * i + 1]; s.ez[i] = (float)em[3 * i + 2];
+            s.kx[i] = s.ky[i] = s.kz[i] = 0.f;
+            if (kdf > 0.f) { s.kx[i] = (float)(c0 / (double)kdf); s.ky[i] = (float)(c1 / (double)kdf); s.kz[i] = (float)(c2 / (double)kdf); }
+            RtmPlaneF32& q = s.planes[j];
+            const v3 prel{position.x - r->refd[0], position.y - r->refd[1], position.z - r->refd[2]};
+            q.nx = (float)normal.x; q.ny = (float)normal.y; q.nz = (float)normal.z;
+            q.d0 = (float)vdot(normal, prel);
+            q.px = (float)prel.x; q.py = (float)prel.y; q.pz = (float)prel.z; q.pad0 = 0.f;
+            q.rx = (float)(right.x / rr); q.ry = (float)(right.y / rr); q.rz = (float)(right.z / rr); q.pad1 = 0.f;
+            q.ux = (float)(upp.x / uu); q.uy = (float)(upp.y / uu); q.uz = (float)(upp.z / uu); q.pad2 = 0.f;
         }
     }
 
@@ -536,7 +599,9 @@ int renderer_create(const rtm_scene_desc* sc, const rtm_options* opt_in, rtm_ren
             CU(cudaMemcpy(c.d_scene64, h64.data(), h64.size() * sizeof(double), cudaMemcpyHostToDevice));
             c.s64.n = n;
             c.s64.cx = c.d_scene64; c.s64.cy = c.s64.cx + n; c.s64.cz = c.s64.cy + n; c.s64.r2 = c.s64.cz + n;
-            c.s64.kd = c.s64.r2 + n; c.s64.emission = c.s64.kd + n; c.s64.color = c.s64.emission + 3 * (size_t)n;
+            c.s64.kd = c.s64.r2 + n; c.s64.emission = c.s64.kd + nm; c.s64.color = c.s64.emission + 3 * nm;
+            c.s64.n_planes = m;
+            c.s64.planes = c.s64.color + 3 * nm;
             if (use_bvh) {
                 // one allocation, float4 units: nodes | leaf_geo | geo | emi | alb | leaf_id (int32, padded)
                 const RtmBvhHost& B = r->bvh_host;
@@ -816,7 +881,7 @@ int rtm_debug_closest_hit(rtm_renderer* r, int32_t mode, uint32_t n, const doubl
             if (r->f32.n != r->n) return fail(RTM_E_UNSUPPORTED, "handle was not created for the FP32 path");
             CU(rtm_upload_scene_f32(r->f32, c.stream));
             if (r->use_bvh) rtm_launch_closest_hit_bvh_f32(c.bvh, c.mat, r->n, r->refd, n, d_org, d_dir, d_oid, d_hit, d_t, c.stream);
-            else rtm_launch_closest_hit_f32(r->n, r->refd, n, d_org, d_dir, d_oid, d_hit, d_t, c.stream);
+            else rtm_launch_closest_hit_f32(r->n, r->n_planes, r->refd, n, d_org, d_dir, d_oid, d_hit, d_t, c.stream);
         }
         CU(cudaGetLastError());
         CU(cudaStreamSynchronize(c.stream));

@@ -49,6 +49,10 @@ struct RtmSceneF64 {
     const double* emission;  // [n][3]
     const double* color;     // [n][3]
     const double* kd;        // (double)(float)max(r,g,b)        src/SettingData.h:14-16
+    // PlaneObject extension: ids n .. n+n_planes-1; kd/emission/color hold n+n_planes entries.
+    // planes[16*j + ..] = normal[0..2], position[3..5], right[6..8], upp[9..11], rr[12], uu[13]
+    int32_t n_planes;
+    const double* planes;
 };
 
 // Two spheres side by side for the packed (f32x2) sphere test of the FP32 megakernel:
@@ -58,6 +62,16 @@ struct __align__(16) RtmPairF32 {
     float2 cx, cy, cz, p2x, p2y, p2z, nK, pad;
 };
 #define RTM_MAX_PAIRS 4
+#define RTM_MAX_PLANES 16
+
+// A plane of the FP32 path, relative to the scene reference point: unit normal + offset, and the two
+// half-extent vectors divided by their squared lengths (inside the square iff both |dots| <= 1).
+struct __align__(16) RtmPlaneF32 {
+    float nx, ny, nz, d0;     // n, n.position
+    float px, py, pz, pad0;   // position
+    float rx, ry, rz, pad1;   // right / |right|^2
+    float ux, uy, uz, pad2;   // upp / |upp|^2
+};
 
 // Per-sphere data of the FP32 path, relative to the scene reference point
 // (the camera origin), SoA.  Filled on the host in double, rounded once.
@@ -72,6 +86,10 @@ struct RtmSceneF32Host {
     float kd[RTM_MAX_CONST_SPHERES];
     RtmPairF32 pairs[RTM_MAX_PAIRS];     // the first 8 spheres again, paired
     uint32_t kd_thr[RTM_MAX_CONST_SPHERES];  // min(kd * 2^32, 2^32-1): roulette continues iff a 32-bit draw < kd_thr
+    // PlaneObject extension: materials of plane j live at index n + j of the arrays above (cx,cy,cz = its normal,
+    // inv_r = 0); geometry here
+    int32_t n_planes;
+    RtmPlaneF32 planes[RTM_MAX_PLANES];
 };
 
 // Sub-pixel record written by the exact primary pass and consumed by the FP32
@@ -137,7 +155,7 @@ void rtm_launch_closest_hit_f64(const RtmSceneF64& sc, uint32_t n, const double*
 cudaError_t rtm_upload_scene_f32(const RtmSceneF32Host& h, cudaStream_t st);
 // cps0: per-sub-pixel c' = |c - P|^2 - r^2 at the primary hit from the FP64 pass, or null when the scene
 // has no sphere small enough for the reference's self-intersection to matter (kernels_radiance.cu: ACNE)
-void rtm_launch_radiance_mega(int32_t n_spheres, const RtmPassParams& p, float4* records, RtmCounters* counters,
+void rtm_launch_radiance_mega(int32_t n_spheres, int32_t n_planes, const RtmPassParams& p, float4* records, RtmCounters* counters,
                               int32_t sm_count, const float* cps0, cudaStream_t st);
 void rtm_launch_radiance_bvh(const RtmBvhDev& bvh, const RtmMatDev& mat, const RtmPassParams& p, float4* records,
                              RtmCounters* counters, int32_t sm_count, const float* cps0, cudaStream_t st);
@@ -151,7 +169,7 @@ void rtm_launch_accumulate(const RtmPassParams& p, const float4* records, float4
 void rtm_launch_sum_partials(const float4* partials /*[G][n_pix]*/, float4* out, uint64_t n_pix, int32_t G, cudaStream_t st);
 void rtm_launch_pack_rgb(const float4* accum, float* out /*[n_pix][3]*/, uint64_t n_pix, cudaStream_t st);
 void rtm_launch_to_u8(const float4* accum, unsigned char* out, uint64_t n_pix, cudaStream_t st);
-void rtm_launch_closest_hit_f32(int32_t n_spheres, const double* refd, uint32_t n, const double* org,
+void rtm_launch_closest_hit_f32(int32_t n_spheres, int32_t n_planes, const double* refd, uint32_t n, const double* org,
                                 const double* dir, const int32_t* origin_id, int32_t* hit, double* t,
                                 cudaStream_t st);
 void rtm_launch_closest_hit_bvh_f32(const RtmBvhDev& bvh, const RtmMatDev& mat, int32_t n_spheres, const double* refd, uint32_t n,

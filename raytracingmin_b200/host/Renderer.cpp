@@ -23,6 +23,12 @@ void Renderer::Render(std::string fileName) {
     sc.radius = data.object.radius.data();
     sc.color = data.object.color.data();
     sc.emission = data.object.emission.data();
+    sc.n_planes = (int32_t)data.plane.size();   // PlaneObject extension (ABI 3)
+    if (sc.n_planes > 0) {
+        sc.plane_position = data.plane.position.data(); sc.plane_up = data.plane.up.data();
+        sc.plane_target = data.plane.target.data(); sc.plane_width = data.plane.width.data();
+        sc.plane_color = data.plane.color.data(); sc.plane_emission = data.plane.emission.data();
+    }
 
     rtm_options opt;
     renderer_default_options(&opt);

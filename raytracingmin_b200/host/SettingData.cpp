@@ -57,14 +57,36 @@ SettingData LoadData::from_json_text(const std::string& text, Compat compat) {
         if (root.contains("02 scene") && root.at("02 scene").contains("00 object")) {
             const Value& objs = root.at("02 scene").at("00 object");
             if (!objs.is_array()) throw SceneError("\"00 object\" must be an array");
+            std::vector<int> order_s, order_p;
+            int k = 0;
             for (size_t i = 0; i < objs.size(); ++i) {
                 const Value& o = objs.at(i);
                 const std::string where = "object " + std::to_string(i);
                 if (o.empty()) continue;  // `{}` (cornellBoxSetting.json:47): skipped, index not consumed
                 const int type = o.contains("00 objectType") ? read_int(o.at("00 objectType"), where + " objectType") : 1;
+                if (type == 2) {
+                    if (compat == Compat::Head) throw SceneError(where + ": planes are an extension of the L-ABC level");
+                    const vec3 pp = read_vec3(need(o, "00 position", where), where + " position");
+                    const vec3 pu = read_vec3(need(o, "01 up", where), where + " up");
+                    const vec3 pt = read_vec3(need(o, "01 target", where), where + " target");
+                    const double w = need(o, "01 width", where).number();
+                    if (!(w > 0.0)) throw SceneError(where + ": plane width must be positive");
+                    const Value& pm = need(o, "02 material", where);
+                    const vec3 pc = read_vec3(need(pm, "color", where + " material"), where + " color");
+                    const vec3 pe = read_vec3(need(pm, "emission", where + " material"), where + " emission");
+                    d.plane.position.insert(d.plane.position.end(), {pp.x, pp.y, pp.z});
+                    d.plane.up.insert(d.plane.up.end(), {pu.x, pu.y, pu.z});
+                    d.plane.target.insert(d.plane.target.end(), {pt.x, pt.y, pt.z});
+                    d.plane.width.push_back(w);
+                    d.plane.color.insert(d.plane.color.end(), {pc.x, pc.y, pc.z});
+                    d.plane.emission.insert(d.plane.emission.end(), {pe.x, pe.y, pe.z});
+                    order_p.push_back(k++);
+                    continue;
+                }
                 if (type != 1)
                     throw SceneError(where + ": objectType " + std::to_string(type) +
-                                     " is not a sphere (the reference stores a null object and crashes)");
+                                     " is neither a sphere (1) nor a plane (2) (the reference stores a null object and crashes)");
+                order_s.push_back(k++);
                 vec3 p = read_vec3(need(o, "00 position", where), where + " position");
                 if (compat == Compat::Head) p = vec3(p.z, 0.0, 0.0);  // F2
                 const float size = (float)need(o, "01 size", where).number();
@@ -76,6 +98,8 @@ SettingData LoadData::from_json_text(const std::string& text, Compat compat) {
                 d.object.color.insert(d.object.color.end(), {c.x, c.y, c.z});
                 d.object.emission.insert(d.object.emission.end(), {e.x, e.y, e.z});
             }
+            d.order = order_s;
+            d.order.insert(d.order.end(), order_p.begin(), order_p.end());
         }
     } catch (const SceneError&) {
         throw;
@@ -107,7 +131,7 @@ std::string LoadData::to_json_text(const SettingData& d) {
     cam["upVec"] = vec3_json(d.camera.upVec.x, d.camera.upVec.y, d.camera.upVec.z);
     cam["fov"] = Value((double)d.camera.fov);
     root["01 camera"] = cam;
-    if (d.object.size() > 0) {
+    if (d.object.size() + d.plane.size() > 0) {
         Value objs = Value::array();
         for (size_t i = 0; i < d.object.size(); ++i) {
             Value o = Value::object();
@@ -117,6 +141,20 @@ std::string LoadData::to_json_text(const SettingData& d) {
             Value m = Value::object();
             m["color"] = vec3_json(d.object.color[3 * i], d.object.color[3 * i + 1], d.object.color[3 * i + 2]);
             m["emission"] = vec3_json(d.object.emission[3 * i], d.object.emission[3 * i + 1], d.object.emission[3 * i + 2]);
+            o["02 material"] = m;
+            objs.push_back(o);
+        }
+        for (size_t j = 0; j < d.plane.size(); ++j) {
+            const PlaneList& P = d.plane;
+            Value o = Value::object();
+            o["00 objectType"] = Value(2);
+            o["00 position"] = vec3_json(P.position[3 * j], P.position[3 * j + 1], P.position[3 * j + 2]);
+            o["01 up"] = vec3_json(P.up[3 * j], P.up[3 * j + 1], P.up[3 * j + 2]);
+            o["01 target"] = vec3_json(P.target[3 * j], P.target[3 * j + 1], P.target[3 * j + 2]);
+            o["01 width"] = Value(P.width[j]);
+            Value m = Value::object();
+            m["color"] = vec3_json(P.color[3 * j], P.color[3 * j + 1], P.color[3 * j + 2]);
+            m["emission"] = vec3_json(P.emission[3 * j], P.emission[3 * j + 1], P.emission[3 * j + 2]);
             o["02 material"] = m;
             objs.push_back(o);
         }

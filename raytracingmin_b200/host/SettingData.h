@@ -29,10 +29,23 @@ struct SphereList {
     size_t size() const { return radius.size(); }
 };
 
+// EXTENSION: the reference's PlaneObject ("00 objectType": 2, src/SettingData.h:33-42), which its
+// parser never builds and its Intersect never finishes.  Flat arrays of the ctor arguments of
+// src/SettingData.cpp:235 (position, up, target, width) + material.  Planes take the object ids
+// behind the spheres; `order` gives every id's position in the JSON object list.
+struct PlaneList {
+    std::vector<double> position, up, target;  // [m][3]
+    std::vector<double> width;                 // [m]
+    std::vector<double> color, emission;       // [m][3]
+    size_t size() const { return width.size(); }
+};
+
 struct SettingData {
     int width = 0, height = 0, samples = 0, superSamples = 0;
     Camera camera;
     SphereList object;
+    PlaneList plane;
+    std::vector<int> order;  // object id (spheres first, then planes) -> index in "00 object" ({} entries not counted)
 };
 
 enum class Compat { Head, Abc };
@@ -49,7 +62,9 @@ public:
     // reference's from_json (src/SettingData.cpp:129-186), SURVEY.md §5.1:
     //   unknown keys ignored; "00 sample" accepted for "00 samples"; missing
     //   "00 superSamples" = 1; object without "00 objectType" = sphere; `{}` skipped;
-    //   objectType != 1 rejected with a message (the reference segfaults on it);
+    //   objectType 2 = plane (extension: keys "00 position", "01 up", "01 target", "01 width",
+    //   "02 material"; Compat::Abc only); any other objectType rejected with a message (the
+    //   reference stores a null object and segfaults);
     //   Compat::Head applies the reference's position bug (posi.x assigned three times,
     //   src/SettingData.cpp:165-167): every sphere lands at (position[2], 0, 0).
     explicit LoadData(const std::string& jsonFile, Compat compat = Compat::Abc);

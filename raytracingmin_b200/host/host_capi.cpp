@@ -40,6 +40,31 @@ int rtmh_load_scene(const char* path, int compat_head, int* dims, double* cam, f
     }
 }
 
+// The planes of a scene file (extension, objectType 2).  Returns the plane count or -1; arrays may be NULL.
+// order_out[n_spheres + n_planes]: object id -> position in the JSON list.
+int rtmh_load_planes(const char* path, int cap, double* position, double* up, double* target, double* width, double* color,
+                     double* emission, int order_cap, int* order_out) {
+    try {
+        png::LoadData ld(path, png::Compat::Abc);
+        const png::PlaneList& P = ld.data.plane;
+        const int m = (int)P.size();
+        if (position && m <= cap) {
+            std::memcpy(position, P.position.data(), sizeof(double) * 3 * m);
+            std::memcpy(up, P.up.data(), sizeof(double) * 3 * m);
+            std::memcpy(target, P.target.data(), sizeof(double) * 3 * m);
+            std::memcpy(width, P.width.data(), sizeof(double) * m);
+            std::memcpy(color, P.color.data(), sizeof(double) * 3 * m);
+            std::memcpy(emission, P.emission.data(), sizeof(double) * 3 * m);
+        }
+        if (order_out && (int)ld.data.order.size() <= order_cap)
+            std::memcpy(order_out, ld.data.order.data(), sizeof(int) * ld.data.order.size());
+        return m;
+    } catch (const std::exception& e) {
+        g_err = e.what();
+        return -1;
+    }
+}
+
 // Round trip: parse `path`, serialise with to_json_text into out (NUL-terminated); returns length or -1.
 int rtmh_roundtrip_json(const char* path, char* out, int cap) {
     try {

@@ -8,7 +8,12 @@ its Python twin with the same policy:
   * unknown keys are ignored (src/SettingData.cpp:130-186 only looks at known ones),
   * "00 sample" is accepted as an alias of "00 samples"; missing "00 superSamples" = 1,
   * an object without "00 objectType" is a sphere (type 1); `{}` is skipped,
-  * objectType != 1 is rejected (the reference pushes a nullptr and segfaults),
+  * objectType 2 is the PlaneObject EXTENSION (the reference declares the
+    type, src/SettingData.h:33-42, but never parses or intersects it): keys "00 position",
+    "01 up", "01 target", "01 width", "02 material" = the ctor arguments of
+    src/SettingData.cpp:235.  Planes are numbered AFTER the spheres (object ids n..n+m-1);
+    `object_order` maps those ids back to positions in the JSON list,
+  * any other objectType is rejected (the reference pushes a nullptr and segfaults),
   * fov is ALWAYS the tangent-space half width (src/Renderer.cpp:207,229),
   * compat="head" reproduces F2: the reference assigns posi.x three times
     (src/SettingData.cpp:165-167), so every sphere lands at (position[2], 0, 0).
@@ -35,10 +40,26 @@ class Scene:
     radius: np.ndarray = field(default_factory=lambda: np.zeros((0,), np.float32))
     color: np.ndarray = field(default_factory=lambda: np.zeros((0, 3)))
     emission: np.ndarray = field(default_factory=lambda: np.zeros((0, 3)))
+    # PlaneObject extension (objectType 2): finite squares, object ids n .. n+n_planes-1
+    pl_position: np.ndarray = field(default_factory=lambda: np.zeros((0, 3)))
+    pl_up: np.ndarray = field(default_factory=lambda: np.zeros((0, 3)))
+    pl_target: np.ndarray = field(default_factory=lambda: np.zeros((0, 3)))
+    pl_width: np.ndarray = field(default_factory=lambda: np.zeros((0,)))
+    pl_color: np.ndarray = field(default_factory=lambda: np.zeros((0, 3)))
+    pl_emission: np.ndarray = field(default_factory=lambda: np.zeros((0, 3)))
+    object_order: np.ndarray = field(default_factory=lambda: np.zeros((0,), np.int32))  # id -> JSON position
 
     @property
     def n(self) -> int:
         return int(self.position.shape[0])
+
+    @property
+    def n_planes(self) -> int:
+        return int(np.asarray(self.pl_position).reshape(-1, 3).shape[0])
+
+    @property
+    def n_objects(self) -> int:
+        return self.n + self.n_planes
 
     @property
     def spp(self) -> int:
@@ -68,6 +89,13 @@ class Scene:
             radius=np.ascontiguousarray(self.radius, np.float32).reshape(-1),
             color=np.ascontiguousarray(self.color, np.float64).reshape(-1, 3),
             emission=np.ascontiguousarray(self.emission, np.float64).reshape(-1, 3),
+            pl_position=np.ascontiguousarray(self.pl_position, np.float64).reshape(-1, 3),
+            pl_up=np.ascontiguousarray(self.pl_up, np.float64).reshape(-1, 3),
+            pl_target=np.ascontiguousarray(self.pl_target, np.float64).reshape(-1, 3),
+            pl_width=np.ascontiguousarray(self.pl_width, np.float64).reshape(-1),
+            pl_color=np.ascontiguousarray(self.pl_color, np.float64).reshape(-1, 3),
+            pl_emission=np.ascontiguousarray(self.pl_emission, np.float64).reshape(-1, 3),
+            object_order=np.ascontiguousarray(self.object_order, np.int32).reshape(-1),
         )
 
 
@@ -89,12 +117,32 @@ def scene_from_dict(d: dict, compat: str = "abc") -> Scene:
         raise SceneError("missing '00 samples'")
     cam = need(d, "01 camera", "scene")
     pos, rad, col, emi = [], [], [], []
+    ppos, pup, ptgt, pwid, pcol, pemi = [], [], [], [], [], []
+    order_s, order_p = [], []
+    k = 0
     for i, o in enumerate(d.get("02 scene", {}).get("00 object", [])):
         if not o:
             continue
         typ = o.get("00 objectType", 1)
+        if typ == 2:
+            if compat == "head":
+                raise SceneError(f"object {i}: planes are an extension of the L-ABC level")
+            mat = need(o, "02 material", f"object {i}")
+            ppos.append([float(v) for v in need(o, "00 position", f"object {i}")])
+            pup.append([float(v) for v in need(o, "01 up", f"object {i}")])
+            ptgt.append([float(v) for v in need(o, "01 target", f"object {i}")])
+            pwid.append(float(need(o, "01 width", f"object {i}")))
+            pcol.append([float(v) for v in need(mat, "color", f"object {i} material")])
+            pemi.append([float(v) for v in need(mat, "emission", f"object {i} material")])
+            if not (pwid[-1] > 0):
+                raise SceneError(f"object {i}: plane width must be positive")
+            order_p.append(k)
+            k += 1
+            continue
         if typ != 1:
-            raise SceneError(f"object {i}: objectType {typ} is not a sphere (the reference would crash)")
+            raise SceneError(f"object {i}: objectType {typ} is neither a sphere (1) nor a plane (2) (the reference would crash)")
+        order_s.append(k)
+        k += 1
         p = need(o, "00 position", f"object {i}")
         mat = need(o, "02 material", f"object {i}")
         if compat == "head":
@@ -116,6 +164,10 @@ def scene_from_dict(d: dict, compat: str = "abc") -> Scene:
         radius=np.array(rad, np.float64).astype(np.float32),  # double size -> float m_size
         color=np.array(col, np.float64).reshape(-1, 3),
         emission=np.array(emi, np.float64).reshape(-1, 3),
+        pl_position=np.array(ppos, np.float64).reshape(-1, 3), pl_up=np.array(pup, np.float64).reshape(-1, 3),
+        pl_target=np.array(ptgt, np.float64).reshape(-1, 3), pl_width=np.array(pwid, np.float64).reshape(-1),
+        pl_color=np.array(pcol, np.float64).reshape(-1, 3), pl_emission=np.array(pemi, np.float64).reshape(-1, 3),
+        object_order=np.array(order_s + order_p, np.int32),
     )
     return sc.normalized()
 
@@ -135,6 +187,15 @@ def scene_to_dict(sc: Scene) -> dict:
             "00 position": [float(v) for v in sc.position[i]],
             "01 size": float(sc.radius[i]),
             "02 material": {"color": [float(v) for v in sc.color[i]], "emission": [float(v) for v in sc.emission[i]]},
+        })
+    for j in range(sc.n_planes):
+        objs.append({
+            "00 objectType": 2,
+            "00 position": [float(v) for v in sc.pl_position[j]],
+            "01 up": [float(v) for v in sc.pl_up[j]],
+            "01 target": [float(v) for v in sc.pl_target[j]],
+            "01 width": float(sc.pl_width[j]),
+            "02 material": {"color": [float(v) for v in sc.pl_color[j]], "emission": [float(v) for v in sc.pl_emission[j]]},
         })
     return {
         "00 width": sc.width, "00 height": sc.height, "00 samples": sc.samples, "00 superSamples": sc.superSamples,

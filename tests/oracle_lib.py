@@ -24,6 +24,9 @@ class _OScene(C.Structure):
         ("fov", C.c_float), ("n", C.c_int32),
         ("pos", C.POINTER(C.c_double)), ("radius", C.POINTER(C.c_float)),
         ("color", C.POINTER(C.c_double)), ("emission", C.POINTER(C.c_double)),
+        ("n_planes", C.c_int32),
+        ("pl_position", C.POINTER(C.c_double)), ("pl_up", C.POINTER(C.c_double)), ("pl_target", C.POINTER(C.c_double)),
+        ("pl_width", C.POINTER(C.c_double)), ("pl_color", C.POINTER(C.c_double)), ("pl_emission", C.POINTER(C.c_double)),
     ]
 
 
@@ -50,6 +53,9 @@ def oracle():
         lib.rtmo_render.argtypes = [P(_OScene), C.c_int, C.c_uint32, vp, P(C.c_uint64), P(C.c_uint64), C.c_int]
         lib.rtmo_to_u8.argtypes = [vp, vp, C.c_size_t]
         lib.rtmo_render_head_exact.argtypes = [P(_OScene), vp]
+        lib.rtmo_plane_frame.argtypes = [vp, vp, vp, C.c_double, vp]
+        lib.rtmo_plane_frame.restype = None
+        lib.rtmo_intersect_plane.argtypes = [vp, vp, vp, C.c_double, vp, vp, P(C.c_double), vp]
         _oracle = lib
     return _oracle
 
@@ -67,6 +73,9 @@ def _oscene(sc):
     s.radius = sc.radius.ctypes.data_as(C.POINTER(C.c_float))
     s.color = sc.color.ctypes.data_as(C.POINTER(C.c_double))
     s.emission = sc.emission.ctypes.data_as(C.POINTER(C.c_double))
+    s.n_planes = sc.n_planes
+    for name in ("pl_position", "pl_up", "pl_target", "pl_width", "pl_color", "pl_emission"):
+        setattr(s, name, getattr(sc, name).ctypes.data_as(C.POINTER(C.c_double)))
     return s, sc  # keep sc alive
 
 

@@ -66,9 +66,9 @@ def test_cpp_loader_superset_policy(hostlib, tmp_path):
     assert dims == [8, 4, 7, 1] and fov == 90.0 and len(rad) == 1
     assert rad[0] == np.float32(0.1) and pos.tolist() == [[1, 2, 3]]
     assert _load(hostlib, str(p), True)[3].tolist() == [[3, 0, 0]]            # F2 in --compat=head
-    d["02 scene"]["00 object"][1]["00 objectType"] = 2
+    d["02 scene"]["00 object"][1]["00 objectType"] = 3
     p.write_text(json.dumps(d))
-    with pytest.raises(ValueError, match="not a sphere"):
+    with pytest.raises(ValueError, match="neither a sphere"):
         _load(hostlib, str(p), False)
     p.write_text('{"00 width": 8,')
     with pytest.raises(ValueError, match="json parse error"):
