@@ -23,7 +23,7 @@ pytestmark = pytest.mark.gpu
 def test_library_is_loaded_and_device_present(gpu_lib):
     import torch
     assert torch.cuda.is_available()
-    assert gpu_lib.renderer_abi_version() == 2
+    assert gpu_lib.renderer_abi_version() == 3
 
 
 def test_philox_device_matches_numpy():
