@@ -197,24 +197,41 @@ __device__ __forceinline__ int trace_f32(const SelfMask& sm, int n_rt, int oid, 
 }
 
 // ---- PlaneObject extension ---------------------------------------
-// Finite squares from constant memory (uniform index: one broadcast per constant), tested after the
-// spheres; (t, id) are updated in place, `t < best` keeps a sphere on an exact tie.  The plane a ray
-// leaves is skipped by id (the FP64 definition rejects it through t > 1e-3: t is 0 there).
+// Finite squares from constant memory, two per instruction (f32x2) like the spheres, branch-free: for
+// each pair t = (d0 - n.o) * rcp(n.d), the point q = o + t d - position, the two half-extent dots, and
+// one predicate per plane (inside, not parallel, t > eps, not the plane the ray leaves, closer than
+// the best so far) that selects (t, id).  Tested after the spheres with a strict `<`, so a sphere keeps
+// an exact tie.  The plane a ray leaves is skipped by id (the FP64 definition rejects it through
+// t > 1e-3: t is 0 there).
 __device__ __forceinline__ void trace_planes_f32(int n_sph, int n_pl, int oid, f3 o, f3 d, float& t, int& id) {
-    for (int j = 0; j < n_pl; ++j) {
-        const RtmPlaneF32& pl = c_scene.planes[j];
-        const float dn = fmaf(pl.nx, d.x, fmaf(pl.ny, d.y, pl.nz * d.z));
-        const float num = pl.d0 - fmaf(pl.nx, o.x, fmaf(pl.ny, o.y, pl.nz * o.z));
-        const float tt = num * fast_rcp(dn);
-        if (n_sph + j != oid && fabsf(dn) >= FLT_EPSILON && tt > RTM_T_EPS && tt < t) {
-            const f3 q = mk(fmaf(d.x, tt, o.x) - pl.px, fmaf(d.y, tt, o.y) - pl.py, fmaf(d.z, tt, o.z) - pl.pz);
-            const float a = fmaf(q.x, pl.rx, fmaf(q.y, pl.ry, q.z * pl.rz));
-            const float b = fmaf(q.x, pl.ux, fmaf(q.y, pl.uy, q.z * pl.uz));
-            if (fabsf(a) <= 1.f && fabsf(b) <= 1.f) {
-                t = tt;
-                id = n_sph + j;
-            }
-        }
+    const u64 dx = pk(d.x, d.x), dy = pk(d.y, d.y), dz = pk(d.z, d.z);
+    const u64 ox = pk(o.x, o.x), oy = pk(o.y, o.y), oz = pk(o.z, o.z);
+    const u64 nox = pk(-o.x, -o.x), noy = pk(-o.y, -o.y), noz = pk(-o.z, -o.z);
+    const int self = oid - n_sph;   // slot of the plane the ray leaves (negative: none)
+    const int np = (n_pl + 1) >> 1;
+    // unrolled with a uniform guard: constant indices let the pair's constants come straight from the
+    // constant bank (LDCU / c[][] operands) instead of one indexed LDC per value
+#pragma unroll
+    for (int j = 0; j < RTM_MAX_PLANES / 2; ++j) {
+        if (j >= np) break;
+        const RtmPlanePairF32& c = c_scene.plane_pairs[j];
+        const u64 nx = pk(c.nx), ny = pk(c.ny), nz = pk(c.nz);
+        float dn0, dn1;
+        unpk(fma2(nx, dx, fma2(ny, dy, mul2(nz, dz))), dn0, dn1);                       // n.d
+        const u64 num2 = fma2(nx, nox, fma2(ny, noy, fma2(nz, noz, pk(c.d0))));         // n.(position - o)
+        const u64 tt2 = mul2(num2, pk(fast_rcp(dn0), fast_rcp(dn1)));
+        const u64 qx = fma2(dx, tt2, add2(ox, pk(c.npx))), qy = fma2(dy, tt2, add2(oy, pk(c.npy))),
+                  qz = fma2(dz, tt2, add2(oz, pk(c.npz)));
+        float a0, a1, b0, b1, t0, t1;
+        unpk(fma2(qx, pk(c.rx), fma2(qy, pk(c.ry), mul2(qz, pk(c.rz)))), a0, a1);
+        unpk(fma2(qx, pk(c.ux), fma2(qy, pk(c.uy), mul2(qz, pk(c.uz)))), b0, b1);
+        unpk(tt2, t0, t1);
+        const bool v0 = fmaxf(fabsf(a0), fabsf(b0)) <= 1.f && fabsf(dn0) >= FLT_EPSILON && t0 > RTM_T_EPS && 2 * j != self && t0 < t;
+        t = v0 ? t0 : t;
+        id = v0 ? n_sph + 2 * j : id;
+        const bool v1 = fmaxf(fabsf(a1), fabsf(b1)) <= 1.f && fabsf(dn1) >= FLT_EPSILON && t1 > RTM_T_EPS && 2 * j + 1 != self && t1 < t;
+        t = v1 ? t1 : t;
+        id = v1 ? n_sph + 2 * j + 1 : id;
     }
 }
 

@@ -508,15 +508,15 @@ int renderer_create(const rtm_scene_desc* sc, const rtm_options* opt_in, rtm_ren
             s.ex[i] = (float)em[3 * i]; s.ey[i] = (float)em[3 * i + 1]; s.ez[i] = (float)em[3 * i + 2];
             s.kx[i] = s.ky[i] = s.kz[i] = 0.f;
             if (kdf > 0.f) { s.kx[i] = (float)(c0 / (double)kdf); s.ky[i] = (float)(c1 / (double)kdf); s.kz[i] = (float)(c2 / (double)kdf); }
-            RtmPlaneF32& q = s.planes[j];
+            float* q = reinterpret_cast<float*>(&s.plane_pairs[j >> 1]) + (j & 1);   // lane of the pair, stride 2 floats
             const v3 prel{position.x - r->refd[0], position.y - r->refd[1], position.z - r->refd[2]};
-            q.nx = (float)normal.x; q.ny = (float)normal.y; q.nz = (float)normal.z;
-            q.d0 = (float)vdot(normal, prel);
-            q.px = (float)prel.x; q.py = (float)prel.y; q.pz = (float)prel.z; q.pad0 = 0.f;
-            q.rx = (float)(right.x / rr); q.ry = (float)(right.y / rr); q.rz = (float)(right.z / rr); q.pad1 = 0.f;
-            q.ux = (float)(upp.x / uu); q.uy = (float)(upp.y / uu); q.uz = (float)(upp.z / uu); q.pad2 = 0.f;
+            const double vals[13] = {normal.x, normal.y, normal.z, vdot(normal, prel), -prel.x, -prel.y, -prel.z,
+                                     right.x / rr, right.y / rr, right.z / rr, upp.x / uu, upp.y / uu, upp.z / uu};
+            for (int k = 0; k < 13; ++k) q[2 * k] = (float)vals[k];
         }
     }
+
+    if (f32_path && (m & 1)) reinterpret_cast<float*>(&r->f32.plane_pairs[m >> 1])[2 * 3 + 1] = -1.0f;   // dummy lane: n = 0, d0 = -1
 
     if (f32_path) {
         // ACNE (kernels_radiance.cu): the reference re-hits the sphere a ray leaves when

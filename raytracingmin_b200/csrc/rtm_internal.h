@@ -64,13 +64,12 @@ struct __align__(16) RtmPairF32 {
 #define RTM_MAX_PAIRS 4
 #define RTM_MAX_PLANES 16
 
-// A plane of the FP32 path, relative to the scene reference point: unit normal + offset, and the two
-// half-extent vectors divided by their squared lengths (inside the square iff both |dots| <= 1).
-struct __align__(16) RtmPlaneF32 {
-    float nx, ny, nz, d0;     // n, n.position
-    float px, py, pz, pad0;   // position
-    float rx, ry, rz, pad1;   // right / |right|^2
-    float ux, uy, uz, pad2;   // upp / |upp|^2
+// Two planes of the FP32 path side by side (lane .x = plane 2j, .y = plane 2j+1), relative to the scene
+// reference point: unit normal, d0 = n.position, -position, and the two half-extent vectors divided by their
+// squared lengths (inside the square iff both |dots| <= 1).  An odd count is padded with a never-hit dummy
+// (n = 0, d0 = -1).
+struct __align__(16) RtmPlanePairF32 {
+    float2 nx, ny, nz, d0, npx, npy, npz, rx, ry, rz, ux, uy, uz, pad0, pad1, pad2;
 };
 
 // Per-sphere data of the FP32 path, relative to the scene reference point
@@ -89,7 +88,7 @@ struct RtmSceneF32Host {
     // PlaneObject extension: materials of plane j live at index n + j of the arrays above (cx,cy,cz = its normal,
     // inv_r = 0); geometry here
     int32_t n_planes;
-    RtmPlaneF32 planes[RTM_MAX_PLANES];
+    RtmPlanePairF32 plane_pairs[RTM_MAX_PLANES / 2];
 };
 
 // Sub-pixel record written by the exact primary pass and consumed by the FP32
