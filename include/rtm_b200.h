@@ -71,6 +71,15 @@ enum {
     RTM_ACCEL_BVH = 2     /* same per-candidate arithmetic and tie rule behind a BVH */
 };
 
+/* Estimator of the bounce loop. */
+enum {
+    RTM_ESTIMATOR_REFERENCE = 0,  /* src/Renderer.cpp:57-117: emission is collected where paths land */
+    RTM_ESTIMATOR_NEE = 1         /* EXTENSION (the reference's SurfaeSample, src/Renderer.cpp:119-198,
+                                     is dead, unfinished code): next-event estimation, one uniformly chosen sphere
+                                     light per vertex, cone sampling + shadow ray.  Same expectation as the reference's
+                                     estimator, less variance.  FP32 brute-force megakernel only. */
+};
+
 /* What png::SettingData holds after LoadData::from_json (src/SettingData.cpp:129-186),
  * flattened.  Doubles in, so the FP64 primary pass sees exactly what the reference parsed. */
 typedef struct rtm_scene_desc {
@@ -121,6 +130,7 @@ typedef struct rtm_options {
                               0,0 = all.  The preferred multi-GPU partition when ss^2 divides by the GPU
                               count: every rank keeps full-length sample loops and a 1/G primary pass.
                               The primary-hit map needs the full grid. */
+    int32_t estimator;     /* RTM_ESTIMATOR_* (ABI 3) */
 } rtm_options;
 
 typedef struct rtm_stats {
@@ -128,7 +138,8 @@ typedef struct rtm_stats {
     uint64_t rays;           /* PathTracing invocations the reference would have made for them
                                 (src/Renderer.cpp:57): sum of path lengths, primary included */
     uint64_t rays_traced;    /* closest-hit queries actually executed on the device (the primary
-                                query is shared by the `samples` samples of a sub-pixel) */
+                                query is shared by the `samples` samples of a sub-pixel; with
+                                RTM_ESTIMATOR_NEE the shadow rays are counted here, not in `rays`) */
     uint64_t sphere_tests;   /* ray-sphere tests actually executed */
     double device_ms;        /* CUDA-event time of the kernels (+ reduce), max over GPUs */
     double e2e_ms;           /* host wall time of the renderer_render call */

@@ -344,6 +344,131 @@ int rtmo_render(const rtmo_scene* s, int level, uint32_t seed, double* image,
     return 0;
 }
 
+/* ---- next-event estimation: EXTENSION ---------------------------------------
+ * Same path as path_trace (L-ABC): closest hit, roulette on kd, cosine-weighted bounce.  Added at every
+ * vertex that survives the roulette: one light k chosen uniformly from the list, a direction l sampled
+ * uniformly inside the cone the light sphere subtends (pdf 1 / (2 pi (1 - cos_max))), a shadow ray, and
+ *     direct = e_k * max(0, w.l) * 2 (1 - cos_max) * n_lights        (Lambert: colorKD * cos / pi / pdf)
+ * when the shadow ray's closest hit is light k.  To count every emitted photon once, a hit reached by a
+ * BOUNCE ray adds its emission only if it was not eligible for the light sampling at the previous vertex:
+ * not in the list, or hit from inside (the previous vertex was inside the sphere: no cone).  The primary
+ * hit always adds its emission.  A vertex ON light k (hitObject == k) skips the sampling: a convex light
+ * does not illuminate itself. */
+typedef struct { int n; int id[RTMO_MAX_LIGHTS]; unsigned char listed[1 << 16]; } lights_t;
+
+static void make_lights(const rtmo_scene* s, lights_t* L) {
+    L->n = 0;
+    memset(L->listed, 0, sizeof L->listed);
+    for (int i = 0; i < s->n && L->n < RTMO_MAX_LIGHTS; ++i) {
+        const double* e = s->emission + 3 * i;
+        if ((e[0] > 0 || e[1] > 0 || e[2] > 0) && s->radius[i] <= 1000.0f) {
+            L->id[L->n++] = i;
+            if (i < (1 << 16)) L->listed[i] = 1;
+        }
+    }
+}
+
+typedef struct { uint64_t rays, shadow; } nee_counters_t;
+
+static v3 path_trace_nee(const rtmo_scene* s, const lights_t* lights, int primary, v3 org, v3 dir, mt19937_t* rng,
+                         nee_counters_t* c) {
+    const double PI = 3.14159265358979323846;
+    double dis;
+    v3 normal;
+    c->rays++;
+    const int hitObject = closest_hit(s, org, dir, &dis, &normal);
+    if (hitObject == -1 || !(dis > 0)) return v3_make(0, 0, 0);
+    const int isPlane = hitObject >= s->n;
+    const v3 color = isPlane ? v3_load(s->pl_color + 3 * (hitObject - s->n)) : v3_load(s->color + 3 * hitObject);
+    v3 emission = isPlane ? v3_load(s->pl_emission + 3 * (hitObject - s->n)) : v3_load(s->emission + 3 * hitObject);
+    const int from_inside = !(dot3(normal, dir) < 0.0);
+    if (!primary && !isPlane && hitObject < (1 << 16) && lights->listed[hitObject] && !from_inside)
+        emission = v3_make(0, 0, 0); /* already counted by the light sampling of the previous vertex */
+    const float kd = material_kd(color);
+    if (!(mt_uniform01(rng) <= kd)) return emission;
+    const v3 colorKD = v3_div(color, (double)kd);
+    const v3 hitPoint = v3_add(v3_scale(dir, dis), org);
+    const v3 w = from_inside ? v3_scale(normal, -1.0) : normal;
+    v3 direct = v3_make(0, 0, 0);
+    if (lights->n > 0) {
+        const double uk = mt_uniform01(rng), u1 = mt_uniform01(rng), u2 = mt_uniform01(rng);
+        int k = (int)(uk * lights->n);
+        if (k >= lights->n) k = lights->n - 1;
+        const int lid = lights->id[k];
+        const v3 v = v3_sub(v3_load(s->pos + 3 * lid), hitPoint);
+        const double d2 = dot3(v, v), r2 = (double)s->radius[lid] * (double)s->radius[lid];
+        if (lid != hitObject && d2 > r2) {
+            const double cos_max = sqrt(1.0 - r2 / d2);
+            const double omc = (r2 / d2) / (1.0 + cos_max); /* 1 - cos_max without cancellation */
+            const double ct = 1.0 - u1 * omc, st = sqrt(u1 * omc * (2.0 - u1 * omc));
+            const v3 a = v3_scale(v, 1.0 / sqrt(d2));
+            v3 t1;
+            if (fabs(a.x) > 0.5) t1 = cross3(v3_make(0, 1, 0), a);
+            else t1 = cross3(v3_make(1, 0, 0), a);
+            t1 = v3_scale(t1, 1.0 / sqrt(dot3(t1, t1)));
+            const v3 t2 = cross3(a, t1);
+            const double ph = 2 * PI * u2;
+            const v3 l = v3_add(v3_scale(a, ct), v3_scale(v3_add(v3_scale(t1, cos(ph)), v3_scale(t2, sin(ph))), st));
+            const double cw = dot3(w, l);
+            if (cw > 0.0) {
+                double sd;
+                v3 sn;
+                c->shadow++;
+                if (closest_hit(s, hitPoint, l, &sd, &sn) == lid)
+                    direct = v3_scale(v3_load(s->emission + 3 * lid), cw * 2.0 * omc * lights->n);
+            }
+        }
+    }
+    const double r1 = 2 * PI * mt_uniform01(rng);
+    const double r2 = mt_uniform01(rng);
+    const double r2s = sqrt(r2);
+    v3 u;
+    if (fabs(w.x) > FLT_MIN) u = normalize3(cross3(v3_make(0, 1, 0), w));
+    else u = normalize3(cross3(v3_make(1, 0, 0), w));
+    const v3 vv = cross3(w, u);
+    const v3 nextDir = normalize3(v3_add(v3_add(v3_scale(v3_scale(u, cos(r1)), r2s), v3_scale(v3_scale(vv, sin(r1)), r2s)),
+                                         v3_scale(w, sqrt(1.0 - r2))));
+    const v3 L = path_trace_nee(s, lights, 0, hitPoint, nextDir, rng, c);
+    return v3_add(v3_mul(colorKD, v3_add(direct, L)), emission);
+}
+
+int rtmo_render_nee(const rtmo_scene* s, uint32_t seed, double* image, uint64_t* rays_out, uint64_t* samples_out,
+                    uint64_t* shadow_out) {
+    const frame_t f = make_frame(s);
+    const v3 org = v3_load(s->cam_origin);
+    uint64_t rays = 0, samples = 0, shadow = 0;
+    lights_t* lights = (lights_t*)malloc(sizeof(lights_t));
+    make_lights(s, lights);
+#pragma omp parallel for schedule(dynamic) reduction(+ : rays, samples, shadow)
+    for (int y = 0; y < s->height; ++y) {
+        mt19937_t rng;
+        nee_counters_t c = {0, 0};
+        mt_seed(&rng, seed + (uint32_t)y);
+        for (int x = 0; x < s->width; ++x) {
+            v3 acc = {0, 0, 0};
+            for (int sx = 1; sx <= s->superSamples; ++sx)
+                for (int sy = 1; sy <= s->superSamples; ++sy)
+                    for (int smp = 0; smp < s->samples; ++smp) {
+                        (void)mt_uniform01(&rng); /* the strategy-pick draw of src/Renderer.cpp:234, kept so that an
+                                                     empty light list reproduces rtmo_render(ABC) bit for bit */
+                        v3 cal = path_trace_nee(s, lights, 1, org, camera_dir(s, &f, x, y, sx, sy), &rng, &c);
+                        cal = v3_div(v3_div(v3_div(cal, s->superSamples), s->superSamples), s->samples);
+                        cal = v3_make(clamp01(cal.x), clamp01(cal.y), clamp01(cal.z));
+                        acc = v3_add(acc, cal);
+                        ++samples;
+                    }
+            v3_store(image + ((size_t)y * s->width + x) * 3, acc);
+        }
+        rays += c.rays;
+        shadow += c.shadow;
+    }
+    free(lights);
+    if (rays_out) *rays_out = rays;
+    if (samples_out) *samples_out = samples;
+    if (shadow_out) *shadow_out = shadow;
+    return 0;
+}
+
 int rtmo_render_head_exact(const rtmo_scene* s, double* image) {
     const frame_t f = make_frame(s);
     const v3 org = v3_load(s->cam_origin);

@@ -71,6 +71,15 @@ int rtmo_primary_hits(const rtmo_scene* s, int32_t* out);
 int rtmo_render(const rtmo_scene* s, int level, uint32_t seed, double* image,
                 uint64_t* rays_out, uint64_t* samples_out, int nthreads);
 
+/* EXTENSION: the L-ABC estimator with next-event estimation.  The reference's own
+ * attempt (SurfaeSample, src/Renderer.cpp:119-198) is dead, unfinished code, so this is a definition, not a
+ * restatement; its EXPECTATION equals rtmo_render(level = ABC)'s, which is what the tests check.  Lights =
+ * the first RTMO_MAX_LIGHTS spheres in index order with a positive emission component and radius <= 1000.
+ * rays_out counts path rays only (comparable with rtmo_render), shadow_out the shadow rays. */
+#define RTMO_MAX_LIGHTS 16
+int rtmo_render_nee(const rtmo_scene* s, uint32_t seed, double* image, uint64_t* rays_out, uint64_t* samples_out,
+                    uint64_t* shadow_out);
+
 /* src/Renderer.cpp:251-254 */
 void rtmo_to_u8(const double* image, unsigned char* out, size_t n);
 

@@ -24,6 +24,8 @@ _COMPAT = {"head": COMPAT_HEAD, "abc": COMPAT_ABC}
 _PRECISION = {"f32": PRECISION_F32, "f64": PRECISION_F64}
 _VARIANT = {"mega": VARIANT_MEGA, "wavefront": VARIANT_WAVEFRONT}
 _ACCEL = {"auto": ACCEL_AUTO, "brute": ACCEL_BRUTE, "bvh": ACCEL_BVH}
+ESTIMATOR_REFERENCE, ESTIMATOR_NEE = 0, 1
+_ESTIMATOR = {"reference": ESTIMATOR_REFERENCE, "nee": ESTIMATOR_NEE}
 
 
 class RtmError(RuntimeError):
@@ -51,7 +53,7 @@ class _Options(C.Structure):
         ("device", C.c_int32), ("n_gpus", C.c_int32), ("compat", C.c_int32), ("precision", C.c_int32),
         ("variant", C.c_int32), ("accel", C.c_int32), ("max_depth", C.c_int32),
         ("sample_begin", C.c_int32), ("sample_end", C.c_int32), ("seed", C.c_uint64),
-        ("sub_begin", C.c_int32), ("sub_end", C.c_int32),
+        ("sub_begin", C.c_int32), ("sub_end", C.c_int32), ("estimator", C.c_int32),
     ]
 
 
@@ -153,7 +155,8 @@ class Renderer:
 
     def __init__(self, scene: Scene, *, device: int = 0, n_gpus: int = 1, compat: str = "abc", precision: str = "f32",
                  variant: str = "mega", accel: str = "auto", max_depth: int = 0, seed: int = 0x5EED,
-                 sample_begin: int = 0, sample_end: int = 0, sub_begin: int = 0, sub_end: int = 0):
+                 sample_begin: int = 0, sample_end: int = 0, sub_begin: int = 0, sub_end: int = 0,
+                 estimator: str = "reference"):
         self._lib = load_library()
         self._h = C.c_void_p()
         sc = scene.normalized()
@@ -167,6 +170,7 @@ class Renderer:
         o.max_depth, o.seed = max_depth, seed
         o.sample_begin, o.sample_end = sample_begin, sample_end
         o.sub_begin, o.sub_end = sub_begin, sub_end
+        o.estimator = _ESTIMATOR[estimator]
         self.compat = compat
         _check(self._lib, self._lib.renderer_create(C.byref(d), C.byref(o), C.byref(self._h)))
 

@@ -143,6 +143,7 @@ struct rtm_renderer {
     std::vector<GpuCtx> gpus;
     int32_t last_launches = 0;
     bool hits_valid = false;
+    bool nee = false;           // next-event-estimation kernels (estimator NEE and at least one listed light)
     bool acne = false;          // the FP32 path models the reference's self-intersection on small spheres
     bool use_bvh = false;       // closest hit through the hierarchy (bvh.h) instead of the O(N) loop
     RtmBvhHost bvh_host;
@@ -188,7 +189,7 @@ RtmPassParams make_params(const rtm_renderer* r, const GpuCtx& c) {
     {
         // 32-bit Philox2x32 key from the 64-bit seed
         uint32_t k = p.seed_lo ^ (p.seed_hi * 0x85EBCA6Bu) ^ (p.seed_hi >> 15);
-        for (int i = 0; i < 10; ++i) p.rk[i] = k + (uint32_t)i * 0x9E3779B9u;
+        for (int i = 0; i < 11; ++i) p.rk[i] = k + (uint32_t)i * 0x9E3779B9u;   // rk[1]: key of the NEE draws
     }
     for (int k = 0; k < 3; ++k) {
         p.refd[k] = r->refd[k];
@@ -253,7 +254,7 @@ int enqueue_pass(rtm_renderer* r, GpuCtx& c, cudaStream_t st, bool want_hits, in
             }
             c.waves = wave;
         } else if (r->use_bvh) rtm_launch_radiance_bvh(c.bvh, c.mat, p, c.records, c.counters, c.sm_count, c.cps0, st);
-        else rtm_launch_radiance_mega(r->n, r->n_planes, p, c.records, c.counters, c.sm_count, c.cps0, st);
+        else rtm_launch_radiance_mega(r->n, r->n_planes, r->nee, p, c.records, c.counters, c.sm_count, c.cps0, st);
         CU(cudaEventRecord(c.ek[2], st));
         rtm_launch_accumulate(p, c.records, c.accum, st);
         CU(cudaEventRecord(c.ek[3], st));
@@ -315,6 +316,7 @@ void renderer_default_options(rtm_options* o) {
     o->accel = RTM_ACCEL_AUTO;
     o->max_depth = 0;
     o->seed = 0x5EEDull;
+    o->estimator = RTM_ESTIMATOR_REFERENCE;
 }
 
 void renderer_destroy(rtm_renderer* r) {
@@ -368,6 +370,11 @@ int renderer_create(const rtm_scene_desc* sc, const rtm_options* opt_in, rtm_ren
     if (f32_path && !use_bvh && sc->n_spheres + m > RTM_MAX_CONST_SPHERES)
         return fail(RTM_E_UNSUPPORTED, "FP32 brute-force path holds at most %d objects (use RTM_ACCEL_BVH / AUTO)",
                     RTM_MAX_CONST_SPHERES);
+    if (opt.estimator != RTM_ESTIMATOR_REFERENCE && opt.estimator != RTM_ESTIMATOR_NEE)
+        return fail(RTM_E_INVALID, "bad estimator %d", opt.estimator);
+    if (opt.estimator == RTM_ESTIMATOR_NEE && (!f32_path || use_bvh || opt.variant != RTM_VARIANT_MEGA))
+        return fail(RTM_E_UNSUPPORTED, "next-event estimation exists in the FP32 brute-force megakernel (COMPAT_ABC, PRECISION_F32, "
+                    "VARIANT_MEGA, <= 64 spheres or RTM_ACCEL_BRUTE)");
     if (m > 0 && opt.compat != RTM_COMPAT_ABC) return fail(RTM_E_UNSUPPORTED, "planes are an extension of COMPAT_ABC");
     if (m > 0 && f32_path && (use_bvh || opt.variant != RTM_VARIANT_MEGA || m > RTM_MAX_PLANES))
         return fail(RTM_E_UNSUPPORTED, "FP32 path: planes go through the brute-force megakernel (<= 64 spheres or RTM_ACCEL_BRUTE, "
@@ -516,6 +523,22 @@ int renderer_create(const rtm_scene_desc* sc, const rtm_options* opt_in, rtm_ren
         }
     }
 
+    if (opt.estimator == RTM_ESTIMATOR_NEE) {
+        // light list: the first RTM_MAX_LIGHTS spheres in index order with a positive emission component and
+        // radius <= 1000.  Without a listed light the estimator IS the reference's.
+        RtmSceneF32Host& s = r->f32;
+        for (int i = 0; i < n && s.n_lights < RTM_MAX_LIGHTS; ++i) {
+            if (!(em[3 * i] > 0.0 || em[3 * i + 1] > 0.0 || em[3 * i + 2] > 0.0) || !(sc->radius[i] <= 1000.f)) continue;
+            const int k = s.n_lights++;
+            s.lgeo[k] = make_float4(s.cx[i], s.cy[i], s.cz[i], sc->radius[i]);
+            s.lemi[k] = make_float4(s.ex[i], s.ey[i], s.ez[i], 0.f);
+            memcpy(&s.lemi[k].w, &i, 4);
+            const int one = 1;
+            memcpy(&s.lit[i], &one, 4);
+        }
+        r->nee = s.n_lights > 0;
+    }
+
     if (f32_path && (m & 1)) reinterpret_cast<float*>(&r->f32.plane_pairs[m >> 1])[2 * 3 + 1] = -1.0f;   // dummy lane: n = 0, d0 = -1
 
     if (f32_path) {
@@ -533,6 +556,7 @@ int renderer_create(const rtm_scene_desc* sc, const rtm_options* opt_in, rtm_ren
         if (D == 0.0) D = 30.0;
         for (int i = 0; i < n; ++i)
             if (kd[i] > 0.0 && 9e-3 * D * D / (double)sc->radius[i] > 1e-2) r->acne = true;
+        if (r->nee) r->acne = false;   // the NEE kernels do not model the reference's self-intersection quirk (no reference to match)
     }
 
     if (use_bvh) {

@@ -63,6 +63,7 @@ struct __align__(16) RtmPairF32 {
 };
 #define RTM_MAX_PAIRS 4
 #define RTM_MAX_PLANES 16
+#define RTM_MAX_LIGHTS 16
 
 // Two planes of the FP32 path side by side (lane .x = plane 2j, .y = plane 2j+1), relative to the scene
 // reference point: unit normal, d0 = n.position, -position, and the two half-extent vectors divided by their
@@ -89,6 +90,11 @@ struct RtmSceneF32Host {
     // inv_r = 0); geometry here
     int32_t n_planes;
     RtmPlanePairF32 plane_pairs[RTM_MAX_PLANES / 2];
+    // next-event estimation (extension): the light list and, per sphere, "is in the list"
+    int32_t n_lights;
+    float4 lgeo[RTM_MAX_LIGHTS];   // centre (relative to the reference point), radius
+    float4 lemi[RTM_MAX_LIGHTS];   // emission rgb, sphere index (int bits)
+    float lit[RTM_MAX_CONST_SPHERES];   // 1 for listed lights (int bits), else 0
 };
 
 // Sub-pixel record written by the exact primary pass and consumed by the FP32
@@ -114,7 +120,7 @@ struct RtmPassParams {
     int32_t max_depth;
     uint32_t seed_lo, seed_hi;
     uint32_t key_mask;        // 0xFFFFFFF8, passed in so that it lives in a register (see key_pack)
-    uint32_t rk[10];          // rk[0] = fold(seed): key of the bounce hash; rk[r] = rk[0] + r*0x9E3779B9 (Philox2x32 round keys, -DRTM_RNG_PHILOX)
+    uint32_t rk[11];          // rk[0] = fold(seed): key of the bounce hash; rk[r] = rk[0] + r*0x9E3779B9 (Philox2x32 round keys, -DRTM_RNG_PHILOX)
     float inv_norm;           // 1/(ss*ss*S) for the FP32 path
     float ref[3];             // reference point (as float, informational)
     double refd[3];           // reference point
@@ -154,8 +160,9 @@ void rtm_launch_closest_hit_f64(const RtmSceneF64& sc, uint32_t n, const double*
 cudaError_t rtm_upload_scene_f32(const RtmSceneF32Host& h, cudaStream_t st);
 // cps0: per-sub-pixel c' = |c - P|^2 - r^2 at the primary hit from the FP64 pass, or null when the scene
 // has no sphere small enough for the reference's self-intersection to matter (kernels_radiance.cu: ACNE)
-void rtm_launch_radiance_mega(int32_t n_spheres, int32_t n_planes, const RtmPassParams& p, float4* records, RtmCounters* counters,
-                              int32_t sm_count, const float* cps0, cudaStream_t st);
+// nee: the next-event-estimation instantiation (needs c_scene.n_lights > 0; cps0 is ignored)
+void rtm_launch_radiance_mega(int32_t n_spheres, int32_t n_planes, bool nee, const RtmPassParams& p, float4* records,
+                              RtmCounters* counters, int32_t sm_count, const float* cps0, cudaStream_t st);
 void rtm_launch_radiance_bvh(const RtmBvhDev& bvh, const RtmMatDev& mat, const RtmPassParams& p, float4* records,
                              RtmCounters* counters, int32_t sm_count, const float* cps0, cudaStream_t st);
 // one wave of the wavefront variant; `wave` counts from 0 (its parity selects the queue)

@@ -35,7 +35,7 @@ void Renderer::Render(std::string fileName) {
     opt.device = options.device; opt.n_gpus = options.n_gpus;
     opt.compat = (options.compat == Compat::Head) ? RTM_COMPAT_HEAD : RTM_COMPAT_ABC;
     opt.precision = options.precision; opt.max_depth = options.max_depth; opt.seed = options.seed;
-    opt.accel = options.accel; opt.variant = options.variant;
+    opt.accel = options.accel; opt.variant = options.variant; opt.estimator = options.estimator;
 
     rtm_renderer* r = nullptr;
     if (renderer_create(&sc, &opt, &r) != RTM_OK) throw std::runtime_error(std::string("renderer_create: ") + renderer_last_error());

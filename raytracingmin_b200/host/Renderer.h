@@ -18,6 +18,7 @@ struct RenderOptions {           // everything the reference does not have; defa
     int max_depth = 0;
     int accel = 0;               // RTM_ACCEL_AUTO: brute force up to 64 spheres, the hierarchy beyond
     int variant = 0;             // RTM_VARIANT_MEGA (1 = wavefront, kept for comparison)
+    int estimator = 0;           // RTM_ESTIMATOR_REFERENCE (1 = next-event estimation, extension)
     uint64_t seed = 0x5EED;
     bool want_hits = false;      // keep the primary-hit map (int32[H][W][ss][ss])
     bool quiet = false;

@@ -37,7 +37,7 @@ void usage() {
               << "-sampleJson : write the sample scene file settingData.json and exit\n"
               << "-json <file> : scene file to render (default settingData.json)\n"
               << "--compat=abc|head  --gpus=N  --device=N  --seed=N  --precision=f32|f64  --max-depth=N\n"
-              << "--accel=auto|brute|bvh  --variant=mega|wavefront\n"
+              << "--accel=auto|brute|bvh  --variant=mega|wavefront  --estimator=reference|nee\n"
               << "--width=N --height=N --samples=N --superSamples=N : override the file's settings\n"
               << "--out=<name> : output base name (default result)  --dump-hits=<file>  --stats  --quiet\n"
               << "--dump-pfm=<file> : the linear image before the 8-bit conversion (float RGB, Portable Float Map)\n";
@@ -69,6 +69,7 @@ int main(int argc, char* argv[]) {
         else if (opt_value(a, "--max-depth", v)) ro.max_depth = std::atoi(v.c_str());
         else if (opt_value(a, "--accel", v)) ro.accel = (v == "brute") ? 1 : (v == "bvh") ? 2 : 0;
         else if (opt_value(a, "--variant", v)) ro.variant = (v == "wavefront") ? 1 : 0;
+        else if (opt_value(a, "--estimator", v)) ro.estimator = (v == "nee") ? 1 : 0;
         else if (opt_value(a, "--width", v)) ow = std::atoi(v.c_str());
         else if (opt_value(a, "--height", v)) oh = std::atoi(v.c_str());
         else if (opt_value(a, "--samples", v)) os = std::atoi(v.c_str());

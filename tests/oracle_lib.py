@@ -53,6 +53,7 @@ def oracle():
         lib.rtmo_render.argtypes = [P(_OScene), C.c_int, C.c_uint32, vp, P(C.c_uint64), P(C.c_uint64), C.c_int]
         lib.rtmo_to_u8.argtypes = [vp, vp, C.c_size_t]
         lib.rtmo_render_head_exact.argtypes = [P(_OScene), vp]
+        lib.rtmo_render_nee.argtypes = [P(_OScene), C.c_uint32, vp, P(C.c_uint64), P(C.c_uint64), P(C.c_uint64)]
         lib.rtmo_plane_frame.argtypes = [vp, vp, vp, C.c_double, vp]
         lib.rtmo_plane_frame.restype = None
         lib.rtmo_intersect_plane.argtypes = [vp, vp, vp, C.c_double, vp, vp, P(C.c_double), vp]
@@ -92,6 +93,15 @@ def oracle_render(sc, level: int = LEVEL_ABC, seed: int = 1234):
     rays, samples = C.c_uint64(), C.c_uint64()
     oracle().rtmo_render(C.byref(s), level, seed, img.ctypes.data, C.byref(rays), C.byref(samples), 0)
     return img, rays.value, samples.value
+
+
+def oracle_render_nee(sc, seed: int = 1234):
+    """The next-event-estimation extension: (image, path rays, samples, shadow rays)."""
+    s, keep = _oscene(sc)
+    img = np.empty((sc.height, sc.width, 3), np.float64)
+    rays, samples, shadow = C.c_uint64(), C.c_uint64(), C.c_uint64()
+    oracle().rtmo_render_nee(C.byref(s), seed, img.ctypes.data, C.byref(rays), C.byref(samples), C.byref(shadow))
+    return img, rays.value, samples.value, shadow.value
 
 
 def oracle_render_head_exact(sc) -> np.ndarray:

@@ -42,7 +42,7 @@ def test_abi_version_and_defaults():
 def test_struct_layout_matches_header():
     """sizeof as the C compiler sees them (LP64): guards the ctypes mirrors."""
     assert C.sizeof(api._SceneDesc) == 16 + 72 + 8 + 32 + 8 + 48
-    assert C.sizeof(api._Options) == 56
+    assert C.sizeof(api._Options) == 64
     assert C.sizeof(api._Stats) == 64
 
 
