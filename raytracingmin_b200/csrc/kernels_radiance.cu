@@ -1104,8 +1104,13 @@ template <int N, bool BVH>
 void launch_mega(const RtmPassParams& p, float4* records, RtmCounters* counters, int n_rt, int n_pl, bool nee, int sm_count, cudaStream_t st,
                  const float* cps0, const RtmBvhDev& bvh = RtmBvhDev{}, const RtmMatDev& mat = RtmMatDev{}) {
     if (nee) {
-        if (n_pl > 0) launch_mega2<N, BVH, false, true, true>(p, records, counters, n_rt, n_pl, sm_count, st, bvh, mat, nullptr);
-        else launch_mega2<N, BVH, false, false, true>(p, records, counters, n_rt, 0, sm_count, st, bvh, mat, nullptr);
+        if (n_pl > 0) {
+            if (cps0) launch_mega2<N, BVH, true, true, true>(p, records, counters, n_rt, n_pl, sm_count, st, bvh, mat, cps0);
+            else launch_mega2<N, BVH, false, true, true>(p, records, counters, n_rt, n_pl, sm_count, st, bvh, mat, nullptr);
+        } else {
+            if (cps0) launch_mega2<N, BVH, true, false, true>(p, records, counters, n_rt, 0, sm_count, st, bvh, mat, cps0);
+            else launch_mega2<N, BVH, false, false, true>(p, records, counters, n_rt, 0, sm_count, st, bvh, mat, nullptr);
+        }
     } else if (n_pl > 0) {
         if (cps0) launch_mega2<N, BVH, true, true>(p, records, counters, n_rt, n_pl, sm_count, st, bvh, mat, cps0);
         else launch_mega2<N, BVH, false, true>(p, records, counters, n_rt, n_pl, sm_count, st, bvh, mat, nullptr);

@@ -556,7 +556,6 @@ int renderer_create(const rtm_scene_desc* sc, const rtm_options* opt_in, rtm_ren
         if (D == 0.0) D = 30.0;
         for (int i = 0; i < n; ++i)
             if (kd[i] > 0.0 && 9e-3 * D * D / (double)sc->radius[i] > 1e-2) r->acne = true;
-        if (r->nee) r->acne = false;   // the NEE kernels do not model the reference's self-intersection quirk (no reference to match)
     }
 
     if (use_bvh) {

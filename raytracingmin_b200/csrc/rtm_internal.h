@@ -160,7 +160,7 @@ void rtm_launch_closest_hit_f64(const RtmSceneF64& sc, uint32_t n, const double*
 cudaError_t rtm_upload_scene_f32(const RtmSceneF32Host& h, cudaStream_t st);
 // cps0: per-sub-pixel c' = |c - P|^2 - r^2 at the primary hit from the FP64 pass, or null when the scene
 // has no sphere small enough for the reference's self-intersection to matter (kernels_radiance.cu: ACNE)
-// nee: the next-event-estimation instantiation (needs c_scene.n_lights > 0; cps0 is ignored)
+// nee: the next-event-estimation instantiation (needs c_scene.n_lights > 0)
 void rtm_launch_radiance_mega(int32_t n_spheres, int32_t n_planes, bool nee, const RtmPassParams& p, float4* records,
                               RtmCounters* counters, int32_t sm_count, const float* cps0, cudaStream_t st);
 void rtm_launch_radiance_bvh(const RtmBvhDev& bvh, const RtmMatDev& mat, const RtmPassParams& p, float4* records,

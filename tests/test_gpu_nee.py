@@ -32,8 +32,9 @@ def test_nee_matches_the_oracle_definition_on_cornell(gpu_lib, scene_path):
     assert np.abs(img - ref).mean() / ref.mean() < 0.022
     rps, rps_o = st.rays / st.samples, rays_o / samples_o
     assert abs(rps - rps_o) < 0.01 * rps_o, (rps, rps_o)                       # path rays: the reference's count
-    sh, sh_o = (st.rays_traced - st.rays) / st.samples, shadow_o / samples_o    # + the primary query shared per sub-pixel
-    assert abs(sh - sh_o) < 0.02 * sh_o + sc.n_sub / st.samples, (sh, sh_o)
+    # rays_traced = bounce + shadow queries + ONE primary query per sub-pixel; rays counts the primary once per sample
+    sh, sh_o = (st.rays_traced - sc.n_sub - (st.rays - st.samples)) / st.samples, shadow_o / samples_o
+    assert abs(sh - sh_o) < 0.01 * sh_o, (sh, sh_o)
 
 
 @pytest.mark.parametrize("name,dims,tol", [("cornellBox", (64, 34, 1024, 2), 0.005), ("settingData", (64, 34, 4096, 1), 0.01),
