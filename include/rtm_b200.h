@@ -99,7 +99,7 @@ typedef struct rtm_scene_desc {
      * falls off the end), so there is no reference behaviour to match; DESIGN.md §10 defines it as a
      * finite square.  Arrays are the ctor arguments of src/SettingData.cpp:235.  Planes take the
      * object ids n_spheres .. n_spheres+n_planes-1 (hit map, tie rule).  COMPAT_ABC only; the FP32
-     * path takes them in the brute-force megakernel (n_spheres + n_planes <= 256, n_planes <= 16).
+     * path takes up to 16 of them, in both megakernels (brute force and hierarchy), not in the wavefront variant.
      * n_planes = 0 (and NULL arrays) = the reference's scenes. */
     int32_t n_planes;
     const double* plane_position;   /* [m][3] */

@@ -14,6 +14,7 @@
 #define RTM_BVH_NONE 0x7FFFFFFF   // "no node": empty hierarchy / bottom of the traversal stack
 #define RTM_BVH_MAX_BIG 8         // spheres too large for the hierarchy, tested for every ray
 #define RTM_BVH_LEAF_MAX 4
+#define RTM_BVH_CTRAV 1.0         // SAH: cost of an inner-node visit in sphere tests
 #define RTM_BVH_STACK 64
 
 // child code: >= 0  inner node index

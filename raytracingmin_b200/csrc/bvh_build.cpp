@@ -2,6 +2,8 @@
 // Runs once per renderer_create; 10 000 spheres take a few milliseconds.
 #include "bvh.h"
 
+#include <cstdlib>
+
 #include <algorithm>
 #include <cfloat>
 #include <cmath>
@@ -67,6 +69,11 @@ struct Builder {
         return s;
     }
 
+    // SAH constants: cost of visiting an inner node (two box tests, a stack operation, a dependent 64-byte load)
+    // relative to one sphere test, and the largest leaf (the leaf code holds up to 8)
+    double c_trav = RTM_BVH_CTRAV;
+    int leaf_max = RTM_BVH_LEAF_MAX;
+
     Sub build(int b, int e, int depth) {
         max_depth = std::max(max_depth, depth);
         const int n = e - b;
@@ -82,7 +89,7 @@ struct Builder {
         if (depth < 32) {
             // binned SAH over the centroid bounds, 16 bins per axis
             const int NB = 16;
-            double best_cost = (n <= RTM_BVH_LEAF_MAX) ? (double)n * bounds.area() : DBL_MAX;
+            double best_cost = (n <= leaf_max) ? (double)n * bounds.area() : DBL_MAX;
             int best_axis = -1, best_bin = -1;
             for (int ax = 0; ax < 3; ++ax) {
                 const double ext = cb.hi[ax] - cb.lo[ax];
@@ -114,7 +121,7 @@ struct Builder {
                     if (cnt[k]) acc.grow(bb[k].lo, bb[k].hi);
                     c += cnt[k];
                     if (c == 0 || right_cnt[k + 1] == 0) continue;
-                    const double cost = 1.0 * bounds.area() + acc.area() * c + right_area[k + 1] * right_cnt[k + 1];
+                    const double cost = c_trav * bounds.area() + acc.area() * c + right_area[k + 1] * right_cnt[k + 1];
                     if (cost < best_cost) { best_cost = cost; best_axis = ax; best_bin = k; }
                 }
             }
@@ -132,7 +139,7 @@ struct Builder {
             }
         }
         if (axis < 0 || split_at <= b || split_at >= e) {
-            if (n <= RTM_BVH_LEAF_MAX) return make_leaf(b, e);
+            if (n <= leaf_max) return make_leaf(b, e);
             // median split by count along the widest centroid axis (also the depth >= 32 rule:
             // halving bounds the remaining depth by log2(n))
             axis = 0;
@@ -200,6 +207,9 @@ bool rtm_bvh_build(int32_t n, const double* position, const float* radius, const
     }
     Builder bl;
     bl.out = &out;
+    // tuning hook for scripts/gpu_sweep_bvh.sh (not part of the interface)
+    if (const char* e = getenv("RTM_BVH_CTRAV_ENV")) bl.c_trav = atof(e);
+    if (const char* e = getenv("RTM_BVH_LEAFMAX_ENV")) bl.leaf_max = std::min(8, std::max(1, atoi(e)));
     bl.prims.reserve(n - out.n_big);
     for (int i = 0; i < n; ++i) {
         if (is_big[i]) continue;

@@ -341,13 +341,27 @@ __device__ __forceinline__ void bvh_leaf_step(const RtmBvhDev& bvh, int oid, f3 
     r.node = stack[--r.sp];
 }
 
+// PlaneObject extension: planes are tested like the big spheres, before the descent, so that the hierarchy is
+// walked with their distance as the pruning bound
+__device__ __forceinline__ void bvh_ray_planes(int n_sph, int n_pl, int oid, f3 o, f3 d, BvhRay& r) {
+    float t = r.best + RTM_T_EPS;
+    int id = r.hit;
+    trace_planes_f32(n_sph, n_pl, oid, o, d, t, id);
+    if (id != r.hit) {
+        r.best = t - RTM_T_EPS;
+        r.hit = id;
+    }
+}
+
 // whole query (test hook; the render kernel interleaves the same steps across its lanes)
 template <int NP>
 __device__ __forceinline__ int trace_bvh_f32(const SelfMask& sm, const SharedBig& big, const RtmBvhDev& bvh, int oid, int oslot,
-                                             f3 o, f3 d, float& t, unsigned key_mask, unsigned& n_tests, unsigned& n_nodes) {
+                                             f3 o, f3 d, float& t, unsigned key_mask, unsigned& n_tests, unsigned& n_nodes,
+                                             int n_sph = 0, int n_pl = 0) {
     BvhRay r;
     int stack[RTM_BVH_STACK_DEV];
     bvh_ray_begin<NP>(sm, big, bvh, oslot, o, d, key_mask, r, stack, n_tests);
+    if (n_pl > 0) bvh_ray_planes(n_sph, n_pl, oid, o, d, r);
     while (r.node != RTM_BVH_NONE_DEV) {
         while (bvh_is_inner(r.node)) {
             bvh_inner_step(bvh, r, stack);
@@ -726,10 +740,12 @@ __global__ void __launch_bounds__(RTM_MEGA_THREADS, BVH ? 4 : 5) radiance_mega_k
 #define RTM_BVH_MINBLOCKS 6
 #endif
 
-template <int NP, bool ACNE>
+// PL: n_pl planes (extension) behind the n_sph spheres in the material records, tested at the start of every ray
+template <int NP, bool ACNE, bool PL>
 __global__ void __launch_bounds__(RTM_MEGA_THREADS, RTM_BVH_MINBLOCKS) radiance_bvh_kernel(RtmPassParams p, float4* __restrict__ records,
                                                                            RtmCounters* __restrict__ counters, RtmBvhDev bvh,
-                                                                           RtmMatDev mat, const float* __restrict__ cps0) {
+                                                                           RtmMatDev mat, const float* __restrict__ cps0, int n_sph,
+                                                                           int n_pl) {
     __shared__ SelfMask sh_mask;
     __shared__ SharedBig sh_big;
     init_selfmask(sh_mask);
@@ -804,6 +820,7 @@ __global__ void __launch_bounds__(RTM_MEGA_THREADS, RTM_BVH_MINBLOCKS) radiance_
                     const float4 g = __ldg(mat.geo + Pid);
                     const float ir = (wbits & RTM_REC_FLIP) ? -g.w : g.w;
                     Pw = mk((P.x - g.x) * ir, (P.y - g.y) * ir, (P.z - g.z) * ir);
+                    if (PL && Pid >= n_sph) Pw = (wbits & RTM_REC_FLIP) ? mk(-g.x, -g.y, -g.z) : mk(g.x, g.y, g.z);
                     acc = mk(0, 0, 0);
                     s = s_begin;
                     o = P; id = Pid; w = Pw;
@@ -833,6 +850,7 @@ __global__ void __launch_bounds__(RTM_MEGA_THREADS, RTM_BVH_MINBLOCKS) radiance_
                 o = mk(fmaf(d.x, t, o.x), fmaf(d.y, t, o.y), fmaf(d.z, t, o.z));     // :79
                 const float4 g = __ldg(mat.geo + id2);
                 f3 nn = mk((o.x - g.x) * g.w, (o.y - g.y) * g.w, (o.z - g.z) * g.w);
+                if (PL && id2 >= n_sph) nn = mk(g.x, g.y, g.z);   // a plane's record holds its normal, 1/r = 0
                 if (g.w > 1e-2f) {
                     // small spheres: t carries an absolute error of ~1e-5 that is not small against
                     // r = 0.05; put the hit back on the surface and make the normal unit
@@ -870,7 +888,7 @@ __global__ void __launch_bounds__(RTM_MEGA_THREADS, RTM_BVH_MINBLOCKS) radiance_
                         ++traced;
                         if (ACNE) {
                             const float cosw = dot(w, d);
-                            if (cpsn + cosw <= 0.f) {
+                            if (cpsn + cosw <= 0.f && !(PL && id >= n_sph)) {
                                 // SettingData.cpp:208-212: the far root of the sphere the ray stands (just) inside
                                 const float rr = fast_rcp(__ldg(mat.geo + id).w);
                                 const float qq = -cpsn * rr * RTM_ACNE_2TAU, bq = rr * cosw;
@@ -903,6 +921,7 @@ __global__ void __launch_bounds__(RTM_MEGA_THREADS, RTM_BVH_MINBLOCKS) radiance_
             // the packed big-sphere test (~140 instructions) runs once, for all lanes that start a ray, instead of
             // once per roulette round with whichever lanes happened to continue in that round
             bvh_ray_begin<NP>(sh_mask, sh_big, bvh, oslot, o, d, key_mask, ray, stack, n_tests);
+            if (PL) bvh_ray_planes(n_sph, n_pl, id, o, d, ray);
             if (ray.node != RTM_BVH_NONE_DEV) {
                 tracing = true;
                 break;
@@ -1044,7 +1063,7 @@ __global__ void closest_hit_f32_kernel(int n_sph, int n_pl, unsigned key_mask, d
 template <int NP>
 __global__ void closest_hit_bvh_f32_kernel(RtmBvhDev bvh, RtmMatDev mat, unsigned key_mask, double rx, double ry, double rz, uint32_t n,
                                            const double* __restrict__ org, const double* __restrict__ dir,
-                                           const int32_t* __restrict__ origin_id, int n_sph, int32_t* __restrict__ hit,
+                                           const int32_t* __restrict__ origin_id, int n_sph, int n_pl, int32_t* __restrict__ hit,
                                            double* __restrict__ tout) {
     __shared__ SelfMask sh_mask;
     __shared__ SharedBig sh_big;
@@ -1056,11 +1075,11 @@ __global__ void closest_hit_bvh_f32_kernel(RtmBvhDev bvh, RtmMatDev mat, unsigne
     const f3 o = mk((float)(org[3 * i] - rx), (float)(org[3 * i + 1] - ry), (float)(org[3 * i + 2] - rz));
     const f3 d = mk((float)dir[3 * i], (float)dir[3 * i + 1], (float)dir[3 * i + 2]);
     int oid = origin_id ? origin_id[i] : -1;
-    if (oid < -1 || oid >= n_sph) oid = -1;
+    if (oid < -1 || oid >= n_sph + n_pl) oid = -1;
     const int oslot = (oid >= 0) ? __float_as_int(__ldg(mat.alb + oid).w) : -1;
     float t;
     unsigned a = 0, b = 0;
-    hit[i] = trace_bvh_f32<NP>(sh_mask, sh_big, bvh, oid, oslot, o, d, t, key_mask, a, b);
+    hit[i] = trace_bvh_f32<NP>(sh_mask, sh_big, bvh, oid, oslot, o, d, t, key_mask, a, b, n_sph, n_pl);
     tout[i] = (double)t;
 }
 
@@ -1187,30 +1206,35 @@ void rtm_launch_wf_extend(int32_t n, bool use_bvh, const RtmBvhDev& bvh, const R
 
 // Hierarchy path: the packed test covers the (padded-to-even) list of big spheres.
 namespace {
+template <int NP, bool ACNE, bool PL>
+void launch_bvh2(const RtmBvhDev& bvh, const RtmMatDev& mat, const RtmPassParams& p, float4* records, RtmCounters* counters,
+                 int sm_count, const float* cps0, int n_sph, int n_pl, cudaStream_t st) {
+    int per_sm = 0;
+    cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, radiance_bvh_kernel<NP, ACNE, PL>, RTM_MEGA_THREADS, 0);
+    if (per_sm < 1) per_sm = 1;
+    radiance_bvh_kernel<NP, ACNE, PL><<<sm_count * per_sm, RTM_MEGA_THREADS, 0, st>>>(p, records, counters, bvh, mat, cps0, n_sph, n_pl);
+}
 template <int NP>
 void launch_bvh(const RtmBvhDev& bvh, const RtmMatDev& mat, const RtmPassParams& p, float4* records, RtmCounters* counters,
-                int sm_count, const float* cps0, cudaStream_t st) {
-    int per_sm = 0;
-    if (cps0) {
-        cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, radiance_bvh_kernel<NP, true>, RTM_MEGA_THREADS, 0);
-        if (per_sm < 1) per_sm = 1;
-        radiance_bvh_kernel<NP, true><<<sm_count * per_sm, RTM_MEGA_THREADS, 0, st>>>(p, records, counters, bvh, mat, cps0);
+                int sm_count, const float* cps0, int n_sph, int n_pl, cudaStream_t st) {
+    if (n_pl > 0) {
+        if (cps0) launch_bvh2<NP, true, true>(bvh, mat, p, records, counters, sm_count, cps0, n_sph, n_pl, st);
+        else launch_bvh2<NP, false, true>(bvh, mat, p, records, counters, sm_count, nullptr, n_sph, n_pl, st);
     } else {
-        cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, radiance_bvh_kernel<NP, false>, RTM_MEGA_THREADS, 0);
-        if (per_sm < 1) per_sm = 1;
-        radiance_bvh_kernel<NP, false><<<sm_count * per_sm, RTM_MEGA_THREADS, 0, st>>>(p, records, counters, bvh, mat, nullptr);
+        if (cps0) launch_bvh2<NP, true, false>(bvh, mat, p, records, counters, sm_count, cps0, n_sph, 0, st);
+        else launch_bvh2<NP, false, false>(bvh, mat, p, records, counters, sm_count, nullptr, n_sph, 0, st);
     }
 }
 }  // namespace
 
 void rtm_launch_radiance_bvh(const RtmBvhDev& bvh, const RtmMatDev& mat, const RtmPassParams& p, float4* records,
-                             RtmCounters* counters, int32_t sm_count, const float* cps0, cudaStream_t st) {
+                             RtmCounters* counters, int32_t sm_count, const float* cps0, int32_t n_sph, int32_t n_pl, cudaStream_t st) {
     switch ((bvh.n_big + 1) / 2) {
-        case 0: launch_bvh<0>(bvh, mat, p, records, counters, sm_count, cps0, st); break;
-        case 1: launch_bvh<1>(bvh, mat, p, records, counters, sm_count, cps0, st); break;
-        case 2: launch_bvh<2>(bvh, mat, p, records, counters, sm_count, cps0, st); break;
-        case 3: launch_bvh<3>(bvh, mat, p, records, counters, sm_count, cps0, st); break;
-        default: launch_bvh<4>(bvh, mat, p, records, counters, sm_count, cps0, st); break;
+        case 0: launch_bvh<0>(bvh, mat, p, records, counters, sm_count, cps0, n_sph, n_pl, st); break;
+        case 1: launch_bvh<1>(bvh, mat, p, records, counters, sm_count, cps0, n_sph, n_pl, st); break;
+        case 2: launch_bvh<2>(bvh, mat, p, records, counters, sm_count, cps0, n_sph, n_pl, st); break;
+        case 3: launch_bvh<3>(bvh, mat, p, records, counters, sm_count, cps0, n_sph, n_pl, st); break;
+        default: launch_bvh<4>(bvh, mat, p, records, counters, sm_count, cps0, n_sph, n_pl, st); break;
     }
 }
 
@@ -1241,12 +1265,12 @@ void rtm_launch_closest_hit_f32(int32_t n_spheres, int32_t n_planes, const doubl
     closest_hit_f32_kernel<<<(n + 127) / 128, 128, 0, st>>>(n_spheres, n_planes, 0xFFFFFFF8u, refd[0], refd[1], refd[2], n, org, dir, origin_id, hit, t);
 }
 
-void rtm_launch_closest_hit_bvh_f32(const RtmBvhDev& bvh, const RtmMatDev& mat, int32_t n_spheres, const double* refd, uint32_t n,
+void rtm_launch_closest_hit_bvh_f32(const RtmBvhDev& bvh, const RtmMatDev& mat, int32_t n_spheres, int32_t n_planes, const double* refd, uint32_t n,
                                     const double* org, const double* dir, const int32_t* origin_id, int32_t* hit, double* t,
                                     cudaStream_t st) {
     const unsigned g = (n + 127) / 128;
     switch ((bvh.n_big + 1) / 2) {
-#define RTM_CASE(NP) closest_hit_bvh_f32_kernel<NP><<<g, 128, 0, st>>>(bvh, mat, 0xFFFFFFF8u, refd[0], refd[1], refd[2], n, org, dir, origin_id, n_spheres, hit, t)
+#define RTM_CASE(NP) closest_hit_bvh_f32_kernel<NP><<<g, 128, 0, st>>>(bvh, mat, 0xFFFFFFF8u, refd[0], refd[1], refd[2], n, org, dir, origin_id, n_spheres, n_planes, hit, t)
         case 0: RTM_CASE(0); break;
         case 1: RTM_CASE(1); break;
         case 2: RTM_CASE(2); break;

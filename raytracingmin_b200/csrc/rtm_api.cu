@@ -253,7 +253,7 @@ int enqueue_pass(rtm_renderer* r, GpuCtx& c, cudaStream_t st, bool want_hits, in
                 if (*c.h_live != (unsigned)wave) break;   // the last wave of the batch queued nothing
             }
             c.waves = wave;
-        } else if (r->use_bvh) rtm_launch_radiance_bvh(c.bvh, c.mat, p, c.records, c.counters, c.sm_count, c.cps0, st);
+        } else if (r->use_bvh) rtm_launch_radiance_bvh(c.bvh, c.mat, p, c.records, c.counters, c.sm_count, c.cps0, r->n, r->n_planes, st);
         else rtm_launch_radiance_mega(r->n, r->n_planes, r->nee, p, c.records, c.counters, c.sm_count, c.cps0, st);
         CU(cudaEventRecord(c.ek[2], st));
         rtm_launch_accumulate(p, c.records, c.accum, st);
@@ -376,9 +376,9 @@ int renderer_create(const rtm_scene_desc* sc, const rtm_options* opt_in, rtm_ren
         return fail(RTM_E_UNSUPPORTED, "next-event estimation exists in the FP32 brute-force megakernel (COMPAT_ABC, PRECISION_F32, "
                     "VARIANT_MEGA, <= 64 spheres or RTM_ACCEL_BRUTE)");
     if (m > 0 && opt.compat != RTM_COMPAT_ABC) return fail(RTM_E_UNSUPPORTED, "planes are an extension of COMPAT_ABC");
-    if (m > 0 && f32_path && (use_bvh || opt.variant != RTM_VARIANT_MEGA || m > RTM_MAX_PLANES))
-        return fail(RTM_E_UNSUPPORTED, "FP32 path: planes go through the brute-force megakernel (<= 64 spheres or RTM_ACCEL_BRUTE, "
-                    "<= %d planes); use RTM_PRECISION_F64 otherwise", RTM_MAX_PLANES);
+    if (m > 0 && f32_path && (opt.variant != RTM_VARIANT_MEGA || m > RTM_MAX_PLANES))
+        return fail(RTM_E_UNSUPPORTED, "FP32 path: planes go through the megakernels (RTM_VARIANT_MEGA, <= %d planes); "
+                    "use RTM_PRECISION_F64 otherwise", RTM_MAX_PLANES);
 
     int ndev = 0;
     cudaError_t ce = cudaGetDeviceCount(&ndev);
@@ -505,16 +505,32 @@ int renderer_create(const rtm_scene_desc* sc, const rtm_options* opt_in, rtm_ren
             em[3 * i + k] = sc->plane_emission[3 * j + k];
             col[3 * i + k] = sc->plane_color[3 * j + k];
         }
+        if (f32_path && use_bvh) {
+            // hierarchy path: the plane's records follow the spheres' in the global-memory arrays
+            const double th = (double)kdf * 4294967296.0;
+            const uint32_t thr = (th >= 4294967295.0) ? 0xFFFFFFFFu : (th <= 0.0 ? 0u : (uint32_t)th);
+            float4 e = make_float4((float)em[3 * i], (float)em[3 * i + 1], (float)em[3 * i + 2], 0.f);
+            memcpy(&e.w, &thr, 4);
+            float4 a = make_float4(0.f, 0.f, 0.f, 0.f);
+            if (kdf > 0.f) a = make_float4((float)(c0 / (double)kdf), (float)(c1 / (double)kdf), (float)(c2 / (double)kdf), 0.f);
+            const int32_t none = -1;
+            memcpy(&a.w, &none, 4);
+            r->mat_geo.push_back(make_float4((float)normal.x, (float)normal.y, (float)normal.z, 0.f));
+            r->mat_emi.push_back(e);
+            r->mat_alb.push_back(a);
+        }
         if (f32_path) {
             RtmSceneF32Host& s = r->f32;
-            const double th = (double)kdf * 4294967296.0;
-            s.kd_thr[i] = (th >= 4294967295.0) ? 0xFFFFFFFFu : (th <= 0.0 ? 0u : (uint32_t)th);
-            s.kd[i] = kdf;
-            s.cx[i] = (float)normal.x; s.cy[i] = (float)normal.y; s.cz[i] = (float)normal.z;   // geo of a plane: its normal, 1/r = 0
-            s.inv_r[i] = 0.f;
-            s.ex[i] = (float)em[3 * i]; s.ey[i] = (float)em[3 * i + 1]; s.ez[i] = (float)em[3 * i + 2];
-            s.kx[i] = s.ky[i] = s.kz[i] = 0.f;
-            if (kdf > 0.f) { s.kx[i] = (float)(c0 / (double)kdf); s.ky[i] = (float)(c1 / (double)kdf); s.kz[i] = (float)(c2 / (double)kdf); }
+            if (!use_bvh) {   // brute force: records in constant -> shared memory, behind the spheres'
+                const double th = (double)kdf * 4294967296.0;
+                s.kd_thr[i] = (th >= 4294967295.0) ? 0xFFFFFFFFu : (th <= 0.0 ? 0u : (uint32_t)th);
+                s.kd[i] = kdf;
+                s.cx[i] = (float)normal.x; s.cy[i] = (float)normal.y; s.cz[i] = (float)normal.z;   // geo of a plane: its normal, 1/r = 0
+                s.inv_r[i] = 0.f;
+                s.ex[i] = (float)em[3 * i]; s.ey[i] = (float)em[3 * i + 1]; s.ez[i] = (float)em[3 * i + 2];
+                s.kx[i] = s.ky[i] = s.kz[i] = 0.f;
+                if (kdf > 0.f) { s.kx[i] = (float)(c0 / (double)kdf); s.ky[i] = (float)(c1 / (double)kdf); s.kz[i] = (float)(c2 / (double)kdf); }
+            }
             float* q = reinterpret_cast<float*>(&s.plane_pairs[j >> 1]) + (j & 1);   // lane of the pair, stride 2 floats
             const v3 prel{position.x - r->refd[0], position.y - r->refd[1], position.z - r->refd[2]};
             const double vals[13] = {normal.x, normal.y, normal.z, vdot(normal, prel), -prel.x, -prel.y, -prel.z,
@@ -903,7 +919,7 @@ int rtm_debug_closest_hit(rtm_renderer* r, int32_t mode, uint32_t n, const doubl
         } else {
             if (r->f32.n != r->n) return fail(RTM_E_UNSUPPORTED, "handle was not created for the FP32 path");
             CU(rtm_upload_scene_f32(r->f32, c.stream));
-            if (r->use_bvh) rtm_launch_closest_hit_bvh_f32(c.bvh, c.mat, r->n, r->refd, n, d_org, d_dir, d_oid, d_hit, d_t, c.stream);
+            if (r->use_bvh) rtm_launch_closest_hit_bvh_f32(c.bvh, c.mat, r->n, r->n_planes, r->refd, n, d_org, d_dir, d_oid, d_hit, d_t, c.stream);
             else rtm_launch_closest_hit_f32(r->n, r->n_planes, r->refd, n, d_org, d_dir, d_oid, d_hit, d_t, c.stream);
         }
         CU(cudaGetLastError());

@@ -164,7 +164,8 @@ cudaError_t rtm_upload_scene_f32(const RtmSceneF32Host& h, cudaStream_t st);
 void rtm_launch_radiance_mega(int32_t n_spheres, int32_t n_planes, bool nee, const RtmPassParams& p, float4* records,
                               RtmCounters* counters, int32_t sm_count, const float* cps0, cudaStream_t st);
 void rtm_launch_radiance_bvh(const RtmBvhDev& bvh, const RtmMatDev& mat, const RtmPassParams& p, float4* records,
-                             RtmCounters* counters, int32_t sm_count, const float* cps0, cudaStream_t st);
+                             RtmCounters* counters, int32_t sm_count, const float* cps0, int32_t n_spheres, int32_t n_planes,
+                             cudaStream_t st);
 // one wave of the wavefront variant; `wave` counts from 0 (its parity selects the queue)
 void rtm_launch_wf_shade(int32_t n_spheres, bool use_bvh, const RtmBvhDev& bvh, const RtmMatDev& mat, const RtmPassParams& p,
                          float4* records, RtmCounters* counters, const float* cps0, const RtmWaveDev& wv, int32_t wave,
@@ -178,7 +179,7 @@ void rtm_launch_to_u8(const float4* accum, unsigned char* out, uint64_t n_pix, c
 void rtm_launch_closest_hit_f32(int32_t n_spheres, int32_t n_planes, const double* refd, uint32_t n, const double* org,
                                 const double* dir, const int32_t* origin_id, int32_t* hit, double* t,
                                 cudaStream_t st);
-void rtm_launch_closest_hit_bvh_f32(const RtmBvhDev& bvh, const RtmMatDev& mat, int32_t n_spheres, const double* refd, uint32_t n,
+void rtm_launch_closest_hit_bvh_f32(const RtmBvhDev& bvh, const RtmMatDev& mat, int32_t n_spheres, int32_t n_planes, const double* refd, uint32_t n,
                                     const double* org, const double* dir, const int32_t* origin_id, int32_t* hit, double* t,
                                     cudaStream_t st);
 void rtm_launch_acne_eps(uint32_t n, const uint32_t* bits, float* out, cudaStream_t st);

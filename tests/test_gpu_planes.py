@@ -80,6 +80,43 @@ def test_closest_hit_f64_planes_behind_hierarchy(gpu_lib):
     assert np.array_equal(hg, ho) and np.array_equal(tg[ho >= 0], to[ho >= 0])
 
 
+def test_closest_hit_f32_planes_behind_hierarchy(gpu_lib):
+    sc = random_plane_scene(9, 150, 9)
+    org, d = _rays(8, 20000, sc)
+    ho, to, _ = O.oracle_closest_hit(sc, org, d)
+    with rtm.Renderer(sc, accel="bvh") as r:
+        hg, tg = r.closest_hit(org, d, "f32")
+    same = hg == ho
+    assert same.mean() > 0.999, same.mean()
+    m = same & (ho >= 0)
+    assert np.abs(tg[m] - to[m]).max() < 2e-4 * max(1.0, to[m].max())
+    assert (ho >= sc.n).sum() > 2000 and ((ho >= 0) & (ho < sc.n)).sum() > 2000
+
+
+def test_radiance_planes_hierarchy_kernel(gpu_lib):
+    """150 spheres in a box of squares: the hierarchy kernel with the plane step against the FP64 kernel, and the
+    planar Cornell box forced through the hierarchy against its brute-force render"""
+    sc = random_plane_scene(21, 150, 8, 64, 36, 512, 1)
+    imgs = {}
+    for precision in ("f32", "f64"):
+        with rtm.Renderer(sc, precision=precision) as r:
+            res = r.render()
+        imgs[precision] = (res.image.astype(np.float64), res.stats.rays / res.stats.samples, res.stats.bvh_nodes)
+    a, b = imgs["f32"], imgs["f64"]
+    assert a[2] > 0 and b[2] > 0                                   # both went through the hierarchy (150 > 64 spheres)
+    assert abs(a[0].mean() - b[0].mean()) < 0.03 * b[0].mean(), (a[0].mean(), b[0].mean())
+    assert abs(a[1] - b[1]) < 0.01 * b[1], (a[1], b[1])
+    pc = rtm.load_scene(PLANES).with_dims(64, 34, 256, 2)
+    out = {}
+    for accel in ("brute", "bvh"):
+        with rtm.Renderer(pc, accel=accel, seed=3) as r:
+            res = r.render(want_hits=True)
+        out[accel] = (res.image.astype(np.float64), res.stats.rays / res.stats.samples, res.hits)
+    assert np.array_equal(out["brute"][2], out["bvh"][2])
+    assert abs(out["brute"][0].mean() - out["bvh"][0].mean()) < 0.01 * out["brute"][0].mean()
+    assert abs(out["brute"][1] - out["bvh"][1]) < 0.005 * out["brute"][1]
+
+
 @pytest.mark.parametrize("n_sph,n_pl", [(3, 6), (8, 12), (20, 16)])
 def test_closest_hit_f32_agrees(gpu_lib, n_sph, n_pl):
     sc = random_plane_scene(300 + n_sph, n_sph, n_pl)
@@ -157,9 +194,7 @@ def test_plane_error_paths(gpu_lib):
     sc = rtm.load_scene(PLANES).with_dims(16, 8, 1, 1)
     with pytest.raises(rtm.RtmError, match="COMPAT_ABC"):
         rtm.Renderer(sc, compat="head")
-    with pytest.raises(rtm.RtmError, match="brute-force megakernel"):
-        rtm.Renderer(sc, accel="bvh")
-    with pytest.raises(rtm.RtmError, match="brute-force megakernel"):
+    with pytest.raises(rtm.RtmError, match="megakernels"):
         rtm.Renderer(sc, variant="wavefront")
     from dataclasses import replace
     bad = replace(sc, pl_target=sc.pl_position.copy())

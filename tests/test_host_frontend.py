@@ -164,3 +164,21 @@ def test_cli_renders_result_files(hostlib, tmp_path, scene_path):
     assert np.array_equal(pfm, res.image)
     st = json.loads(r.stdout.strip().splitlines()[-1])
     assert st["samples"] == 96 * 50 * 16 and st["rays"] == res.stats.rays
+
+
+@pytest.mark.gpu
+def test_cli_renders_the_plane_scene_with_both_estimators(hostlib, tmp_path):
+    """extensions through the drop-in CLI: objectType 2 in the scene file, --estimator=nee"""
+    from PIL import Image
+    import raytracingmin_b200 as rtm
+    scene = os.path.join(ROOT, "scenes", "cornellBoxPlanes.json")
+    sc = rtm.load_scene(scene).with_dims(96, 50, 4, 2)
+    for est in ("reference", "nee"):
+        r = subprocess.run([CLI, "-json", scene, "--width=96", "--height=50", "--samples=4", "--superSamples=2", "--stats",
+                            f"--estimator={est}"], capture_output=True, text=True, cwd=tmp_path)
+        assert r.returncode == 0, r.stderr
+        bmp = np.asarray(Image.open(tmp_path / "result.bmp").convert("RGB"))
+        with rtm.Renderer(sc, estimator=est) as rr:
+            rr.render()
+            u8 = rr.read_u8()
+        assert np.array_equal(bmp, u8), est

@@ -163,3 +163,17 @@ def test_planar_cornell_oracle_known_answers():
     assert hist[1 + 3] > 0 and hist[1 + 4] > 0 and abs(int(hist[1 + 3]) - int(hist[1 + 4])) < 0.35 * hist[1 + 3]
     img, rays, samples = O.oracle_render(sc.with_dims(60, 32, 8, 1), O.LEVEL_ABC, 3)
     assert np.isfinite(img).all() and img.min() >= 0 and 4.0 < rays / samples < 7.0
+
+
+def test_extension_known_answers_are_stable():
+    """Regression pins of the two extension definitions (generated by this oracle, committed here: there is no
+    reference output for them): the planar Cornell hit histogram at 480x252 ss=2, and one small image each."""
+    sc = rtm.load_scene(PLANES).with_dims(480, 252, 1, 2)
+    hist = np.bincount(O.oracle_primary_hits(sc).ravel() + 1, minlength=10).tolist()
+    assert hist == [4, 27554, 12178, 15889, 163419, 163203, 22171, 26245, 53177, 0]
+    # the light sphere's 27554 is the sphere Cornell box's count at the same size (SURVEY.md §8c): same sphere, same camera
+    small = sc.with_dims(32, 18, 4, 1)
+    img, rays, samples = O.oracle_render(small, O.LEVEL_ABC, 1234)
+    assert (rays, samples) == (11996, 2304) and abs(img.sum() - 931.4044779993226) < 1e-9
+    img, rays, samples, shadow = O.oracle_render_nee(small, 1234)
+    assert (rays, samples, shadow) == (11896, 2304, 8718) and abs(img.sum() - 1010.8715379767282) < 1e-9
