@@ -311,9 +311,9 @@ __device__ __forceinline__ void bvh_inner_step(const RtmBvhDev& bvh, BvhRay& r, 
     }
 }
 
-// one leaf: 1..4 spheres in the direct form, then pop
-__device__ __forceinline__ void bvh_leaf_step(const RtmBvhDev& bvh, int oid, f3 o, f3 d, BvhRay& r, int* stack, unsigned& n_tests) {
-    const unsigned code = ~(unsigned)r.node;
+// one leaf: 1..4 spheres in the direct form
+__device__ __forceinline__ void bvh_leaf_test(const RtmBvhDev& bvh, int leaf, int oid, f3 o, f3 d, BvhRay& r, unsigned& n_tests) {
+    const unsigned code = ~(unsigned)leaf;
     const unsigned first = code >> 3, cnt = (code & 7u) + 1u;
     for (unsigned k = 0; k < cnt; ++k) {
         const float4 g = __ldg(bvh.leaf_geo + first + k);
@@ -338,6 +338,10 @@ __device__ __forceinline__ void bvh_leaf_step(const RtmBvhDev& bvh, int oid, f3 
         r.hit = ok ? sid : r.hit;
     }
     n_tests += cnt;
+}
+// ... then pop
+__device__ __forceinline__ void bvh_leaf_step(const RtmBvhDev& bvh, int oid, f3 o, f3 d, BvhRay& r, int* stack, unsigned& n_tests) {
+    bvh_leaf_test(bvh, r.node, oid, o, d, r, n_tests);
     r.node = stack[--r.sp];
 }
 
@@ -739,6 +743,9 @@ __global__ void __launch_bounds__(RTM_MEGA_THREADS, BVH ? 4 : 5) radiance_mega_k
 #ifndef RTM_BVH_MINBLOCKS
 #define RTM_BVH_MINBLOCKS 6
 #endif
+#ifndef RTM_BVH_HOLD
+#define RTM_BVH_HOLD 0
+#endif
 
 // PL: n_pl planes (extension) behind the n_sph spheres in the material records, tested at the start of every ray
 template <int NP, bool ACNE, bool PL>
@@ -935,12 +942,31 @@ __global__ void __launch_bounds__(RTM_MEGA_THREADS, RTM_BVH_MINBLOCKS) radiance_
         while (still) {
             // at most RTM_BVH_BURST inner nodes per round: a lane on its long first descent must not
             // keep the lanes that hop between neighbouring leaves (2-3 nodes apart) waiting
+#if RTM_BVH_HOLD
+            // a lane that reaches a leaf inside the burst parks it and goes on with the next node of its stack, so it
+            // keeps the inner-node block company instead of idling until the leaf block (Aila & Laine's speculative
+            // traversal); a second leaf makes it wait
+            int held = 0;   // leaf codes are negative
+#pragma unroll 1
+            for (int k = 0; k < RTM_BVH_BURST; ++k) {
+                if (tracing && ray.node < 0 && held == 0) {
+                    held = ray.node;
+                    ray.node = stack[--ray.sp];
+                }
+                if (!(tracing && bvh_is_inner(ray.node))) break;
+                bvh_inner_step(bvh, ray, stack);
+                ++n_nodes;
+            }
+            if (tracing && held != 0) bvh_leaf_test(bvh, held, id, o, d, ray, n_tests);
+            else if (tracing && ray.node < 0) bvh_leaf_step(bvh, id, o, d, ray, stack, n_tests);
+#else
 #pragma unroll 1
             for (int k = 0; k < RTM_BVH_BURST && tracing && bvh_is_inner(ray.node); ++k) {
                 bvh_inner_step(bvh, ray, stack);
                 ++n_nodes;
             }
             if (tracing && ray.node < 0) bvh_leaf_step(bvh, id, o, d, ray, stack, n_tests);
+#endif
             if (tracing && ray.node == RTM_BVH_NONE_DEV) {
                 tracing = false;
                 pending = true;
