@@ -450,6 +450,9 @@ __device__ __forceinline__ float ref_normalize_eps(uint32_t bits) {
 
 #define RTM_MEGA_THREADS 128
 #define RTM_MEGA_CHUNK 64u  // sub-pixels a warp reserves per global atomic
+#ifndef RTM_MEGA_RETRY
+#define RTM_MEGA_RETRY 12   // lanes killed by the roulette in one round that trigger another round before the bounce block
+#endif
 
 // ---- the radiance megakernel ---------------------------------------------------
 // Persistent: grid = SMs x resident blocks.  A lane owns one sub-pixel (unit) at a time
@@ -472,7 +475,8 @@ __device__ __forceinline__ float ref_normalize_eps(uint32_t bits) {
 // if it reaches the light.  A bounce ray that lands on a listed light from outside adds no emission (it was
 // counted by the sampling at the previous vertex); from inside it does (no cone there).  Same expectation
 // as the reference's estimator, ~8x less variance on the Cornell box.
-template <int N, bool BVH, bool ACNE, bool PL, bool NEE>
+// RT: roulette rounds (see the loop body) — chosen by the host for scenes whose visible surfaces kill most paths.
+template <int N, bool BVH, bool ACNE, bool PL, bool NEE, bool RT>
 __global__ void __launch_bounds__(RTM_MEGA_THREADS, BVH ? 4 : 5) radiance_mega_kernel(RtmPassParams p, float4* __restrict__ records,
                                                                                       RtmCounters* __restrict__ counters, int n_rt,
                                                                                       RtmBvhDev bvh, RtmMatDev mat,
@@ -591,12 +595,51 @@ __global__ void __launch_bounds__(RTM_MEGA_THREADS, BVH ? 4 : 5) radiance_mega_k
             continue;
         }
 
-        if (have) {
-            const uint2 rnd = rtm_bounce_rng(make_uint2(q, ((unsigned)s << 9) | (unsigned)depth), p.rk);
+        // closes the sample (Renderer.cpp:240-242), then finishes the sub-pixel or restarts at the primary hit
+        auto close_sample = [&]() {
+            acc.x += clamp01f(L.x * inv_norm);
+            acc.y += clamp01f(L.y * inv_norm);
+            acc.z += clamp01f(L.z * inv_norm);
+            ++s;
+            if (s == s_end) {
+                records[ql] = make_float4(acc.x, acc.y, acc.z, 0.f);
+                rays_ref += (unsigned)(s_end - s_begin);
+                have = false;
+            } else {
+                const float4 e0 = recs.emi(Pid);
+                o = P; id = Pid; w = Pw;
+                T = mk(1, 1, 1); L = mk(e0.x, e0.y, e0.z); depth = 0;
+                if (ACNE) cpsn = Pcpsn;
+            }
+        };
+        // Russian roulette, Renderer.cpp:78.  A killed path closes its sample and the lane stands on the primary hit
+        // of the next one.  RT instantiation: when RTM_MEGA_RETRY or more lanes of the warp are in that position they
+        // draw again before the (expensive) bounce block, so that scenes where most paths die at once
+        // (simpleSetting1/2: kd = 0.25 over most of the image, 1.1-1.3 rays per sample) do not run it at a quarter of
+        // the lanes: C3 108.7 -> 145 Grays/s.  On the Cornell box (19 % kills per round, ~5 lanes) the rounds never
+        // trigger, but the loop's mere presence costs 8 % (111 vs 120.5 Grays/s), hence a template flag set by the
+        // host from the scene (rtm_api.cu).  Draws are keyed by (sub-pixel, sample, depth): the image does not depend
+        // on the number of rounds, nor on the flag.
+        uint2 rnd = make_uint2(0u, 0u);
+        bool go = false, killed = false;
+        auto roulette = [&]() {
+            rnd = rtm_bounce_rng(make_uint2(q, ((unsigned)s << 9) | (unsigned)depth), p.rk);
             const float4 em = recs.emi(id);
-            // Russian roulette, Renderer.cpp:78
-            bool end = !((rnd.x < __float_as_uint(em.w)) && (depth + 1 < p.max_depth));
-            if (!end) {
+            go = (rnd.x < __float_as_uint(em.w)) && (depth + 1 < p.max_depth);
+            killed = !go;
+        };
+        if (have) roulette();
+        while (RT && __popc(__ballot_sync(0xffffffffu, killed)) >= RTM_MEGA_RETRY) {   // warp-uniform
+            if (killed) {
+                killed = false;
+                close_sample();
+                if (have) roulette();
+            }
+        }
+        // the common case closes a killed path's sample together with the paths the bounce block ends (one pass)
+        bool end = killed;
+        if (have && go) {
+            {
                 const float4 al = recs.alb(id);
                 T.x *= al.x; T.y *= al.y; T.z *= al.z;   // colorKD, SettingData.h:11-13
                 if (NEE) {
@@ -683,24 +726,8 @@ __global__ void __launch_bounds__(RTM_MEGA_THREADS, BVH ? 4 : 5) radiance_mega_k
                     end = true;  // miss: the recursion returns 0 (Renderer.cpp:116)
                 }
             }
-            if (end) {
-                // Renderer.cpp:240-242
-                acc.x += clamp01f(L.x * inv_norm);
-                acc.y += clamp01f(L.y * inv_norm);
-                acc.z += clamp01f(L.z * inv_norm);
-                ++s;
-                if (s == s_end) {
-                    records[ql] = make_float4(acc.x, acc.y, acc.z, 0.f);
-                    rays_ref += (unsigned)(s_end - s_begin);
-                    have = false;
-                } else {
-                    const float4 e0 = recs.emi(Pid);
-                    o = P; id = Pid; w = Pw;
-                    T = mk(1, 1, 1); L = mk(e0.x, e0.y, e0.z); depth = 0;
-                    if (ACNE) cpsn = Pcpsn;
-                }
-            }
         }
+        if (end) close_sample();
     }
 
     rays_ref += traced;
@@ -1136,19 +1163,22 @@ __global__ void __launch_bounds__(256) fma_peak_kernel(float* __restrict__ sink,
     if (r == 12345.678f) sink[0] = r;
 }
 
-template <int N, bool BVH, bool ACNE, bool PL, bool NEE = false>
+template <int N, bool BVH, bool ACNE, bool PL, bool NEE = false, bool RT = false>
 void launch_mega2(const RtmPassParams& p, float4* records, RtmCounters* counters, int n_rt, int n_pl, int sm_count, cudaStream_t st,
                   const RtmBvhDev& bvh, const RtmMatDev& mat, const float* cps0) {
     int per_sm = 0;
-    cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, radiance_mega_kernel<N, BVH, ACNE, PL, NEE>, RTM_MEGA_THREADS, 0);
+    cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, radiance_mega_kernel<N, BVH, ACNE, PL, NEE, RT>, RTM_MEGA_THREADS, 0);
     if (per_sm < 1) per_sm = 1;
-    radiance_mega_kernel<N, BVH, ACNE, PL, NEE><<<sm_count * per_sm, RTM_MEGA_THREADS, 0, st>>>(p, records, counters, n_rt, bvh, mat, cps0, n_pl);
+    radiance_mega_kernel<N, BVH, ACNE, PL, NEE, RT><<<sm_count * per_sm, RTM_MEGA_THREADS, 0, st>>>(p, records, counters, n_rt, bvh, mat, cps0, n_pl);
 }
 // cps0 != null selects the ACNE instantiation (see ref_normalize_eps), n_pl > 0 the one with the plane loop
 template <int N, bool BVH>
-void launch_mega(const RtmPassParams& p, float4* records, RtmCounters* counters, int n_rt, int n_pl, bool nee, int sm_count, cudaStream_t st,
-                 const float* cps0, const RtmBvhDev& bvh = RtmBvhDev{}, const RtmMatDev& mat = RtmMatDev{}) {
-    if (nee) {
+void launch_mega(const RtmPassParams& p, float4* records, RtmCounters* counters, int n_rt, int n_pl, bool nee, bool retry, int sm_count,
+                 cudaStream_t st, const float* cps0, const RtmBvhDev& bvh = RtmBvhDev{}, const RtmMatDev& mat = RtmMatDev{}) {
+    if (retry && !nee && n_pl == 0) {   // roulette rounds: instantiated for the reference's own scene model
+        if (cps0) launch_mega2<N, BVH, true, false, false, true>(p, records, counters, n_rt, 0, sm_count, st, bvh, mat, cps0);
+        else launch_mega2<N, BVH, false, false, false, true>(p, records, counters, n_rt, 0, sm_count, st, bvh, mat, nullptr);
+    } else if (nee) {
         if (n_pl > 0) {
             if (cps0) launch_mega2<N, BVH, true, true, true>(p, records, counters, n_rt, n_pl, sm_count, st, bvh, mat, cps0);
             else launch_mega2<N, BVH, false, true, true>(p, records, counters, n_rt, n_pl, sm_count, st, bvh, mat, nullptr);
@@ -1167,18 +1197,18 @@ void launch_mega(const RtmPassParams& p, float4* records, RtmCounters* counters,
 
 }  // namespace
 
-void rtm_launch_radiance_mega(int32_t n, int32_t n_pl, bool nee, const RtmPassParams& p, float4* records, RtmCounters* counters,
-                              int32_t sm_count, const float* cps0, cudaStream_t st) {
+void rtm_launch_radiance_mega(int32_t n, int32_t n_pl, bool nee, bool retry, const RtmPassParams& p, float4* records,
+                              RtmCounters* counters, int32_t sm_count, const float* cps0, cudaStream_t st) {
     switch (n) {
-        case 1: launch_mega<1, false>(p, records, counters, n, n_pl, nee, sm_count, st, cps0); break;
-        case 2: launch_mega<2, false>(p, records, counters, n, n_pl, nee, sm_count, st, cps0); break;
-        case 3: launch_mega<3, false>(p, records, counters, n, n_pl, nee, sm_count, st, cps0); break;
-        case 4: launch_mega<4, false>(p, records, counters, n, n_pl, nee, sm_count, st, cps0); break;
-        case 5: launch_mega<5, false>(p, records, counters, n, n_pl, nee, sm_count, st, cps0); break;
-        case 6: launch_mega<6, false>(p, records, counters, n, n_pl, nee, sm_count, st, cps0); break;
-        case 7: launch_mega<7, false>(p, records, counters, n, n_pl, nee, sm_count, st, cps0); break;
-        case 8: launch_mega<8, false>(p, records, counters, n, n_pl, nee, sm_count, st, cps0); break;
-        default: launch_mega<0, false>(p, records, counters, n, n_pl, nee, sm_count, st, cps0); break;
+        case 1: launch_mega<1, false>(p, records, counters, n, n_pl, nee, retry, sm_count, st, cps0); break;
+        case 2: launch_mega<2, false>(p, records, counters, n, n_pl, nee, retry, sm_count, st, cps0); break;
+        case 3: launch_mega<3, false>(p, records, counters, n, n_pl, nee, retry, sm_count, st, cps0); break;
+        case 4: launch_mega<4, false>(p, records, counters, n, n_pl, nee, retry, sm_count, st, cps0); break;
+        case 5: launch_mega<5, false>(p, records, counters, n, n_pl, nee, retry, sm_count, st, cps0); break;
+        case 6: launch_mega<6, false>(p, records, counters, n, n_pl, nee, retry, sm_count, st, cps0); break;
+        case 7: launch_mega<7, false>(p, records, counters, n, n_pl, nee, retry, sm_count, st, cps0); break;
+        case 8: launch_mega<8, false>(p, records, counters, n, n_pl, nee, retry, sm_count, st, cps0); break;
+        default: launch_mega<0, false>(p, records, counters, n, n_pl, nee, retry, sm_count, st, cps0); break;
     }
 }
 

@@ -143,6 +143,7 @@ struct rtm_renderer {
     std::vector<GpuCtx> gpus;
     int32_t last_launches = 0;
     bool hits_valid = false;
+    bool retry = false;         // roulette-rounds megakernel: the surfaces the camera sees kill most paths at once
     bool nee = false;           // next-event-estimation kernels (estimator NEE and at least one listed light)
     bool acne = false;          // the FP32 path models the reference's self-intersection on small spheres
     bool use_bvh = false;       // closest hit through the hierarchy (bvh.h) instead of the O(N) loop
@@ -254,7 +255,7 @@ int enqueue_pass(rtm_renderer* r, GpuCtx& c, cudaStream_t st, bool want_hits, in
             }
             c.waves = wave;
         } else if (r->use_bvh) rtm_launch_radiance_bvh(c.bvh, c.mat, p, c.records, c.counters, c.sm_count, c.cps0, r->n, r->n_planes, st);
-        else rtm_launch_radiance_mega(r->n, r->n_planes, r->nee, p, c.records, c.counters, c.sm_count, c.cps0, st);
+        else rtm_launch_radiance_mega(r->n, r->n_planes, r->nee, r->retry, p, c.records, c.counters, c.sm_count, c.cps0, st);
         CU(cudaEventRecord(c.ek[2], st));
         rtm_launch_accumulate(p, c.records, c.accum, st);
         CU(cudaEventRecord(c.ek[3], st));
@@ -553,6 +554,24 @@ int renderer_create(const rtm_scene_desc* sc, const rtm_options* opt_in, rtm_ren
             memcpy(&s.lit[i], &one, 4);
         }
         r->nee = s.n_lights > 0;
+    }
+
+    if (f32_path && !use_bvh) {
+        // Which megakernel: estimate the roulette's survival probability at the primary vertices as the mean kd of the
+        // reflecting spheres weighted by their apparent size from the camera (r^2 / d^2, 1 when the camera is inside;
+        // occlusion ignored).  Below 0.6 (simpleSetting1/2: 0.25 surfaces fill the image) the bounce block would run
+        // at a fraction of the lanes -> roulette rounds.  Either kernel renders the same image, bit for bit.
+        double wsum = 0.0, ksum = 0.0;
+        for (int i = 0; i < n; ++i) {
+            if (!(kd[i] > 0.0)) continue;
+            const double dx = cx[i] - r->refd[0], dy = cy[i] - r->refd[1], dz = cz[i] - r->refd[2];
+            const double d2 = dx * dx + dy * dy + dz * dz, rr = (double)sc->radius[i] * (double)sc->radius[i];
+            const double wgt = (d2 > rr) ? rr / d2 : 1.0;
+            wsum += wgt;
+            ksum += wgt * kd[i];
+        }
+        r->retry = wsum > 0.0 && ksum / wsum < 0.6;
+        if (const char* e = getenv("RTM_MEGA_RETRY_FORCE")) r->retry = (e[0] == '1');   // test hook: both kernels, same scene
     }
 
     if (f32_path && (m & 1)) reinterpret_cast<float*>(&r->f32.plane_pairs[m >> 1])[2 * 3 + 1] = -1.0f;   // dummy lane: n = 0, d0 = -1

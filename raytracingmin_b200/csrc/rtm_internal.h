@@ -161,7 +161,8 @@ cudaError_t rtm_upload_scene_f32(const RtmSceneF32Host& h, cudaStream_t st);
 // cps0: per-sub-pixel c' = |c - P|^2 - r^2 at the primary hit from the FP64 pass, or null when the scene
 // has no sphere small enough for the reference's self-intersection to matter (kernels_radiance.cu: ACNE)
 // nee: the next-event-estimation instantiation (needs c_scene.n_lights > 0)
-void rtm_launch_radiance_mega(int32_t n_spheres, int32_t n_planes, bool nee, const RtmPassParams& p, float4* records,
+// retry: the roulette-rounds instantiation (scenes whose visible surfaces kill most paths at once)
+void rtm_launch_radiance_mega(int32_t n_spheres, int32_t n_planes, bool nee, bool retry, const RtmPassParams& p, float4* records,
                               RtmCounters* counters, int32_t sm_count, const float* cps0, cudaStream_t st);
 void rtm_launch_radiance_bvh(const RtmBvhDev& bvh, const RtmMatDev& mat, const RtmPassParams& p, float4* records,
                              RtmCounters* counters, int32_t sm_count, const float* cps0, int32_t n_spheres, int32_t n_planes,

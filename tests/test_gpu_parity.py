@@ -360,3 +360,18 @@ def test_c2_radiance_rmse_vs_reference_objects_band():
         assert (np.abs(bias) <= np.abs(bias_band).max(axis=0) + 4.0 * bias_band.std(axis=0)).all(), (precision, bias, bias_band)
         rps = res.stats.rays / res.stats.samples
         assert abs(rps - float(g["rays_per_sample"])) < 0.005 * rps
+
+
+@pytest.mark.parametrize("name", ["simple2", "cornellBox", "settingData"])
+def test_roulette_rounds_kernel_renders_the_same_image(scene_path, name, monkeypatch):
+    """The megakernel instantiation with roulette rounds (picked for scenes whose visible surfaces kill most
+    paths) and the plain one: same draws per (sub-pixel, sample, depth), same image bit for bit, same ray count."""
+    sc = rtm.load_scene(scene_path(name), "abc").with_dims(96, 54, 32, 2)
+    out = {}
+    for force in ("0", "1"):
+        monkeypatch.setenv("RTM_MEGA_RETRY_FORCE", force)
+        with rtm.Renderer(sc, seed=5) as r:
+            res = r.render()
+        out[force] = (res.image.copy(), res.stats.rays, res.stats.rays_traced)
+    assert np.array_equal(out["0"][0], out["1"][0])
+    assert out["0"][1:] == out["1"][1:]
