@@ -773,6 +773,9 @@ __global__ void __launch_bounds__(RTM_MEGA_THREADS, BVH ? 4 : 5) radiance_mega_k
 #ifndef RTM_BVH_HOLD
 #define RTM_BVH_HOLD 0
 #endif
+#ifndef RTM_BVH_S_ROUND
+#define RTM_BVH_S_ROUND 1   // lanes that must need another roulette decision for the S block to run another round (swept: 1 4.50, 2 4.46, 4 4.45, 8 4.34 Grays/s on C5)
+#endif
 
 // PL: n_pl planes (extension) behind the n_sph spheres in the material records, tested at the start of every ray
 template <int NP, bool ACNE, bool PL>
@@ -876,8 +879,15 @@ __global__ void __launch_bounds__(RTM_MEGA_THREADS, RTM_BVH_MINBLOCKS) radiance_
             continue;
         }
 
-        // ---- S block
-        if ((tr == 0u || __popc(sready) >= RTM_BVH_S_THRESH) && have && !tracing) {
+        // ---- S block.  Entered by the whole warp (warp-uniform control flow, lanes outside it are predicated off):
+        // the roulette runs in ROUNDS shared by all S lanes, and the packed big-sphere test + ray start run once,
+        // after the rounds, for every lane that has a direction.  (With per-lane loops the compiler let each lane
+        // leave the roulette loop on its own: the ~140-instruction ray start then ran once per group of lanes that
+        // left together, 3.3 times per entry at 6 of 32 lanes — ncu_bvh_v3.)  A lane whose path is killed in the last
+        // round closes its sample and stays S-ready; another round is run only while RTM_BVH_S_ROUND or more lanes
+        // need one.
+        const bool in_s = (tr == 0u || __popc(sready) >= RTM_BVH_S_THRESH) && have && !tracing;
+        if (__any_sync(0xffffffffu, in_s)) {
             // a finished ray is applied to the path; returns true when the path ends there
             auto apply_hit = [&](int id2, float t) -> bool {
                 if (id2 < 0) return true;                                            // miss: Renderer.cpp:116
@@ -903,64 +913,70 @@ __global__ void __launch_bounds__(RTM_MEGA_THREADS, RTM_BVH_MINBLOCKS) radiance_
                 return __float_as_uint(e2.w) == 0u;                                  // kd == 0: the next roulette cannot continue
             };
             bool end = false;
-            if (pending) {
+            if (in_s && pending) {
                 pending = false;
                 end = apply_hit(ray.hit, ray.best + RTM_T_EPS);
             }
-            for (;;) {   // usually one round; another one only with an empty hierarchy
-            int oslot = -2;   // >= -1: a bounce direction is ready, start the ray after the loop
+            bool deciding = in_s, start = false;
+            int oslot = -1;
             for (;;) {
-                if (!end) {
-                    const uint2 rnd = rtm_bounce_rng(make_uint2(q, ((unsigned)s << 9) | (unsigned)depth), p.rk);
-                    const float4 em = __ldg(mat.emi + id);
-                    end = !((rnd.x < __float_as_uint(em.w)) && (depth + 1 < p.max_depth));   // Renderer.cpp:78
+                if (deciding) {
                     if (!end) {
-                        const float4 al = __ldg(mat.alb + id);
-                        T.x *= al.x; T.y *= al.y; T.z *= al.z;                               // colorKD
-                        d = cosine_dir(w, rnd.y, ((rnd.x & 0xFFFu) << 10) | (rnd.y & 0x3FFu));
-                        eps_bits = rnd.x ^ (rnd.y * 0x9E3779B9u);
-                        ++traced;
-                        if (ACNE) {
-                            const float cosw = dot(w, d);
-                            if (cpsn + cosw <= 0.f && !(PL && id >= n_sph)) {
-                                // SettingData.cpp:208-212: the far root of the sphere the ray stands (just) inside
-                                const float rr = fast_rcp(__ldg(mat.geo + id).w);
-                                const float qq = -cpsn * rr * RTM_ACNE_2TAU, bq = rr * cosw;
-                                end = apply_hit(id, qq * fast_rcp(bq + fast_sqrt(fmaf(bq, bq, qq))));
-                                continue;
+                        const uint2 rnd = rtm_bounce_rng(make_uint2(q, ((unsigned)s << 9) | (unsigned)depth), p.rk);
+                        const float4 em = __ldg(mat.emi + id);
+                        end = !((rnd.x < __float_as_uint(em.w)) && (depth + 1 < p.max_depth));   // Renderer.cpp:78
+                        if (!end) {
+                            const float4 al = __ldg(mat.alb + id);
+                            T.x *= al.x; T.y *= al.y; T.z *= al.z;                               // colorKD
+                            d = cosine_dir(w, rnd.y, ((rnd.x & 0xFFFu) << 10) | (rnd.y & 0x3FFu));
+                            eps_bits = rnd.x ^ (rnd.y * 0x9E3779B9u);
+                            ++traced;
+                            bool self = false;
+                            if (ACNE) {
+                                const float cosw = dot(w, d);
+                                if (cpsn + cosw <= 0.f && !(PL && id >= n_sph)) {
+                                    // SettingData.cpp:208-212: the far root of the sphere the ray stands (just) inside
+                                    const float rr = fast_rcp(__ldg(mat.geo + id).w);
+                                    const float qq = -cpsn * rr * RTM_ACNE_2TAU, bq = rr * cosw;
+                                    end = apply_hit(id, qq * fast_rcp(bq + fast_sqrt(fmaf(bq, bq, qq))));
+                                    self = true;   // stands on the next vertex: decide again
+                                }
+                            }
+                            if (!self) {
+                                oslot = __float_as_int(al.w);
+                                start = true;
+                                deciding = false;
                             }
                         }
-                        oslot = __float_as_int(al.w);
-                        break;
+                    }
+                    if (deciding && end) {
+                        // the sample is complete: Renderer.cpp:240-242
+                        acc.x += clamp01f(L.x * inv_norm);
+                        acc.y += clamp01f(L.y * inv_norm);
+                        acc.z += clamp01f(L.z * inv_norm);
+                        ++s;
+                        if (s == s_end) {
+                            records[ql] = make_float4(acc.x, acc.y, acc.z, 0.f);
+                            rays_ref += (unsigned)(s_end - s_begin);
+                            have = false;
+                            deciding = false;
+                        } else {
+                            const float4 e0 = __ldg(mat.emi + Pid);
+                            o = P; id = Pid; w = Pw;
+                            T = mk(1, 1, 1); L = mk(e0.x, e0.y, e0.z); depth = 0;
+                            if (ACNE) cpsn = Pcpsn;
+                            end = false;
+                        }
                     }
                 }
-                // the sample is complete: Renderer.cpp:240-242
-                acc.x += clamp01f(L.x * inv_norm);
-                acc.y += clamp01f(L.y * inv_norm);
-                acc.z += clamp01f(L.z * inv_norm);
-                ++s;
-                if (s == s_end) {
-                    records[ql] = make_float4(acc.x, acc.y, acc.z, 0.f);
-                    rays_ref += (unsigned)(s_end - s_begin);
-                    have = false;
-                    break;
-                }
-                const float4 e0 = __ldg(mat.emi + Pid);
-                o = P; id = Pid; w = Pw;
-                T = mk(1, 1, 1); L = mk(e0.x, e0.y, e0.z); depth = 0;
-                if (ACNE) cpsn = Pcpsn;
-                end = false;
+                if (__popc(__ballot_sync(0xffffffffu, deciding)) < RTM_BVH_S_ROUND) break;
             }
-            if (oslot < -1) break;   // the sub-pixel is finished
-            // the packed big-sphere test (~140 instructions) runs once, for all lanes that start a ray, instead of
-            // once per roulette round with whichever lanes happened to continue in that round
-            bvh_ray_begin<NP>(sh_mask, sh_big, bvh, oslot, o, d, key_mask, ray, stack, n_tests);
-            if (PL) bvh_ray_planes(n_sph, n_pl, id, o, d, ray);
-            if (ray.node != RTM_BVH_NONE_DEV) {
-                tracing = true;
-                break;
-            }
-            end = apply_hit(ray.hit, ray.best + RTM_T_EPS);
+            if (start) {
+                // the packed big-sphere test (~140 instructions) and the planes: once, for all lanes that start a ray
+                bvh_ray_begin<NP>(sh_mask, sh_big, bvh, oslot, o, d, key_mask, ray, stack, n_tests);
+                if (PL) bvh_ray_planes(n_sph, n_pl, id, o, d, ray);
+                if (ray.node != RTM_BVH_NONE_DEV) tracing = true;
+                else pending = true;   // empty hierarchy: the hit (big spheres / planes) is applied at the next entry
             }
         }
 
