@@ -768,7 +768,7 @@ __global__ void __launch_bounds__(RTM_MEGA_THREADS, BVH ? 4 : 5) radiance_mega_k
 #define RTM_BVH_BURST 8
 #endif
 #ifndef RTM_BVH_MINBLOCKS
-#define RTM_BVH_MINBLOCKS 6
+#define RTM_BVH_MINBLOCKS 7
 #endif
 #ifndef RTM_BVH_HOLD
 #define RTM_BVH_HOLD 0
@@ -802,13 +802,26 @@ __global__ void __launch_bounds__(RTM_MEGA_THREADS, RTM_BVH_MINBLOCKS) radiance_
     unsigned w_next = 0, w_end = 0;
     bool have = false, done = false, tracing = false, pending = false;
     unsigned q = 0, ql = 0;
-    f3 P = mk(0, 0, 0), Pw = mk(0, 0, 1);
-    int Pid = 0;
     f3 acc = mk(0, 0, 0);
     f3 o = mk(0, 0, 0), w = mk(0, 0, 1), T = mk(1, 1, 1), L = mk(0, 0, 0), d = mk(0, 0, 1);
     int id = 0, s = 0, depth = 0;
-    float cpsn = 0.f, Pcpsn = 0.f;
+    float cpsn = 0.f;
     uint32_t eps_bits = 0;
+    // the primary hit of the lane's sub-pixel is NOT lane state here: it is re-read from records[ql] (which holds it
+    // until the sub-pixel's sum is written) at every sample restart — 8 registers less, which is what lets
+    // RTM_BVH_MINBLOCKS blocks stay resident
+    auto stand_on_primary = [&](const float4 rec) {
+        const unsigned wbits = __float_as_uint(rec.w);
+        const int pid = (int)(wbits & RTM_REC_IDMASK);
+        const float4 g = __ldg(mat.geo + pid), e0 = __ldg(mat.emi + pid);
+        const float ir = (wbits & RTM_REC_FLIP) ? -g.w : g.w;
+        o = mk(rec.x, rec.y, rec.z);
+        w = mk((o.x - g.x) * ir, (o.y - g.y) * ir, (o.z - g.z) * ir);
+        if (PL && pid >= n_sph) w = (wbits & RTM_REC_FLIP) ? mk(-g.x, -g.y, -g.z) : mk(g.x, g.y, g.z);
+        id = pid;
+        T = mk(1, 1, 1); L = mk(e0.x, e0.y, e0.z); depth = 0;
+        if (ACNE) cpsn = (wbits & RTM_REC_FLIP) ? 0.f : cps0[ql] * g.w * RTM_ACNE_INV2TAU;
+    };
     BvhRay ray;
     ray.node = RTM_BVH_NONE_DEV;
     int stack[RTM_BVH_STACK_DEV];
@@ -840,7 +853,7 @@ __global__ void __launch_bounds__(RTM_MEGA_THREADS, RTM_BVH_MINBLOCKS) radiance_
                 const unsigned wbits = __float_as_uint(rec.w);
                 const unsigned ns = (unsigned)(s_end - s_begin);
                 const bool miss = (wbits == RTM_REC_MISS);
-                Pid = miss ? 0 : (int)(wbits & RTM_REC_IDMASK);
+                const int Pid = miss ? 0 : (int)(wbits & RTM_REC_IDMASK);
                 const float4 e0 = __ldg(mat.emi + Pid);
                 if (miss || __float_as_uint(e0.w) == 0u) {
                     float4 out = make_float4(0.f, 0.f, 0.f, 0.f);
@@ -853,19 +866,9 @@ __global__ void __launch_bounds__(RTM_MEGA_THREADS, RTM_BVH_MINBLOCKS) radiance_
                     rays_ref += ns;
                 } else {
                     have = true;
-                    P = mk(rec.x, rec.y, rec.z);
-                    const float4 g = __ldg(mat.geo + Pid);
-                    const float ir = (wbits & RTM_REC_FLIP) ? -g.w : g.w;
-                    Pw = mk((P.x - g.x) * ir, (P.y - g.y) * ir, (P.z - g.z) * ir);
-                    if (PL && Pid >= n_sph) Pw = (wbits & RTM_REC_FLIP) ? mk(-g.x, -g.y, -g.z) : mk(g.x, g.y, g.z);
                     acc = mk(0, 0, 0);
                     s = s_begin;
-                    o = P; id = Pid; w = Pw;
-                    T = mk(1, 1, 1); L = mk(e0.x, e0.y, e0.z); depth = 0;
-                    if (ACNE) {
-                        Pcpsn = (wbits & RTM_REC_FLIP) ? 0.f : cps0[ql] * g.w * RTM_ACNE_INV2TAU;
-                        cpsn = Pcpsn;
-                    }
+                    stand_on_primary(rec);
                 }
             }
             const unsigned took = (__popc(need) < avail) ? __popc(need) : avail;
@@ -961,10 +964,7 @@ __global__ void __launch_bounds__(RTM_MEGA_THREADS, RTM_BVH_MINBLOCKS) radiance_
                             have = false;
                             deciding = false;
                         } else {
-                            const float4 e0 = __ldg(mat.emi + Pid);
-                            o = P; id = Pid; w = Pw;
-                            T = mk(1, 1, 1); L = mk(e0.x, e0.y, e0.z); depth = 0;
-                            if (ACNE) cpsn = Pcpsn;
+                            stand_on_primary(records[ql]);
                             end = false;
                         }
                     }
