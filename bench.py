@@ -206,7 +206,7 @@ def run_gpu_arm(args):
 
     # device-resident handle: the library writes its partial framebuffer straight into a
     # torch tensor (the NCCL send buffer); no host sync between the last kernel and the reduce.
-    r = rtm.Renderer(sc, device=local, seed=0x5EED, variant=args.variant, **plan)
+    r = rtm.Renderer(sc, device=local, seed=0x5EED, variant=args.variant, estimator=args.estimator, **plan)
     accum = torch.zeros((sc.height, sc.width, 4), dtype=torch.float32, device=dev)
     r.set_accum_buffer(accum.data_ptr())
     stream = torch.cuda.current_stream()
@@ -349,6 +349,10 @@ def run_gpu_arm(args):
                        **({"n_planes": sc.n_planes, "flops_note": "plane tests are not counted (the 17-flop figure is the sphere test's)"}
                           if sc.n_planes else {}),
                        "variant": args.variant,
+                       **({"estimator": "nee (extension, DESIGN.md §11): `value` counts the PATH rays of the reference's estimator; "
+                                        f"the kernel also traced {(st.rays_traced - n_sub - (st.rays - st.samples)) / max(1, st.samples):.2f} "
+                                        "shadow rays per sample; the roofline's flops count their sphere tests, nothing else of them"}
+                          if args.estimator == "nee" else {}),
                        "closest_hit": "brute force (packed pairs)" if sc.n <= 64 else
                                       f"hierarchy: {st.sphere_tests / max(1, st.rays_traced):.1f} sphere tests + "
                                       f"{st.bvh_nodes / max(1, st.rays_traced):.1f} nodes per traced ray",
@@ -368,7 +372,7 @@ def run_gpu_arm(args):
             "kernel_ms": {"primary_f64": kms[0], "radiance_mega": kms[1], "accumulate": kms[2]},
             "roofline": {"bound": "fp32", "achieved": achieved, "peak": fp32_peak, "unit": "TFLOP/s",
                          "frac": achieved / fp32_peak if fp32_peak else None,
-                         "traffic": ncu_traffic_bytes(args.workload, args.variant) if world == 1 else None,
+                         "traffic": ncu_traffic_bytes(args.workload, args.variant) if (world == 1 and args.estimator == "reference") else None,
                          "traffic_note": "bytes per launch, dram read+write from the committed ncu --set full capture "
                                          "(profiles/r01); algorithmic = records read + written = 32 B per sub-pixel",
                          "algorithmic_bytes_per_launch": 32.0 * n_sub,
@@ -421,6 +425,8 @@ def main():
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--reduce", default="nccl", choices=["peer", "nccl"],
                     help="N > 1: how the partial framebuffers reach rank 0 (peer-memory gather kernel path, or ncclReduce)")
+    ap.add_argument("--estimator", default="reference", choices=["reference", "nee"],
+                    help="nee = next-event estimation (extension); the headline metric is quoted on `reference`")
     ap.add_argument("--variant", default="mega", choices=["mega", "wavefront"],
                     help="kernel organisation of the FP32 bounce loop (DESIGN.md: megakernel vs wavefront)")
     args = ap.parse_args()
