@@ -210,3 +210,28 @@ def test_wavefront_matches_megakernel(scene_path, synth, which):
     assert abs(ia.mean() - ib.mean()) <= 5e-3 * ia.mean()
     same = np.isclose(ia, ib, rtol=1e-4, atol=1e-6).all(axis=-1).mean()
     assert same > 0.9, same
+
+
+def test_hierarchy_100k_spheres_hit_map_bit_exact_and_radiance_runs(gpu_lib):
+    """size edge: 100 000 spheres (hierarchy depth 19, 59 k nodes) — exact hit map against the oracle's O(N) loop
+    on a small image, FP32 and FP64 bounce loops agree on the mean"""
+    rng = np.random.default_rng(1)
+    n = 100000
+    pos = rng.uniform(-50, 50, (n, 3))
+    rad = (np.round(np.exp(rng.uniform(np.log(0.05), np.log(0.8), n)) * 1024) / 1024).astype(np.float32)
+    emi = np.zeros((n, 3))
+    emi[::50] = 6.0
+    sc = rtm.Scene(width=64, height=36, samples=64, superSamples=1, cam_origin=np.array([0.0, 0.0, -60.0]), cam_target=np.zeros(3),
+                   cam_up=np.array([0.0, 1.0, 0.0]), fov=float(np.float32(0.8)), position=pos, radius=rad,
+                   color=rng.uniform(0.1, 0.9, (n, 3)), emission=emi).normalized()
+    want = O.oracle_primary_hits(sc)
+    out = {}
+    for precision in ("f32", "f64"):
+        with rtm.Renderer(sc, precision=precision) as r:
+            res = r.render(want_hits=True)
+        assert np.array_equal(res.hits, want), precision
+        assert res.stats.bvh_nodes > 0 and np.isfinite(res.image).all()
+        out[precision] = (float(res.image.astype(np.float64).mean()), res.stats.rays / res.stats.samples)
+    assert (want >= 0).mean() > 0.5
+    assert abs(out["f32"][0] - out["f64"][0]) < 0.05 * out["f64"][0] + 1e-4, out
+    assert abs(out["f32"][1] - out["f64"][1]) < 0.02 * out["f64"][1], out
