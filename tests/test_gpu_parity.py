@@ -375,3 +375,25 @@ def test_roulette_rounds_kernel_renders_the_same_image(scene_path, name, monkeyp
         out[force] = (res.image.copy(), res.stats.rays, res.stats.rays_traced)
     assert np.array_equal(out["0"][0], out["1"][0])
     assert out["0"][1:] == out["1"][1:]
+
+
+def test_single_process_multi_gpu_mode(scene_path):
+    """rtm_options.n_gpus > 1: one process drives several devices (the C++ front end's mode), the sample budget is
+    sliced across them and the partial framebuffers are summed with one ncclReduce (NCCL through dlopen)."""
+    import torch
+    n = min(torch.cuda.device_count(), 4)
+    if n < 2:
+        pytest.skip("needs at least 2 GPUs (run with gpurun --gpus 2)")
+    sc = rtm.load_scene(scene_path("cornellBox"), "abc").with_dims(160, 84, 8, 2)
+    with rtm.Renderer(sc, seed=3) as r:
+        one = r.render(want_hits=True)
+    with rtm.Renderer(sc, seed=3, n_gpus=n) as r:
+        many = r.render(want_hits=True)
+    assert many.stats.n_gpus == n and many.stats.samples == one.stats.samples and many.stats.rays == one.stats.rays
+    assert np.array_equal(many.hits, one.hits)
+    assert np.allclose(many.image, one.image, rtol=0, atol=2e-6 * float(one.image.max()))
+    with rtm.Renderer(sc, compat="head", n_gpus=n) as r:
+        head_many = r.render().image
+    with rtm.Renderer(sc, compat="head") as r:
+        head_one = r.render().image
+    assert np.allclose(head_many, head_one, rtol=0, atol=2e-6 * float(head_one.max()))
