@@ -117,7 +117,9 @@ def cpu_render_sample(sc, wl, target_seconds: float):
     as fit in ~target_seconds.  Returns dict(value Mrays/s, msamples, cores, kind, sample)."""
     sys.path.insert(0, os.path.join(ROOT, "tests"))
     import oracle_lib as O
-    cores = os.cpu_count() or 1
+    # the thread count is passed explicitly: torchrun exports OMP_NUM_THREADS=1 to its workers, which would
+    # silently time a single-threaded run while the line says "all host cores"
+    cores = len(os.sched_getaffinity(0)) if hasattr(os, "sched_getaffinity") else (os.cpu_count() or 1)
     w, h = max(16, sc.width // 8), max(9, sc.height // 8)
     small = sc.with_dims(w, h, 1, sc.superSamples)
     use_ref = O.ref_available("abc") and sc.n_planes == 0   # the reference's objects cannot hold a plane
@@ -127,10 +129,10 @@ def cpu_render_sample(sc, wl, target_seconds: float):
         t0 = time.perf_counter()
         if use_ref:
             rs = O.RefScene("abc", s2)
-            _, rays, samples = rs.render(1234, 0)
+            _, rays, samples = rs.render(1234, cores)
             rs.close()
         else:
-            _, rays, samples = O.oracle_render(s2, O.LEVEL_ABC, 1234)
+            _, rays, samples = O.oracle_render(s2, O.LEVEL_ABC, 1234, cores)
         return time.perf_counter() - t0, rays, samples
 
     S, t = 1, 0.0

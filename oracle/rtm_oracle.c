@@ -16,6 +16,9 @@
 #include <math.h>
 #include <stdlib.h>
 #include <string.h>
+#ifdef _OPENMP
+#include <omp.h>
+#endif
 
 typedef struct { double x, y, z; } v3;
 
@@ -310,11 +313,12 @@ int rtmo_render(const rtmo_scene* s, int level, uint32_t seed, double* image,
     const frame_t f = make_frame(s);
     const v3 org = v3_load(s->cam_origin);
     uint64_t rays = 0, samples = 0;
-    (void)nthreads;
 #ifdef _OPENMP
-    if (nthreads <= 0) nthreads = 0;
+    if (nthreads <= 0) nthreads = omp_get_max_threads();   /* an explicit count overrides OMP_NUM_THREADS (torchrun sets it to 1) */
+#else
+    (void)nthreads;
 #endif
-#pragma omp parallel for schedule(dynamic) reduction(+ : rays, samples)
+#pragma omp parallel for schedule(dynamic) num_threads(nthreads) reduction(+ : rays, samples)
     for (int y = 0; y < s->height; ++y) {
         mt19937_t rng;
         counters_t c = {0};

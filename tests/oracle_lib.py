@@ -87,11 +87,11 @@ def oracle_primary_hits(sc) -> np.ndarray:
     return out
 
 
-def oracle_render(sc, level: int = LEVEL_ABC, seed: int = 1234):
+def oracle_render(sc, level: int = LEVEL_ABC, seed: int = 1234, nthreads: int = 0):
     s, keep = _oscene(sc)
     img = np.empty((sc.height, sc.width, 3), np.float64)
     rays, samples = C.c_uint64(), C.c_uint64()
-    oracle().rtmo_render(C.byref(s), level, seed, img.ctypes.data, C.byref(rays), C.byref(samples), 0)
+    oracle().rtmo_render(C.byref(s), level, seed, img.ctypes.data, C.byref(rays), C.byref(samples), nthreads)
     return img, rays.value, samples.value
 
 
