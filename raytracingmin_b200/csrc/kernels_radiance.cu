@@ -20,6 +20,7 @@
 #include "philox.cuh"
 
 #include <float.h>
+#include <stdlib.h>
 
 __constant__ RtmSceneF32Host c_scene;
 
@@ -271,7 +272,9 @@ struct BvhRay {
 };
 
 // the packed test over the big list, then position the lane on the root
-template <int NP>
+// ST = distance in ints between two consecutive entries of a lane's stack: 1 for a private (local-memory) array,
+// the block size for the interleaved shared-memory layout stack[level][thread]
+template <int NP, int ST = 1>
 __device__ __forceinline__ void bvh_ray_begin(const SelfMask& sm, const SharedBig& big, const RtmBvhDev& bvh, int oslot, f3 o, f3 d,
                                               unsigned key_mask, BvhRay& r, int* stack, unsigned& n_tests) {
     r.best = FLT_MAX;
@@ -288,10 +291,11 @@ __device__ __forceinline__ void bvh_ray_begin(const SelfMask& sm, const SharedBi
     r.oi = mk(o.x * r.inv.x, o.y * r.inv.y, o.z * r.inv.z);
     r.node = bvh.root;
     r.sp = 0;
-    stack[r.sp++] = RTM_BVH_NONE_DEV;
+    stack[ST * r.sp++] = RTM_BVH_NONE_DEV;
 }
 
 // one inner node: test both children, descend into the nearer one, push the other
+template <int ST = 1>
 __device__ __forceinline__ void bvh_inner_step(const RtmBvhDev& bvh, BvhRay& r, int* stack) {
     const float4* q = bvh.nodes + 4 * r.node;
     const float4 q0 = __ldg(q), q1 = __ldg(q + 1), q2 = __ldg(q + 2), q3 = __ldg(q + 3);
@@ -302,12 +306,12 @@ __device__ __forceinline__ void bvh_inner_step(const RtmBvhDev& bvh, BvhRay& r, 
     const int c0 = __float_as_int(q3.x), c1 = __float_as_int(q3.y);
     if (h0 && h1) {
         const bool swap = n1 < n0;
-        stack[r.sp++] = swap ? c0 : c1;
+        stack[ST * r.sp++] = swap ? c0 : c1;
         r.node = swap ? c1 : c0;
     } else if (h0 || h1) {
         r.node = h0 ? c0 : c1;
     } else {
-        r.node = stack[--r.sp];
+        r.node = stack[ST * --r.sp];
     }
 }
 
@@ -340,9 +344,10 @@ __device__ __forceinline__ void bvh_leaf_test(const RtmBvhDev& bvh, int leaf, in
     n_tests += cnt;
 }
 // ... then pop
+template <int ST = 1>
 __device__ __forceinline__ void bvh_leaf_step(const RtmBvhDev& bvh, int oid, f3 o, f3 d, BvhRay& r, int* stack, unsigned& n_tests) {
     bvh_leaf_test(bvh, r.node, oid, o, d, r, n_tests);
-    r.node = stack[--r.sp];
+    r.node = stack[ST * --r.sp];
 }
 
 // PlaneObject extension: planes are tested like the big spheres, before the descent, so that the hierarchy is
@@ -778,7 +783,13 @@ __global__ void __launch_bounds__(RTM_MEGA_THREADS, BVH ? 4 : 5) radiance_mega_k
 #endif
 
 // PL: n_pl planes (extension) behind the n_sph spheres in the material records, tested at the start of every ray
-template <int NP, bool ACNE, bool PL>
+// SST: the per-lane traversal stack lives in shared memory, stack[level][thread], RTM_BVH_SSTACK levels (the host
+// picks it when the tree is shallow enough: depth + 2 entries are the most a walk can hold); otherwise a private
+// 64-entry array in local memory.
+#ifndef RTM_BVH_SSTACK
+#define RTM_BVH_SSTACK 24
+#endif
+template <int NP, bool ACNE, bool PL, bool SST>
 __global__ void __launch_bounds__(RTM_MEGA_THREADS, RTM_BVH_MINBLOCKS) radiance_bvh_kernel(RtmPassParams p, float4* __restrict__ records,
                                                                            RtmCounters* __restrict__ counters, RtmBvhDev bvh,
                                                                            RtmMatDev mat, const float* __restrict__ cps0, int n_sph,
@@ -824,7 +835,10 @@ __global__ void __launch_bounds__(RTM_MEGA_THREADS, RTM_BVH_MINBLOCKS) radiance_
     };
     BvhRay ray;
     ray.node = RTM_BVH_NONE_DEV;
-    int stack[RTM_BVH_STACK_DEV];
+    constexpr int ST = SST ? RTM_MEGA_THREADS : 1;
+    __shared__ int sh_stack[SST ? RTM_BVH_SSTACK * RTM_MEGA_THREADS : 1];
+    int lstack[SST ? 1 : RTM_BVH_STACK_DEV];
+    int* const stack = SST ? (sh_stack + threadIdx.x) : lstack;
     unsigned long long rays_ref = 0, traced = 0;
     unsigned n_tests = 0, n_nodes = 0;
 
@@ -973,7 +987,7 @@ __global__ void __launch_bounds__(RTM_MEGA_THREADS, RTM_BVH_MINBLOCKS) radiance_
             }
             if (start) {
                 // the packed big-sphere test (~140 instructions) and the planes: once, for all lanes that start a ray
-                bvh_ray_begin<NP>(sh_mask, sh_big, bvh, oslot, o, d, key_mask, ray, stack, n_tests);
+                bvh_ray_begin<NP, ST>(sh_mask, sh_big, bvh, oslot, o, d, key_mask, ray, stack, n_tests);
                 if (PL) bvh_ray_planes(n_sph, n_pl, id, o, d, ray);
                 if (ray.node != RTM_BVH_NONE_DEV) tracing = true;
                 else pending = true;   // empty hierarchy: the hit (big spheres / planes) is applied at the next entry
@@ -994,21 +1008,21 @@ __global__ void __launch_bounds__(RTM_MEGA_THREADS, RTM_BVH_MINBLOCKS) radiance_
             for (int k = 0; k < RTM_BVH_BURST; ++k) {
                 if (tracing && ray.node < 0 && held == 0) {
                     held = ray.node;
-                    ray.node = stack[--ray.sp];
+                    ray.node = stack[ST * --ray.sp];
                 }
                 if (!(tracing && bvh_is_inner(ray.node))) break;
-                bvh_inner_step(bvh, ray, stack);
+                bvh_inner_step<ST>(bvh, ray, stack);
                 ++n_nodes;
             }
             if (tracing && held != 0) bvh_leaf_test(bvh, held, id, o, d, ray, n_tests);
-            else if (tracing && ray.node < 0) bvh_leaf_step(bvh, id, o, d, ray, stack, n_tests);
+            else if (tracing && ray.node < 0) bvh_leaf_step<ST>(bvh, id, o, d, ray, stack, n_tests);
 #else
 #pragma unroll 1
             for (int k = 0; k < RTM_BVH_BURST && tracing && bvh_is_inner(ray.node); ++k) {
-                bvh_inner_step(bvh, ray, stack);
+                bvh_inner_step<ST>(bvh, ray, stack);
                 ++n_nodes;
             }
-            if (tracing && ray.node < 0) bvh_leaf_step(bvh, id, o, d, ray, stack, n_tests);
+            if (tracing && ray.node < 0) bvh_leaf_step<ST>(bvh, id, o, d, ray, stack, n_tests);
 #endif
             if (tracing && ray.node == RTM_BVH_NONE_DEV) {
                 tracing = false;
@@ -1278,13 +1292,21 @@ void rtm_launch_wf_extend(int32_t n, bool use_bvh, const RtmBvhDev& bvh, const R
 
 // Hierarchy path: the packed test covers the (padded-to-even) list of big spheres.
 namespace {
+template <int NP, bool ACNE, bool PL, bool SST>
+void launch_bvh3(const RtmBvhDev& bvh, const RtmMatDev& mat, const RtmPassParams& p, float4* records, RtmCounters* counters,
+                 int sm_count, const float* cps0, int n_sph, int n_pl, cudaStream_t st) {
+    int per_sm = 0;
+    cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, radiance_bvh_kernel<NP, ACNE, PL, SST>, RTM_MEGA_THREADS, 0);
+    if (per_sm < 1) per_sm = 1;
+    radiance_bvh_kernel<NP, ACNE, PL, SST><<<sm_count * per_sm, RTM_MEGA_THREADS, 0, st>>>(p, records, counters, bvh, mat, cps0, n_sph, n_pl);
+}
 template <int NP, bool ACNE, bool PL>
 void launch_bvh2(const RtmBvhDev& bvh, const RtmMatDev& mat, const RtmPassParams& p, float4* records, RtmCounters* counters,
                  int sm_count, const float* cps0, int n_sph, int n_pl, cudaStream_t st) {
-    int per_sm = 0;
-    cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, radiance_bvh_kernel<NP, ACNE, PL>, RTM_MEGA_THREADS, 0);
-    if (per_sm < 1) per_sm = 1;
-    radiance_bvh_kernel<NP, ACNE, PL><<<sm_count * per_sm, RTM_MEGA_THREADS, 0, st>>>(p, records, counters, bvh, mat, cps0, n_sph, n_pl);
+    // a walk holds at most depth + 2 stack entries (one per level + the sentinel)
+    static const bool want = [] { const char* e = getenv("RTM_BVH_SSTACK_OFF"); return !(e && *e == '1'); }();
+    if (want && bvh.depth + 2 <= RTM_BVH_SSTACK) launch_bvh3<NP, ACNE, PL, true>(bvh, mat, p, records, counters, sm_count, cps0, n_sph, n_pl, st);
+    else launch_bvh3<NP, ACNE, PL, false>(bvh, mat, p, records, counters, sm_count, cps0, n_sph, n_pl, st);
 }
 template <int NP>
 void launch_bvh(const RtmBvhDev& bvh, const RtmMatDev& mat, const RtmPassParams& p, float4* records, RtmCounters* counters,

@@ -683,6 +683,7 @@ int renderer_create(const rtm_scene_desc* sc, const rtm_options* opt_in, rtm_ren
                 c.bvh.root = B.root;
                 c.bvh.n_big = B.n_big;
                 for (int j = 0; j < 8; ++j) c.bvh.big_id[j] = B.big_id[j];
+                c.bvh.depth = B.depth;
                 c.s64.use_bvh = 1;
                 c.s64.bvh = c.bvh;
                 for (int k = 0; k < 3; ++k) c.s64.ref[k] = r->refd[k];

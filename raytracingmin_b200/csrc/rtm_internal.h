@@ -25,6 +25,7 @@ struct RtmBvhDev {
     int32_t root;             // child code of the root, RTM_BVH_NONE when empty
     int32_t n_big;            // spheres kept out of the hierarchy, tested for every ray
     int32_t big_id[8];        //   ascending original index
+    int32_t depth;            // levels of the tree (a walk holds at most depth + 2 stack entries)
 };
 
 // Per-sphere records of the FP32 path in GLOBAL memory (hierarchy path, any N): the
