@@ -130,8 +130,11 @@ __device__ __forceinline__ unsigned key_pack(unsigned x, unsigned mask_reg, unsi
 // up: below the FP32 error of t itself), the index in the low 3; positive floats order
 // like unsigned integers, so an unsigned min does the accept test, the tie rule and the
 // bookkeeping.  Returns the key; RTM_KEY_INF or above = miss.
-template <int NP>
+// NS = number of slots that hold (or may hold) a sphere: with NS odd the upper half of the last pair is padding, and
+// its scalar tail (sqrt, copysign, rcp, min, key) is not issued — 5 of ~280 instructions of a Cornell-box bounce.
+template <int NS>
 __device__ __forceinline__ unsigned trace_pairs_f32(const SelfMask& sm, int oid, f3 o, f3 d, unsigned key_mask) {
+    constexpr int NP = (NS + 1) / 2;
     const float noo = -dot(o, o), ndO = -dot(d, o);
     const u64 dx = pk(d.x, d.x), dy = pk(d.y, d.y), dz = pk(d.z, d.z);
     // o.(2c) is formed as (2o).c — bit-identical (power-of-two scaling) and the pair needs 4 constants, not 7
@@ -151,17 +154,22 @@ __device__ __forceinline__ unsigned trace_pairs_f32(const SelfMask& sm, int oid,
         unpk(b2, b0, b1);
         float D0, D1;
         unpk(fma2(b2, b2, ncp), D0, D1);
-        const float s0 = fast_sqrt(D0), s1 = fast_sqrt(D1);          // NaN when the ray misses the sphere
-        const u64 tq2 = add2(b2, pk(copysignf(s0, b0), copysignf(s1, b1)));
+        const bool pad = (NS & 1) && j == NP - 1;                    // compile-time: slot 2j+1 is padding
+        const float s0 = fast_sqrt(D0), s1 = pad ? 0.f : fast_sqrt(D1);   // NaN when the ray misses the sphere
+        const u64 tq2 = add2(b2, pk(copysignf(s0, b0), pad ? 0.f : copysignf(s1, b1)));
         float q0, q1;
         unpk(tq2, q0, q1);
-        const u64 rn = pk(fast_rcp(-q0), fast_rcp(-q1));
+        const u64 rn = pk(fast_rcp(-q0), pad ? 0.f : fast_rcp(-q1));
         float ta0, ta1, tb0, tb1;
         unpk(add2(tq2, neps2), ta0, ta1);                            // tq - eps
         unpk(fma2(ncp, rn, neps2), tb0, tb1);                        // c'/tq - eps
         const unsigned k0 = key_pack(min(__float_as_uint(ta0), __float_as_uint(tb0)), key_mask, 2 * j);
-        const unsigned k1 = key_pack(min(__float_as_uint(ta1), __float_as_uint(tb1)), key_mask, 2 * j + 1);
-        best = min(best, min(k0, k1));
+        if (pad) {
+            best = min(best, k0);
+        } else {
+            const unsigned k1 = key_pack(min(__float_as_uint(ta1), __float_as_uint(tb1)), key_mask, 2 * j + 1);
+            best = min(best, min(k0, k1));
+        }
     }
     return best;
 }
@@ -190,7 +198,7 @@ __device__ __forceinline__ int trace_loop_f32(int n, int oid, f3 o, f3 d, float&
 template <int N>
 __device__ __forceinline__ int trace_f32(const SelfMask& sm, int n_rt, int oid, f3 o, f3 d, float& t, unsigned key_mask) {
     if (N > 0) {
-        const unsigned key = trace_pairs_f32<(N + 1) / 2>(sm, oid, o, d, key_mask);
+        const unsigned key = trace_pairs_f32<N>(sm, oid, o, d, key_mask);
         t = __uint_as_float(key & ~7u) + RTM_T_EPS;
         return (key < RTM_KEY_INF) ? (int)(key & 7u) : -1;
     }
@@ -280,7 +288,7 @@ __device__ __forceinline__ void bvh_ray_begin(const SelfMask& sm, const SharedBi
     r.best = FLT_MAX;
     r.hit = -1;
     if (NP > 0) {
-        const unsigned key = trace_pairs_f32<NP>(sm, oslot, o, d, key_mask);
+        const unsigned key = trace_pairs_f32<2 * NP>(sm, oslot, o, d, key_mask);   // the big list is padded to even at run time
         if (key < RTM_KEY_INF) {
             r.best = __uint_as_float(key & ~7u);
             r.hit = big.id[key & 7u];

@@ -182,7 +182,7 @@ __global__ void __launch_bounds__(128) wf_shade_kernel(RtmPassParams p, float4* 
                     if (BVH) {
                         // the big-sphere list is tested here, where all lanes are active
                         if (N > 0) {
-                            const unsigned key = trace_pairs_f32<N / 2>(sh_mask, __float_as_int(al.w), o, d, p.key_mask);
+                            const unsigned key = trace_pairs_f32<N>(sh_mask, __float_as_int(al.w), o, d, p.key_mask);
                             if (key < RTM_KEY_INF) {
                                 ray_t = __uint_as_float(key & ~7u) + RTM_T_EPS;
                                 ray_hit = sh_big.id[key & 7u];
