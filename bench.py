@@ -396,7 +396,7 @@ def run_gpu_arm(args):
 def ncu_traffic_bytes(workload: str, variant: str):
     """dram__bytes_read.sum + dram__bytes_write.sum of the dominant kernel, per launch, from the committed
     `ncu --set full` capture of this very command (profiles/r01/); None when no capture exists for it."""
-    name = {("c4", "mega"): "ncu_megav5_c4_summary.txt", ("c3", "mega"): "ncu_megav5_rt_c3_summary.txt", ("c2p", "mega"): "ncu_planes_v2_c2p_summary.txt", ("c5", "mega"): "ncu_bvh_v4_c5_summary.txt"}.get((workload, variant))
+    name = {("c4", "mega"): "ncu_megav6_c4_summary.txt", ("c3", "mega"): "ncu_megav5_rt_c3_summary.txt", ("c2p", "mega"): "ncu_planes_v2_c2p_summary.txt", ("c5", "mega"): "ncu_bvh_v4_c5_summary.txt"}.get((workload, variant))
     if not name:
         return None
     unit = {"Gbyte": 1e9, "Mbyte": 1e6, "Kbyte": 1e3, "byte": 1.0}
