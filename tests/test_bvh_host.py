@@ -127,6 +127,9 @@ def _traverse(sc, b, o, d):
 
     stack, node = [NONE], b["root"]
     while node != NONE:
+        # the bound the FP32 kernel's shared-memory stack instantiation relies on (kernels_radiance.cu, SST):
+        # one entry per level of the current path + the sentinel
+        assert len(stack) <= b["depth"] + 1
         if node >= 0:
             nd = b["nodes"][node]
             c0, c1 = _children(nd)
