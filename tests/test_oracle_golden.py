@@ -127,8 +127,12 @@ needs_ref = pytest.mark.skipif(not (O.ref_available("head") and O.ref_available(
 
 @needs_ref
 @pytest.mark.parametrize("level", LEVELS)
-def test_oracle_vs_reference_objects_random_scene(level):
-    sc = rtm.random_scene(seed=11, n=9, width=40, height=24, samples=2, superSamples=3)
+@pytest.mark.parametrize("seed,n,ss,closed", [(11, 9, 3, True), (3, 1, 1, False), (29, 40, 2, True), (57, 120, 1, False),
+                                              (71, 6, 4, True)])
+def test_oracle_vs_reference_objects_random_scene(level, seed, n, ss, closed):
+    """The C restatement against the reference's own compiled objects on scenes neither was written for: hit maps,
+    ray counts and the double image bit for bit (same mt19937 stream per row)."""
+    sc = rtm.random_scene(seed=seed, n=n, width=40, height=24, samples=2, superSamples=ss, closed=closed)
     rs = O.RefScene(level, sc)
     assert np.array_equal(rs.primary_hits(0), O.oracle_primary_hits(sc))
     img_ref, rays_ref, _ = rs.render(4321)
