@@ -228,6 +228,12 @@ int rtm_debug_acne_eps(int32_t device, uint32_t n, const uint32_t* bits, float* 
 int rtm_debug_bvh(const rtm_scene_desc* scene, int32_t* info, float* nodes_out, float* leaf_geo_out,
                   int32_t* leaf_id_out);
 
+/* The 4-wide collapse of that hierarchy (experimental traversal, RTM_BVH_WIDE=1; host only).
+ * info4[3] = {wide nodes, root code, depth}.  nodes4_out float[32*nodes] or NULL: 8 float4 per node —
+ * lo.x[4] hi.x[4] lo.y[4] hi.y[4] lo.z[4] hi.z[4], child codes[4] (int bits, 0x7FFFFFFF = empty), rmin[4].
+ * Leaf codes index the leaf arrays of rtm_debug_bvh. */
+int rtm_debug_bvh4(const rtm_scene_desc* scene, int32_t* info4, float* nodes4_out);
+
 /* FP32 FMA-chain microbenchmark: measured FP32 peak of the device in TFLOP/s. */
 int rtm_debug_fp32_peak(int32_t device, double* tflops_out, double* sm_clock_mhz_out);
 

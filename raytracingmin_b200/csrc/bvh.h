@@ -40,3 +40,17 @@ struct RtmBvhHost {
 // position[n][3] / radius[n] as in rtm_scene_desc; ref = scene reference point.
 // Throws nothing; returns false when the tree would exceed RTM_BVH_STACK levels.
 bool rtm_bvh_build(int32_t n, const double* position, const float* radius, const double ref[3], RtmBvhHost& out);
+
+// ---- 4-wide form of the same tree (experimental, opt-in: RTM_BVH_WIDE=1) ----------------
+// Greedy collapse of the two-child tree: a node adopts its grandchildren (largest box first) until it holds 4
+// children.  The child boxes ARE the two-child tree's boxes, the leaves are shared (same leaf codes, same
+// leaf_geo / leaf_id), so the set of candidates a ray reaches can only shrink in visits, never change in winners.
+// Node = 8 x float4 (128 B, one cache line), children side by side:
+//   q[0] lo.x[4]  q[1] hi.x[4]  q[2] lo.y[4]  q[3] hi.y[4]  q[4] lo.z[4]  q[5] hi.z[4]
+//   q[6] child codes[4] (int bits; RTM_BVH_NONE = empty slot)   q[7] rmin[4]
+struct RtmBvh4Host {
+    std::vector<float4> nodes;       // 8 per node, breadth-first
+    int32_t root = RTM_BVH_NONE;     // child code of the root (a leaf code when the tree is a single leaf)
+    int32_t depth = 0;               // deepest leaf, root = 0: a walk holds at most 3 * depth + 1 stack entries
+};
+void rtm_bvh_collapse4(const RtmBvhHost& in, RtmBvh4Host& out);

@@ -264,3 +264,76 @@ bool rtm_bvh_build(int32_t n, const double* position, const float* radius, const
     }
     return bl.max_depth + 2 < RTM_BVH_STACK;
 }
+
+// ---- 4-wide collapse (bvh.h) -----------------------------------------------------------------------------
+namespace {
+struct Kid4 {
+    int32_t code;
+    float lo[3], hi[3], rmin;
+    double area() const {
+        const double ex = (double)hi[0] - lo[0], ey = (double)hi[1] - lo[1], ez = (double)hi[2] - lo[2];
+        return 2.0 * (ex * ey + ey * ez + ez * ex);
+    }
+};
+void kids_of(const RtmBvhHost& in, int32_t node, Kid4 out[2]) {
+    const float4 q0 = in.nodes[4 * (size_t)node], q1 = in.nodes[4 * (size_t)node + 1], q2 = in.nodes[4 * (size_t)node + 2],
+                 q3 = in.nodes[4 * (size_t)node + 3];
+    memcpy(&out[0].code, &q3.x, 4);
+    memcpy(&out[1].code, &q3.y, 4);
+    out[0].lo[0] = q0.x; out[0].hi[0] = q0.y; out[0].lo[1] = q0.z; out[0].hi[1] = q0.w; out[0].lo[2] = q2.x; out[0].hi[2] = q2.y;
+    out[1].lo[0] = q1.x; out[1].hi[0] = q1.y; out[1].lo[1] = q1.z; out[1].hi[1] = q1.w; out[1].lo[2] = q2.z; out[1].hi[2] = q2.w;
+    out[0].rmin = q3.z;
+    out[1].rmin = q3.w;
+}
+}  // namespace
+
+void rtm_bvh_collapse4(const RtmBvhHost& in, RtmBvh4Host& out) {
+    out.nodes.clear();
+    out.root = in.root;
+    out.depth = 0;
+    if (in.root < 0 || in.root == RTM_BVH_NONE) return;   // empty tree or a single leaf: nothing to widen
+    // breadth-first over the wide nodes; each queue entry is the two-child node the wide node is grown from
+    std::vector<int32_t> src{in.root}, level{0};
+    for (size_t k = 0; k < src.size(); ++k) {
+        std::vector<Kid4> kids(2);
+        kids_of(in, src[k], kids.data());
+        while (kids.size() < 4) {
+            int pick = -1;
+            double best = -1.0;
+            for (size_t i = 0; i < kids.size(); ++i)
+                if (kids[i].code >= 0 && kids[i].area() > best) {
+                    best = kids[i].area();
+                    pick = (int)i;
+                }
+            if (pick < 0) break;
+            Kid4 two[2];
+            kids_of(in, kids[pick].code, two);
+            kids[pick] = two[0];
+            kids.push_back(two[1]);
+        }
+        float v[8][4];
+        int32_t code[4];
+        for (int j = 0; j < 4; ++j) {
+            const bool real = j < (int)kids.size();
+            for (int a = 0; a < 3; ++a) {
+                v[2 * a][j] = real ? kids[j].lo[a] : 1e30f;       // an empty slot: a far, empty box and the NONE code
+                v[2 * a + 1][j] = real ? kids[j].hi[a] : 1e30f;
+            }
+            v[7][j] = real ? kids[j].rmin : 1.f;
+            code[j] = RTM_BVH_NONE;
+            if (real) {
+                if (kids[j].code >= 0) {
+                    code[j] = (int32_t)src.size();                 // index the child will get
+                    src.push_back(kids[j].code);
+                    level.push_back(level[k] + 1);
+                } else {
+                    code[j] = kids[j].code;                        // leaf: the two-child tree's leaf code
+                    out.depth = std::max(out.depth, level[k] + 1);
+                }
+            }
+        }
+        memcpy(v[6], code, 16);
+        for (int j = 0; j < 8; ++j) out.nodes.push_back(make_float4(v[j][0], v[j][1], v[j][2], v[j][3]));
+    }
+    out.root = 0;
+}

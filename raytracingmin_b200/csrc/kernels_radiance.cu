@@ -323,6 +323,41 @@ __device__ __forceinline__ void bvh_inner_step(const RtmBvhDev& bvh, BvhRay& r, 
     }
 }
 
+// one inner node of the 4-wide tree (bvh.h: RtmBvh4Host; experimental, RTM_BVH_WIDE=1): one 128-byte fetch, four
+// slab tests, the hit children ordered near to far.  The entry distance (>= 0, so its bits order like an unsigned
+// integer) and the child's slot share one key — two low mantissa bits are given up to the slot — and a 5-exchange
+// min/max network sorts the four keys; a missed or empty child has the all-ones key.
+template <int ST = 1>
+__device__ __forceinline__ void bvh4_inner_step(const RtmBvhDev& bvh, BvhRay& r, int* stack) {
+    const float4* q = bvh.nodes4 + 8 * r.node;
+    const float4 lx = __ldg(q), hx = __ldg(q + 1), ly = __ldg(q + 2), hy = __ldg(q + 3), lz = __ldg(q + 4), hz = __ldg(q + 5);
+    const float4 cf = __ldg(q + 6);
+    const int c0 = __float_as_int(cf.x), c1 = __float_as_int(cf.y), c2 = __float_as_int(cf.z), c3 = __float_as_int(cf.w);
+    const float tm = r.best + 2.f * RTM_T_EPS;
+    float n0, n1, n2, n3;
+    const bool h0 = box_test_f32(lx.x, hx.x, ly.x, hy.x, lz.x, hz.x, r.oi, r.inv, tm, n0) && c0 != RTM_BVH_NONE_DEV;
+    const bool h1 = box_test_f32(lx.y, hx.y, ly.y, hy.y, lz.y, hz.y, r.oi, r.inv, tm, n1) && c1 != RTM_BVH_NONE_DEV;
+    const bool h2 = box_test_f32(lx.z, hx.z, ly.z, hy.z, lz.z, hz.z, r.oi, r.inv, tm, n2) && c2 != RTM_BVH_NONE_DEV;
+    const bool h3 = box_test_f32(lx.w, hx.w, ly.w, hy.w, lz.w, hz.w, r.oi, r.inv, tm, n3) && c3 != RTM_BVH_NONE_DEV;
+    unsigned k0 = h0 ? ((__float_as_uint(n0) & ~3u) | 0u) : 0xFFFFFFFFu;
+    unsigned k1 = h1 ? ((__float_as_uint(n1) & ~3u) | 1u) : 0xFFFFFFFFu;
+    unsigned k2 = h2 ? ((__float_as_uint(n2) & ~3u) | 2u) : 0xFFFFFFFFu;
+    unsigned k3 = h3 ? ((__float_as_uint(n3) & ~3u) | 3u) : 0xFFFFFFFFu;
+    unsigned a, b;
+    a = min(k0, k1); b = max(k0, k1); k0 = a; k1 = b;
+    a = min(k2, k3); b = max(k2, k3); k2 = a; k3 = b;
+    a = min(k0, k2); b = max(k0, k2); k0 = a; k2 = b;
+    a = min(k1, k3); b = max(k1, k3); k1 = a; k3 = b;
+    a = min(k1, k2); b = max(k1, k2); k1 = a; k2 = b;
+    auto child = [&](unsigned k) { const unsigned i = k & 3u; return (i == 0u) ? c0 : (i == 1u) ? c1 : (i == 2u) ? c2 : c3; };
+    // far to near onto the stack, the nearest is walked next
+    if (k3 != 0xFFFFFFFFu) stack[ST * r.sp++] = child(k3);
+    if (k2 != 0xFFFFFFFFu) stack[ST * r.sp++] = child(k2);
+    if (k1 != 0xFFFFFFFFu) stack[ST * r.sp++] = child(k1);
+    if (k0 != 0xFFFFFFFFu) r.node = child(k0);
+    else r.node = stack[ST * --r.sp];
+}
+
 // one leaf: 1..4 spheres in the direct form
 __device__ __forceinline__ void bvh_leaf_test(const RtmBvhDev& bvh, int leaf, int oid, f3 o, f3 d, BvhRay& r, unsigned& n_tests) {
     const unsigned code = ~(unsigned)leaf;
@@ -797,8 +832,9 @@ __global__ void __launch_bounds__(RTM_MEGA_THREADS, BVH ? 4 : 5) radiance_mega_k
 #ifndef RTM_BVH_SSTACK
 #define RTM_BVH_SSTACK 24
 #endif
-template <int NP, bool ACNE, bool PL, bool SST>
-__global__ void __launch_bounds__(RTM_MEGA_THREADS, RTM_BVH_MINBLOCKS) radiance_bvh_kernel(RtmPassParams p, float4* __restrict__ records,
+// W4: walk the 4-wide form of the tree (bvh4_inner_step) — experimental, opt-in, same leaves and same candidates.
+template <int NP, bool ACNE, bool PL, bool SST, bool W4 = false>
+__global__ void __launch_bounds__(RTM_MEGA_THREADS, W4 ? 6 : RTM_BVH_MINBLOCKS) radiance_bvh_kernel(RtmPassParams p, float4* __restrict__ records,
                                                                            RtmCounters* __restrict__ counters, RtmBvhDev bvh,
                                                                            RtmMatDev mat, const float* __restrict__ cps0, int n_sph,
                                                                            int n_pl) {
@@ -996,6 +1032,7 @@ __global__ void __launch_bounds__(RTM_MEGA_THREADS, RTM_BVH_MINBLOCKS) radiance_
             if (start) {
                 // the packed big-sphere test (~140 instructions) and the planes: once, for all lanes that start a ray
                 bvh_ray_begin<NP, ST>(sh_mask, sh_big, bvh, oslot, o, d, key_mask, ray, stack, n_tests);
+                if (W4) ray.node = bvh.root4;
                 if (PL) bvh_ray_planes(n_sph, n_pl, id, o, d, ray);
                 if (ray.node != RTM_BVH_NONE_DEV) tracing = true;
                 else pending = true;   // empty hierarchy: the hit (big spheres / planes) is applied at the next entry
@@ -1026,8 +1063,9 @@ __global__ void __launch_bounds__(RTM_MEGA_THREADS, RTM_BVH_MINBLOCKS) radiance_
             else if (tracing && ray.node < 0) bvh_leaf_step<ST>(bvh, id, o, d, ray, stack, n_tests);
 #else
 #pragma unroll 1
-            for (int k = 0; k < RTM_BVH_BURST && tracing && bvh_is_inner(ray.node); ++k) {
-                bvh_inner_step<ST>(bvh, ray, stack);
+            for (int k = 0; k < (W4 ? (RTM_BVH_BURST + 1) / 2 : RTM_BVH_BURST) && tracing && bvh_is_inner(ray.node); ++k) {
+                if (W4) bvh4_inner_step<ST>(bvh, ray, stack);
+                else bvh_inner_step<ST>(bvh, ray, stack);
                 ++n_nodes;
             }
             if (tracing && ray.node < 0) bvh_leaf_step<ST>(bvh, id, o, d, ray, stack, n_tests);
@@ -1313,6 +1351,14 @@ void launch_bvh2(const RtmBvhDev& bvh, const RtmMatDev& mat, const RtmPassParams
                  int sm_count, const float* cps0, int n_sph, int n_pl, cudaStream_t st) {
     // a walk holds at most depth + 2 stack entries (one per level + the sentinel)
     static const bool want = [] { const char* e = getenv("RTM_BVH_SSTACK_OFF"); return !(e && *e == '1'); }();
+    if (!PL && bvh.nodes4 && bvh.root4 >= 0 && 3 * bvh.depth4 + 1 <= RTM_BVH_STACK_DEV) {
+        // experimental wide walk (RTM_BVH_WIDE=1 at renderer_create): local-memory stack, spheres only
+        int per_sm = 0;
+        cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, radiance_bvh_kernel<NP, ACNE, false, false, true>, RTM_MEGA_THREADS, 0);
+        if (per_sm < 1) per_sm = 1;
+        radiance_bvh_kernel<NP, ACNE, false, false, true><<<sm_count * per_sm, RTM_MEGA_THREADS, 0, st>>>(p, records, counters, bvh, mat, cps0, n_sph, n_pl);
+        return;
+    }
     if (want && bvh.depth + 2 <= RTM_BVH_SSTACK) launch_bvh3<NP, ACNE, PL, true>(bvh, mat, p, records, counters, sm_count, cps0, n_sph, n_pl, st);
     else launch_bvh3<NP, ACNE, PL, false>(bvh, mat, p, records, counters, sm_count, cps0, n_sph, n_pl, st);
 }

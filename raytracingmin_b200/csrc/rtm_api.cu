@@ -664,7 +664,12 @@ int renderer_create(const rtm_scene_desc* sc, const rtm_options* opt_in, rtm_ren
                 // one allocation, float4 units: nodes | leaf_geo | geo | emi | alb | leaf_id (int32, padded)
                 const RtmBvhHost& B = r->bvh_host;
                 const size_t n_nodes4 = B.nodes.size(), n_slots = B.leaf_geo.size(), n_mat = r->mat_geo.size();
-                const size_t total4 = n_nodes4 + n_slots + 3 * n_mat + (n_slots + 3) / 4 + 1;
+                // experimental 4-wide walk of the FP32 hierarchy kernel: opt-in, spheres only
+                RtmBvh4Host W4;
+                const char* wide_env = getenv("RTM_BVH_WIDE");
+                if (wide_env && wide_env[0] == '1' && f32_path && m == 0) rtm_bvh_collapse4(B, W4);
+                const size_t n_wide4 = (W4.root >= 0 && W4.root != RTM_BVH_NONE) ? W4.nodes.size() : 0;
+                const size_t total4 = n_nodes4 + n_slots + 3 * n_mat + (n_slots + 3) / 4 + 1 + n_wide4;
                 CU(cudaMalloc(&c.d_bvh, total4 * sizeof(float4)));
                 float4* d = c.d_bvh;
                 auto put = [&](const void* src, size_t count4, size_t bytes) -> float4* {
@@ -684,6 +689,9 @@ int renderer_create(const rtm_scene_desc* sc, const rtm_options* opt_in, rtm_ren
                 c.bvh.n_big = B.n_big;
                 for (int j = 0; j < 8; ++j) c.bvh.big_id[j] = B.big_id[j];
                 c.bvh.depth = B.depth;
+                c.bvh.nodes4 = n_wide4 ? put(W4.nodes.data(), n_wide4, n_wide4 * sizeof(float4)) : nullptr;
+                c.bvh.root4 = W4.root;
+                c.bvh.depth4 = W4.depth;
                 c.s64.use_bvh = 1;
                 c.s64.bvh = c.bvh;
                 for (int k = 0; k < 3; ++k) c.s64.ref[k] = r->refd[k];
@@ -984,6 +992,20 @@ int rtm_debug_bvh(const rtm_scene_desc* sc, int32_t* info, float* nodes_out, flo
     if (leaf_geo_out) memcpy(leaf_geo_out, B.leaf_geo.data(), B.leaf_geo.size() * sizeof(float4));
     if (leaf_id_out) memcpy(leaf_id_out, B.leaf_id.data(), B.leaf_id.size() * sizeof(int32_t));
     return ok ? RTM_OK : fail(RTM_E_UNSUPPORTED, "sphere hierarchy too deep (%d levels)", B.depth);
+}
+
+int rtm_debug_bvh4(const rtm_scene_desc* sc, int32_t* info4, float* nodes4_out) {
+    if (!sc || !info4) return fail(RTM_E_INVALID, "null argument");
+    RtmBvhHost B;
+    if (!rtm_bvh_build(sc->n_spheres, sc->position, sc->radius, sc->cam_origin, B))
+        return fail(RTM_E_UNSUPPORTED, "sphere hierarchy too deep (%d levels)", B.depth);
+    RtmBvh4Host W;
+    rtm_bvh_collapse4(B, W);
+    info4[0] = (int32_t)(W.nodes.size() / 8);
+    info4[1] = W.root;
+    info4[2] = W.depth;
+    if (nodes4_out) memcpy(nodes4_out, W.nodes.data(), W.nodes.size() * sizeof(float4));
+    return RTM_OK;
 }
 
 int rtm_debug_fp32_peak(int32_t device, double* tflops_out, double* mhz_out) {

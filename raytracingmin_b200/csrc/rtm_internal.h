@@ -26,6 +26,10 @@ struct RtmBvhDev {
     int32_t n_big;            // spheres kept out of the hierarchy, tested for every ray
     int32_t big_id[8];        //   ascending original index
     int32_t depth;            // levels of the tree (a walk holds at most depth + 2 stack entries)
+    // 4-wide form of the same tree (bvh.h: RtmBvh4Host), uploaded only when RTM_BVH_WIDE=1 (experimental)
+    const float4* nodes4;     // 8 float4 per wide node, NULL = not built
+    int32_t root4;
+    int32_t depth4;           // a walk of the wide tree holds at most 3 * depth4 + 1 stack entries
 };
 
 // Per-sphere records of the FP32 path in GLOBAL memory (hierarchy path, any N): the
