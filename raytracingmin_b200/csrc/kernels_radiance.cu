@@ -832,6 +832,9 @@ __global__ void __launch_bounds__(RTM_MEGA_THREADS, BVH ? 4 : 5) radiance_mega_k
 #ifndef RTM_BVH_SSTACK
 #define RTM_BVH_SSTACK 24
 #endif
+#ifndef RTM_BVH_SSTACK_W4
+#define RTM_BVH_SSTACK_W4 28   // the wide walk pushes up to 3 entries a level: 3 * depth4 + 1 (synth10k: 25)
+#endif
 // W4: walk the 4-wide form of the tree (bvh4_inner_step) — experimental, opt-in, same leaves and same candidates.
 template <int NP, bool ACNE, bool PL, bool SST, bool W4 = false>
 __global__ void __launch_bounds__(RTM_MEGA_THREADS, W4 ? 6 : RTM_BVH_MINBLOCKS) radiance_bvh_kernel(RtmPassParams p, float4* __restrict__ records,
@@ -880,7 +883,7 @@ __global__ void __launch_bounds__(RTM_MEGA_THREADS, W4 ? 6 : RTM_BVH_MINBLOCKS) 
     BvhRay ray;
     ray.node = RTM_BVH_NONE_DEV;
     constexpr int ST = SST ? RTM_MEGA_THREADS : 1;
-    __shared__ int sh_stack[SST ? RTM_BVH_SSTACK * RTM_MEGA_THREADS : 1];
+    __shared__ int sh_stack[SST ? (W4 ? RTM_BVH_SSTACK_W4 : RTM_BVH_SSTACK) * RTM_MEGA_THREADS : 1];
     int lstack[SST ? 1 : RTM_BVH_STACK_DEV];
     int* const stack = SST ? (sh_stack + threadIdx.x) : lstack;
     unsigned long long rays_ref = 0, traced = 0;
@@ -1352,8 +1355,14 @@ void launch_bvh2(const RtmBvhDev& bvh, const RtmMatDev& mat, const RtmPassParams
     // a walk holds at most depth + 2 stack entries (one per level + the sentinel)
     static const bool want = [] { const char* e = getenv("RTM_BVH_SSTACK_OFF"); return !(e && *e == '1'); }();
     if (!PL && bvh.nodes4 && bvh.root4 >= 0 && 3 * bvh.depth4 + 1 <= RTM_BVH_STACK_DEV) {
-        // experimental wide walk (RTM_BVH_WIDE=1 at renderer_create): local-memory stack, spheres only
+        // experimental wide walk (RTM_BVH_WIDE=1 at renderer_create: local-memory stack; =2: shared-memory stack), spheres only
         int per_sm = 0;
+        if (bvh.wide_mode == 2 && 3 * bvh.depth4 + 1 <= RTM_BVH_SSTACK_W4) {
+            cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, radiance_bvh_kernel<NP, ACNE, false, true, true>, RTM_MEGA_THREADS, 0);
+            if (per_sm < 1) per_sm = 1;
+            radiance_bvh_kernel<NP, ACNE, false, true, true><<<sm_count * per_sm, RTM_MEGA_THREADS, 0, st>>>(p, records, counters, bvh, mat, cps0, n_sph, n_pl);
+            return;
+        }
         cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, radiance_bvh_kernel<NP, ACNE, false, false, true>, RTM_MEGA_THREADS, 0);
         if (per_sm < 1) per_sm = 1;
         radiance_bvh_kernel<NP, ACNE, false, false, true><<<sm_count * per_sm, RTM_MEGA_THREADS, 0, st>>>(p, records, counters, bvh, mat, cps0, n_sph, n_pl);

@@ -667,7 +667,8 @@ int renderer_create(const rtm_scene_desc* sc, const rtm_options* opt_in, rtm_ren
                 // experimental 4-wide walk of the FP32 hierarchy kernel: opt-in, spheres only
                 RtmBvh4Host W4;
                 const char* wide_env = getenv("RTM_BVH_WIDE");
-                if (wide_env && wide_env[0] == '1' && f32_path && m == 0) rtm_bvh_collapse4(B, W4);
+                const int wide_mode = (wide_env && (wide_env[0] == '1' || wide_env[0] == '2')) ? wide_env[0] - '0' : 0;
+                if (wide_mode && f32_path && m == 0) rtm_bvh_collapse4(B, W4);
                 const size_t n_wide4 = (W4.root >= 0 && W4.root != RTM_BVH_NONE) ? W4.nodes.size() : 0;
                 const size_t total4 = n_nodes4 + n_slots + 3 * n_mat + (n_slots + 3) / 4 + 1 + n_wide4;
                 CU(cudaMalloc(&c.d_bvh, total4 * sizeof(float4)));
@@ -692,6 +693,7 @@ int renderer_create(const rtm_scene_desc* sc, const rtm_options* opt_in, rtm_ren
                 c.bvh.nodes4 = n_wide4 ? put(W4.nodes.data(), n_wide4, n_wide4 * sizeof(float4)) : nullptr;
                 c.bvh.root4 = W4.root;
                 c.bvh.depth4 = W4.depth;
+                c.bvh.wide_mode = wide_mode;
                 c.s64.use_bvh = 1;
                 c.s64.bvh = c.bvh;
                 for (int k = 0; k < 3; ++k) c.s64.ref[k] = r->refd[k];

@@ -30,6 +30,7 @@ struct RtmBvhDev {
     const float4* nodes4;     // 8 float4 per wide node, NULL = not built
     int32_t root4;
     int32_t depth4;           // a walk of the wide tree holds at most 3 * depth4 + 1 stack entries
+    int32_t wide_mode;        // RTM_BVH_WIDE: 1 = local-memory stack, 2 = shared-memory stack
 };
 
 // Per-sphere records of the FP32 path in GLOBAL memory (hierarchy path, any N): the
