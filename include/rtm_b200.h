@@ -30,7 +30,7 @@
 extern "C" {
 #endif
 
-#define RTM_ABI_VERSION 3
+#define RTM_ABI_VERSION 4
 
 enum {
     RTM_OK = 0,
@@ -114,7 +114,9 @@ typedef struct rtm_options {
     int32_t device;        /* CUDA ordinal of the (first) GPU */
     int32_t n_gpus;        /* 1: this device only.  >1: devices device..device+n_gpus-1 driven by
                               this process, sample budget sliced across them, partial buffers
-                              summed with one ncclReduce to `device` */
+                              summed with one ncclReduce to `device`.  COMPAT_HEAD is deterministic and
+                              one cheap kernel: it always runs on `device` alone (rtm_stats.n_gpus = 1), so
+                              its double image stays bit-exact */
     int32_t compat;        /* RTM_COMPAT_* */
     int32_t precision;     /* RTM_PRECISION_* */
     int32_t variant;       /* RTM_VARIANT_* */
@@ -131,6 +133,16 @@ typedef struct rtm_options {
                               count: every rank keeps full-length sample loops and a 1/G primary pass.
                               The primary-hit map needs the full grid. */
     int32_t estimator;     /* RTM_ESTIMATOR_* (ABI 3) */
+    /* ABI 4: test / A-B knobs.  They replace the environment variables round 1's library read (a product .so takes
+     * its switches through its interface, not through getenv); 0 everywhere = the product defaults. */
+    int32_t debug_retry;        /* roulette-rounds megakernel: 0 = chosen from the scene, 1 = forced off, 2 = forced on
+                                   (both render the same image bit for bit) */
+    int32_t debug_bvh_walk;     /* hierarchy kernel: 0 = default (traversal stack in shared memory when the tree is
+                                   shallow enough), 1 = stack in local memory */
+    int32_t debug_bvh_leaf_max; /* SAH build: largest leaf, 1..8; 0 = default (4) */
+    float   debug_bvh_ctrav;    /* SAH build: cost of an inner-node visit in sphere tests; 0 = default (1.0) */
+    int32_t debug_clamp;        /* 0 = the per-sample clamp (src/Renderer.cpp:240-241) is compiled out when the host can
+                                   prove it never engages, 1 = always evaluated */
 } rtm_options;
 
 typedef struct rtm_stats {
@@ -197,7 +209,8 @@ int renderer_sum_partials(rtm_renderer* r, const void* partials, int32_t n_slots
 /* COMPAT_HEAD only: the double image double[H][W][3], bit-exact against the reference. */
 int renderer_read_image_f64(rtm_renderer* r, double* image_out);
 
-/* src/Renderer.cpp:251-254 on the device: u8[H][W][3] = (unsigned char)(255*min(v,1)). */
+/* src/Renderer.cpp:251-254 on the device: u8[H][W][3] = (unsigned char)(255*min(v,1)).  COMPAT_HEAD converts the
+ * DOUBLE image (bytes identical to the reference's); COMPAT_ABC converts the float accumulation buffer. */
 int renderer_read_u8(rtm_renderer* r, unsigned char* rgb8_out);
 
 void renderer_destroy(rtm_renderer* r);
@@ -221,14 +234,14 @@ int rtm_debug_closest_hit(rtm_renderer* r, int32_t mode, uint32_t n, const doubl
  * from the 32 random bits bits[i]. */
 int rtm_debug_acne_eps(int32_t device, uint32_t n, const uint32_t* bits, float* eps_out);
 
-/* The sphere hierarchy renderer_create would build for `scene` (host only, no GPU needed).
+/* The sphere hierarchy renderer_create would build for `scene` with default options (host only, no GPU needed).
  * info[13] = {inner nodes, leaf slots, root code, depth, n_big, big_id[8]}.  Call once with the
  * three arrays NULL to size them: nodes_out float[16*nodes] (4 float4 per node: child boxes,
  * child codes, rmin), leaf_geo_out float[4*slots], leaf_id_out int32[slots]. */
 int rtm_debug_bvh(const rtm_scene_desc* scene, int32_t* info, float* nodes_out, float* leaf_geo_out,
                   int32_t* leaf_id_out);
 
-/* The 4-wide collapse of that hierarchy (experimental traversal, RTM_BVH_WIDE=1; host only).
+/* The 4-wide collapse of that hierarchy (design study; host only).
  * info4[3] = {wide nodes, root code, depth}.  nodes4_out float[32*nodes] or NULL: 8 float4 per node —
  * lo.x[4] hi.x[4] lo.y[4] hi.y[4] lo.z[4] hi.z[4], child codes[4] (int bits, 0x7FFFFFFF = empty), rmin[4].
  * Leaf codes index the leaf arrays of rtm_debug_bvh. */

@@ -237,10 +237,23 @@ int refh_primary_hits(void* h, int32_t* out, int mode) {
 // Linear double image [H][W][3] exactly as src/Renderer.cpp:223-248 accumulates
 // it, with rnd = std::mt19937(seed + y) private to row y.  rays = number of
 // PathTracing invocations, samples = innermost-loop iterations.
+// Window variant: only the pixels [x0,x0+w) x [y0,y0+h) of the full width x height frame are evaluated
+// (same camera rays as the full frame, row generator still mt19937(seed + y) with y the FULL-frame row);
+// image is double[h][w][3].  refh_render = the window that covers the frame.
+int refh_render_window(void* h, uint32_t seed, int x0, int y0, int w, int hgt, double* image, uint64_t* rays_out,
+                       uint64_t* samples_out, int nthreads);
+
 int refh_render(void* h, uint32_t seed, double* image, uint64_t* rays_out, uint64_t* samples_out, int nthreads) {
+    Scene* s = (Scene*)h;
+    return refh_render_window(h, seed, 0, 0, s->data.width, s->data.height, image, rays_out, samples_out, nthreads);
+}
+
+int refh_render_window(void* h, uint32_t seed, int x0, int y0, int w, int hgt, double* image, uint64_t* rays_out,
+                       uint64_t* samples_out, int nthreads) {
     Scene* s = (Scene*)h;
     png::SettingData& data = s->data;
     if (data.object.empty()) return -1;
+    if (x0 < 0 || y0 < 0 || w <= 0 || hgt <= 0 || x0 + w > data.width || y0 + hgt > data.height) return -2;
     const CameraFrame f = make_frame(data);
     png::Object* real0 = data.object[0];
     CountingProxy proxy(real0);
@@ -248,12 +261,12 @@ int refh_render(void* h, uint32_t seed, double* image, uint64_t* rays_out, uint6
     uint64_t rays = 0, samples = 0;
     if (nthreads <= 0) nthreads = omp_get_max_threads();
 #pragma omp parallel for schedule(dynamic) num_threads(nthreads) reduction(+ : rays, samples)
-    for (int y = 0; y < data.height; ++y) {
+    for (int y = y0; y < y0 + hgt; ++y) {
         std::mt19937 rnd(seed + (uint32_t)y);
         std::uniform_real_distribution<double> dist(0.0, 1.0);
         const std::function<double()> randomGene = [&rnd, &dist]() { return dist(rnd); };
         const uint64_t before = t_intersect_calls;
-        for (int x = 0; x < data.width; ++x) {
+        for (int x = x0; x < x0 + w; ++x) {
             png::vec3 accumulatedColor(0, 0, 0);
             for (int sx = 1; sx <= data.superSamples; ++sx)
                 for (int sy = 1; sy <= data.superSamples; ++sy)
@@ -270,7 +283,7 @@ int refh_render(void* h, uint32_t seed, double* image, uint64_t* rays_out, uint6
                         accumulatedColor += cal;
                         ++samples;
                     }
-            double* px = image + ((size_t)y * data.width + x) * 3;
+            double* px = image + ((size_t)(y - y0) * w + (x - x0)) * 3;
             px[0] = accumulatedColor.x; px[1] = accumulatedColor.y; px[2] = accumulatedColor.z;
         }
         rays += t_intersect_calls - before;

@@ -54,6 +54,9 @@ class _Options(C.Structure):
         ("variant", C.c_int32), ("accel", C.c_int32), ("max_depth", C.c_int32),
         ("sample_begin", C.c_int32), ("sample_end", C.c_int32), ("seed", C.c_uint64),
         ("sub_begin", C.c_int32), ("sub_end", C.c_int32), ("estimator", C.c_int32),
+        # ABI 4: test / A-B knobs (0 = product defaults); they replace round 1's environment variables
+        ("debug_retry", C.c_int32), ("debug_bvh_walk", C.c_int32), ("debug_bvh_leaf_max", C.c_int32),
+        ("debug_bvh_ctrav", C.c_float), ("debug_clamp", C.c_int32),
     ]
 
 
@@ -157,7 +160,8 @@ class Renderer:
     def __init__(self, scene: Scene, *, device: int = 0, n_gpus: int = 1, compat: str = "abc", precision: str = "f32",
                  variant: str = "mega", accel: str = "auto", max_depth: int = 0, seed: int = 0x5EED,
                  sample_begin: int = 0, sample_end: int = 0, sub_begin: int = 0, sub_end: int = 0,
-                 estimator: str = "reference"):
+                 estimator: str = "reference", debug_retry: int = 0, debug_bvh_walk: int = 0, debug_bvh_leaf_max: int = 0,
+                 debug_bvh_ctrav: float = 0.0, debug_clamp: int = 0):
         self._lib = load_library()
         self._h = C.c_void_p()
         sc = scene.normalized()
@@ -172,6 +176,8 @@ class Renderer:
         o.sample_begin, o.sample_end = sample_begin, sample_end
         o.sub_begin, o.sub_end = sub_begin, sub_end
         o.estimator = _ESTIMATOR[estimator]
+        o.debug_retry, o.debug_bvh_walk, o.debug_bvh_leaf_max = debug_retry, debug_bvh_walk, debug_bvh_leaf_max
+        o.debug_bvh_ctrav, o.debug_clamp = debug_bvh_ctrav, debug_clamp
         self.compat = compat
         _check(self._lib, self._lib.renderer_create(C.byref(d), C.byref(o), C.byref(self._h)))
 

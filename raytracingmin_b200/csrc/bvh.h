@@ -16,6 +16,7 @@
 #define RTM_BVH_LEAF_MAX 4
 #define RTM_BVH_CTRAV 1.0         // SAH: cost of an inner-node visit in sphere tests
 #define RTM_BVH_STACK 64
+#define RTM_BVH_BIG_RADIUS 256.0  // absolute "too large for the FP32 leaf test" radius
 
 // child code: >= 0  inner node index
 //             <  0  leaf: ~code = (first_slot << 3) | (count - 1)
@@ -35,13 +36,19 @@ struct RtmBvhHost {
     int32_t n_big = 0;
     int32_t big_id[RTM_BVH_MAX_BIG] = {0};
     int32_t depth = 0;
+    int32_t n_big_overflow = 0;      // spheres that qualify as big but did not fit the big list
 };
 
 // position[n][3] / radius[n] as in rtm_scene_desc; ref = scene reference point.
 // Throws nothing; returns false when the tree would exceed RTM_BVH_STACK levels.
-bool rtm_bvh_build(int32_t n, const double* position, const float* radius, const double ref[3], RtmBvhHost& out);
+// c_trav / leaf_max: SAH constants (0 = the defaults above).  A sphere is kept out of the tree ("big") when its radius
+// exceeds 8 x the median radius or RTM_BVH_BIG_RADIUS: the FP32 leaf test evaluates |c - o|^2 - r^2 directly, which is
+// only accurate for small r; out.n_big_overflow counts the big spheres beyond RTM_BVH_MAX_BIG that had to stay in leaves
+// (fine for the exact FP64 walk; the FP32 path refuses such a scene).
+bool rtm_bvh_build(int32_t n, const double* position, const float* radius, const double ref[3], RtmBvhHost& out,
+                   double c_trav = 0.0, int leaf_max = 0);
 
-// ---- 4-wide form of the same tree (experimental, opt-in: RTM_BVH_WIDE=1) ----------------
+// ---- 4-wide form of the same tree (host-side design study) ----------------
 // Greedy collapse of the two-child tree: a node adopts its grandchildren (largest box first) until it holds 4
 // children.  The child boxes ARE the two-child tree's boxes, the leaves are shared (same leaf codes, same
 // leaf_geo / leaf_id), so the set of candidates a ray reaches can only shrink in visits, never change in winners.

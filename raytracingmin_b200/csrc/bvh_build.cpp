@@ -2,8 +2,6 @@
 // Runs once per renderer_create; 10 000 spheres take a few milliseconds.
 #include "bvh.h"
 
-#include <cstdlib>
-
 #include <algorithm>
 #include <cfloat>
 #include <cmath>
@@ -186,7 +184,8 @@ struct Builder {
 
 }  // namespace
 
-bool rtm_bvh_build(int32_t n, const double* position, const float* radius, const double ref[3], RtmBvhHost& out) {
+bool rtm_bvh_build(int32_t n, const double* position, const float* radius, const double ref[3], RtmBvhHost& out, double c_trav,
+                   int leaf_max) {
     out = RtmBvhHost();
     if (n <= 0) return true;
     // Spheres far larger than the typical one (the r = 1e4 "walls" of the Cornell scenes) would
@@ -196,9 +195,13 @@ bool rtm_bvh_build(int32_t n, const double* position, const float* radius, const
     const double median = rs[n / 2];
     std::vector<int32_t> cand;
     for (int i = 0; i < n; ++i)
-        if ((double)radius[i] > 8.0 * median) cand.push_back(i);
+        if ((double)radius[i] > 8.0 * median || (double)radius[i] >= RTM_BVH_BIG_RADIUS) cand.push_back(i);
     std::sort(cand.begin(), cand.end(), [&](int a, int b) { return radius[a] > radius[b] || (radius[a] == radius[b] && a < b); });
-    if ((int)cand.size() > RTM_BVH_MAX_BIG) cand.resize(RTM_BVH_MAX_BIG);
+    if ((int)cand.size() > RTM_BVH_MAX_BIG) {
+        for (size_t k = RTM_BVH_MAX_BIG; k < cand.size(); ++k)
+            if ((double)radius[cand[k]] >= RTM_BVH_BIG_RADIUS) ++out.n_big_overflow;
+        cand.resize(RTM_BVH_MAX_BIG);
+    }
     std::sort(cand.begin(), cand.end());  // ascending original index: the tie rule of Renderer.cpp:67
     std::vector<char> is_big(n, 0);
     for (int32_t i : cand) {
@@ -207,9 +210,8 @@ bool rtm_bvh_build(int32_t n, const double* position, const float* radius, const
     }
     Builder bl;
     bl.out = &out;
-    // tuning hook for scripts/gpu_sweep_bvh.sh (not part of the interface)
-    if (const char* e = getenv("RTM_BVH_CTRAV_ENV")) bl.c_trav = atof(e);
-    if (const char* e = getenv("RTM_BVH_LEAFMAX_ENV")) bl.leaf_max = std::min(8, std::max(1, atoi(e)));
+    if (c_trav > 0.0) bl.c_trav = c_trav;                                   // rtm_options.debug_bvh_ctrav / _leaf_max
+    if (leaf_max > 0) bl.leaf_max = std::min(8, std::max(1, leaf_max));
     bl.prims.reserve(n - out.n_big);
     for (int i = 0; i < n; ++i) {
         if (is_big[i]) continue;

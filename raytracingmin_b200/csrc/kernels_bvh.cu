@@ -1,0 +1,382 @@
+// kernels_bvh.cu — the FP32 bounce loop of the hierarchy path (scenes of more than 64 spheres, config C5).
+#include "kernels_common.cuh"
+
+namespace {
+
+// ---- the radiance kernel of the hierarchy path -------------------------------------------
+// Same estimator, same lane-owns-a-sub-pixel work distribution as radiance_mega_kernel, but a
+// closest-hit query now costs ~25 node visits + ~11 sphere tests with a large spread, so "one
+// loop iteration = one bounce" would leave a warp waiting for its longest traversal with the
+// shading code interleaved at 1/32 occupancy (measured: 6.3 of 32 lanes active on average).
+// Here a lane is in one of two phases and the warp runs them as separate, coherent blocks:
+//   S (shade)  standing on a hit: apply a finished ray, roulette, sample the bounce, start the
+//              next ray (or close the sample / the sub-pixel);
+//   T (trace)  walk the hierarchy, while-while: all lanes step through inner nodes until each
+//              holds a leaf, then all test their leaf's spheres.
+// The T block keeps stepping until at least RTM_BVH_S_THRESH lanes have finished their rays;
+// only then is the S block run (for those lanes together), so S code runs at >= 25 % and T code
+// at >= 75 % lane occupancy (Aila & Laine's persistent threads with a refill threshold).
+#ifndef RTM_BVH_S_THRESH
+#define RTM_BVH_S_THRESH 16
+#endif
+#ifndef RTM_BVH_BURST
+#define RTM_BVH_BURST 8
+#endif
+#ifndef RTM_BVH_MINBLOCKS
+#define RTM_BVH_MINBLOCKS 7
+#endif
+#ifndef RTM_BVH_HOLD
+#define RTM_BVH_HOLD 0
+#endif
+#ifndef RTM_BVH_S_ROUND
+#define RTM_BVH_S_ROUND 1   // lanes that must need another roulette decision for the S block to run another round (swept: 1 4.50, 2 4.46, 4 4.45, 8 4.34 Grays/s on C5)
+#endif
+
+// PL: n_pl planes (extension) behind the n_sph spheres in the material records, tested at the start of every ray
+// SST: the per-lane traversal stack lives in shared memory, stack[level][thread], RTM_BVH_SSTACK levels (the host
+// picks it when the tree is shallow enough: depth + 2 entries are the most a walk can hold); otherwise a private
+// 64-entry array in local memory.
+#ifndef RTM_BVH_SSTACK
+#define RTM_BVH_SSTACK 24
+#endif
+template <int NP, bool ACNE, bool PL, bool SST>
+__global__ void __launch_bounds__(RTM_MEGA_THREADS, RTM_BVH_MINBLOCKS)
+radiance_bvh_kernel(const __grid_constant__ RtmHotScene hot, const __grid_constant__ RtmPassParams p, float4* __restrict__ records,
+                    RtmCounters* __restrict__ counters, RtmBvhDev bvh, RtmMatDev mat, const float* __restrict__ cps0, int n_sph, int n_pl) {
+    __shared__ SelfMask sh_mask;
+    __shared__ SharedBig sh_big;
+    init_selfmask(sh_mask);
+    if (threadIdx.x < 8) sh_big.id[threadIdx.x] = (threadIdx.x < (unsigned)bvh.n_big) ? bvh.big_id[threadIdx.x] : 0;
+    __syncthreads();
+
+    const unsigned lane = threadIdx.x & 31u;
+    const unsigned lt_mask = (1u << lane) - 1u;
+    const unsigned n_sub = (unsigned)p.n_sub;
+    const int s_begin = p.s_begin, s_end = p.s_end;
+    const float inv_norm = p.inv_norm;
+    const unsigned sub_begin = (unsigned)p.sub_begin, sub_count = (unsigned)p.sub_count;
+    const unsigned grid = (unsigned)(p.frame.ss * p.frame.ss);
+    const bool full_grid = (sub_count == grid);
+    const unsigned key_mask = p.key_mask;
+
+    unsigned w_next = 0, w_end = 0;
+    bool have = false, done = false, tracing = false, pending = false;
+    unsigned q = 0, ql = 0;
+    f3 acc = mk(0, 0, 0);
+    f3 o = mk(0, 0, 0), w = mk(0, 0, 1), T = mk(1, 1, 1), L = mk(0, 0, 0), d = mk(0, 0, 1);
+    int id = 0, s = 0, depth = 0;
+    float cpsn = 0.f;
+    int sslot = -1;                  // leaf slot of the sphere the current ray leaves (self test inside the leaves)
+    uint32_t eps_bits = 0;
+    // the primary hit of the lane's sub-pixel is NOT lane state here: it is re-read from records[ql] (which holds it
+    // until the sub-pixel's sum is written) at every sample restart — 8 registers less, which is what lets
+    // RTM_BVH_MINBLOCKS blocks stay resident
+    auto stand_on_primary = [&](const float4 rec) {
+        const unsigned wbits = __float_as_uint(rec.w);
+        const int pid = (int)(wbits & RTM_REC_IDMASK);
+        const float4 g = __ldg(mat.geo + pid), e0 = __ldg(mat.emi + pid);
+        const float ir = (wbits & RTM_REC_FLIP) ? -g.w : g.w;
+        o = mk(rec.x, rec.y, rec.z);
+        w = mk((o.x - g.x) * ir, (o.y - g.y) * ir, (o.z - g.z) * ir);
+        if (PL && pid >= n_sph) w = (wbits & RTM_REC_FLIP) ? mk(-g.x, -g.y, -g.z) : mk(g.x, g.y, g.z);
+        id = pid;
+        T = mk(1, 1, 1); L = mk(e0.x, e0.y, e0.z); depth = 0;
+        if (ACNE) cpsn = (wbits & RTM_REC_FLIP) ? 0.f : cps0[ql] * g.w * RTM_ACNE_INV2TAU;
+    };
+    BvhRay ray;
+    ray.node = RTM_BVH_NONE_DEV;
+    constexpr int ST = SST ? RTM_MEGA_THREADS : 1;
+    __shared__ int sh_stack[SST ? RTM_BVH_SSTACK * RTM_MEGA_THREADS : 1];
+    int lstack[SST ? 1 : RTM_BVH_STACK_DEV];
+    int* const stack = SST ? (sh_stack + threadIdx.x) : lstack;
+    unsigned long long rays_ref = 0, traced = 0;
+    unsigned n_tests = 0, n_nodes = 0;
+
+    for (;;) {
+        // ---- refill (warp-uniform): lanes without a sub-pixel take the next ones of the warp's chunk
+        unsigned need = __ballot_sync(0xffffffffu, !have && !done);
+        while (need) {
+            if (w_next == w_end) {
+                unsigned long long start = 0;
+                if (lane == 0) start = atomicAdd(&counters->work_next, (unsigned long long)RTM_MEGA_CHUNK);
+                start = __shfl_sync(0xffffffffu, start, 0);
+                if (start >= (unsigned long long)n_sub) {
+                    if (!have) done = true;
+                    break;
+                }
+                w_next = (unsigned)start;
+                w_end = (start + RTM_MEGA_CHUNK < (unsigned long long)n_sub) ? (unsigned)start + RTM_MEGA_CHUNK : n_sub;
+            }
+            const unsigned avail = w_end - w_next;
+            const unsigned rank = __popc(need & lt_mask);
+            const bool mine = ((need >> lane) & 1u) && rank < avail;
+            if (mine) {
+                ql = w_next + rank;
+                q = full_grid ? ql : (ql / sub_count) * grid + sub_begin + (ql % sub_count);
+                const float4 rec = records[ql];
+                const unsigned wbits = __float_as_uint(rec.w);
+                const unsigned ns = (unsigned)(s_end - s_begin);
+                const bool miss = (wbits == RTM_REC_MISS);
+                const int Pid = miss ? 0 : (int)(wbits & RTM_REC_IDMASK);
+                const float4 e0 = __ldg(mat.emi + Pid);
+                if (miss || __float_as_uint(e0.w) == 0u) {
+                    float4 out = make_float4(0.f, 0.f, 0.f, 0.f);
+                    if (!miss) {
+                        out.x = clamp01f(e0.x * inv_norm) * (float)ns;
+                        out.y = clamp01f(e0.y * inv_norm) * (float)ns;
+                        out.z = clamp01f(e0.z * inv_norm) * (float)ns;
+                    }
+                    records[ql] = out;
+                    rays_ref += ns;
+                } else {
+                    have = true;
+                    acc = mk(0, 0, 0);
+                    s = s_begin;
+                    stand_on_primary(rec);
+                }
+            }
+            const unsigned took = (__popc(need) < avail) ? __popc(need) : avail;
+            w_next += took;
+            need = __ballot_sync(0xffffffffu, !have && !done && !mine);
+        }
+        const unsigned tr = __ballot_sync(0xffffffffu, tracing);
+        const unsigned sready = __ballot_sync(0xffffffffu, have && !tracing);
+        if ((tr | sready) == 0u) {
+            if (__all_sync(0xffffffffu, done)) break;
+            continue;
+        }
+
+        // ---- S block.  Entered by the whole warp (warp-uniform control flow, lanes outside it are predicated off):
+        // the roulette runs in ROUNDS shared by all S lanes, and the packed big-sphere test + ray start run once,
+        // after the rounds, for every lane that has a direction.  (With per-lane loops the compiler let each lane
+        // leave the roulette loop on its own: the ~140-instruction ray start then ran once per group of lanes that
+        // left together, 3.3 times per entry at 6 of 32 lanes — ncu_bvh_v3.)  A lane whose path is killed in the last
+        // round closes its sample and stays S-ready; another round is run only while RTM_BVH_S_ROUND or more lanes
+        // need one.
+        const bool in_s = (tr == 0u || __popc(sready) >= RTM_BVH_S_THRESH) && have && !tracing;
+        if (__any_sync(0xffffffffu, in_s)) {
+            // a finished ray is applied to the path; returns true when the path ends there
+            auto apply_hit = [&](int id2, float t) -> bool {
+                if (id2 < 0) return true;                                            // miss: Renderer.cpp:116
+                o = mk(fmaf(d.x, t, o.x), fmaf(d.y, t, o.y), fmaf(d.z, t, o.z));     // :79
+                const float4 g = __ldg(mat.geo + id2);
+                f3 nn = mk((o.x - g.x) * g.w, (o.y - g.y) * g.w, (o.z - g.z) * g.w);
+                if (PL && id2 >= n_sph) nn = mk(g.x, g.y, g.z);   // a plane's record holds its normal, 1/r = 0
+                if (g.w > 1e-2f) {
+                    // small spheres: t carries an absolute error of ~1e-5 that is not small against
+                    // r = 0.05; put the hit back on the surface and make the normal unit
+                    const float inv = fast_rsqrt(dot(nn, nn));
+                    nn = mk(nn.x * inv, nn.y * inv, nn.z * inv);
+                    const float rr = fast_rcp(g.w);
+                    o = mk(fmaf(rr, nn.x, g.x), fmaf(rr, nn.y, g.y), fmaf(rr, nn.z, g.z));
+                }
+                const bool flip = !(dot(nn, d) < 0.f);                               // :82-83
+                w = flip ? mk(-nn.x, -nn.y, -nn.z) : nn;
+                id = id2;
+                ++depth;
+                if (ACNE) cpsn = flip ? 0.f : t * t * ref_normalize_eps(eps_bits) * g.w * RTM_ACNE_INV2TAU;
+                const float4 e2 = __ldg(mat.emi + id2);
+                L.x = fmaf(T.x, e2.x, L.x); L.y = fmaf(T.y, e2.y, L.y); L.z = fmaf(T.z, e2.z, L.z);
+                return __float_as_uint(e2.w) == 0u;                                  // kd == 0: the next roulette cannot continue
+            };
+            bool end = false;
+            if (in_s && pending) {
+                pending = false;
+                end = apply_hit(bvh_resolve_hit(bvh, ray.hit), ray.best + RTM_T_EPS);
+            }
+            bool deciding = in_s, start = false;
+            int ocode = -1;
+            for (;;) {
+                if (deciding) {
+                    if (!end) {
+                        const uint2 rnd = rtm_bounce_rng(make_uint2(q, ((unsigned)s << 9) | (unsigned)depth), p.rk);
+                        const float4 em = __ldg(mat.emi + id);
+                        end = !((rnd.x < __float_as_uint(em.w)) && (depth + 1 < p.max_depth));   // Renderer.cpp:78
+                        if (!end) {
+                            const float4 al = __ldg(mat.alb + id);
+                            T.x *= al.x; T.y *= al.y; T.z *= al.z;                               // colorKD
+                            d = cosine_dir(w, rnd.y, ((rnd.x & 0xFFFu) << 10) | (rnd.y & 0x3FFu));
+                            eps_bits = rnd.x ^ (rnd.y * 0x9E3779B9u);
+                            ++traced;
+                            bool self = false;
+                            if (ACNE) {
+                                const float cosw = dot(w, d);
+                                if (cpsn + cosw <= 0.f && !(PL && id >= n_sph)) {
+                                    // SettingData.cpp:208-212: the far root of the sphere the ray stands (just) inside
+                                    const float rr = fast_rcp(__ldg(mat.geo + id).w);
+                                    const float qq = -cpsn * rr * RTM_ACNE_2TAU, bq = rr * cosw;
+                                    end = apply_hit(id, qq * fast_rcp(bq + fast_sqrt(fmaf(bq, bq, qq))));
+                                    self = true;   // stands on the next vertex: decide again
+                                }
+                            }
+                            if (!self) {
+                                ocode = __float_as_int(al.w);
+                                start = true;
+                                deciding = false;
+                            }
+                        }
+                    }
+                    if (deciding && end) {
+                        // the sample is complete: Renderer.cpp:240-242
+                        acc.x += clamp01f(L.x * inv_norm);
+                        acc.y += clamp01f(L.y * inv_norm);
+                        acc.z += clamp01f(L.z * inv_norm);
+                        ++s;
+                        if (s == s_end) {
+                            records[ql] = make_float4(acc.x, acc.y, acc.z, 0.f);
+                            rays_ref += (unsigned)(s_end - s_begin);
+                            have = false;
+                            deciding = false;
+                        } else {
+                            stand_on_primary(records[ql]);
+                            end = false;
+                        }
+                    }
+                }
+                if (__popc(__ballot_sync(0xffffffffu, deciding)) < RTM_BVH_S_ROUND) break;
+            }
+            if (start) {
+                // the packed big-sphere test (~140 instructions) and the planes: once, for all lanes that start a ray
+                bvh_ray_begin<NP, ST>(hot, sh_mask, sh_big, bvh, bvh_big_slot(ocode), o, d, key_mask, ray, stack, n_tests);
+                sslot = bvh_leaf_slot(ocode);
+                if (PL) bvh_ray_planes(hot, n_sph, n_pl, id, o, d, ray);
+                if (ray.node != RTM_BVH_NONE_DEV) tracing = true;
+                else pending = true;   // empty hierarchy: the hit (big spheres / planes) is applied at the next entry
+            }
+        }
+
+        // ---- T block: while-while until enough lanes are ready for the S block
+        unsigned still = __ballot_sync(0xffffffffu, tracing);
+        while (still) {
+            // at most RTM_BVH_BURST inner nodes per round: a lane on its long first descent must not
+            // keep the lanes that hop between neighbouring leaves (2-3 nodes apart) waiting
+#if RTM_BVH_HOLD
+            // a lane that reaches a leaf inside the burst parks it and goes on with the next node of its stack, so it
+            // keeps the inner-node block company instead of idling until the leaf block (Aila & Laine's speculative
+            // traversal); a second leaf makes it wait
+            int held = 0;   // leaf codes are negative
+#pragma unroll 1
+            for (int k = 0; k < RTM_BVH_BURST; ++k) {
+                if (tracing && ray.node < 0 && held == 0) {
+                    held = ray.node;
+                    ray.node = stack[ST * --ray.sp];
+                }
+                if (!(tracing && bvh_is_inner(ray.node))) break;
+                bvh_inner_step<ST>(bvh, ray, stack);
+                ++n_nodes;
+            }
+            if (tracing && held != 0) bvh_leaf_test(bvh, held, sslot, o, d, ray, n_tests);
+            else if (tracing && ray.node < 0) bvh_leaf_step<ST>(bvh, sslot, o, d, ray, stack, n_tests);
+#else
+#pragma unroll 1
+            for (int k = 0; k < RTM_BVH_BURST && tracing && bvh_is_inner(ray.node); ++k) {
+                bvh_inner_step<ST>(bvh, ray, stack);
+                ++n_nodes;
+            }
+            if (tracing && ray.node < 0) bvh_leaf_step<ST>(bvh, sslot, o, d, ray, stack, n_tests);
+#endif
+            if (tracing && ray.node == RTM_BVH_NONE_DEV) {
+                tracing = false;
+                pending = true;
+            }
+            still = __ballot_sync(0xffffffffu, tracing);
+            const unsigned ready = __ballot_sync(0xffffffffu, !tracing && !done);
+            if (__popc(ready) >= RTM_BVH_S_THRESH) break;
+        }
+    }
+
+    rays_ref += traced;
+    unsigned long long tests = n_tests, nodes = n_nodes;
+    for (int off = 16; off > 0; off >>= 1) {
+        rays_ref += __shfl_down_sync(0xffffffffu, rays_ref, off);
+        traced += __shfl_down_sync(0xffffffffu, traced, off);
+        tests += __shfl_down_sync(0xffffffffu, tests, off);
+        nodes += __shfl_down_sync(0xffffffffu, nodes, off);
+    }
+    if (lane == 0) {
+        atomicAdd(&counters->rays_ref, rays_ref);
+        atomicAdd(&counters->rays_traced, traced);
+        atomicAdd(&counters->tests, tests);
+        atomicAdd(&counters->nodes, nodes);
+    }
+}
+
+// the hierarchy variant of the hook: same trace function as radiance_mega_kernel<*, true>
+template <int NP>
+__global__ void closest_hit_bvh_f32_kernel(const __grid_constant__ RtmHotScene hot, RtmBvhDev bvh, RtmMatDev mat, unsigned key_mask, double rx, double ry, double rz, uint32_t n,
+                                           const double* __restrict__ org, const double* __restrict__ dir,
+                                           const int32_t* __restrict__ origin_id, int n_sph, int n_pl, int32_t* __restrict__ hit,
+                                           double* __restrict__ tout) {
+    __shared__ SelfMask sh_mask;
+    __shared__ SharedBig sh_big;
+    init_selfmask(sh_mask);
+    if (threadIdx.x < 8) sh_big.id[threadIdx.x] = (threadIdx.x < (unsigned)bvh.n_big) ? bvh.big_id[threadIdx.x] : 0;
+    __syncthreads();
+    const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    const f3 o = mk((float)(org[3 * i] - rx), (float)(org[3 * i + 1] - ry), (float)(org[3 * i + 2] - rz));
+    const f3 d = mk((float)dir[3 * i], (float)dir[3 * i + 1], (float)dir[3 * i + 2]);
+    int oid = origin_id ? origin_id[i] : -1;
+    if (oid < -1 || oid >= n_sph + n_pl) oid = -1;
+    const int ocode = (oid >= 0) ? __float_as_int(__ldg(mat.alb + oid).w) : -1;
+    float t;
+    unsigned a = 0, b = 0;
+    hit[i] = trace_bvh_f32<NP>(hot, sh_mask, sh_big, bvh, oid, ocode, o, d, t, key_mask, a, b, n_sph, n_pl);
+    tout[i] = (double)t;
+}
+
+template <int NP, bool ACNE, bool PL, bool SST>
+void launch_bvh3(const RtmHotScene& hot, const RtmBvhDev& bvh, const RtmMatDev& mat, const RtmPassParams& p, float4* records, RtmCounters* counters,
+                 int sm_count, const float* cps0, int n_sph, int n_pl, cudaStream_t st) {
+    int per_sm = 0;
+    cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, radiance_bvh_kernel<NP, ACNE, PL, SST>, RTM_MEGA_THREADS, 0);
+    if (per_sm < 1) per_sm = 1;
+    radiance_bvh_kernel<NP, ACNE, PL, SST><<<sm_count * per_sm, RTM_MEGA_THREADS, 0, st>>>(hot, p, records, counters, bvh, mat, cps0, n_sph, n_pl);
+}
+template <int NP, bool ACNE, bool PL>
+void launch_bvh2(const RtmHotScene& hot, const RtmBvhDev& bvh, const RtmMatDev& mat, const RtmPassParams& p, float4* records, RtmCounters* counters,
+                 int sm_count, const float* cps0, int n_sph, int n_pl, int walk, cudaStream_t st) {
+    // a walk holds at most depth + 2 stack entries (one per level + the sentinel); walk == 1 (rtm_options.debug_bvh_walk,
+    // A/B runs) keeps the stack in local memory
+    if (walk != 1 && bvh.depth + 2 <= RTM_BVH_SSTACK) launch_bvh3<NP, ACNE, PL, true>(hot, bvh, mat, p, records, counters, sm_count, cps0, n_sph, n_pl, st);
+    else launch_bvh3<NP, ACNE, PL, false>(hot, bvh, mat, p, records, counters, sm_count, cps0, n_sph, n_pl, st);
+}
+template <int NP>
+void launch_bvh(const RtmHotScene& hot, const RtmBvhDev& bvh, const RtmMatDev& mat, const RtmPassParams& p, float4* records, RtmCounters* counters,
+                int sm_count, const float* cps0, int n_sph, int n_pl, int walk, cudaStream_t st) {
+    if (n_pl > 0) {
+        if (cps0) launch_bvh2<NP, true, true>(hot, bvh, mat, p, records, counters, sm_count, cps0, n_sph, n_pl, walk, st);
+        else launch_bvh2<NP, false, true>(hot, bvh, mat, p, records, counters, sm_count, nullptr, n_sph, n_pl, walk, st);
+    } else {
+        if (cps0) launch_bvh2<NP, true, false>(hot, bvh, mat, p, records, counters, sm_count, cps0, n_sph, 0, walk, st);
+        else launch_bvh2<NP, false, false>(hot, bvh, mat, p, records, counters, sm_count, nullptr, n_sph, 0, walk, st);
+    }
+}
+}  // namespace
+
+void rtm_launch_radiance_bvh(const RtmHotScene& hot, const RtmBvhDev& bvh, const RtmMatDev& mat, const RtmPassParams& p, float4* records,
+                             RtmCounters* counters, int32_t sm_count, const float* cps0, int32_t n_sph, int32_t n_pl, int32_t walk,
+                             cudaStream_t st) {
+    switch ((bvh.n_big + 1) / 2) {
+        case 0: launch_bvh<0>(hot, bvh, mat, p, records, counters, sm_count, cps0, n_sph, n_pl, walk, st); break;
+        case 1: launch_bvh<1>(hot, bvh, mat, p, records, counters, sm_count, cps0, n_sph, n_pl, walk, st); break;
+        case 2: launch_bvh<2>(hot, bvh, mat, p, records, counters, sm_count, cps0, n_sph, n_pl, walk, st); break;
+        case 3: launch_bvh<3>(hot, bvh, mat, p, records, counters, sm_count, cps0, n_sph, n_pl, walk, st); break;
+        default: launch_bvh<4>(hot, bvh, mat, p, records, counters, sm_count, cps0, n_sph, n_pl, walk, st); break;
+    }
+}
+
+void rtm_launch_closest_hit_bvh_f32(const RtmHotScene& hot, const RtmBvhDev& bvh, const RtmMatDev& mat, int32_t n_spheres, int32_t n_planes,
+                                    const double* refd, uint32_t n, const double* org, const double* dir, const int32_t* origin_id,
+                                    int32_t* hit, double* t, cudaStream_t st) {
+    const unsigned g = (n + 127) / 128;
+    switch ((bvh.n_big + 1) / 2) {
+#define RTM_CASE(NP) closest_hit_bvh_f32_kernel<NP><<<g, 128, 0, st>>>(hot, bvh, mat, 0xFFFFFFF8u, refd[0], refd[1], refd[2], n, org, dir, origin_id, n_spheres, n_planes, hit, t)
+        case 0: RTM_CASE(0); break;
+        case 1: RTM_CASE(1); break;
+        case 2: RTM_CASE(2); break;
+        case 3: RTM_CASE(3); break;
+        default: RTM_CASE(4); break;
+#undef RTM_CASE
+    }
+}

@@ -1,0 +1,523 @@
+// kernels_common.cuh — device helpers shared by the FP32 kernel translation units (kernels_mega.cu, kernels_bvh.cu,
+// kernels_wave.cu, kernels_small.cu): the packed ray/sphere test, the plane test, the hierarchy steps, the cosine
+// sampler and the model of the reference's self-intersection.  Everything here is `static` device code inside an
+// anonymous namespace; every TU gets its own copy, so a change to one kernel cannot perturb another's schedule.
+//
+// The sphere test is NOT the reference's formula evaluated in float (that flips
+// 7 % of Cornell hits).  It is rearranged so that FP32 carries it:
+//   * positions are relative to the camera origin; c' = |o-c|^2 - r^2 is expanded
+//     as |o|^2 - 2 o.c + (|c|^2 - r^2), the last term precomputed in double, so the
+//     1e8-magnitude squares of the r=1e4 wall spheres never meet in float;
+//   * roots come from q = b + sign(b) sqrt(b^2 - c'), t = {q, c'/q}: no cancellation;
+//   * a ray leaving sphere k's surface gets c'_k = 0 exactly, which is what the
+//     reference's 1e-5 / 1e-3 epsilons (SettingData.cpp:208-212) achieve in double.
+//
+// Scene data: there is NO process-global state.  Each launch receives the handle's own RtmHotScene as a
+// __grid_constant__ kernel parameter (constant bank 0: the packed sphere / plane constants become uniform-register
+// operands exactly as a __constant__ symbol's would) plus a pointer to the handle's device copy of the full
+// per-sphere block, which the kernels stage into shared memory.
+#pragma once
+#include "rtm_internal.h"
+#include "philox.cuh"
+
+#include <float.h>
+
+#define RTM_MEGA_THREADS 128
+#define RTM_MEGA_CHUNK 64u  // sub-pixels a warp reserves per global atomic
+
+namespace {
+
+struct f3 {
+    float x, y, z;
+};
+__device__ __forceinline__ f3 mk(float x, float y, float z) { return f3{x, y, z}; }
+__device__ __forceinline__ float dot(f3 a, f3 b) { return fmaf(a.x, b.x, fmaf(a.y, b.y, a.z * b.z)); }
+
+__device__ __forceinline__ float fast_sqrt(float x) {
+    float r;
+    asm("sqrt.approx.ftz.f32 %0, %1;" : "=f"(r) : "f"(x));
+    return r;
+}
+__device__ __forceinline__ float fast_rcp(float x) {
+    float r;
+    asm("rcp.approx.ftz.f32 %0, %1;" : "=f"(r) : "f"(x));
+    return r;
+}
+
+__device__ __forceinline__ float fast_rsqrt(float x) {
+    float r;
+    asm("rsqrt.approx.ftz.f32 %0, %1;" : "=f"(r) : "f"(x));
+    return r;
+}
+
+// ---- ray/sphere test of the FP32 path ------------------------------------------
+// Semantics of SettingData.cpp:197-223 + the accept rule of Renderer.cpp:67, stated as
+// "the smallest root greater than RTM_T_EPS; lowest index wins exact ties".  The
+// reference takes the near root t1 when t1 > 1e-3, else the far root t2 when t2 >= 1e-5;
+// the two rules differ only for a far root inside [1e-5, 1e-3], i.e. for chords shorter
+// than 1e-3 (documented in DESIGN.md; invisible at the radiance tolerance).
+//
+// Roots without cancellation: tq = b + sign(b) sqrt(b^2 - c'), the other root is c'/tq.
+// A negative discriminant makes sqrt.approx return NaN, which propagates into both
+// candidates; the unsigned-integer minimum below ignores NaNs and negative values by
+// construction (their bit patterns are above +inf), so no explicit D >= 0 / t > 0 tests
+// are issued.
+#define RTM_T_EPS 1e-3f
+#define RTM_KEY_INF 0x7F800000u
+
+__device__ __forceinline__ void sphere_roots_f32(bool self, f3 o, f3 d, float oo, float dO, float cx, float cy, float cz,
+                                                 float m2cx, float m2cy, float m2cz, float K, float& ta, float& tb) {
+    const float b = fmaf(d.x, cx, fmaf(d.y, cy, fmaf(d.z, cz, -dO)));           // (c-o).d
+    float cp = fmaf(o.x, m2cx, fmaf(o.y, m2cy, fmaf(o.z, m2cz, oo + K)));       // |c-o|^2 - r^2
+    cp = self ? 0.f : cp;                                                       // leaving this sphere's surface
+    const float s = fast_sqrt(fmaf(b, b, -cp));
+    const float tq = b + copysignf(s, b);
+    ta = tq - RTM_T_EPS;
+    tb = fmaf(cp, fast_rcp(tq), -RTM_T_EPS);
+}
+
+// ---- packed FP32 (sm_100 f32x2): two spheres per instruction ----------------------
+typedef unsigned long long u64;
+__device__ __forceinline__ u64 pk(float lo, float hi) {
+    u64 r;
+    asm("mov.b64 %0, {%1, %2};" : "=l"(r) : "f"(lo), "f"(hi));
+    return r;
+}
+__device__ __forceinline__ u64 pk(float2 v) { return pk(v.x, v.y); }
+__device__ __forceinline__ void unpk(u64 v, float& lo, float& hi) { asm("mov.b64 {%0, %1}, %2;" : "=f"(lo), "=f"(hi) : "l"(v)); }
+__device__ __forceinline__ u64 fma2(u64 a, u64 b, u64 c) {
+    u64 r;
+    asm("fma.rn.f32x2 %0, %1, %2, %3;" : "=l"(r) : "l"(a), "l"(b), "l"(c));
+    return r;
+}
+__device__ __forceinline__ u64 add2(u64 a, u64 b) {
+    u64 r;
+    asm("add.rn.f32x2 %0, %1, %2;" : "=l"(r) : "l"(a), "l"(b));
+    return r;
+}
+__device__ __forceinline__ u64 mul2(u64 a, u64 b) {
+    u64 r;
+    asm("mul.rn.f32x2 %0, %1, %2;" : "=l"(r) : "l"(a), "l"(b));
+    return r;
+}
+// Row oid+1 of this table is 1 everywhere except column oid: multiplying -c' by it zeroes
+// c' of the sphere the ray leaves (2 LDS.128 + one FMUL2 per pair instead of a compare and
+// a select per sphere).  Row 0 (oid = -1: no origin sphere) is all ones.
+struct SelfMask {
+    float4 lo[9], hi[9];   // row r = (lo[r], hi[r]).  Rows 1..8 of `lo` (and of `hi`) cover the 32 banks once: lanes that
+                           // leave different spheres read without bank conflicts (round 1's row[9][2] layout put rows r
+                           // and r+4 on the same banks: 21 % of the megakernel's shared-memory wavefronts were replays)
+};
+__device__ __forceinline__ void init_selfmask(SelfMask& m) {
+    for (int i = threadIdx.x; i < 9 * 8; i += blockDim.x) {
+        const int r = i >> 3, c = i & 7;
+        float* dst = (c < 4) ? reinterpret_cast<float*>(&m.lo[r]) : reinterpret_cast<float*>(&m.hi[r]);
+        dst[c & 3] = (c == r - 1) ? 0.f : 1.f;
+    }
+}
+// (x & mask) | idx in ONE LOP3: the mask sits in a register (an immediate mask plus an
+// immediate index would take two instructions).
+__device__ __forceinline__ unsigned key_pack(unsigned x, unsigned mask_reg, unsigned idx) {
+    unsigned r;
+    asm("lop3.b32 %0, %1, %2, %3, 0xEA;" : "=r"(r) : "r"(x), "r"(mask_reg), "r"(idx));
+    return r;
+}
+
+// Closest hit for N <= 8: spheres are tested in PAIRS with FFMA2/FADD2 (one instruction
+// does the same step for two spheres; the ray operand is broadcast, the sphere constants
+// come as 64-bit uniform-register pairs from constant memory).  The candidate (t - eps)
+// and the sphere index share one 32-bit key, t in the upper 29 bits (8 ulp of t are given
+// up: below the FP32 error of t itself), the index in the low 3; positive floats order
+// like unsigned integers, so an unsigned min does the accept test, the tie rule and the
+// bookkeeping.  Returns the key; RTM_KEY_INF or above = miss.
+// NS = number of slots that hold (or may hold) a sphere: with NS odd the upper half of the last pair is padding, and
+// its scalar tail (sqrt, copysign, rcp, min, key) is not issued — 5 of ~280 instructions of a Cornell-box bounce.
+template <int NS>
+__device__ __forceinline__ unsigned trace_pairs_f32(const RtmHotScene& hot, const SelfMask& sm, int oid, f3 o, f3 d, unsigned key_mask) {
+    constexpr int NP = (NS + 1) / 2;
+    const float noo = -dot(o, o), ndO = -dot(d, o);
+    const u64 dx = pk(d.x, d.x), dy = pk(d.y, d.y), dz = pk(d.z, d.z);
+    // o.(2c) is formed as (2o).c — bit-identical (power-of-two scaling) and the pair needs 4 constants, not 7
+    const float o2x = o.x + o.x, o2y = o.y + o.y, o2z = o.z + o.z;
+    const u64 ox = pk(o2x, o2x), oy = pk(o2y, o2y), oz = pk(o2z, o2z);
+    const u64 noo2 = pk(noo, noo), ndO2 = pk(ndO, ndO), neps2 = pk(-RTM_T_EPS, -RTM_T_EPS);
+    unsigned best = RTM_KEY_INF;
+    const float4 m0 = sm.lo[oid + 1], m1 = sm.hi[oid + 1];
+    const u64 mask[4] = {pk(m0.x, m0.y), pk(m0.z, m0.w), pk(m1.x, m1.y), pk(m1.z, m1.w)};
+#pragma unroll
+    for (int j = 0; j < NP; ++j) {
+        const RtmPairF32& c = hot.pairs[j];
+        const u64 b2 = fma2(dx, pk(c.cx), fma2(dy, pk(c.cy), fma2(dz, pk(c.cz), ndO2)));                   // (c-o).d
+        const u64 ncp2 = fma2(ox, pk(c.cx), fma2(oy, pk(c.cy), fma2(oz, pk(c.cz), add2(noo2, pk(c.nK)))));     // r^2 - |c-o|^2
+        const u64 ncp = mul2(ncp2, mask[j]);   // leaving this sphere's surface: c' = 0 exactly
+        float b0, b1;
+        unpk(b2, b0, b1);
+        float D0, D1;
+        unpk(fma2(b2, b2, ncp), D0, D1);
+        const bool pad = (NS & 1) && j == NP - 1;                    // compile-time: slot 2j+1 is padding
+        const float s0 = fast_sqrt(D0), s1 = pad ? 0.f : fast_sqrt(D1);   // NaN when the ray misses the sphere
+        const u64 tq2 = add2(b2, pk(copysignf(s0, b0), pad ? 0.f : copysignf(s1, b1)));
+        float q0, q1;
+        unpk(tq2, q0, q1);
+        const u64 rn = pk(fast_rcp(-q0), pad ? 0.f : fast_rcp(-q1));
+        float ta0, ta1, tb0, tb1;
+        unpk(add2(tq2, neps2), ta0, ta1);                            // tq - eps
+        unpk(fma2(ncp, rn, neps2), tb0, tb1);                        // c'/tq - eps
+        const unsigned k0 = key_pack(min(__float_as_uint(ta0), __float_as_uint(tb0)), key_mask, 2 * j);
+        if (pad) {
+            best = min(best, k0);
+        } else {
+            const unsigned k1 = key_pack(min(__float_as_uint(ta1), __float_as_uint(tb1)), key_mask, 2 * j + 1);
+            best = min(best, min(k0, k1));
+        }
+    }
+    return best;
+}
+
+// Per-sphere data addressed with a per-lane index (the hit id): shared memory, three
+// 16-byte records per sphere so that a lane needs three LDS.128 per hit.  K is read by the runtime-N loop only.
+struct SharedScene {
+    float4 geo[RTM_MAX_CONST_SPHERES];  // cx, cy, cz, 1/r
+    float4 emi[RTM_MAX_CONST_SPHERES];  // emission rgb, roulette threshold (uint bits)
+    float4 alb[RTM_MAX_CONST_SPHERES];  // color/kd rgb (colorKD, SettingData.h:11-13), "listed light" flag (NEE)
+    float K[RTM_MAX_CONST_SPHERES];     // |c|^2 - r^2
+};
+
+// Runtime-N version (any N up to RTM_MAX_CONST_SPHERES): explicit (t, id) pair; the sphere constants come from the
+// block's shared-memory copy (uniform index: broadcast reads).
+__device__ __forceinline__ int trace_loop_f32(const SharedScene& sh, int n, int oid, f3 o, f3 d, float& t) {
+    const float oo = dot(o, o), dO = dot(d, o);
+    float best = FLT_MAX;
+    int id = -1;
+#pragma unroll 4
+    for (int i = 0; i < n; ++i) {
+        float ta, tb;
+        const float4 g = sh.geo[i];
+        sphere_roots_f32(i == oid, o, d, oo, dO, g.x, g.y, g.z, -2.0f * g.x, -2.0f * g.y, -2.0f * g.z, sh.K[i], ta, tb);
+        // candidates are (root - eps); valid iff > 0; NaN fails every comparison
+        const float c1 = (ta > 0.f) ? ta : FLT_MAX, c2 = (tb > 0.f) ? tb : FLT_MAX;
+        const float c = fminf(c1, c2);
+        const bool ok = c < best;
+        best = ok ? c : best;
+        id = ok ? i : id;
+    }
+    t = best + RTM_T_EPS;
+    return id;
+}
+
+template <int N>
+__device__ __forceinline__ int trace_f32(const RtmHotScene& hot, const SharedScene& sh, const SelfMask& sm, int n_rt, int oid, f3 o, f3 d,
+                                         float& t, unsigned key_mask) {
+    if (N > 0) {
+        const unsigned key = trace_pairs_f32<N>(hot, sm, oid, o, d, key_mask);
+        t = __uint_as_float(key & ~7u) + RTM_T_EPS;
+        return (key < RTM_KEY_INF) ? (int)(key & 7u) : -1;
+    }
+    return trace_loop_f32(sh, n_rt, oid, o, d, t);
+}
+
+// ---- PlaneObject extension ---------------------------------------
+// Finite squares from constant memory, two per instruction (f32x2) like the spheres, branch-free: for
+// each pair t = (d0 - n.o) * rcp(n.d), the point q = o + t d - position, the two half-extent dots, and
+// one predicate per plane (inside, not parallel, t > eps, not the plane the ray leaves, closer than
+// the best so far) that selects (t, id).  Tested after the spheres with a strict `<`, so a sphere keeps
+// an exact tie.  The plane a ray leaves is skipped by id (the FP64 definition rejects it through
+// t > 1e-3: t is 0 there).
+__device__ __forceinline__ void trace_planes_f32(const RtmHotScene& hot, int n_sph, int n_pl, int oid, f3 o, f3 d, float& t, int& id) {
+    const u64 dx = pk(d.x, d.x), dy = pk(d.y, d.y), dz = pk(d.z, d.z);
+    const u64 ox = pk(o.x, o.x), oy = pk(o.y, o.y), oz = pk(o.z, o.z);
+    const u64 nox = pk(-o.x, -o.x), noy = pk(-o.y, -o.y), noz = pk(-o.z, -o.z);
+    const int self = oid - n_sph;   // slot of the plane the ray leaves (negative: none)
+    const int np = (n_pl + 1) >> 1;
+    // unrolled with a uniform guard: constant indices let the pair's constants come straight from the
+    // constant bank (LDCU / c[][] operands) instead of one indexed LDC per value
+#pragma unroll
+    for (int j = 0; j < RTM_MAX_PLANES / 2; ++j) {
+        if (j >= np) break;
+        const RtmPlanePairF32& c = hot.plane_pairs[j];
+        const u64 nx = pk(c.nx), ny = pk(c.ny), nz = pk(c.nz);
+        float dn0, dn1;
+        unpk(fma2(nx, dx, fma2(ny, dy, mul2(nz, dz))), dn0, dn1);                       // n.d
+        const u64 num2 = fma2(nx, nox, fma2(ny, noy, fma2(nz, noz, pk(c.d0))));         // n.(position - o)
+        const u64 tt2 = mul2(num2, pk(fast_rcp(dn0), fast_rcp(dn1)));
+        const u64 qx = fma2(dx, tt2, add2(ox, pk(c.npx))), qy = fma2(dy, tt2, add2(oy, pk(c.npy))),
+                  qz = fma2(dz, tt2, add2(oz, pk(c.npz)));
+        float a0, a1, b0, b1, t0, t1;
+        unpk(fma2(qx, pk(c.rx), fma2(qy, pk(c.ry), mul2(qz, pk(c.rz)))), a0, a1);
+        unpk(fma2(qx, pk(c.ux), fma2(qy, pk(c.uy), mul2(qz, pk(c.uz)))), b0, b1);
+        unpk(tt2, t0, t1);
+        const bool v0 = fmaxf(fabsf(a0), fabsf(b0)) <= 1.f && fabsf(dn0) >= FLT_EPSILON && t0 > RTM_T_EPS && 2 * j != self && t0 < t;
+        t = v0 ? t0 : t;
+        id = v0 ? n_sph + 2 * j : id;
+        const bool v1 = fmaxf(fabsf(a1), fabsf(b1)) <= 1.f && fabsf(dn1) >= FLT_EPSILON && t1 > RTM_T_EPS && 2 * j + 1 != self && t1 < t;
+        t = v1 ? t1 : t;
+        id = v1 ? n_sph + 2 * j + 1 : id;
+    }
+}
+
+// ---- closest hit through the hierarchy (bvh.h), FP32 ------------------------------
+// Up to 8 "big" spheres (the r = 1e4 walls) go through the packed pair test above with the
+// cancellation-free K form; everything else sits in a two-child hierarchy walked per lane
+// (while-while, near child first, explicit stack in local memory).  Small spheres use the
+// direct form p = c - o, c' = |p|^2 - r^2: for r <= 1 the squares are small and the direct
+// form is the more accurate one next to the surface the ray leaves.
+__device__ __forceinline__ bool box_test_f32(float lx, float hx, float ly, float hy, float lz, float hz, f3 oi, f3 inv,
+                                             float tmax_in, float& tnear) {
+    // (plane - o) / d as one FMA per plane; NaN (0 * inf) drops out of fminf/fmaxf: that slab is ignored
+    const float ax = fmaf(lx, inv.x, -oi.x), bx = fmaf(hx, inv.x, -oi.x);
+    const float ay = fmaf(ly, inv.y, -oi.y), by = fmaf(hy, inv.y, -oi.y);
+    const float az = fmaf(lz, inv.z, -oi.z), bz = fmaf(hz, inv.z, -oi.z);
+    // nested so that the compiler can form 3-input FMNMX3
+    const float tmin = fmaxf(fmaxf(fminf(ax, bx), fminf(ay, by)), fmaxf(fminf(az, bz), 0.f));
+    const float tmax = fminf(fminf(fmaxf(ax, bx), fmaxf(ay, by)), fminf(fmaxf(az, bz), tmax_in));
+    tnear = tmin;
+    return tmin <= tmax;
+}
+
+struct SharedBig {
+    int id[8];
+};
+
+#define RTM_BVH_NONE_DEV 0x7FFFFFFF
+__device__ __forceinline__ bool bvh_is_inner(int node) { return (unsigned)node < 0x7FFFFFFFu; }   // leaves are negative
+
+// Ray state of one lane inside the hierarchy.  best = candidate (root - eps), as in the packed test.
+struct BvhRay {
+    f3 inv, oi;      // 1/d and o/d
+    float best;
+    int hit;         // original sphere index of the current winner, -1 = none
+    int node;        // current node (child code), RTM_BVH_NONE_DEV when the traversal is over
+    int sp;
+};
+
+// the packed test over the big list, then position the lane on the root
+// ST = distance in ints between two consecutive entries of a lane's stack: 1 for a private (local-memory) array,
+// the block size for the interleaved shared-memory layout stack[level][thread]
+template <int NP, int ST = 1>
+__device__ __forceinline__ void bvh_ray_begin(const RtmHotScene& hot, const SelfMask& sm, const SharedBig& big, const RtmBvhDev& bvh, int oslot,
+                                              f3 o, f3 d, unsigned key_mask, BvhRay& r, int* stack, unsigned& n_tests) {
+    r.best = FLT_MAX;
+    r.hit = -1;
+    if (NP > 0) {
+        const unsigned key = trace_pairs_f32<2 * NP>(hot, sm, oslot, o, d, key_mask);   // the big list is padded to even at run time
+        if (key < RTM_KEY_INF) {
+            r.best = __uint_as_float(key & ~7u);
+            r.hit = big.id[key & 7u];
+        }
+        n_tests += 2 * NP;
+    }
+    r.inv = mk(fast_rcp(d.x), fast_rcp(d.y), fast_rcp(d.z));
+    r.oi = mk(o.x * r.inv.x, o.y * r.inv.y, o.z * r.inv.z);
+    r.node = bvh.root;
+    r.sp = 0;
+    stack[ST * r.sp++] = RTM_BVH_NONE_DEV;
+}
+
+// 32 bytes per lane in ONE request (sm_100: LDG.E.256).  The walk is bound by L1 wavefronts (every lane of a warp
+// sits on a different node, so each load instruction costs one wavefront per active lane): a 64-byte node fetched as
+// 2 x 32 bytes costs half the wavefronts of 4 x 16 bytes.  `p` must be 32-byte aligned.
+#ifndef RTM_BVH_LDG128
+__device__ __forceinline__ void ldg256(const float4* p, float4& a, float4& b) {
+    asm("ld.global.nc.v8.f32 {%0,%1,%2,%3,%4,%5,%6,%7}, [%8];"
+        : "=f"(a.x), "=f"(a.y), "=f"(a.z), "=f"(a.w), "=f"(b.x), "=f"(b.y), "=f"(b.z), "=f"(b.w)
+        : "l"(p));
+}
+#else
+__device__ __forceinline__ void ldg256(const float4* p, float4& a, float4& b) { a = __ldg(p); b = __ldg(p + 1); }
+#endif
+
+// one inner node: test both children, descend into the nearer one, push the other
+template <int ST = 1>
+__device__ __forceinline__ void bvh_inner_step(const RtmBvhDev& bvh, BvhRay& r, int* stack) {
+    const float4* q = bvh.nodes + 4 * r.node;
+    float4 q0, q1, q2, q3;
+    ldg256(q, q0, q1);
+    ldg256(q + 2, q2, q3);
+    float n0, n1;
+    const float tm = r.best + 2.f * RTM_T_EPS;
+    const bool h0 = box_test_f32(q0.x, q0.y, q0.z, q0.w, q2.x, q2.y, r.oi, r.inv, tm, n0);
+    const bool h1 = box_test_f32(q1.x, q1.y, q1.z, q1.w, q2.z, q2.w, r.oi, r.inv, tm, n1);
+    const int c0 = __float_as_int(q3.x), c1 = __float_as_int(q3.y);
+    if (h0 && h1) {
+        const bool swap = n1 < n0;
+        stack[ST * r.sp++] = swap ? c0 : c1;
+        r.node = swap ? c1 : c0;
+    } else if (h0 || h1) {
+        r.node = h0 ? c0 : c1;
+    } else {
+        r.node = stack[ST * --r.sp];
+    }
+}
+
+// Winner of a hierarchy walk, BvhRay::hit: -1 none, >= 0 an original object index (big spheres, planes), <= -2 the
+// leaf SLOT s of a hierarchy sphere coded as -2 - s.  Every sphere sits in exactly one slot, so the slot identifies it
+// during the walk; the original index (bvh.leaf_id) is fetched once per ray for the winner, not once per candidate
+// (10.9 candidates per ray on synth10k).
+__device__ __forceinline__ int bvh_resolve_hit(const RtmBvhDev& bvh, int hit) { return (hit < -1) ? __ldg(bvh.leaf_id + (-2 - hit)) : hit; }
+// alb.w of an object: its slot in the big list (0..7), 8 + its leaf slot, or -1 (a plane)
+__device__ __forceinline__ int bvh_big_slot(int code) { return (code >= 8) ? -1 : code; }
+__device__ __forceinline__ int bvh_leaf_slot(int code) { return code - 8; }
+
+// one leaf: 1..4 spheres in the direct form; self_slot = leaf slot of the sphere the ray leaves (negative: none)
+__device__ __forceinline__ void bvh_leaf_test(const RtmBvhDev& bvh, int leaf, int self_slot, f3 o, f3 d, BvhRay& r, unsigned& n_tests) {
+    const unsigned code = ~(unsigned)leaf;
+    const unsigned first = code >> 3, cnt = (code & 7u) + 1u;
+    for (unsigned k = 0; k < cnt; ++k) {
+        const float4 g = __ldg(bvh.leaf_geo + first + k);
+        const int slot = (int)(first + k);
+        const f3 p = mk(g.x - o.x, g.y - o.y, g.z - o.z);
+        const float b = dot(p, d);
+        // discriminant as r^2 - |p - b d|^2: b^2 - (|p|^2 - r^2) cancels at |p|^2 ~ 400 and
+        // leaves an error of 3e-4 against r^2 = 2.5e-3 for the smallest spheres
+        const f3 l = mk(fmaf(-b, d.x, p.x), fmaf(-b, d.y, p.y), fmaf(-b, d.z, p.z));
+        float D = g.w - dot(l, l);
+        float cp = dot(p, p) - g.w;
+        const bool self = (slot == self_slot);             // leaving this sphere's surface
+        cp = self ? 0.f : cp;
+        D = self ? b * b : D;
+        const float s = fast_sqrt(D);                      // NaN: the ray misses
+        const float tq = b + copysignf(s, b);
+        const float ta = tq - RTM_T_EPS, tb = fmaf(cp, fast_rcp(tq), -RTM_T_EPS);
+        const float c1 = (ta > 0.f) ? ta : FLT_MAX, c2 = (tb > 0.f) ? tb : FLT_MAX;
+        const float c = fminf(c1, c2);
+        bool ok = c < r.best;
+        if (c == r.best && r.hit != -1)                    // exact tie (measure zero): the lowest ORIGINAL index wins, Renderer.cpp:67
+            ok = __ldg(bvh.leaf_id + slot) < bvh_resolve_hit(bvh, r.hit);
+        r.best = ok ? c : r.best;
+        r.hit = ok ? (-2 - slot) : r.hit;
+    }
+    n_tests += cnt;
+}
+// ... then pop
+template <int ST = 1>
+__device__ __forceinline__ void bvh_leaf_step(const RtmBvhDev& bvh, int self_slot, f3 o, f3 d, BvhRay& r, int* stack, unsigned& n_tests) {
+    bvh_leaf_test(bvh, r.node, self_slot, o, d, r, n_tests);
+    r.node = stack[ST * --r.sp];
+}
+
+// the wavefront variant's leaf step: candidates identified by their original index (one more 4-byte load per candidate)
+__device__ __forceinline__ void bvh_leaf_step_ids(const RtmBvhDev& bvh, int oid, f3 o, f3 d, BvhRay& r, int* stack, unsigned& n_tests) {
+    const unsigned code = ~(unsigned)r.node;
+    const unsigned first = code >> 3, cnt = (code & 7u) + 1u;
+    for (unsigned k = 0; k < cnt; ++k) {
+        const float4 g = __ldg(bvh.leaf_geo + first + k);
+        const int sid = __ldg(bvh.leaf_id + first + k);
+        const f3 p = mk(g.x - o.x, g.y - o.y, g.z - o.z);
+        const float b = dot(p, d);
+        const f3 l = mk(fmaf(-b, d.x, p.x), fmaf(-b, d.y, p.y), fmaf(-b, d.z, p.z));
+        float D = g.w - dot(l, l);
+        float cp = dot(p, p) - g.w;
+        const bool self = (sid == oid);
+        cp = self ? 0.f : cp;
+        D = self ? b * b : D;
+        const float s = fast_sqrt(D);
+        const float tq = b + copysignf(s, b);
+        const float ta = tq - RTM_T_EPS, tb = fmaf(cp, fast_rcp(tq), -RTM_T_EPS);
+        const float c1 = (ta > 0.f) ? ta : FLT_MAX, c2 = (tb > 0.f) ? tb : FLT_MAX;
+        const float c = fminf(c1, c2);
+        const bool ok = (c < r.best) || (c == r.best && sid < r.hit);
+        r.best = ok ? c : r.best;
+        r.hit = ok ? sid : r.hit;
+    }
+    n_tests += cnt;
+    r.node = stack[--r.sp];
+}
+
+// PlaneObject extension: planes are tested like the big spheres, before the descent, so that the hierarchy is
+// walked with their distance as the pruning bound
+__device__ __forceinline__ void bvh_ray_planes(const RtmHotScene& hot, int n_sph, int n_pl, int oid, f3 o, f3 d, BvhRay& r) {
+    float t = r.best + RTM_T_EPS;
+    int id = r.hit;
+    trace_planes_f32(hot, n_sph, n_pl, oid, o, d, t, id);
+    if (id != r.hit) {
+        r.best = t - RTM_T_EPS;
+        r.hit = id;
+    }
+}
+
+// whole query (test hook; the render kernel interleaves the same steps across its lanes).  ocode = alb.w of the
+// object the ray leaves (or -1)
+template <int NP>
+__device__ __forceinline__ int trace_bvh_f32(const RtmHotScene& hot, const SelfMask& sm, const SharedBig& big, const RtmBvhDev& bvh, int oid, int ocode,
+                                             f3 o, f3 d, float& t, unsigned key_mask, unsigned& n_tests, unsigned& n_nodes,
+                                             int n_sph = 0, int n_pl = 0) {
+    BvhRay r;
+    int stack[RTM_BVH_STACK_DEV];
+    bvh_ray_begin<NP>(hot, sm, big, bvh, bvh_big_slot(ocode), o, d, key_mask, r, stack, n_tests);
+    if (n_pl > 0) bvh_ray_planes(hot, n_sph, n_pl, oid, o, d, r);
+    while (r.node != RTM_BVH_NONE_DEV) {
+        while (bvh_is_inner(r.node)) {
+            bvh_inner_step(bvh, r, stack);
+            ++n_nodes;
+        }
+        if (r.node < 0) bvh_leaf_step(bvh, bvh_leaf_slot(ocode), o, d, r, stack, n_tests);
+    }
+    t = r.best + RTM_T_EPS;
+    return bvh_resolve_hit(bvh, r.hit);
+}
+
+// Hierarchy path: the per-sphere records stay in global memory (L1/L2 resident); shared
+// memory only holds the original indices of the "big" spheres the packed test covers.
+template <bool BVH>
+struct SceneRecs {
+    const SharedScene* sh;
+    RtmMatDev m;
+    __device__ __forceinline__ float4 geo(int i) const { return BVH ? __ldg(m.geo + i) : sh->geo[i]; }
+    __device__ __forceinline__ float4 emi(int i) const { return BVH ? __ldg(m.emi + i) : sh->emi[i]; }
+    __device__ __forceinline__ float4 alb(int i) const { return BVH ? __ldg(m.alb + i) : sh->alb[i]; }
+};
+
+__device__ __forceinline__ void load_shared_scene(SharedScene& s, const RtmSceneF32Host* __restrict__ f, int n) {
+    for (int i = threadIdx.x; i < n; i += blockDim.x) {
+        s.geo[i] = make_float4(__ldg(f->cx + i), __ldg(f->cy + i), __ldg(f->cz + i), __ldg(f->inv_r + i));
+        s.emi[i] = make_float4(__ldg(f->ex + i), __ldg(f->ey + i), __ldg(f->ez + i), __uint_as_float(__ldg(f->kd_thr + i)));
+        s.alb[i] = make_float4(__ldg(f->kx + i), __ldg(f->ky + i), __ldg(f->kz + i), __ldg(f->lit + i));
+        s.K[i] = __ldg(f->K + i);
+    }
+    __syncthreads();
+}
+
+// Cosine-weighted direction about the unit normal w (Renderer.cpp:88-107): a uniform
+// point s on the unit sphere added to w and normalised is cosine-distributed about w,
+// which needs no tangent frame.  The reference builds u,v from Cross(axis,w); the
+// azimuth is uniform, so the distribution of the sampled direction is the same.
+//   phi = 2*pi*xi1 (from 32 bits), z = 1 - 2*xi2 (22 bits, centred: never exactly +-1)
+__device__ __forceinline__ f3 cosine_dir(f3 w, uint32_t u_phi, uint32_t u_z22) {
+    const float z = fmaf((float)u_z22, -4.76837158203125e-7f, 1.0f - 2.384185791015625e-7f);  // 1 - (2k+1)/2^22
+    const float rxy = fast_sqrt(fmaf(-z, z, 1.0f));
+    float sn, cs;
+    __sincosf((float)u_phi * 1.4629180792671596e-9f, &sn, &cs);  // 2*pi / 2^32
+    const f3 v = mk(fmaf(rxy, cs, w.x), fmaf(rxy, sn, w.y), w.z + z);
+    const float inv = fast_rsqrt(fmaxf(dot(v, v), 1e-12f));
+    return mk(v.x * inv, v.y * inv, v.z * inv);
+}
+
+__device__ __forceinline__ float clamp01f(float v) { return __saturatef(v); }
+
+// ---- the reference's self-intersection on small spheres ("ACNE") ---------------------
+// Ray.h:67-72 normalises with a FLOAT sqrt, so every direction has |d|^2 = 1 + eps,
+// eps ~ 1e-7.  SettingData.cpp:197-223 assumes a unit direction, so a hit reported at
+// distance t sits at |x - c|^2 = r^2 + t^2 eps: OFF the surface by t^2 eps / 2r, which for
+// r = 0.05, t = 15 is 2e-4.  When that point is inside the sphere (eps < 0), the next,
+// outward ray finds the far root t2 = |c'| / (|b| + sqrt(b^2 + |c'|)) of its own sphere
+// with c' = t^2 eps, b = -r cos(theta); it is accepted when t2 >= 1e-5 (:208-209), i.e. when
+//     -c' >= 2 tau r cos(theta) + tau^2,   tau = 1e-5f.
+// The path then continues from the same point with the normal flipped INWARD and stays
+// inside the sphere.  The r = 1e4 walls never qualify (cos(theta) < 1e-3); 0.05..0.3 spheres
+// do for about a fifth of the bounces and half of the primary hits, which darkens them
+// visibly in the reference's images — so the FP32 path carries c' as explicit lane state:
+// exact for primary hits (from the FP64 pass), and for bounce rays drawn from the
+// distribution the reference's arithmetic produces: eta = |v|^2 - 1 before normalisation
+// (std 5.3e-8, four summed bytes), x = fl32(1 + eta), m = sqrtf(x), eps = eta - 2(m - 1).
+// State: cpsn = c' / (2 tau r) (0 when the normal is flipped: an inward ray takes the
+// ordinary far root), test: cpsn + cos(theta) <= 0.
+#define RTM_ACNE_INV2TAU 5.0000001e4f   // 1 / (2 * (double)1e-5f)
+#define RTM_ACNE_2TAU 1.99999995e-5f
+__device__ __forceinline__ float ref_normalize_eps(uint32_t bits) {
+    const int S = (int)__dp4a(bits, 0x01010101u, 0u);
+    const float eta = (float)(S - 510) * 3.586e-10f;
+    const float m = __fsqrt_rn(1.0f + eta);
+    return eta - 2.0f * (m - 1.0f);
+}
+
+}  // namespace

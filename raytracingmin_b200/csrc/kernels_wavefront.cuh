@@ -1,6 +1,6 @@
 // kernels_wavefront.cuh — the WAVEFRONT organisation of the FP32 bounce loop
-// (RTM_VARIANT_WAVEFRONT), included into kernels_radiance.cu (same translation unit: it
-// shares the sphere tests, the hierarchy steps, the sampler and the __constant__ scene).
+// (RTM_VARIANT_WAVEFRONT), included into kernels_wave.cu (it
+// shares the sphere tests, the hierarchy steps and the sampler: kernels_common.cuh).
 //
 // Same estimator and same RNG keys as the megakernels — the image is bit-identical for
 // brute-force scenes — but the lane state lives in global memory (RtmWaveDev) and a render
@@ -17,7 +17,7 @@
 // path state through HBM, which the megakernel keeps in registers.
 
 template <int N, bool BVH, bool ACNE>
-__global__ void __launch_bounds__(128) wf_shade_kernel(RtmPassParams p, float4* __restrict__ records,
+__global__ void __launch_bounds__(128) wf_shade_kernel(const __grid_constant__ RtmHotScene hot, RtmPassParams p, float4* __restrict__ records,
                                                        RtmCounters* __restrict__ counters, int n_rt, RtmBvhDev bvh, RtmMatDev mat,
                                                        const float* __restrict__ cps0, RtmWaveDev wv, int wave) {
     __shared__ SharedScene sh;
@@ -28,7 +28,7 @@ __global__ void __launch_bounds__(128) wf_shade_kernel(RtmPassParams p, float4* 
         if (threadIdx.x < 8) sh_big.id[threadIdx.x] = (threadIdx.x < (unsigned)bvh.n_big) ? bvh.big_id[threadIdx.x] : 0;
         __syncthreads();
     } else {
-        load_shared_scene(sh, (N > 0) ? N : n_rt);
+        load_shared_scene(sh, hot.full, (N > 0) ? N : n_rt);
     }
     SceneRecs<BVH> recs;
     recs.sh = &sh;
@@ -64,7 +64,7 @@ __global__ void __launch_bounds__(128) wf_shade_kernel(RtmPassParams p, float4* 
             w = mk(v1.x, v1.y, v1.z); cpsn = v1.w;
             T = mk(v2.x, v2.y, v2.z);
             const unsigned sd = __float_as_uint(v2.w);
-            s = (int)(sd >> 10); depth = (int)(sd & 1023u);
+            s = (int)(sd >> 9); depth = (int)(sd & 511u);
             L = mk(v3.x, v3.y, v3.z);
             acc = mk(v4.x, v4.y, v4.z); ql = __float_as_uint(v4.w);
         }
@@ -182,7 +182,7 @@ __global__ void __launch_bounds__(128) wf_shade_kernel(RtmPassParams p, float4* 
                     if (BVH) {
                         // the big-sphere list is tested here, where all lanes are active
                         if (N > 0) {
-                            const unsigned key = trace_pairs_f32<N>(sh_mask, __float_as_int(al.w), o, d, p.key_mask);
+                            const unsigned key = trace_pairs_f32<N>(hot, sh_mask, bvh_big_slot(__float_as_int(al.w)), o, d, p.key_mask);
                             if (key < RTM_KEY_INF) {
                                 ray_t = __uint_as_float(key & ~7u) + RTM_T_EPS;
                                 ray_hit = sh_big.id[key & 7u];
@@ -222,7 +222,7 @@ __global__ void __launch_bounds__(128) wf_shade_kernel(RtmPassParams p, float4* 
         if (have) {
             wv.a0[slot] = make_float4(o.x, o.y, o.z, __int_as_float(id));
             wv.a1[slot] = make_float4(w.x, w.y, w.z, cpsn);
-            wv.a2[slot] = make_float4(T.x, T.y, T.z, __uint_as_float(((unsigned)s << 10) | (unsigned)depth));
+            wv.a2[slot] = make_float4(T.x, T.y, T.z, __uint_as_float(((unsigned)s << 9) | (unsigned)depth));
             wv.a4[slot] = make_float4(acc.x, acc.y, acc.z, __uint_as_float(ql));
             if (want_ray) {
                 wv.ray[slot] = make_float4(d.x, d.y, d.z, __uint_as_float(eps_bits));
@@ -257,11 +257,12 @@ __global__ void __launch_bounds__(128) wf_shade_kernel(RtmPassParams p, float4* 
 
 // ---- extend, brute force: one thread per queued ray --------------------------------------
 template <int N>
-__global__ void __launch_bounds__(128) wf_extend_brute_kernel(RtmWaveDev wv, int wave, int n_rt, unsigned key_mask,
-                                                              RtmCounters* __restrict__ counters) {
+__global__ void __launch_bounds__(128) wf_extend_brute_kernel(const __grid_constant__ RtmHotScene hot, RtmWaveDev wv, int wave, int n_rt,
+                                                              unsigned key_mask, RtmCounters* __restrict__ counters) {
     __shared__ SelfMask sh_mask;
+    __shared__ SharedScene sh;
     init_selfmask(sh_mask);
-    __syncthreads();
+    load_shared_scene(sh, hot.full, (N > 0) ? N : n_rt);
     const int parity = wave & 1;
     const unsigned i = blockIdx.x * blockDim.x + threadIdx.x;
     const unsigned count = wv.ctrl[parity];
@@ -273,7 +274,7 @@ __global__ void __launch_bounds__(128) wf_extend_brute_kernel(RtmWaveDev wv, int
     const int slot = wv.queue[parity][i];
     const float4 v0 = wv.a0[slot], rv = wv.ray[slot];
     float t;
-    const int id2 = trace_f32<N>(sh_mask, n_rt, __float_as_int(v0.w), mk(v0.x, v0.y, v0.z), mk(rv.x, rv.y, rv.z), t, key_mask);
+    const int id2 = trace_f32<N>(hot, sh, sh_mask, n_rt, __float_as_int(v0.w), mk(v0.x, v0.y, v0.z), mk(rv.x, rv.y, rv.z), t, key_mask);
     wv.hit[slot] = make_float2(t, __int_as_float(id2));
 }
 
@@ -330,7 +331,7 @@ __global__ void __launch_bounds__(128, 6) wf_extend_bvh_kernel(RtmBvhDev bvh, Rt
             bvh_inner_step(bvh, r, stack);
             ++n_nodes;
         }
-        if (active && r.node < 0) bvh_leaf_step(bvh, oid, o, d, r, stack, n_tests);
+        if (active && r.node < 0) bvh_leaf_step_ids(bvh, oid, o, d, r, stack, n_tests);
         if (active && r.node == RTM_BVH_NONE_DEV) {
             wv.hit[slot] = make_float2(r.best + RTM_T_EPS, __int_as_float(r.hit));
             active = false;

@@ -125,6 +125,8 @@ struct GpuCtx {
     RtmBvhDev bvh{};
     RtmMatDev mat{};
     float* d_rgb = nullptr;     // float[H][W][3] staging for renderer_render's rgb_out
+    RtmSceneF32Host* d_f32 = nullptr;   // this handle's device copy of the FP32 per-sphere block (no process-global scene)
+    RtmHotScene hot{};                  // kernel-parameter part of it (hot.full = d_f32)
     float4* peer_stage = nullptr;   // exported gather buffer: G partial framebuffers written by peer GPUs
     void* peer_opened = nullptr;    // a peer's gather buffer opened through CUDA IPC
     int32_t s_begin = 0, s_end = 0;
@@ -144,6 +146,7 @@ struct rtm_renderer {
     int32_t last_launches = 0;
     bool hits_valid = false;
     bool retry = false;         // roulette-rounds megakernel: the surfaces the camera sees kill most paths at once
+    bool clamp = true;          // the per-sample clamp of Renderer.cpp:240-241 can engage (false: proven impossible for this scene)
     bool nee = false;           // next-event-estimation kernels (estimator NEE and at least one listed light)
     bool acne = false;          // the FP32 path models the reference's self-intersection on small spheres
     bool use_bvh = false;       // closest hit through the hierarchy (bvh.h) instead of the O(N) loop
@@ -168,6 +171,7 @@ void free_ctx(GpuCtx& c) {
     if (c.d_wave) cudaFree(c.d_wave);
     if (c.h_live) cudaFreeHost(c.h_live);
     if (c.d_rgb) cudaFree(c.d_rgb);
+    if (c.d_f32) cudaFree(c.d_f32);
     if (c.peer_opened) cudaIpcCloseMemHandle(c.peer_opened);
     if (c.peer_stage) cudaFree(c.peer_stage);
     if (c.ev0) cudaEventDestroy(c.ev0);
@@ -234,7 +238,6 @@ int enqueue_pass(rtm_renderer* r, GpuCtx& c, cudaStream_t st, bool want_hits, in
             int rc = ensure_hits(r, c);
             if (rc) return rc;
         }
-        CU(rtm_upload_scene_f32(r->f32, st));
         CU(cudaEventRecord(c.ek[0], st));
         rtm_launch_primary_f64(c.s64, p, want_hits ? c.hits : nullptr, c.records, c.counters, c.cps0, st);
         CU(cudaEventRecord(c.ek[1], st));
@@ -245,8 +248,8 @@ int enqueue_pass(rtm_renderer* r, GpuCtx& c, cudaStream_t st, bool want_hits, in
             int wave = 0;
             for (;;) {
                 for (int k = 0; k < 32; ++k, ++wave) {
-                    rtm_launch_wf_shade(r->n, r->use_bvh, c.bvh, c.mat, p, c.records, c.counters, c.cps0, c.wv, wave, st);
-                    rtm_launch_wf_extend(r->n, r->use_bvh, c.bvh, c.wv, wave, c.counters, c.sm_count, st);
+                    rtm_launch_wf_shade(c.hot, r->n, r->use_bvh, c.bvh, c.mat, p, c.records, c.counters, c.cps0, c.wv, wave, st);
+                    rtm_launch_wf_extend(c.hot, r->n, r->use_bvh, c.bvh, c.wv, wave, c.counters, c.sm_count, st);
                 }
                 *launches += 64;
                 CU(cudaMemcpyAsync(c.h_live, c.wv.ctrl + 3, sizeof(unsigned), cudaMemcpyDeviceToHost, st));
@@ -254,8 +257,8 @@ int enqueue_pass(rtm_renderer* r, GpuCtx& c, cudaStream_t st, bool want_hits, in
                 if (*c.h_live != (unsigned)wave) break;   // the last wave of the batch queued nothing
             }
             c.waves = wave;
-        } else if (r->use_bvh) rtm_launch_radiance_bvh(c.bvh, c.mat, p, c.records, c.counters, c.sm_count, c.cps0, r->n, r->n_planes, st);
-        else rtm_launch_radiance_mega(r->n, r->n_planes, r->nee, r->retry, p, c.records, c.counters, c.sm_count, c.cps0, st);
+        } else if (r->use_bvh) rtm_launch_radiance_bvh(c.hot, c.bvh, c.mat, p, c.records, c.counters, c.sm_count, c.cps0, r->n, r->n_planes, r->opt.debug_bvh_walk, st);
+        else rtm_launch_radiance_mega(c.hot, r->n, r->n_planes, r->nee, r->retry, r->clamp, p, c.records, c.counters, c.sm_count, c.cps0, st);
         CU(cudaEventRecord(c.ek[2], st));
         rtm_launch_accumulate(p, c.records, c.accum, st);
         CU(cudaEventRecord(c.ek[3], st));
@@ -318,6 +321,7 @@ void renderer_default_options(rtm_options* o) {
     o->max_depth = 0;
     o->seed = 0x5EEDull;
     o->estimator = RTM_ESTIMATOR_REFERENCE;
+    // debug_* stay 0: the product defaults
 }
 
 void renderer_destroy(rtm_renderer* r) {
@@ -343,6 +347,9 @@ int renderer_create(const rtm_scene_desc* sc, const rtm_options* opt_in, rtm_ren
                             !sc->plane_emission)))
         return fail(RTM_E_INVALID, "scene arrays missing for %d planes", m);
     if (opt.n_gpus < 1) opt.n_gpus = 1;
+    // COMPAT_HEAD is deterministic and one cheap kernel: all samples run on `device`, so that image64 (and the
+    // bytes derived from it) stay the reference's, whatever n_gpus says
+    if (opt.compat == RTM_COMPAT_HEAD) opt.n_gpus = 1;
     if (opt.max_depth <= 0) opt.max_depth = 256;
     if (opt.compat != RTM_COMPAT_HEAD && opt.compat != RTM_COMPAT_ABC) return fail(RTM_E_INVALID, "bad compat %d", opt.compat);
     if (opt.precision != RTM_PRECISION_F32 && opt.precision != RTM_PRECISION_F64)
@@ -371,6 +378,11 @@ int renderer_create(const rtm_scene_desc* sc, const rtm_options* opt_in, rtm_ren
     if (f32_path && !use_bvh && sc->n_spheres + m > RTM_MAX_CONST_SPHERES)
         return fail(RTM_E_UNSUPPORTED, "FP32 brute-force path holds at most %d objects (use RTM_ACCEL_BVH / AUTO)",
                     RTM_MAX_CONST_SPHERES);
+    if (opt.debug_retry < 0 || opt.debug_retry > 2 || opt.debug_bvh_walk < 0 || opt.debug_bvh_walk > 1 || opt.debug_bvh_leaf_max < 0 ||
+        opt.debug_bvh_leaf_max > 8 || !(opt.debug_bvh_ctrav >= 0.f) || opt.debug_clamp < 0 || opt.debug_clamp > 1)
+        return fail(RTM_E_INVALID, "bad debug_* option");
+    if (opt.variant == RTM_VARIANT_WAVEFRONT && sc->samples >= (1 << 22))
+        return fail(RTM_E_INVALID, "samples %d exceeds 2^22-1 (wavefront variant)", sc->samples);
     if (opt.estimator != RTM_ESTIMATOR_REFERENCE && opt.estimator != RTM_ESTIMATOR_NEE)
         return fail(RTM_E_INVALID, "bad estimator %d", opt.estimator);
     if (opt.estimator == RTM_ESTIMATOR_NEE && (!f32_path || use_bvh || opt.variant != RTM_VARIANT_MEGA))
@@ -571,7 +583,7 @@ int renderer_create(const rtm_scene_desc* sc, const rtm_options* opt_in, rtm_ren
             ksum += wgt * kd[i];
         }
         r->retry = wsum > 0.0 && ksum / wsum < 0.6;
-        if (const char* e = getenv("RTM_MEGA_RETRY_FORCE")) r->retry = (e[0] == '1');   // test hook: both kernels, same scene
+        if (opt.debug_retry) r->retry = (opt.debug_retry == 2);   // test hook: both kernels, same scene
     }
 
     if (f32_path && (m & 1)) reinterpret_cast<float*>(&r->f32.plane_pairs[m >> 1])[2 * 3 + 1] = -1.0f;   // dummy lane: n = 0, d0 = -1
@@ -593,14 +605,48 @@ int renderer_create(const rtm_scene_desc* sc, const rtm_options* opt_in, rtm_ren
             if (kd[i] > 0.0 && 9e-3 * D * D / (double)sc->radius[i] > 1e-2) r->acne = true;
     }
 
+    if (f32_path) {
+        // Per-sample clamp (Renderer.cpp:240-241): clamp(L / spp, 0, 1).  L >= 0 when every emission is >= 0.  colorKD has
+        // components <= 1 (+1 ulp), so a path's throughput never exceeds ~1 and L <= (number of emitters a path can
+        // collect) x (largest emission): 1 when every emitter has kd == 0 (the path ends on it), else max_depth.
+        // When that bound / spp stays below 1 the clamp is the identity and the megakernel drops it (and with it the
+        // per-sample accumulator: one running sum per sub-pixel).
+        double e_max = 0.0;
+        bool nonneg = true, lights_end = true;
+        for (size_t i = 0; i < nm; ++i) {
+            bool emits = false;
+            for (int k = 0; k < 3; ++k) {
+                const double e = em[3 * i + k];
+                if (!(e >= 0.0) || !std::isfinite(e)) nonneg = false;
+                if (e > 0.0) emits = true;
+                e_max = std::max(e_max, e);
+            }
+            if (emits && kd[i] > 0.0) lights_end = false;
+        }
+        const double bound = e_max * (lights_end ? 1.0 : (double)opt.max_depth) * 1.001;
+        r->clamp = opt.debug_clamp == 1 || !nonneg || !(bound / ((double)r->ss * r->ss * r->S) <= 1.0);
+    }
+
     if (use_bvh) {
-        if (!rtm_bvh_build(n, sc->position, sc->radius, r->refd, r->bvh_host)) {
+        if (!rtm_bvh_build(n, sc->position, sc->radius, r->refd, r->bvh_host, (double)opt.debug_bvh_ctrav, opt.debug_bvh_leaf_max)) {
             const int d = r->bvh_host.depth;
             delete r;
             return fail(RTM_E_UNSUPPORTED, "sphere hierarchy too deep (%d levels)", d);
         }
-        if (f32_path)
+        if (f32_path && r->bvh_host.n_big_overflow > 0) {
+            const int k = r->bvh_host.n_big_overflow;
+            delete r;
+            return fail(RTM_E_UNSUPPORTED, "%d sphere(s) of radius >= %g beyond the %d the FP32 hierarchy path tests for every ray: "
+                        "use RTM_ACCEL_BRUTE or RTM_PRECISION_F64", k, RTM_BVH_BIG_RADIUS, RTM_BVH_MAX_BIG);
+        }
+        if (f32_path) {
+            // alb.w of a sphere: its slot in the big list (0..7) or 8 + its leaf slot (kernels_common.cuh: bvh_big_slot / bvh_leaf_slot)
             for (int j = 0; j < r->bvh_host.n_big; ++j) memcpy(&r->mat_alb[r->bvh_host.big_id[j]].w, &j, 4);
+            for (size_t sl = 0; sl < r->bvh_host.leaf_id.size(); ++sl) {
+                const int32_t code = 8 + (int32_t)sl;
+                memcpy(&r->mat_alb[r->bvh_host.leaf_id[sl]].w, &code, 4);
+            }
+        }
     }
 
     if (f32_path) {
@@ -664,18 +710,13 @@ int renderer_create(const rtm_scene_desc* sc, const rtm_options* opt_in, rtm_ren
                 // one allocation, float4 units: nodes | leaf_geo | geo | emi | alb | leaf_id (int32, padded)
                 const RtmBvhHost& B = r->bvh_host;
                 const size_t n_nodes4 = B.nodes.size(), n_slots = B.leaf_geo.size(), n_mat = r->mat_geo.size();
-                // experimental 4-wide walk of the FP32 hierarchy kernel: opt-in, spheres only
-                RtmBvh4Host W4;
-                const char* wide_env = getenv("RTM_BVH_WIDE");
-                const int wide_mode = (wide_env && (wide_env[0] == '1' || wide_env[0] == '2')) ? wide_env[0] - '0' : 0;
-                if (wide_mode && f32_path && m == 0) rtm_bvh_collapse4(B, W4);
-                const size_t n_wide4 = (W4.root >= 0 && W4.root != RTM_BVH_NONE) ? W4.nodes.size() : 0;
-                const size_t total4 = n_nodes4 + n_slots + 3 * n_mat + (n_slots + 3) / 4 + 1 + n_wide4;
+                const size_t total4 = n_nodes4 + n_slots + 3 * n_mat + (n_slots + 3) / 4 + 1;
                 CU(cudaMalloc(&c.d_bvh, total4 * sizeof(float4)));
                 float4* d = c.d_bvh;
+                cudaError_t put_err = cudaSuccess;
                 auto put = [&](const void* src, size_t count4, size_t bytes) -> float4* {
                     float4* at = d;
-                    if (bytes) cudaMemcpy(at, src, bytes, cudaMemcpyHostToDevice);
+                    if (bytes && put_err == cudaSuccess) put_err = cudaMemcpy(at, src, bytes, cudaMemcpyHostToDevice);
                     d += count4;
                     return at;
                 };
@@ -685,18 +726,24 @@ int renderer_create(const rtm_scene_desc* sc, const rtm_options* opt_in, rtm_ren
                 c.mat.emi = put(r->mat_emi.data(), n_mat, n_mat * sizeof(float4));
                 c.mat.alb = put(r->mat_alb.data(), n_mat, n_mat * sizeof(float4));
                 c.bvh.leaf_id = (const int32_t*)put(B.leaf_id.data(), (n_slots + 3) / 4, n_slots * sizeof(int32_t));
-                CU(cudaGetLastError());
+                CU(put_err);
                 c.bvh.root = B.root;
                 c.bvh.n_big = B.n_big;
                 for (int j = 0; j < 8; ++j) c.bvh.big_id[j] = B.big_id[j];
                 c.bvh.depth = B.depth;
-                c.bvh.nodes4 = n_wide4 ? put(W4.nodes.data(), n_wide4, n_wide4 * sizeof(float4)) : nullptr;
-                c.bvh.root4 = W4.root;
-                c.bvh.depth4 = W4.depth;
-                c.bvh.wide_mode = wide_mode;
                 c.s64.use_bvh = 1;
                 c.s64.bvh = c.bvh;
                 for (int k = 0; k < 3; ++k) c.s64.ref[k] = r->refd[k];
+            }
+            if (f32_path) {
+                CU(cudaMalloc(&c.d_f32, sizeof(RtmSceneF32Host)));
+                CU(cudaMemcpy(c.d_f32, &r->f32, sizeof(RtmSceneF32Host), cudaMemcpyHostToDevice));
+                memcpy(c.hot.pairs, r->f32.pairs, sizeof c.hot.pairs);
+                memcpy(c.hot.plane_pairs, r->f32.plane_pairs, sizeof c.hot.plane_pairs);
+                c.hot.n = r->f32.n;
+                c.hot.n_planes = r->f32.n_planes;
+                c.hot.n_lights = r->f32.n_lights;
+                c.hot.full = c.d_f32;
             }
             if (r->acne) CU(cudaMalloc(&c.cps0, r->n_sub * sizeof(float)));
             if (opt.variant == RTM_VARIANT_WAVEFRONT) {
@@ -840,6 +887,8 @@ int renderer_render(rtm_renderer* r, float* rgb_out, int32_t* hit_out, rtm_stats
         GpuCtx& c = r->gpus[g];
         CU(cudaSetDevice(c.device));
         CU(cudaEventRecord(c.ev0, c.stream));
+        // the host-buffer entry point takes its inputs from host memory on every call: the scene block travels again
+        if (c.d_f32) CU(cudaMemcpyAsync(c.d_f32, &r->f32, sizeof(RtmSceneF32Host), cudaMemcpyHostToDevice, c.stream));
         int rc = enqueue_pass(r, c, c.stream, hit_out != nullptr && g == 0, &launches);
         if (rc) return rc;
     }
@@ -903,7 +952,12 @@ int renderer_read_u8(rtm_renderer* r, unsigned char* out) {
     GpuCtx& c = r->gpus[0];
     CU(cudaSetDevice(c.device));
     if (!c.u8) CU(cudaMalloc(&c.u8, r->n_pix * 3));
-    rtm_launch_to_u8(c.accum, c.u8, r->n_pix, c.stream);
+    if (r->opt.compat == RTM_COMPAT_HEAD) {
+        if (!c.image64) return fail(RTM_E_INVALID, "render first");
+        rtm_launch_to_u8_f64(c.image64, c.u8, r->n_pix, c.stream);   // the reference converts its DOUBLE image
+    } else {
+        rtm_launch_to_u8(c.accum, c.u8, r->n_pix, c.stream);
+    }
     CU(cudaGetLastError());
     CU(cudaMemcpyAsync(out, c.u8, r->n_pix * 3, cudaMemcpyDeviceToHost, c.stream));
     CU(cudaStreamSynchronize(c.stream));
@@ -948,9 +1002,9 @@ int rtm_debug_closest_hit(rtm_renderer* r, int32_t mode, uint32_t n, const doubl
             rtm_launch_closest_hit_f64(c.s64, n, d_org, d_dir, d_hit, d_t, c.stream);
         } else {
             if (r->f32.n != r->n) return fail(RTM_E_UNSUPPORTED, "handle was not created for the FP32 path");
-            CU(rtm_upload_scene_f32(r->f32, c.stream));
-            if (r->use_bvh) rtm_launch_closest_hit_bvh_f32(c.bvh, c.mat, r->n, r->n_planes, r->refd, n, d_org, d_dir, d_oid, d_hit, d_t, c.stream);
-            else rtm_launch_closest_hit_f32(r->n, r->n_planes, r->refd, n, d_org, d_dir, d_oid, d_hit, d_t, c.stream);
+            if (!c.d_f32) return fail(RTM_E_UNSUPPORTED, "handle was not created for the FP32 path");
+            if (r->use_bvh) rtm_launch_closest_hit_bvh_f32(c.hot, c.bvh, c.mat, r->n, r->n_planes, r->refd, n, d_org, d_dir, d_oid, d_hit, d_t, c.stream);
+            else rtm_launch_closest_hit_f32(c.hot, r->n, r->n_planes, r->refd, n, d_org, d_dir, d_oid, d_hit, d_t, c.stream);
         }
         CU(cudaGetLastError());
         CU(cudaStreamSynchronize(c.stream));

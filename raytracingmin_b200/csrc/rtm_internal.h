@@ -26,11 +26,6 @@ struct RtmBvhDev {
     int32_t n_big;            // spheres kept out of the hierarchy, tested for every ray
     int32_t big_id[8];        //   ascending original index
     int32_t depth;            // levels of the tree (a walk holds at most depth + 2 stack entries)
-    // 4-wide form of the same tree (bvh.h: RtmBvh4Host), uploaded only when RTM_BVH_WIDE=1 (experimental)
-    const float4* nodes4;     // 8 float4 per wide node, NULL = not built
-    int32_t root4;
-    int32_t depth4;           // a walk of the wide tree holds at most 3 * depth4 + 1 stack entries
-    int32_t wide_mode;        // RTM_BVH_WIDE: 1 = local-memory stack, 2 = shared-memory stack
 };
 
 // Per-sphere records of the FP32 path in GLOBAL memory (hierarchy path, any N): the
@@ -103,6 +98,17 @@ struct RtmSceneF32Host {
     float lit[RTM_MAX_CONST_SPHERES];   // 1 for listed lights (int bits), else 0
 };
 
+// What the FP32 bounce kernels read through constant-bank operands.  Handed to every launch BY VALUE as a
+// __grid_constant__ kernel parameter, so it is private to the launch (and to the handle that made it): there is
+// no process-global scene, two handles may render concurrently on one device.  `full` is the handle's device
+// copy of the whole per-sphere block; the kernels stage what they need of it into shared memory.
+struct RtmHotScene {
+    RtmPairF32 pairs[RTM_MAX_PAIRS];                  // the first 8 spheres (brute force) or the big list (hierarchy), paired
+    RtmPlanePairF32 plane_pairs[RTM_MAX_PLANES / 2];
+    int32_t n, n_planes, n_lights, pad;
+    const RtmSceneF32Host* full;
+};
+
 // Sub-pixel record written by the exact primary pass and consumed by the FP32
 // bounce kernels: primary hit point (relative to the reference point, rounded
 // to float from the double hit point) and the hit id.  w = id | flip<<30, or
@@ -140,7 +146,7 @@ struct RtmPassParams {
 struct RtmWaveDev {
     float4* a0;        // o.xyz, id
     float4* a1;        // w.xyz (oriented normal), cpsn
-    float4* a2;        // T.xyz, s << 10 | depth
+    float4* a2;        // T.xyz, s << 9 | depth
     float4* a3;        // L.xyz, flags (0 empty, 1 sub-pixel in flight, 2 + ray pending)
     float4* a4;        // acc.xyz, ql
     float4* a5;        // P.xyz, Pid             (constant while the slot holds a sub-pixel)
@@ -163,32 +169,35 @@ void rtm_launch_radiance_f64(const RtmSceneF64& sc, const RtmPassParams& p, floa
 void rtm_launch_closest_hit_f64(const RtmSceneF64& sc, uint32_t n, const double* org, const double* dir,
                                 int32_t* hit, double* t, cudaStream_t st);
 
-cudaError_t rtm_upload_scene_f32(const RtmSceneF32Host& h, cudaStream_t st);
 // cps0: per-sub-pixel c' = |c - P|^2 - r^2 at the primary hit from the FP64 pass, or null when the scene
-// has no sphere small enough for the reference's self-intersection to matter (kernels_radiance.cu: ACNE)
-// nee: the next-event-estimation instantiation (needs c_scene.n_lights > 0)
+// has no sphere small enough for the reference's self-intersection to matter (kernels_common.cuh: ACNE)
+// nee: the next-event-estimation instantiation (needs hot.n_lights > 0)
 // retry: the roulette-rounds instantiation (scenes whose visible surfaces kill most paths at once)
-void rtm_launch_radiance_mega(int32_t n_spheres, int32_t n_planes, bool nee, bool retry, const RtmPassParams& p, float4* records,
-                              RtmCounters* counters, int32_t sm_count, const float* cps0, cudaStream_t st);
-void rtm_launch_radiance_bvh(const RtmBvhDev& bvh, const RtmMatDev& mat, const RtmPassParams& p, float4* records,
+// clamp: evaluate the per-sample clamp of Renderer.cpp:240-241 (false only when the host proved it can never engage)
+void rtm_launch_radiance_mega(const RtmHotScene& hot, int32_t n_spheres, int32_t n_planes, bool nee, bool retry, bool clamp,
+                              const RtmPassParams& p, float4* records, RtmCounters* counters, int32_t sm_count, const float* cps0,
+                              cudaStream_t st);
+// walk: RTM_BVH_WALK_* (rtm_options.debug_bvh_walk), 0 = the product default
+void rtm_launch_radiance_bvh(const RtmHotScene& hot, const RtmBvhDev& bvh, const RtmMatDev& mat, const RtmPassParams& p, float4* records,
                              RtmCounters* counters, int32_t sm_count, const float* cps0, int32_t n_spheres, int32_t n_planes,
-                             cudaStream_t st);
+                             int32_t walk, cudaStream_t st);
 // one wave of the wavefront variant; `wave` counts from 0 (its parity selects the queue)
-void rtm_launch_wf_shade(int32_t n_spheres, bool use_bvh, const RtmBvhDev& bvh, const RtmMatDev& mat, const RtmPassParams& p,
-                         float4* records, RtmCounters* counters, const float* cps0, const RtmWaveDev& wv, int32_t wave,
-                         cudaStream_t st);
-void rtm_launch_wf_extend(int32_t n_spheres, bool use_bvh, const RtmBvhDev& bvh, const RtmWaveDev& wv, int32_t wave,
+void rtm_launch_wf_shade(const RtmHotScene& hot, int32_t n_spheres, bool use_bvh, const RtmBvhDev& bvh, const RtmMatDev& mat,
+                         const RtmPassParams& p, float4* records, RtmCounters* counters, const float* cps0, const RtmWaveDev& wv,
+                         int32_t wave, cudaStream_t st);
+void rtm_launch_wf_extend(const RtmHotScene& hot, int32_t n_spheres, bool use_bvh, const RtmBvhDev& bvh, const RtmWaveDev& wv, int32_t wave,
                           RtmCounters* counters, int32_t sm_count, cudaStream_t st);
 void rtm_launch_accumulate(const RtmPassParams& p, const float4* records, float4* accum, cudaStream_t st);
 void rtm_launch_sum_partials(const float4* partials /*[G][n_pix]*/, float4* out, uint64_t n_pix, int32_t G, cudaStream_t st);
 void rtm_launch_pack_rgb(const float4* accum, float* out /*[n_pix][3]*/, uint64_t n_pix, cudaStream_t st);
 void rtm_launch_to_u8(const float4* accum, unsigned char* out, uint64_t n_pix, cudaStream_t st);
-void rtm_launch_closest_hit_f32(int32_t n_spheres, int32_t n_planes, const double* refd, uint32_t n, const double* org,
+void rtm_launch_to_u8_f64(const double* image64 /*[n_pix][3]*/, unsigned char* out, uint64_t n_pix, cudaStream_t st);
+void rtm_launch_closest_hit_f32(const RtmHotScene& hot, int32_t n_spheres, int32_t n_planes, const double* refd, uint32_t n, const double* org,
                                 const double* dir, const int32_t* origin_id, int32_t* hit, double* t,
                                 cudaStream_t st);
-void rtm_launch_closest_hit_bvh_f32(const RtmBvhDev& bvh, const RtmMatDev& mat, int32_t n_spheres, int32_t n_planes, const double* refd, uint32_t n,
-                                    const double* org, const double* dir, const int32_t* origin_id, int32_t* hit, double* t,
-                                    cudaStream_t st);
+void rtm_launch_closest_hit_bvh_f32(const RtmHotScene& hot, const RtmBvhDev& bvh, const RtmMatDev& mat, int32_t n_spheres, int32_t n_planes,
+                                    const double* refd, uint32_t n, const double* org, const double* dir, const int32_t* origin_id,
+                                    int32_t* hit, double* t, cudaStream_t st);
 void rtm_launch_acne_eps(uint32_t n, const uint32_t* bits, float* out, cudaStream_t st);
 void rtm_launch_philox(uint32_t n, uint32_t c1, uint32_t c2, uint32_t c3, uint32_t k0, uint32_t k1, uint32_t* out,
                        cudaStream_t st);

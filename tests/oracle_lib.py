@@ -171,6 +171,8 @@ def ref_lib(level: str):
         lib.refh_primary_hits.argtypes = [vp, vp, C.c_int]
         lib.refh_render.argtypes = [vp, C.c_uint32, vp, C.POINTER(C.c_uint64), C.POINTER(C.c_uint64), C.c_int]
         lib.refh_to_u8.argtypes = [vp, vp, C.c_size_t]
+        if hasattr(lib, "refh_render_window"):
+            lib.refh_render_window.argtypes = [vp, C.c_uint32] + [C.c_int] * 4 + [vp, C.POINTER(C.c_uint64), C.POINTER(C.c_uint64), C.c_int]
         _refs[level] = lib
     return _refs[level]
 
@@ -215,6 +217,16 @@ class RefScene:
         img = np.empty((self.height, self.width, 3), np.float64)
         rays, samples = C.c_uint64(), C.c_uint64()
         self.lib.refh_render(self.h, seed, img.ctypes.data, C.byref(rays), C.byref(samples), nthreads)
+        return img, rays.value, samples.value
+
+    def render_window(self, seed: int, x0: int, y0: int, w: int, h: int, nthreads: int = 0):
+        """Only the pixels [x0,x0+w) x [y0,y0+h) of the full frame (same camera rays, row generators keyed by the
+        full-frame row)."""
+        img = np.empty((h, w, 3), np.float64)
+        rays, samples = C.c_uint64(), C.c_uint64()
+        rc = self.lib.refh_render_window(self.h, seed, x0, y0, w, h, img.ctypes.data, C.byref(rays), C.byref(samples), nthreads)
+        if rc:
+            raise ValueError(f"refh_render_window: {rc}")
         return img, rays.value, samples.value
 
     def intersect(self, obj: int, org, dir):

@@ -31,7 +31,7 @@ def test_header_symbols_are_exported():
 
 def test_abi_version_and_defaults():
     lib = rtm.load_library()
-    assert lib.renderer_abi_version() == 3
+    assert lib.renderer_abi_version() == 4
     o = api._Options()
     lib.renderer_default_options(C.byref(o))
     assert (o.device, o.n_gpus, o.compat, o.precision, o.variant, o.accel) == (0, 1, api.COMPAT_ABC, api.PRECISION_F32,
@@ -42,7 +42,7 @@ def test_abi_version_and_defaults():
 def test_struct_layout_matches_header():
     """sizeof as the C compiler sees them (LP64): guards the ctypes mirrors."""
     assert C.sizeof(api._SceneDesc) == 16 + 72 + 8 + 32 + 8 + 48
-    assert C.sizeof(api._Options) == 64
+    assert C.sizeof(api._Options) == 80
     assert C.sizeof(api._Stats) == 64
 
 

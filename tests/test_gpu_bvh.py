@@ -185,30 +185,19 @@ def test_bvh_deterministic_and_slices_add_up(synth):
     assert np.allclose(parts, full.image, rtol=2e-6, atol=1e-7)
 
 
-def test_shared_and_local_stack_instantiations_render_the_same_image(synth, tmp_path):
+def test_shared_and_local_stack_instantiations_render_the_same_image(synth):
     """radiance_bvh_kernel<..., SST>: the traversal stack in shared memory (host-selected for trees of depth + 2 <= 24)
-    against the local-memory stack (RTM_BVH_SSTACK_OFF=1, read once per process: rendered in a child process).
-    Same walk, same candidates, same RNG counters: bit-identical image and counters."""
-    import subprocess
-    import sys
+    against the local-memory stack (rtm_options.debug_bvh_walk = 1).  Same walk, same candidates, same RNG counters:
+    bit-identical image and counters."""
     sc = synth.with_dims(64, 36, 8, 2)
     with rtm.Renderer(sc, seed=1) as r:
         here = r.render()
-    out = tmp_path / "local_stack.npz"
-    code = ("import os, sys, numpy as np\n"
-            f"sys.path.insert(0, {ROOT!r})\n"
-            "import raytracingmin_b200 as rtm\n"
-            f"sc = rtm.load_scene(os.path.join({ROOT!r}, 'scenes', 'synth10k.json'), 'abc').with_dims(64, 36, 8, 2)\n"
-            "with rtm.Renderer(sc, seed=1) as r:\n"
-            "    res = r.render()\n"
-            f"np.savez({str(out)!r}, image=res.image, rays=res.stats.rays, tests=res.stats.sphere_tests, nodes=res.stats.bvh_nodes)\n")
-    env = dict(os.environ, RTM_BVH_SSTACK_OFF="1")
-    subprocess.run([sys.executable, "-c", code], check=True, env=env, timeout=300)
-    there = np.load(out)
-    assert np.array_equal(there["image"], here.image)
-    assert int(there["rays"]) == here.stats.rays
-    assert int(there["tests"]) == here.stats.sphere_tests
-    assert int(there["nodes"]) == here.stats.bvh_nodes
+    with rtm.Renderer(sc, seed=1, debug_bvh_walk=1) as r:
+        there = r.render()
+    assert np.array_equal(there.image, here.image)
+    assert there.stats.rays == here.stats.rays
+    assert there.stats.sphere_tests == here.stats.sphere_tests
+    assert there.stats.bvh_nodes == here.stats.bvh_nodes
 
 
 # ---------------- wavefront variant (same estimator, state in global memory) ----------------

@@ -23,7 +23,7 @@ pytestmark = pytest.mark.gpu
 def test_library_is_loaded_and_device_present(gpu_lib):
     import torch
     assert torch.cuda.is_available()
-    assert gpu_lib.renderer_abi_version() == 3
+    assert gpu_lib.renderer_abi_version() == 4
 
 
 def test_philox_device_matches_numpy():
@@ -363,18 +363,37 @@ def test_c2_radiance_rmse_vs_reference_objects_band():
 
 
 @pytest.mark.parametrize("name", ["simple2", "cornellBox", "settingData"])
-def test_roulette_rounds_kernel_renders_the_same_image(scene_path, name, monkeypatch):
+def test_roulette_rounds_kernel_renders_the_same_image(scene_path, name):
     """The megakernel instantiation with roulette rounds (picked for scenes whose visible surfaces kill most
-    paths) and the plain one: same draws per (sub-pixel, sample, depth), same image bit for bit, same ray count."""
+    paths) and the plain one (rtm_options.debug_retry 2 / 1): same draws per (sub-pixel, sample, depth), same image
+    bit for bit, same ray count."""
     sc = rtm.load_scene(scene_path(name), "abc").with_dims(96, 54, 32, 2)
     out = {}
-    for force in ("0", "1"):
-        monkeypatch.setenv("RTM_MEGA_RETRY_FORCE", force)
-        with rtm.Renderer(sc, seed=5) as r:
+    for force in (1, 2):
+        with rtm.Renderer(sc, seed=5, debug_retry=force) as r:
             res = r.render()
         out[force] = (res.image.copy(), res.stats.rays, res.stats.rays_traced)
-    assert np.array_equal(out["0"][0], out["1"][0])
-    assert out["0"][1:] == out["1"][1:]
+    assert np.array_equal(out[1][0], out[2][0])
+    assert out[1][1:] == out[2][1:]
+
+
+@pytest.mark.parametrize("name", ["cornellBox", "simple1"])
+def test_clamp_free_kernel_matches_the_clamping_one(scene_path, name):
+    """When the host can prove that the per-sample clamp of src/Renderer.cpp:240-241 never engages, the megakernel keeps
+    one running sum per sub-pixel instead of clamping and adding every sample (rtm_options.debug_clamp = 1 forces the
+    clamping instantiation): same paths (equal ray counts), images equal up to FP32 summation order."""
+    sc = rtm.load_scene(scene_path(name), "abc").with_dims(96, 54, 16, 2)
+    with rtm.Renderer(sc, seed=11) as r:
+        a = r.render()
+    with rtm.Renderer(sc, seed=11, debug_clamp=1) as r:
+        b = r.render()
+    assert a.stats.rays == b.stats.rays and a.stats.rays_traced == b.stats.rays_traced
+    assert np.allclose(a.image, b.image, rtol=2e-5, atol=1e-6)
+    # a scene whose emission can exceed spp must keep the clamp: 2 spp, emission 5 -> per-sample values clip at 1
+    hot = rtm.load_scene(scene_path("cornellBox"), "abc").with_dims(48, 26, 2, 1)
+    with rtm.Renderer(hot, seed=1) as r:
+        img = r.render().image
+    assert img.max() <= 2.0 + 1e-6
 
 
 def test_single_process_multi_gpu_mode(scene_path):
