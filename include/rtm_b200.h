@@ -206,6 +206,12 @@ int renderer_peer_export(rtm_renderer* r, int32_t n_slots, void* handle64, void*
 int renderer_peer_open(rtm_renderer* r, const void* handle64, void** device_ptr);
 int renderer_sum_partials(rtm_renderer* r, const void* partials, int32_t n_slots, void* out_float4, void* stream);
 
+/* The accumulation buffer as renderer_render returns it — float[H][W][3] in HOST memory — for callers that drive the
+ * device-resident entry points themselves (one process per GPU: render_async on every rank, a sum-reduce of the partial
+ * framebuffers into rank 0's buffer, then this call on rank 0).  The repack kernel and the copy are enqueued on `stream`
+ * (a cudaStream_t, the one the reduce ran on; NULL = the handle's own stream), which is synchronised before returning. */
+int renderer_read_rgb(rtm_renderer* r, float* rgb_out, void* stream);
+
 /* COMPAT_HEAD only: the double image double[H][W][3], bit-exact against the reference. */
 int renderer_read_image_f64(rtm_renderer* r, double* image_out);
 

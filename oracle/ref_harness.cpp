@@ -15,6 +15,7 @@
 // Built by oracle/Makefile into oracle/_ref/libref_{head,abc}.so.
 #include "Renderer.h"
 #include "SettingData.h"
+#include "stb_image_write.h"   // declarations only: the implementation is compiled into the reference's Renderer.o (src/Renderer.cpp:5-6)
 
 #include <cstdint>
 #include <cstring>
@@ -292,6 +293,15 @@ int refh_render_window(void* h, uint32_t seed, int x0, int y0, int w, int hgt, d
     if (rays_out) *rays_out = rays;
     if (samples_out) *samples_out = samples;
     return 0;
+}
+
+// The reference's file output, src/Renderer.cpp:256-257, through the stb object code the reference itself compiled:
+// <prefix>.jpg (quality 60) and <prefix>.bmp from a u8 RGB buffer.
+int refh_stb_write(const char* prefix, const unsigned char* rgb, int w, int h, int quality) {
+    const std::string p(prefix);
+    const int a = stbi_write_jpg((p + ".jpg").c_str(), w, h, 3, rgb, quality);
+    const int b = stbi_write_bmp((p + ".bmp").c_str(), w, h, 3, rgb);
+    return (a && b) ? 0 : -1;
 }
 
 // 8-bit conversion exactly as src/Renderer.cpp:251-254.

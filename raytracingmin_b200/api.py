@@ -91,7 +91,7 @@ class RenderResult:
 EXPORTS = [
     "renderer_abi_version", "renderer_default_options", "renderer_create", "renderer_render",
     "renderer_render_async", "renderer_read_stats", "renderer_read_kernel_ms", "renderer_device_accum", "renderer_device_hits",
-    "renderer_set_accum_buffer", "renderer_peer_export", "renderer_peer_open", "renderer_sum_partials", "renderer_read_image_f64", "renderer_read_u8", "renderer_destroy",
+    "renderer_set_accum_buffer", "renderer_peer_export", "renderer_peer_open", "renderer_sum_partials", "renderer_read_rgb", "renderer_read_image_f64", "renderer_read_u8", "renderer_destroy",
     "renderer_last_error", "rtm_debug_philox", "rtm_debug_closest_hit", "rtm_debug_fp32_peak", "rtm_debug_bvh", "rtm_debug_bvh4", "rtm_debug_acne_eps",
 ]
 
@@ -130,6 +130,7 @@ def load_library():
     lib.renderer_peer_export.argtypes = [vp, C.c_int32, vp, P(vp)]
     lib.renderer_peer_open.argtypes = [vp, vp, P(vp)]
     lib.renderer_sum_partials.argtypes = [vp, vp, C.c_int32, vp, vp]
+    lib.renderer_read_rgb.argtypes = [vp, vp, vp]
     lib.renderer_read_image_f64.argtypes = [vp, vp]
     lib.renderer_read_u8.argtypes = [vp, vp]
     lib.renderer_destroy.argtypes = [vp]
@@ -252,6 +253,15 @@ class Renderer:
     def sum_partials(self, partials_ptr: int, n_slots: int, out_ptr: int, stream: int = 0) -> None:
         _check(self._lib, self._lib.renderer_sum_partials(self._h, C.c_void_p(partials_ptr), n_slots, C.c_void_p(out_ptr),
                                                           C.c_void_p(stream)))
+
+    def read_rgb(self, out: Optional[np.ndarray] = None, stream: int = 0) -> np.ndarray:
+        """The accumulation buffer as float32 [H][W][3] in host memory (renderer_read_rgb)."""
+        sc = self.scene
+        if out is None:
+            out = np.empty((sc.height, sc.width, 3), np.float32)
+        assert out.dtype == np.float32 and out.shape == (sc.height, sc.width, 3) and out.flags.c_contiguous
+        _check(self._lib, self._lib.renderer_read_rgb(self._h, out.ctypes.data, C.c_void_p(stream)))
+        return out
 
     def read_image_f64(self) -> np.ndarray:
         sc = self.scene

@@ -937,6 +937,19 @@ int renderer_render(rtm_renderer* r, float* rgb_out, int32_t* hit_out, rtm_stats
     return RTM_OK;
 }
 
+int renderer_read_rgb(rtm_renderer* r, float* rgb_out, void* stream) {
+    if (!r || !rgb_out) return fail(RTM_E_INVALID, "null argument");
+    GpuCtx& c = r->gpus[0];
+    CU(cudaSetDevice(c.device));
+    cudaStream_t st = stream ? (cudaStream_t)stream : c.stream;
+    if (!c.d_rgb) CU(cudaMalloc(&c.d_rgb, r->n_pix * 3 * sizeof(float)));
+    rtm_launch_pack_rgb(c.accum, c.d_rgb, r->n_pix, st);
+    CU(cudaGetLastError());
+    CU(cudaMemcpyAsync(rgb_out, c.d_rgb, r->n_pix * 3 * sizeof(float), cudaMemcpyDeviceToHost, st));
+    CU(cudaStreamSynchronize(st));
+    return RTM_OK;
+}
+
 int renderer_read_image_f64(rtm_renderer* r, double* out) {
     if (!r || !out) return fail(RTM_E_INVALID, "null argument");
     if (r->opt.compat != RTM_COMPAT_HEAD) return fail(RTM_E_UNSUPPORTED, "the double image exists in COMPAT_HEAD only");

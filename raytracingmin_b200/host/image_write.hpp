@@ -1,10 +1,16 @@
 // image_write.hpp — BMP and baseline-JPEG writers for the host front end.
-// The reference writes its result through stb_image_write (src/Renderer.cpp:256-257:
-// stbi_write_jpg(..., quality 60) and stbi_write_bmp).  stb is a third-party tree that
-// is not part of this repository, so the front end carries its own small encoders that
-// produce the same kinds of file: a 24-bit uncompressed BMP and a baseline sequential
-// JPEG (ITU-T T.81: 8x8 FDCT, Annex K quantisation tables scaled by the IJG quality
-// rule, Annex K Huffman tables, YCbCr 4:4:4).  Input is u8 RGB, row-major, top row first.
+// The reference writes its result through stb_image_write v1.15 (src/Renderer.cpp:256-257:
+// stbi_write_jpg(..., quality 60) and stbi_write_bmp; stb/stb_image_write.h:491-498, 1440-1560).  stb is a
+// third-party tree that is not part of this repository, so the front end carries its own encoders — written to make
+// the SAME FILES, byte for byte, as that stb version does for 3-component input (tests/test_host_frontend.py compares
+// them with the files the reference's own stb object writes):
+//   BMP   24 bpp, bottom-up, rows padded to 4 bytes, biSizeImage and the resolution fields left 0 as stb leaves them;
+//   JPEG  baseline sequential (ITU-T T.81), Annex K tables scaled by the IJG quality rule, ONE DQT and ONE DHT segment
+//         holding all tables, 2x2 chroma subsampling (16x16 MCUs, box filter) at quality <= 90 and 4:4:4 above,
+//         the Arai-Agui-Nakajima float DCT with the scale factors folded into the quantiser, round-half-away-from-zero
+//         by truncation of v +- 0.5, edge replication for partial blocks, one-padding of the last byte.
+// Single-precision operation order is part of the contract (build with -ffp-contract=off, as the Makefile does).
+// Input is u8 RGB, row-major, top row first.
 #pragma once
 #include <cmath>
 #include <cstdint>
@@ -32,7 +38,7 @@ inline std::vector<uint8_t> encode_bmp(const uint8_t* rgb, int w, int h) {
     out[0] = 'B'; out[1] = 'M';
     put32(2, off + data); put32(10, off);
     put32(14, 40); put32(18, (uint32_t)w); put32(22, (uint32_t)h);
-    put16(26, 1); put16(28, 24); put32(34, data);
+    put16(26, 1); put16(28, 24);   // biSizeImage (offset 34) stays 0: allowed for BI_RGB, and what stb writes
     for (int y = 0; y < h; ++y) {
         uint8_t* row = out.data() + off + (size_t)(h - 1 - y) * stride;
         const uint8_t* src = rgb + (size_t)y * w * 3;
@@ -115,32 +121,71 @@ struct BitWriter {
     void flush() { if (n > 0) put(0x7F, 8 - n); }  // pad with ones
 };
 
+// One 8-point Arai-Agui-Nakajima forward DCT (scaled: the missing factors live in the quantiser), in place on
+// d[0], d[st], ..., d[7 st].  Five multiplies; the operation order below is what fixes the bytes.
+inline void aan_dct8(float* d, int st) {
+    const float a0 = d[0], a1 = d[st], a2 = d[2 * st], a3 = d[3 * st], a4 = d[4 * st], a5 = d[5 * st], a6 = d[6 * st], a7 = d[7 * st];
+    const float s07 = a0 + a7, m07 = a0 - a7, s16 = a1 + a6, m16 = a1 - a6, s25 = a2 + a5, m25 = a2 - a5, s34 = a3 + a4, m34 = a3 - a4;
+    // even half
+    const float e0 = s07 + s34, e3 = s07 - s34, e1 = s16 + s25, e2 = s16 - s25;
+    d[0] = e0 + e1;
+    d[4 * st] = e0 - e1;
+    const float r = (e2 + e3) * 0.707106781f;
+    d[2 * st] = e3 + r;
+    d[6 * st] = e3 - r;
+    // odd half (rotator without extra negations)
+    const float o0 = m34 + m25, o1 = m25 + m16, o2 = m16 + m07;
+    const float z5 = (o0 - o2) * 0.382683433f;
+    const float z2 = o0 * 0.541196100f + z5;
+    const float z4 = o2 * 1.306562965f + z5;
+    const float z3 = o1 * 0.707106781f;
+    const float p = m07 + z3, m = m07 - z3;
+    d[5 * st] = m + z2;
+    d[3 * st] = m - z2;
+    d[st] = p + z4;
+    d[7 * st] = p - z4;
+}
+
 }  // namespace detail
 
 inline std::vector<uint8_t> encode_jpeg(const uint8_t* rgb, int w, int h, int quality) {
     using namespace detail;
+    quality = quality ? quality : 90;
+    const bool subsample = quality <= 90;
     quality = quality < 1 ? 1 : (quality > 100 ? 100 : quality);
     const int scale = quality < 50 ? 5000 / quality : 200 - quality * 2;  // IJG quality scaling
-    uint8_t q[2][64];
-    for (int i = 0; i < 64; ++i) {
+    uint8_t qz[2][64];        // quantisation tables in ZIGZAG order (as the DQT segment stores them)
+    for (int z = 0; z < 64; ++z) {
+        const int i = kZigzag[z];
         const int l = (kQLuma[i] * scale + 50) / 100, c = (kQChroma[i] * scale + 50) / 100;
-        q[0][i] = (uint8_t)(l < 1 ? 1 : (l > 255 ? 255 : l));
-        q[1][i] = (uint8_t)(c < 1 ? 1 : (c > 255 ? 255 : c));
+        qz[0][z] = (uint8_t)(l < 1 ? 1 : (l > 255 ? 255 : l));
+        qz[1][z] = (uint8_t)(c < 1 ? 1 : (c > 255 ? 255 : c));
     }
+    // natural index -> zigzag position
+    uint8_t zpos[64];
+    for (int z = 0; z < 64; ++z) zpos[kZigzag[z]] = (uint8_t)z;
+    // descale factors of the AAN DCT folded into the quantiser: 1 / (q * s[row] * s[col])
+    static const float aan[8] = {1.0f * 2.828427125f, 1.387039845f * 2.828427125f, 1.306562965f * 2.828427125f, 1.175875602f * 2.828427125f,
+                                 1.0f * 2.828427125f, 0.785694958f * 2.828427125f, 0.541196100f * 2.828427125f, 0.275899379f * 2.828427125f};
+    float fq[2][64];
+    for (int row = 0, k = 0; row < 8; ++row)
+        for (int col = 0; col < 8; ++col, ++k)
+            for (int t = 0; t < 2; ++t) fq[t][k] = 1 / (qz[t][zpos[k]] * aan[row] * aan[col]);
+
     std::vector<uint8_t> out;
+    out.reserve((size_t)w * h / 4 + 1024);
     auto b8 = [&](int v) { out.push_back((uint8_t)v); };
     auto b16 = [&](int v) { b8(v >> 8); b8(v & 255); };
     b16(0xFFD8);                                                        // SOI
     b16(0xFFE0); b16(16); for (char ch : {'J', 'F', 'I', 'F', '\0'}) b8(ch);
     b16(0x0101); b8(0); b16(1); b16(1); b8(0); b8(0);                  // JFIF 1.01, aspect 1:1
-    for (int t = 0; t < 2; ++t) {                                       // DQT (zigzag order)
-        b16(0xFFDB); b16(67); b8(t);
-        for (int i = 0; i < 64; ++i) b8(q[t][kZigzag[i]]);
-    }
-    b16(0xFFC0); b16(17); b8(8); b16(h); b16(w); b8(3);                // SOF0, 3 components 1x1
-    b8(1); b8(0x11); b8(0); b8(2); b8(0x11); b8(1); b8(3); b8(0x11); b8(1);
+    b16(0xFFDB); b16(2 + 65 + 65);                                      // ONE DQT segment, both tables
+    for (int t = 0; t < 2; ++t) { b8(t); for (int z = 0; z < 64; ++z) b8(qz[t][z]); }
+    b16(0xFFC0); b16(17); b8(8); b16(h); b16(w); b8(3);                // SOF0
+    b8(1); b8(subsample ? 0x22 : 0x11); b8(0); b8(2); b8(0x11); b8(1); b8(3); b8(0x11); b8(1);
+    b16(0xFFC4); b16(2 + (17 + 12) + (17 + 162) + (17 + 12) + (17 + 162));   // ONE DHT segment, four tables
     auto dht = [&](int cls_id, const uint8_t* bits, const uint8_t* vals, int nvals) {
-        b16(0xFFC4); b16(19 + nvals); b8(cls_id);
+        b8(cls_id);
         for (int i = 0; i < 16; ++i) b8(bits[i]);
         for (int i = 0; i < nvals; ++i) b8(vals[i]);
     };
@@ -152,65 +197,76 @@ inline std::vector<uint8_t> encode_jpeg(const uint8_t* rgb, int w, int h, int qu
 
     const HuffTable dcL(kDcLumaBits, kDcVals), acL(kAcLumaBits, kAcLumaVals);
     const HuffTable dcC(kDcChromaBits, kDcVals), acC(kAcChromaBits, kAcChromaVals);
-    float cosT[8][8];
-    for (int u = 0; u < 8; ++u)
-        for (int x = 0; x < 8; ++x)
-            cosT[u][x] = (float)(std::cos((2 * x + 1) * u * 3.14159265358979323846 / 16.0) * (u == 0 ? std::sqrt(0.125) : 0.5));
     BitWriter bw(out);
-    int pred[3] = {0, 0, 0};
-    float blk[3][64], tmp[64], coef[64];
-    for (int by = 0; by < h; by += 8)
-        for (int bx = 0; bx < w; bx += 8) {
-            for (int y = 0; y < 8; ++y)
-                for (int x = 0; x < 8; ++x) {
-                    const int sy = (by + y < h) ? by + y : h - 1, sx = (bx + x < w) ? bx + x : w - 1;  // edge replicate
+
+    // one 8x8 data unit inside `du` (row stride `st`): DCT, quantise, entropy-code; returns the new DC predictor
+    auto code_unit = [&](float* du, int st, const float* fqt, int pred, const HuffTable& dc, const HuffTable& ac) -> int {
+        for (int y = 0; y < 8; ++y) aan_dct8(du + y * st, 1);          // rows
+        for (int x = 0; x < 8; ++x) aan_dct8(du + x, st);              // columns
+        int zz[64];
+        for (int y = 0, j = 0; y < 8; ++y)
+            for (int x = 0; x < 8; ++x, ++j) {
+                const float v = du[y * st + x] * fqt[j];
+                zz[zpos[j]] = (int)(v < 0 ? v - 0.5f : v + 0.5f);
+            }
+        auto magnitude = [](int v, int& nbits, uint32_t& bits) {
+            int a = v < 0 ? -v : v;
+            nbits = 0;
+            while (a) { ++nbits; a >>= 1; }
+            bits = (uint32_t)(v < 0 ? v + (1 << nbits) - 1 : v);
+        };
+        int nb; uint32_t bits;
+        magnitude(zz[0] - pred, nb, bits);
+        bw.put(dc.code[nb], dc.len[nb]);
+        if (nb) bw.put(bits, nb);
+        int run = 0, last = 63;
+        while (last > 0 && zz[last] == 0) --last;
+        for (int i = 1; i <= last; ++i) {
+            if (zz[i] == 0) { ++run; continue; }
+            while (run >= 16) { bw.put(ac.code[0xF0], ac.len[0xF0]); run -= 16; }  // ZRL
+            magnitude(zz[i], nb, bits);
+            bw.put(ac.code[(run << 4) | nb], ac.len[(run << 4) | nb]);
+            bw.put(bits, nb);
+            run = 0;
+        }
+        if (last < 63) bw.put(ac.code[0x00], ac.len[0x00]);                        // EOB
+        return zz[0];
+    };
+
+    int pY = 0, pU = 0, pV = 0;
+    const int B = subsample ? 16 : 8;                                   // MCU edge in pixels
+    std::vector<float> Yb(B * B), Ub(B * B), Vb(B * B);
+    for (int by = 0; by < h; by += B)
+        for (int bx = 0; bx < w; bx += B) {
+            for (int y = 0, pos = 0; y < B; ++y) {
+                const int sy = (by + y < h) ? by + y : h - 1;          // edge replicate
+                for (int x = 0; x < B; ++x, ++pos) {
+                    const int sx = (bx + x < w) ? bx + x : w - 1;
                     const uint8_t* p = rgb + ((size_t)sy * w + sx) * 3;
                     const float r = p[0], g = p[1], b = p[2];
-                    blk[0][y * 8 + x] = 0.299f * r + 0.587f * g + 0.114f * b - 128.f;
-                    blk[1][y * 8 + x] = -0.168736f * r - 0.331264f * g + 0.5f * b;
-                    blk[2][y * 8 + x] = 0.5f * r - 0.418688f * g - 0.081312f * b;
+                    Yb[pos] = +0.29900f * r + 0.58700f * g + 0.11400f * b - 128;
+                    Ub[pos] = -0.16874f * r - 0.33126f * g + 0.50000f * b;
+                    Vb[pos] = +0.50000f * r - 0.41869f * g - 0.08131f * b;
                 }
-            for (int c = 0; c < 3; ++c) {
-                for (int y = 0; y < 8; ++y)      // rows
-                    for (int u = 0; u < 8; ++u) {
-                        float s = 0;
-                        for (int x = 0; x < 8; ++x) s += blk[c][y * 8 + x] * cosT[u][x];
-                        tmp[y * 8 + u] = s;
+            }
+            if (subsample) {
+                pY = code_unit(Yb.data() + 0, 16, fq[0], pY, dcL, acL);
+                pY = code_unit(Yb.data() + 8, 16, fq[0], pY, dcL, acL);
+                pY = code_unit(Yb.data() + 128, 16, fq[0], pY, dcL, acL);
+                pY = code_unit(Yb.data() + 136, 16, fq[0], pY, dcL, acL);
+                float su[64], sv[64];
+                for (int yy = 0, pos = 0; yy < 8; ++yy)
+                    for (int xx = 0; xx < 8; ++xx, ++pos) {
+                        const int j = yy * 32 + xx * 2;
+                        su[pos] = (Ub[j] + Ub[j + 1] + Ub[j + 16] + Ub[j + 17]) * 0.25f;
+                        sv[pos] = (Vb[j] + Vb[j + 1] + Vb[j + 16] + Vb[j + 17]) * 0.25f;
                     }
-                for (int u = 0; u < 8; ++u)      // columns
-                    for (int v = 0; v < 8; ++v) {
-                        float s = 0;
-                        for (int y = 0; y < 8; ++y) s += tmp[y * 8 + u] * cosT[v][y];
-                        coef[v * 8 + u] = s;
-                    }
-                const uint8_t* qt = q[c == 0 ? 0 : 1];
-                int zz[64];
-                for (int i = 0; i < 64; ++i) zz[i] = (int)std::lround(coef[kZigzag[i]] / qt[kZigzag[i]]);
-                const HuffTable& dc = (c == 0) ? dcL : dcC;
-                const HuffTable& ac = (c == 0) ? acL : acC;
-                auto magnitude = [](int v, int& nbits, uint32_t& bits) {
-                    int a = v < 0 ? -v : v;
-                    nbits = 0;
-                    while (a) { ++nbits; a >>= 1; }
-                    bits = (uint32_t)(v < 0 ? v + (1 << nbits) - 1 : v);
-                };
-                int nb; uint32_t bits;
-                const int diff = zz[0] - pred[c];
-                pred[c] = zz[0];
-                magnitude(diff, nb, bits);
-                bw.put(dc.code[nb], dc.len[nb]);
-                if (nb) bw.put(bits, nb);
-                int run = 0, last = 63;
-                while (last > 0 && zz[last] == 0) --last;
-                for (int i = 1; i <= last; ++i) {
-                    if (zz[i] == 0) { ++run; continue; }
-                    while (run >= 16) { bw.put(ac.code[0xF0], ac.len[0xF0]); run -= 16; }  // ZRL
-                    magnitude(zz[i], nb, bits);
-                    bw.put(ac.code[(run << 4) | nb], ac.len[(run << 4) | nb]);
-                    bw.put(bits, nb);
-                    run = 0;
-                }
-                if (last < 63) bw.put(ac.code[0x00], ac.len[0x00]);                        // EOB
+                pU = code_unit(su, 8, fq[1], pU, dcC, acC);
+                pV = code_unit(sv, 8, fq[1], pV, dcC, acC);
+            } else {
+                pY = code_unit(Yb.data(), 8, fq[0], pY, dcL, acL);
+                pU = code_unit(Ub.data(), 8, fq[1], pU, dcC, acC);
+                pV = code_unit(Vb.data(), 8, fq[1], pV, dcC, acC);
             }
         }
     bw.flush();

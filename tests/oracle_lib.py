@@ -171,6 +171,8 @@ def ref_lib(level: str):
         lib.refh_primary_hits.argtypes = [vp, vp, C.c_int]
         lib.refh_render.argtypes = [vp, C.c_uint32, vp, C.POINTER(C.c_uint64), C.POINTER(C.c_uint64), C.c_int]
         lib.refh_to_u8.argtypes = [vp, vp, C.c_size_t]
+        if hasattr(lib, "refh_stb_write"):
+            lib.refh_stb_write.argtypes = [C.c_char_p, vp, C.c_int, C.c_int, C.c_int]
         if hasattr(lib, "refh_render_window"):
             lib.refh_render_window.argtypes = [vp, C.c_uint32] + [C.c_int] * 4 + [vp, C.POINTER(C.c_uint64), C.POINTER(C.c_uint64), C.c_int]
         _refs[level] = lib
