@@ -208,7 +208,11 @@ def run_gpu_arm(args):
 
     # device-resident handle: the library writes its partial framebuffer straight into a
     # torch tensor (the NCCL send buffer); no host sync between the last kernel and the reduce.
-    r = rtm.Renderer(sc, device=local, seed=0x5EED, variant=args.variant, estimator=args.estimator, **plan)
+    knobs = {}
+    for kv in args.knob:       # rtm_options.debug_* A/B knobs, e.g. --knob debug_bvh_walk=2
+        k, v = kv.split("=", 1)
+        knobs[k] = float(v) if k == "debug_bvh_ctrav" else int(v)
+    r = rtm.Renderer(sc, device=local, seed=0x5EED, variant=args.variant, estimator=args.estimator, **plan, **knobs)
     accum = torch.zeros((sc.height, sc.width, 4), dtype=torch.float32, device=dev)
     r.set_accum_buffer(accum.data_ptr())
     stream = torch.cuda.current_stream()
@@ -351,6 +355,7 @@ def run_gpu_arm(args):
                        **({"n_planes": sc.n_planes, "flops_note": "plane tests are not counted (the 17-flop figure is the sphere test's)"}
                           if sc.n_planes else {}),
                        "variant": args.variant,
+                       **({"knobs": knobs} if knobs else {}),
                        **({"estimator": "nee (extension, DESIGN.md §11): `value` counts the PATH rays of the reference's estimator; "
                                         f"the kernel also traced {(st.rays_traced - n_sub - (st.rays - st.samples)) / max(1, st.samples):.2f} "
                                         "shadow rays per sample; the roofline's flops count their sphere tests, nothing else of them"}
@@ -429,6 +434,8 @@ def main():
                     help="N > 1: how the partial framebuffers reach rank 0 (peer-memory gather kernel path, or ncclReduce)")
     ap.add_argument("--estimator", default="reference", choices=["reference", "nee"],
                     help="nee = next-event estimation (extension); the headline metric is quoted on `reference`")
+    ap.add_argument("--knob", action="append", default=[], metavar="debug_x=v",
+                    help="rtm_options.debug_* knob for A/B runs (repeatable); the default line uses none")
     ap.add_argument("--variant", default="mega", choices=["mega", "wavefront"],
                     help="kernel organisation of the FP32 bounce loop (DESIGN.md: megakernel vs wavefront)")
     args = ap.parse_args()

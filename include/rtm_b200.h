@@ -137,8 +137,9 @@ typedef struct rtm_options {
      * its switches through its interface, not through getenv); 0 everywhere = the product defaults. */
     int32_t debug_retry;        /* roulette-rounds megakernel: 0 = chosen from the scene, 1 = forced off, 2 = forced on
                                    (both render the same image bit for bit) */
-    int32_t debug_bvh_walk;     /* hierarchy kernel: 0 = default (traversal stack in shared memory when the tree is
-                                   shallow enough), 1 = stack in local memory */
+    int32_t debug_bvh_walk;     /* hierarchy kernel, bit mask: 0 = default (traversal stack in shared memory when the tree
+                                   is shallow enough; compact half-precision nodes when they fit the scene),
+                                   bit 0 = stack in local memory, bit 1 = full-precision 64-byte nodes */
     int32_t debug_bvh_leaf_max; /* SAH build: largest leaf, 1..8; 0 = default (4) */
     float   debug_bvh_ctrav;    /* SAH build: cost of an inner-node visit in sphere tests; 0 = default (1.0) */
     int32_t debug_clamp;        /* 0 = the per-sample clamp (src/Renderer.cpp:240-241) is compiled out when the host can
@@ -246,6 +247,11 @@ int rtm_debug_acne_eps(int32_t device, uint32_t n, const uint32_t* bits, float* 
  * child codes, rmin), leaf_geo_out float[4*slots], leaf_id_out int32[slots]. */
 int rtm_debug_bvh(const rtm_scene_desc* scene, int32_t* info, float* nodes_out, float* leaf_geo_out,
                   int32_t* leaf_id_out);
+
+/* The compact form of that hierarchy which the FP32 walk uses (half-precision (centre, half-extent) child boxes,
+ * 32 bytes per node; host only).  meta6 = {frame centre x y z, 1/scale, median leaf-box inflation, usable (0/1)};
+ * nodes16_out uint32[8*nodes] or NULL: cx|cy, cz|hx, hy|hz of child 0, the same of child 1, the two child codes. */
+int rtm_debug_bvh16(const rtm_scene_desc* scene, int32_t* n_nodes_out, float* meta6, uint32_t* nodes16_out);
 
 /* The 4-wide collapse of that hierarchy (design study; host only).
  * info4[3] = {wide nodes, root code, depth}.  nodes4_out float[32*nodes] or NULL: 8 float4 per node —

@@ -92,7 +92,7 @@ EXPORTS = [
     "renderer_abi_version", "renderer_default_options", "renderer_create", "renderer_render",
     "renderer_render_async", "renderer_read_stats", "renderer_read_kernel_ms", "renderer_device_accum", "renderer_device_hits",
     "renderer_set_accum_buffer", "renderer_peer_export", "renderer_peer_open", "renderer_sum_partials", "renderer_read_rgb", "renderer_read_image_f64", "renderer_read_u8", "renderer_destroy",
-    "renderer_last_error", "rtm_debug_philox", "rtm_debug_closest_hit", "rtm_debug_fp32_peak", "rtm_debug_bvh", "rtm_debug_bvh4", "rtm_debug_acne_eps",
+    "renderer_last_error", "rtm_debug_philox", "rtm_debug_closest_hit", "rtm_debug_fp32_peak", "rtm_debug_bvh", "rtm_debug_bvh16", "rtm_debug_bvh4", "rtm_debug_acne_eps",
 ]
 
 
@@ -140,6 +140,7 @@ def load_library():
     lib.rtm_debug_closest_hit.argtypes = [vp, C.c_int32, C.c_uint32, vp, vp, vp, vp, vp]
     lib.rtm_debug_fp32_peak.argtypes = [C.c_int32, P(C.c_double), P(C.c_double)]
     lib.rtm_debug_bvh.argtypes = [P(_SceneDesc), vp, vp, vp, vp]
+    lib.rtm_debug_bvh16.argtypes = [P(_SceneDesc), vp, vp, vp]
     lib.rtm_debug_bvh4.argtypes = [P(_SceneDesc), vp, vp]
     lib.rtm_debug_acne_eps.argtypes = [C.c_int32, C.c_uint32, vp, vp]
     _lib = lib
@@ -326,6 +327,17 @@ def build_bvh(scene: Scene) -> dict:
     _check(lib, rc)
     return dict(nodes=nodes, leaf_geo=leaf_geo, leaf_id=leaf_id, root=int(info[2]), depth=int(info[3]),
                 big_id=[int(v) for v in info[5:5 + int(info[4])]])
+
+
+def build_bvh16(scene: Scene) -> dict:
+    """The compact half-precision form of build_bvh's tree (host code only): nodes[k] = 8 uint32."""
+    lib = load_library()
+    d = Renderer._desc(scene.normalized())
+    n, meta = C.c_int32(), np.zeros(6, np.float32)
+    _check(lib, lib.rtm_debug_bvh16(C.byref(d), C.byref(n), meta.ctypes.data, None))
+    nodes = np.zeros((n.value, 8), np.uint32)
+    _check(lib, lib.rtm_debug_bvh16(C.byref(d), C.byref(n), meta.ctypes.data, nodes.ctypes.data))
+    return dict(nodes=nodes, ref=meta[:3].astype(np.float64), inv_scale=float(meta[3]), inflation=float(meta[4]), ok=bool(meta[5]))
 
 
 def build_bvh4(scene: Scene) -> dict:

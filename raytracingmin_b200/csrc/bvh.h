@@ -48,6 +48,26 @@ struct RtmBvhHost {
 bool rtm_bvh_build(int32_t n, const double* position, const float* radius, const double ref[3], RtmBvhHost& out,
                    double c_trav = 0.0, int leaf_max = 0);
 
+// ---- compact form of the same tree for the FP32 walk: 32 bytes per inner node ---------------------------------
+// The FP32 hierarchy kernel is bound by L1 wavefronts (one per lane per load instruction, every lane on a different
+// node: ncu, profiles/r02).  A node that fits ONE 32-byte request halves them again after the 2 x 32-byte fetch of the
+// float node.  Child boxes are stored as (centre, half-extent) in IEEE half precision, in a frame centred on the root
+// box and scaled by a power of two so that the scene spans [-2^14, 2^14):
+//   u32[0..2]  child 0: cx|cy, cz|hx, hy|hz   (low half first)      u32[3..5]  child 1      u32[6], u32[7]  child codes
+// The (centre, half-extent) form needs no per-axis min/max in the slab test (near = c.inv - oi - |h.inv|, far = ... + |h.inv|).
+// Conservative by construction: the half box {c16 -+ h16} contains the padded float box of RtmBvhHost (h16 is rounded
+// up after the centre has been rounded), so the compact walk visits a superset of the candidates and finds the same
+// winner.  `inflation` = median over the leaf children of (h16 - h) / h on the widest-error axis: the host uses the form
+// only when that stays small (a scene whose features are tiny against its extent keeps the float nodes).
+struct RtmBvh16Host {
+    std::vector<uint32_t> nodes;     // 8 per inner node, same node numbering as RtmBvhHost
+    float ref[3] = {0.f, 0.f, 0.f};  // centre of the frame, relative to the scene reference point
+    float inv_scale = 1.f;           // 1 / scale (a power of two)
+    double inflation = 0.0;
+    bool ok = false;                 // false: empty tree, a single leaf, or a coordinate out of half range
+};
+void rtm_bvh_compact16(const RtmBvhHost& in, RtmBvh16Host& out);
+
 // ---- 4-wide form of the same tree (host-side design study) ----------------
 // Greedy collapse of the two-child tree: a node adopts its grandchildren (largest box first) until it holds 4
 // children.  The child boxes ARE the two-child tree's boxes, the leaves are shared (same leaf codes, same

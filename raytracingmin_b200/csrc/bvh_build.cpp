@@ -267,7 +267,6 @@ bool rtm_bvh_build(int32_t n, const double* position, const float* radius, const
     return bl.max_depth + 2 < RTM_BVH_STACK;
 }
 
-// ---- 4-wide collapse (bvh.h) -----------------------------------------------------------------------------
 namespace {
 struct Kid4 {
     int32_t code;
@@ -288,6 +287,97 @@ void kids_of(const RtmBvhHost& in, int32_t node, Kid4 out[2]) {
     out[1].rmin = q3.w;
 }
 }  // namespace
+
+// ---- compact half-precision form (bvh.h: RtmBvh16Host) ---------------------------------------------------------
+namespace {
+// IEEE binary16 from a finite double, round to nearest even / toward +infinity (up = true).  Returns 0x7C00 (inf) on overflow.
+uint16_t to_half(double v, bool up) {
+    const uint16_t sign = std::signbit(v) ? 0x8000 : 0;
+    const double a = std::fabs(v);
+    if (a == 0.0) return sign;
+    int e;
+    const double m = std::frexp(a, &e);          // a = m 2^e, m in [0.5, 1)
+    const int E = e - 1;                         // a = (2m) 2^E, 2m in [1, 2)
+    double q;                                    // fraction of a in units of the half's ulp at that magnitude
+    int bias_e;
+    if (E < -14) { q = std::ldexp(a, 24); bias_e = 0; }          // subnormal: ulp = 2^-24
+    else { q = std::ldexp(2.0 * m - 1.0, 10); bias_e = E + 15; } // 10 fraction bits
+    double f = std::floor(q);
+    const double rem = q - f;
+    // toward +infinity: a positive value moves to the next half, a negative one is truncated
+    const bool round_up = up ? (rem > 0.0 && !sign) : (rem > 0.5 || (rem == 0.5 && std::fmod(f, 2.0) == 1.0));
+    if (round_up) f += 1.0;
+    uint32_t bits;
+    if (bias_e == 0) bits = (uint32_t)f;                          // may carry into the smallest normal: still correct
+    else {
+        uint32_t frac = (uint32_t)f;
+        if (frac == 1024u) { frac = 0; ++bias_e; }
+        if (bias_e >= 31) return (uint16_t)(sign | 0x7C00);
+        bits = ((uint32_t)bias_e << 10) | frac;
+    }
+    return (uint16_t)(sign | bits);
+}
+double from_half(uint16_t h) {
+    const int e = (h >> 10) & 31, f = h & 1023;
+    const double v = (e == 0) ? std::ldexp((double)f, -24) : (e == 31 ? INFINITY : std::ldexp(1.0 + f / 1024.0, e - 15));
+    return (h & 0x8000) ? -v : v;
+}
+}  // namespace
+
+void rtm_bvh_compact16(const RtmBvhHost& in, RtmBvh16Host& out) {
+    out = RtmBvh16Host();
+    if (in.root < 0 || in.root == RTM_BVH_NONE) return;           // empty tree or a single leaf: nothing to walk
+    const size_t n_nodes = in.nodes.size() / 4;
+    // frame: centre of the root box, power-of-two scale that maps the largest |coordinate - centre| into [2^13, 2^14)
+    Kid4 rk[2];
+    kids_of(in, in.root, rk);
+    double lo[3], hi[3];
+    for (int a = 0; a < 3; ++a) {
+        lo[a] = std::min((double)rk[0].lo[a], (double)rk[1].lo[a]);
+        hi[a] = std::max((double)rk[0].hi[a], (double)rk[1].hi[a]);
+        out.ref[a] = (float)(0.5 * (lo[a] + hi[a]));
+    }
+    double ext = 0.0;
+    for (int a = 0; a < 3; ++a) ext = std::max(ext, std::max(std::fabs(lo[a] - out.ref[a]), std::fabs(hi[a] - out.ref[a])));
+    if (!(ext > 0.0) || !std::isfinite(ext)) return;
+    int e;
+    std::frexp(ext, &e);                                          // ext < 2^e
+    const double scale = std::ldexp(1.0, 14 - e);                 // ext * scale < 2^14
+    out.inv_scale = (float)(1.0 / scale);
+    out.nodes.assign(n_nodes * 8, 0u);
+    std::vector<double> infl;
+    for (size_t i = 0; i < n_nodes; ++i) {
+        Kid4 k[2];
+        kids_of(in, (int32_t)i, k);
+        uint32_t* w = out.nodes.data() + 8 * i;
+        for (int j = 0; j < 2; ++j) {
+            uint16_t c16[3], h16[3];
+            double worst = 0.0;
+            for (int a = 0; a < 3; ++a) {
+                const double l = ((double)k[j].lo[a] - out.ref[a]) * scale, h = ((double)k[j].hi[a] - out.ref[a]) * scale;
+                c16[a] = to_half(0.5 * (l + h), false);
+                const double c = from_half(c16[a]);
+                const double need = std::max(h - c, c - l);       // half-extent that covers [l, h] around the ROUNDED centre
+                h16[a] = to_half(need * (1.0 + 1e-7), true);
+                if (h16[a] == 0x7C00 || (c16[a] & 0x7FFF) == 0x7C00) { out.nodes.clear(); return; }
+                const double true_h = 0.5 * (h - l);
+                if (true_h > 0.0) worst = std::max(worst, (from_half(h16[a]) - true_h) / true_h);
+            }
+            if (k[j].code < 0) infl.push_back(worst);
+            w[3 * j + 0] = (uint32_t)c16[0] | ((uint32_t)c16[1] << 16);
+            w[3 * j + 1] = (uint32_t)c16[2] | ((uint32_t)h16[0] << 16);
+            w[3 * j + 2] = (uint32_t)h16[1] | ((uint32_t)h16[2] << 16);
+            w[6 + j] = (uint32_t)k[j].code;
+        }
+    }
+    if (!infl.empty()) {
+        std::nth_element(infl.begin(), infl.begin() + infl.size() / 2, infl.end());
+        out.inflation = infl[infl.size() / 2];
+    }
+    out.ok = true;
+}
+
+// ---- 4-wide collapse (bvh.h) -----------------------------------------------------------------------------
 
 void rtm_bvh_collapse4(const RtmBvhHost& in, RtmBvh4Host& out) {
     out.nodes.clear();

@@ -39,7 +39,8 @@ namespace {
 #ifndef RTM_BVH_SSTACK
 #define RTM_BVH_SSTACK 24
 #endif
-template <int NP, bool ACNE, bool PL, bool SST>
+// H16: walk the compact half-precision nodes (one 32-byte request per visit; bvh.h: RtmBvh16Host)
+template <int NP, bool ACNE, bool PL, bool SST, bool H16>
 __global__ void __launch_bounds__(RTM_MEGA_THREADS, RTM_BVH_MINBLOCKS)
 radiance_bvh_kernel(const __grid_constant__ RtmHotScene hot, const __grid_constant__ RtmPassParams p, float4* __restrict__ records,
                     RtmCounters* __restrict__ counters, RtmBvhDev bvh, RtmMatDev mat, const float* __restrict__ cps0, int n_sph, int n_pl) {
@@ -237,7 +238,7 @@ radiance_bvh_kernel(const __grid_constant__ RtmHotScene hot, const __grid_consta
             }
             if (start) {
                 // the packed big-sphere test (~140 instructions) and the planes: once, for all lanes that start a ray
-                bvh_ray_begin<NP, ST>(hot, sh_mask, sh_big, bvh, bvh_big_slot(ocode), o, d, key_mask, ray, stack, n_tests);
+                bvh_ray_begin<NP, ST, H16>(hot, sh_mask, sh_big, bvh, bvh_big_slot(ocode), o, d, key_mask, ray, stack, n_tests);
                 sslot = bvh_leaf_slot(ocode);
                 if (PL) bvh_ray_planes(hot, n_sph, n_pl, id, o, d, ray);
                 if (ray.node != RTM_BVH_NONE_DEV) tracing = true;
@@ -262,7 +263,8 @@ radiance_bvh_kernel(const __grid_constant__ RtmHotScene hot, const __grid_consta
                     ray.node = stack[ST * --ray.sp];
                 }
                 if (!(tracing && bvh_is_inner(ray.node))) break;
-                bvh_inner_step<ST>(bvh, ray, stack);
+                if (H16) bvh16_inner_step<ST>(bvh, ray, stack);
+                else bvh_inner_step<ST>(bvh, ray, stack);
                 ++n_nodes;
             }
             if (tracing && held != 0) bvh_leaf_test(bvh, held, sslot, o, d, ray, n_tests);
@@ -270,7 +272,8 @@ radiance_bvh_kernel(const __grid_constant__ RtmHotScene hot, const __grid_consta
 #else
 #pragma unroll 1
             for (int k = 0; k < RTM_BVH_BURST && tracing && bvh_is_inner(ray.node); ++k) {
-                bvh_inner_step<ST>(bvh, ray, stack);
+                if (H16) bvh16_inner_step<ST>(bvh, ray, stack);
+                else bvh_inner_step<ST>(bvh, ray, stack);
                 ++n_nodes;
             }
             if (tracing && ray.node < 0) bvh_leaf_step<ST>(bvh, sslot, o, d, ray, stack, n_tests);
@@ -302,7 +305,7 @@ radiance_bvh_kernel(const __grid_constant__ RtmHotScene hot, const __grid_consta
 }
 
 // the hierarchy variant of the hook: same trace function as radiance_mega_kernel<*, true>
-template <int NP>
+template <int NP, bool H16>
 __global__ void closest_hit_bvh_f32_kernel(const __grid_constant__ RtmHotScene hot, RtmBvhDev bvh, RtmMatDev mat, unsigned key_mask, double rx, double ry, double rz, uint32_t n,
                                            const double* __restrict__ org, const double* __restrict__ dir,
                                            const int32_t* __restrict__ origin_id, int n_sph, int n_pl, int32_t* __restrict__ hit,
@@ -321,24 +324,30 @@ __global__ void closest_hit_bvh_f32_kernel(const __grid_constant__ RtmHotScene h
     const int ocode = (oid >= 0) ? __float_as_int(__ldg(mat.alb + oid).w) : -1;
     float t;
     unsigned a = 0, b = 0;
-    hit[i] = trace_bvh_f32<NP>(hot, sh_mask, sh_big, bvh, oid, ocode, o, d, t, key_mask, a, b, n_sph, n_pl);
+    hit[i] = trace_bvh_f32<NP, H16>(hot, sh_mask, sh_big, bvh, oid, ocode, o, d, t, key_mask, a, b, n_sph, n_pl);
     tout[i] = (double)t;
 }
 
+template <int NP, bool ACNE, bool PL, bool SST, bool H16>
+void launch_bvh4(const RtmHotScene& hot, const RtmBvhDev& bvh, const RtmMatDev& mat, const RtmPassParams& p, float4* records, RtmCounters* counters,
+                 int sm_count, const float* cps0, int n_sph, int n_pl, cudaStream_t st) {
+    int per_sm = 0;
+    cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, radiance_bvh_kernel<NP, ACNE, PL, SST, H16>, RTM_MEGA_THREADS, 0);
+    if (per_sm < 1) per_sm = 1;
+    radiance_bvh_kernel<NP, ACNE, PL, SST, H16><<<sm_count * per_sm, RTM_MEGA_THREADS, 0, st>>>(hot, p, records, counters, bvh, mat, cps0, n_sph, n_pl);
+}
 template <int NP, bool ACNE, bool PL, bool SST>
 void launch_bvh3(const RtmHotScene& hot, const RtmBvhDev& bvh, const RtmMatDev& mat, const RtmPassParams& p, float4* records, RtmCounters* counters,
                  int sm_count, const float* cps0, int n_sph, int n_pl, cudaStream_t st) {
-    int per_sm = 0;
-    cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, radiance_bvh_kernel<NP, ACNE, PL, SST>, RTM_MEGA_THREADS, 0);
-    if (per_sm < 1) per_sm = 1;
-    radiance_bvh_kernel<NP, ACNE, PL, SST><<<sm_count * per_sm, RTM_MEGA_THREADS, 0, st>>>(hot, p, records, counters, bvh, mat, cps0, n_sph, n_pl);
+    if (bvh.nodes16) launch_bvh4<NP, ACNE, PL, SST, true>(hot, bvh, mat, p, records, counters, sm_count, cps0, n_sph, n_pl, st);
+    else launch_bvh4<NP, ACNE, PL, SST, false>(hot, bvh, mat, p, records, counters, sm_count, cps0, n_sph, n_pl, st);
 }
 template <int NP, bool ACNE, bool PL>
 void launch_bvh2(const RtmHotScene& hot, const RtmBvhDev& bvh, const RtmMatDev& mat, const RtmPassParams& p, float4* records, RtmCounters* counters,
                  int sm_count, const float* cps0, int n_sph, int n_pl, int walk, cudaStream_t st) {
-    // a walk holds at most depth + 2 stack entries (one per level + the sentinel); walk == 1 (rtm_options.debug_bvh_walk,
+    // a walk holds at most depth + 2 stack entries (one per level + the sentinel); walk & 1 (rtm_options.debug_bvh_walk,
     // A/B runs) keeps the stack in local memory
-    if (walk != 1 && bvh.depth + 2 <= RTM_BVH_SSTACK) launch_bvh3<NP, ACNE, PL, true>(hot, bvh, mat, p, records, counters, sm_count, cps0, n_sph, n_pl, st);
+    if (!(walk & 1) && bvh.depth + 2 <= RTM_BVH_SSTACK) launch_bvh3<NP, ACNE, PL, true>(hot, bvh, mat, p, records, counters, sm_count, cps0, n_sph, n_pl, st);
     else launch_bvh3<NP, ACNE, PL, false>(hot, bvh, mat, p, records, counters, sm_count, cps0, n_sph, n_pl, st);
 }
 template <int NP>
@@ -371,7 +380,11 @@ void rtm_launch_closest_hit_bvh_f32(const RtmHotScene& hot, const RtmBvhDev& bvh
                                     int32_t* hit, double* t, cudaStream_t st) {
     const unsigned g = (n + 127) / 128;
     switch ((bvh.n_big + 1) / 2) {
-#define RTM_CASE(NP) closest_hit_bvh_f32_kernel<NP><<<g, 128, 0, st>>>(hot, bvh, mat, 0xFFFFFFF8u, refd[0], refd[1], refd[2], n, org, dir, origin_id, n_spheres, n_planes, hit, t)
+#define RTM_CASE(NP)                                                                                                                              \
+    do {                                                                                                                                          \
+        if (bvh.nodes16) closest_hit_bvh_f32_kernel<NP, true><<<g, 128, 0, st>>>(hot, bvh, mat, 0xFFFFFFF8u, refd[0], refd[1], refd[2], n, org, dir, origin_id, n_spheres, n_planes, hit, t); \
+        else closest_hit_bvh_f32_kernel<NP, false><<<g, 128, 0, st>>>(hot, bvh, mat, 0xFFFFFFF8u, refd[0], refd[1], refd[2], n, org, dir, origin_id, n_spheres, n_planes, hit, t);          \
+    } while (0)
         case 0: RTM_CASE(0); break;
         case 1: RTM_CASE(1); break;
         case 2: RTM_CASE(2); break;

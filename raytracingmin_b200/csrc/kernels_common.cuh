@@ -20,6 +20,7 @@
 #include "rtm_internal.h"
 #include "philox.cuh"
 
+#include <cuda_fp16.h>
 #include <float.h>
 
 #define RTM_MEGA_THREADS 128
@@ -293,7 +294,9 @@ struct BvhRay {
 // the packed test over the big list, then position the lane on the root
 // ST = distance in ints between two consecutive entries of a lane's stack: 1 for a private (local-memory) array,
 // the block size for the interleaved shared-memory layout stack[level][thread]
-template <int NP, int ST = 1>
+// H16: the lane will walk the compact half-precision nodes (bvh.h: RtmBvh16Host), whose frame is centred on bvh.ref16
+// and scaled by a power of two: inv = (1/d) / scale, oi = (o - ref16) / d  (t is unchanged by the change of frame)
+template <int NP, int ST = 1, bool H16 = false>
 __device__ __forceinline__ void bvh_ray_begin(const RtmHotScene& hot, const SelfMask& sm, const SharedBig& big, const RtmBvhDev& bvh, int oslot,
                                               f3 o, f3 d, unsigned key_mask, BvhRay& r, int* stack, unsigned& n_tests) {
     r.best = FLT_MAX;
@@ -307,7 +310,12 @@ __device__ __forceinline__ void bvh_ray_begin(const RtmHotScene& hot, const Self
         n_tests += 2 * NP;
     }
     r.inv = mk(fast_rcp(d.x), fast_rcp(d.y), fast_rcp(d.z));
-    r.oi = mk(o.x * r.inv.x, o.y * r.inv.y, o.z * r.inv.z);
+    if (H16) {
+        r.oi = mk((o.x - bvh.ref16[0]) * r.inv.x, (o.y - bvh.ref16[1]) * r.inv.y, (o.z - bvh.ref16[2]) * r.inv.z);
+        r.inv = mk(r.inv.x * bvh.inv_scale16, r.inv.y * bvh.inv_scale16, r.inv.z * bvh.inv_scale16);
+    } else {
+        r.oi = mk(o.x * r.inv.x, o.y * r.inv.y, o.z * r.inv.z);
+    }
     r.node = bvh.root;
     r.sp = 0;
     stack[ST * r.sp++] = RTM_BVH_NONE_DEV;
@@ -338,6 +346,45 @@ __device__ __forceinline__ void bvh_inner_step(const RtmBvhDev& bvh, BvhRay& r, 
     const bool h0 = box_test_f32(q0.x, q0.y, q0.z, q0.w, q2.x, q2.y, r.oi, r.inv, tm, n0);
     const bool h1 = box_test_f32(q1.x, q1.y, q1.z, q1.w, q2.z, q2.w, r.oi, r.inv, tm, n1);
     const int c0 = __float_as_int(q3.x), c1 = __float_as_int(q3.y);
+    if (h0 && h1) {
+        const bool swap = n1 < n0;
+        stack[ST * r.sp++] = swap ? c0 : c1;
+        r.node = swap ? c1 : c0;
+    } else if (h0 || h1) {
+        r.node = h0 ? c0 : c1;
+    } else {
+        r.node = stack[ST * --r.sp];
+    }
+}
+
+// ---- the same step on the compact node (bvh.h: RtmBvh16Host): ONE 32-byte request, (centre, half-extent) boxes in half
+// precision.  near/far = (c.inv - oi) -+ |h.inv|: no per-axis min/max.  NaN (0 * inf) drops out of the min/max as in
+// box_test_f32: that slab is ignored.
+__device__ __forceinline__ bool box_test_h16(unsigned w0, unsigned w1, unsigned w2, f3 oi, f3 inv, float tmax_in, float& tnear) {
+    const float2 a = __half22float2(*reinterpret_cast<const __half2*>(&w0));   // cx, cy
+    const float2 b = __half22float2(*reinterpret_cast<const __half2*>(&w1));   // cz, hx
+    const float2 c = __half22float2(*reinterpret_cast<const __half2*>(&w2));   // hy, hz
+    const float tx = fmaf(a.x, inv.x, -oi.x), ty = fmaf(a.y, inv.y, -oi.y), tz = fmaf(b.x, inv.z, -oi.z);
+    const float px = fabsf(b.y * inv.x), py = fabsf(c.x * inv.y), pz = fabsf(c.y * inv.z);
+    const float tmin = fmaxf(fmaxf(tx - px, ty - py), fmaxf(tz - pz, 0.f));
+    const float tmax = fminf(fminf(tx + px, ty + py), fminf(tz + pz, tmax_in));
+    tnear = tmin;
+    return tmin <= tmax;
+}
+__device__ __forceinline__ void ldg256u(const uint32_t* p, uint4& a, uint4& b) {
+    asm("ld.global.nc.v8.u32 {%0,%1,%2,%3,%4,%5,%6,%7}, [%8];"
+        : "=r"(a.x), "=r"(a.y), "=r"(a.z), "=r"(a.w), "=r"(b.x), "=r"(b.y), "=r"(b.z), "=r"(b.w)
+        : "l"(p));
+}
+template <int ST = 1>
+__device__ __forceinline__ void bvh16_inner_step(const RtmBvhDev& bvh, BvhRay& r, int* stack) {
+    uint4 a, b;
+    ldg256u(bvh.nodes16 + 8 * r.node, a, b);
+    float n0, n1;
+    const float tm = r.best + 2.f * RTM_T_EPS;
+    const bool h0 = box_test_h16(a.x, a.y, a.z, r.oi, r.inv, tm, n0);
+    const bool h1 = box_test_h16(a.w, b.x, b.y, r.oi, r.inv, tm, n1);
+    const int c0 = (int)b.z, c1 = (int)b.w;
     if (h0 && h1) {
         const bool swap = n1 < n0;
         stack[ST * r.sp++] = swap ? c0 : c1;
@@ -437,17 +484,18 @@ __device__ __forceinline__ void bvh_ray_planes(const RtmHotScene& hot, int n_sph
 
 // whole query (test hook; the render kernel interleaves the same steps across its lanes).  ocode = alb.w of the
 // object the ray leaves (or -1)
-template <int NP>
+template <int NP, bool H16>
 __device__ __forceinline__ int trace_bvh_f32(const RtmHotScene& hot, const SelfMask& sm, const SharedBig& big, const RtmBvhDev& bvh, int oid, int ocode,
                                              f3 o, f3 d, float& t, unsigned key_mask, unsigned& n_tests, unsigned& n_nodes,
                                              int n_sph = 0, int n_pl = 0) {
     BvhRay r;
     int stack[RTM_BVH_STACK_DEV];
-    bvh_ray_begin<NP>(hot, sm, big, bvh, bvh_big_slot(ocode), o, d, key_mask, r, stack, n_tests);
+    bvh_ray_begin<NP, 1, H16>(hot, sm, big, bvh, bvh_big_slot(ocode), o, d, key_mask, r, stack, n_tests);
     if (n_pl > 0) bvh_ray_planes(hot, n_sph, n_pl, oid, o, d, r);
     while (r.node != RTM_BVH_NONE_DEV) {
         while (bvh_is_inner(r.node)) {
-            bvh_inner_step(bvh, r, stack);
+            if (H16) bvh16_inner_step(bvh, r, stack);
+            else bvh_inner_step(bvh, r, stack);
             ++n_nodes;
         }
         if (r.node < 0) bvh_leaf_step(bvh, bvh_leaf_slot(ocode), o, d, r, stack, n_tests);

@@ -151,6 +151,7 @@ struct rtm_renderer {
     bool acne = false;          // the FP32 path models the reference's self-intersection on small spheres
     bool use_bvh = false;       // closest hit through the hierarchy (bvh.h) instead of the O(N) loop
     RtmBvhHost bvh_host;
+    RtmBvh16Host bvh16;         // compact form of bvh_host for the FP32 walk (ok = false: the float nodes are walked)
     std::vector<float4> mat_geo, mat_emi, mat_alb;
 };
 
@@ -378,7 +379,7 @@ int renderer_create(const rtm_scene_desc* sc, const rtm_options* opt_in, rtm_ren
     if (f32_path && !use_bvh && sc->n_spheres + m > RTM_MAX_CONST_SPHERES)
         return fail(RTM_E_UNSUPPORTED, "FP32 brute-force path holds at most %d objects (use RTM_ACCEL_BVH / AUTO)",
                     RTM_MAX_CONST_SPHERES);
-    if (opt.debug_retry < 0 || opt.debug_retry > 2 || opt.debug_bvh_walk < 0 || opt.debug_bvh_walk > 1 || opt.debug_bvh_leaf_max < 0 ||
+    if (opt.debug_retry < 0 || opt.debug_retry > 2 || opt.debug_bvh_walk < 0 || opt.debug_bvh_walk > 3 || opt.debug_bvh_leaf_max < 0 ||
         opt.debug_bvh_leaf_max > 8 || !(opt.debug_bvh_ctrav >= 0.f) || opt.debug_clamp < 0 || opt.debug_clamp > 1)
         return fail(RTM_E_INVALID, "bad debug_* option");
     if (opt.variant == RTM_VARIANT_WAVEFRONT && sc->samples >= (1 << 22))
@@ -639,6 +640,12 @@ int renderer_create(const rtm_scene_desc* sc, const rtm_options* opt_in, rtm_ren
             return fail(RTM_E_UNSUPPORTED, "%d sphere(s) of radius >= %g beyond the %d the FP32 hierarchy path tests for every ray: "
                         "use RTM_ACCEL_BRUTE or RTM_PRECISION_F64", k, RTM_BVH_BIG_RADIUS, RTM_BVH_MAX_BIG);
         }
+        if (f32_path && !(opt.debug_bvh_walk & 2)) {
+            // compact half-precision nodes for the FP32 walk, unless rounding the boxes to half precision would inflate
+            // the typical leaf box by more than a quarter (features tiny against the scene's extent)
+            rtm_bvh_compact16(r->bvh_host, r->bvh16);
+            if (r->bvh16.ok && r->bvh16.inflation > 0.25) r->bvh16.ok = false;
+        }
         if (f32_path) {
             // alb.w of a sphere: its slot in the big list (0..7) or 8 + its leaf slot (kernels_common.cuh: bvh_big_slot / bvh_leaf_slot)
             for (int j = 0; j < r->bvh_host.n_big; ++j) memcpy(&r->mat_alb[r->bvh_host.big_id[j]].w, &j, 4);
@@ -710,7 +717,8 @@ int renderer_create(const rtm_scene_desc* sc, const rtm_options* opt_in, rtm_ren
                 // one allocation, float4 units: nodes | leaf_geo | geo | emi | alb | leaf_id (int32, padded)
                 const RtmBvhHost& B = r->bvh_host;
                 const size_t n_nodes4 = B.nodes.size(), n_slots = B.leaf_geo.size(), n_mat = r->mat_geo.size();
-                const size_t total4 = n_nodes4 + n_slots + 3 * n_mat + (n_slots + 3) / 4 + 1;
+                const size_t n_16 = r->bvh16.ok ? r->bvh16.nodes.size() / 4 : 0;     // float4 units: 2 per node
+                const size_t total4 = n_nodes4 + n_16 + n_slots + 3 * n_mat + (n_slots + 3) / 4 + 1;
                 CU(cudaMalloc(&c.d_bvh, total4 * sizeof(float4)));
                 float4* d = c.d_bvh;
                 cudaError_t put_err = cudaSuccess;
@@ -721,6 +729,10 @@ int renderer_create(const rtm_scene_desc* sc, const rtm_options* opt_in, rtm_ren
                     return at;
                 };
                 c.bvh.nodes = put(B.nodes.data(), n_nodes4, n_nodes4 * sizeof(float4));
+                // right behind the 64-byte float nodes: 32-byte aligned, as the 256-bit loads need
+                c.bvh.nodes16 = n_16 ? (const uint32_t*)put(r->bvh16.nodes.data(), n_16, n_16 * sizeof(float4)) : nullptr;
+                for (int k = 0; k < 3; ++k) c.bvh.ref16[k] = r->bvh16.ref[k];
+                c.bvh.inv_scale16 = r->bvh16.inv_scale;
                 c.bvh.leaf_geo = put(B.leaf_geo.data(), n_slots, n_slots * sizeof(float4));
                 c.mat.geo = put(r->mat_geo.data(), n_mat, n_mat * sizeof(float4));
                 c.mat.emi = put(r->mat_emi.data(), n_mat, n_mat * sizeof(float4));
@@ -1061,6 +1073,20 @@ int rtm_debug_bvh(const rtm_scene_desc* sc, int32_t* info, float* nodes_out, flo
     if (leaf_geo_out) memcpy(leaf_geo_out, B.leaf_geo.data(), B.leaf_geo.size() * sizeof(float4));
     if (leaf_id_out) memcpy(leaf_id_out, B.leaf_id.data(), B.leaf_id.size() * sizeof(int32_t));
     return ok ? RTM_OK : fail(RTM_E_UNSUPPORTED, "sphere hierarchy too deep (%d levels)", B.depth);
+}
+
+int rtm_debug_bvh16(const rtm_scene_desc* sc, int32_t* n_nodes_out, float* meta6, uint32_t* nodes16_out) {
+    if (!sc || !n_nodes_out || !meta6) return fail(RTM_E_INVALID, "null argument");
+    RtmBvhHost B;
+    if (!rtm_bvh_build(sc->n_spheres, sc->position, sc->radius, sc->cam_origin, B))
+        return fail(RTM_E_UNSUPPORTED, "sphere hierarchy too deep (%d levels)", B.depth);
+    RtmBvh16Host H;
+    rtm_bvh_compact16(B, H);
+    *n_nodes_out = (int32_t)(H.nodes.size() / 8);
+    meta6[0] = H.ref[0]; meta6[1] = H.ref[1]; meta6[2] = H.ref[2];
+    meta6[3] = H.inv_scale; meta6[4] = (float)H.inflation; meta6[5] = H.ok ? 1.f : 0.f;
+    if (nodes16_out && H.ok) memcpy(nodes16_out, H.nodes.data(), H.nodes.size() * sizeof(uint32_t));
+    return RTM_OK;
 }
 
 int rtm_debug_bvh4(const rtm_scene_desc* sc, int32_t* info4, float* nodes4_out) {

@@ -26,6 +26,10 @@ struct RtmBvhDev {
     int32_t n_big;            // spheres kept out of the hierarchy, tested for every ray
     int32_t big_id[8];        //   ascending original index
     int32_t depth;            // levels of the tree (a walk holds at most depth + 2 stack entries)
+    // compact form for the FP32 walk (bvh.h: RtmBvh16Host): 8 x u32 per inner node, NULL = not used
+    const uint32_t* nodes16;
+    float ref16[3];           // centre of the half-precision frame, relative to the scene reference point
+    float inv_scale16;        // 1 / (power-of-two scale of that frame)
 };
 
 // Per-sphere records of the FP32 path in GLOBAL memory (hierarchy path, any N): the

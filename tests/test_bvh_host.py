@@ -312,3 +312,41 @@ def test_wide_walk_equals_brute_force(synth):
                 node = stack.pop()
         assert hit == want, (i, hit, want)
     assert visits_w / n < 40
+
+
+# ---------------- compact half-precision nodes (bvh.h: RtmBvh16Host): what the FP32 hierarchy kernel walks ----------------
+def _half_box(words, ref, inv_scale):
+    """u32[3] -> (lo[3], hi[3]) in the float nodes' frame."""
+    h = np.array(words, np.uint32).view(np.float16).astype(np.float64)     # cx cy cz hx hy hz
+    c, e = h[:3], h[3:]
+    return (c - e) * inv_scale + ref, (c + e) * inv_scale + ref
+
+
+def test_compact16_boxes_contain_the_float_boxes(synth):
+    """Conservativeness: every child box of the compact tree, decoded as the kernel decodes it, contains the padded float
+    box of the same child — the compact walk can only visit MORE candidates than the float walk, never miss one.  Codes and
+    node numbering are shared with the float tree."""
+    sc, b = synth
+    h = api.build_bvh16(sc)
+    assert h["ok"] and len(h["nodes"]) == len(b["nodes"])
+    assert 0.0 <= h["inflation"] < 0.1, h["inflation"]                     # synth10k: boxes of r >= 0.05 spheres in a 20-unit room
+    worst = 0.0
+    for nd, w in zip(b["nodes"], h["nodes"]):
+        codes, boxes = _children(nd), _boxes(nd)
+        assert (int(np.int32(w[6])), int(np.int32(w[7]))) == tuple(int(c) for c in codes)
+        for j in range(2):
+            lo, hi = _half_box(w[3 * j:3 * j + 3], h["ref"], h["inv_scale"])
+            bx = boxes[j]
+            flo, fhi = np.array([bx[0], bx[2], bx[4]], np.float64), np.array([bx[1], bx[3], bx[5]], np.float64)
+            assert (lo <= flo).all() and (hi >= fhi).all(), (lo, flo, hi, fhi)
+            worst = max(worst, float(((hi - lo) / np.maximum(fhi - flo, 1e-30)).max()))
+    assert worst < 1.5, worst                                              # no box more than half again as wide
+
+
+def test_compact16_reports_what_half_precision_cannot_hold():
+    """A scene whose features are tiny against its extent (two clusters of small spheres a million units apart): the
+    median leaf box would be inflated far beyond the host's threshold (0.25), so renderer_create keeps the float nodes."""
+    sc = rtm.random_scene(3, 200, width=8, height=8, samples=1, superSamples=1, closed=False)
+    sc.position[:100, 0] += 1e6
+    h = api.build_bvh16(sc.normalized())
+    assert (not h["ok"]) or h["inflation"] > 0.25, h

@@ -200,6 +200,22 @@ def test_shared_and_local_stack_instantiations_render_the_same_image(synth):
     assert there.stats.bvh_nodes == here.stats.bvh_nodes
 
 
+def test_compact_half_precision_nodes_render_the_same_image(synth):
+    """radiance_bvh_kernel<..., H16>: 32-byte nodes with half-precision (centre, half-extent) child boxes (one L1 request
+    per visit) against the 64-byte float nodes (rtm_options.debug_bvh_walk bit 1).  The compact boxes contain the float
+    ones, so the walk meets a superset of the candidates and keeps the same winner: same paths, bit-identical image and
+    ray count; only the visit counters may differ (by the few percent the boxes are wider)."""
+    sc = synth.with_dims(96, 54, 8, 2)
+    with rtm.Renderer(sc, seed=4) as r:
+        a = r.render()
+    with rtm.Renderer(sc, seed=4, debug_bvh_walk=2) as r:
+        b = r.render()
+    assert np.array_equal(a.image, b.image)
+    assert a.stats.rays == b.stats.rays and a.stats.rays_traced == b.stats.rays_traced
+    assert b.stats.bvh_nodes <= a.stats.bvh_nodes <= 1.15 * b.stats.bvh_nodes
+    assert b.stats.sphere_tests <= a.stats.sphere_tests <= 1.15 * b.stats.sphere_tests
+
+
 # ---------------- wavefront variant (same estimator, state in global memory) ----------------
 @pytest.mark.parametrize("which", ["cornell", "random200_brute", "random200_bvh", "synth10k"])
 def test_wavefront_matches_megakernel(scene_path, synth, which):
