@@ -98,15 +98,23 @@ radiance_bvh_kernel(const __grid_constant__ RtmHotScene hot, const __grid_consta
         unsigned need = __ballot_sync(0xffffffffu, !have && !done);
         while (need) {
             if (w_next == w_end) {
+                // guided self-scheduling (see radiance_mega_kernel): full chunks while plenty is left, smaller ones near the end
                 unsigned long long start = 0;
-                if (lane == 0) start = atomicAdd(&counters->work_next, (unsigned long long)RTM_MEGA_CHUNK);
+                unsigned chunk = RTM_MEGA_CHUNK;
+                if (lane == 0) {
+                    const unsigned long long seen = *(volatile unsigned long long*)&counters->work_next;
+                    const unsigned long long fair = (seen < n_sub ? n_sub - seen : 0ull) / (2ull * gridDim.x * (RTM_MEGA_THREADS / 32));
+                    chunk = fair >= RTM_MEGA_CHUNK ? RTM_MEGA_CHUNK : (fair < 4ull ? 4u : (unsigned)fair);
+                    start = atomicAdd(&counters->work_next, (unsigned long long)chunk);
+                }
                 start = __shfl_sync(0xffffffffu, start, 0);
+                chunk = __shfl_sync(0xffffffffu, chunk, 0);
                 if (start >= (unsigned long long)n_sub) {
                     if (!have) done = true;
                     break;
                 }
                 w_next = (unsigned)start;
-                w_end = (start + RTM_MEGA_CHUNK < (unsigned long long)n_sub) ? (unsigned)start + RTM_MEGA_CHUNK : n_sub;
+                w_end = (start + chunk < (unsigned long long)n_sub) ? (unsigned)start + chunk : n_sub;
             }
             const unsigned avail = w_end - w_next;
             const unsigned rank = __popc(need & lt_mask);

@@ -55,11 +55,22 @@ __device__ __forceinline__ uint2 rtm_philox2x32_10(uint2 c, const uint32_t* __re
 // 9 multiply-adds + 3 shifts/xors against ~45 instructions of Philox2x32-10, which is 12 % of a
 // 280-instruction Cornell bounce.  -DRTM_RNG_PHILOX selects Philox2x32-10 again (A/B runs).
 // Counter-based either way: the image is a pure function of (scene, seed).
-__device__ __forceinline__ uint2 rtm_bounce_rng(uint2 c, const uint32_t* __restrict__ rk) {
+// The first word's LCG step only changes when the lane moves to another sub-pixel: the megakernel keeps
+// rtm_bounce_prep(q) as lane state instead of q and calls rtm_bounce_rng_pre (one multiply-add less per hit).
+__device__ __forceinline__ uint32_t rtm_bounce_prep(uint32_t q) {
 #ifdef RTM_RNG_PHILOX
-    return rtm_philox2x32_10(c, rk);
+    return q;
 #else
-    uint32_t x = c.x * 1664525u + 1013904223u, y = c.y * 1664525u + 1013904223u, z = rk[0] * 1664525u + 1013904223u;
+    return q * 1664525u + 1013904223u;
+#endif
+}
+__device__ __forceinline__ uint2 rtm_bounce_rng_pre(uint32_t qx, uint32_t cy, const uint32_t* __restrict__ rk);
+__device__ __forceinline__ uint2 rtm_bounce_rng(uint2 c, const uint32_t* __restrict__ rk) { return rtm_bounce_rng_pre(rtm_bounce_prep(c.x), c.y, rk); }
+__device__ __forceinline__ uint2 rtm_bounce_rng_pre(uint32_t qx, uint32_t cy, const uint32_t* __restrict__ rk) {
+#ifdef RTM_RNG_PHILOX
+    return rtm_philox2x32_10(make_uint2(qx, cy), rk);
+#else
+    uint32_t x = qx, y = cy * 1664525u + 1013904223u, z = rk[0] * 1664525u + 1013904223u;
     x += y * z; y += z * x; z += x * y;
     x ^= x >> 16; y ^= y >> 16; z ^= z >> 16;
     x += y * z; y += z * x; z += x * y;
