@@ -151,6 +151,41 @@ def cpu_render_sample(sc, wl, target_seconds: float):
             "seconds": t}
 
 
+def cpu_cli_as_is(sc, wl, budget_s: float = 25.0):
+    """The reference's CLI AS IS (oracle/_ref/ref_abc_cli: its own main.cpp + Render(), src/Renderer.cpp:200-258 — one
+    shared, racing mt19937, an OpenMP fork/join per image row, stb file writes), run on a copy of the workload's scene
+    file scaled down until it fits `budget_s` (the stock loop is ~16x slower than the fair harness).  Wall time of the
+    whole process, as a user of the reference sees it.  None when the binary was not built (no /root/reference)."""
+    exe = os.path.join(ROOT, "oracle", "_ref", "ref_abc_cli")
+    if not os.path.exists(exe) or sc.n_planes or sc.n > 64:
+        return None
+    import tempfile
+    src = json.load(open(os.path.join(ROOT, "scenes", wl.get("file", wl["scene"] + ".head.json"))))
+    cores = len(os.sched_getaffinity(0)) if hasattr(os, "sched_getaffinity") else (os.cpu_count() or 1)
+    # ~1.5 Msamples/s (Cornell) .. 11 Msamples/s (simpleSetting1) on 16 cores in round 1: size the run for the slow end
+    target = 1.2e6 * budget_s
+    w, h, S, ss = sc.width, sc.height, sc.samples, sc.superSamples
+    while w * h * S * ss * ss > target and (w > 60 or S > 1):
+        if w > 60:
+            w, h = w // 2, h // 2
+        else:
+            S = max(1, S // 2)
+    src["00 width"], src["00 height"], src["00 samples"], src["00 superSamples"] = w, h, S, ss
+    with tempfile.TemporaryDirectory() as tmp:
+        jf = os.path.join(tmp, "scene.json")
+        json.dump(src, open(jf, "w"))
+        env = dict(os.environ, OMP_NUM_THREADS=str(cores))
+        t0 = time.perf_counter()
+        rc = subprocess.run([exe, "-json", jf], cwd=tmp, env=env, stdout=subprocess.DEVNULL, stderr=subprocess.DEVNULL,
+                            timeout=max(120.0, 8 * budget_s)).returncode
+        dt = time.perf_counter() - t0
+        ok = rc == 0 and os.path.exists(os.path.join(tmp, "result.bmp"))
+    samples = w * h * S * ss * ss
+    return {"msamples_per_s": samples / dt / 1e6, "wall_s": dt, "cores": cores, "ok": ok,
+            "sample": f"{wl['scene']} {w}x{h} ss={ss} samples={S}: ref_abc_cli -json <file> (stock Render(): shared racing mt19937, "
+                      f"per-row fork/join, result.jpg + result.bmp written), whole-process wall time"}
+
+
 def run_reference_arm(args):
     rank = int(os.environ.get("RANK", "0"))
     if rank != 0:
@@ -298,21 +333,42 @@ def run_gpu_arm(args):
         e2e_s = (time.perf_counter() - t0) / e2e_steps
         d2h = n_pix * 12
     else:
-        host_img = torch.empty((sc.height, sc.width, 4), dtype=torch.float32, pin_memory=True)
+        # N > 1: every rank renders its slice (renderer_render_async), one NCCL sum-reduce into rank 0's accumulation buffer,
+        # then rank 0 reads the image back THROUGH THE C ABI (renderer_read_rgb: repack kernel + one 12 B/pixel copy into a
+        # host buffer, on the stream the reduce ran on) — the same bytes the N = 1 leg's renderer_render delivers
+        host_rgb = np.zeros((sc.height, sc.width, 3), np.float32)
+        if rank == 0:
+            r.read_rgb(host_rgb, stream.cuda_stream)
         fence()
         t0 = time.perf_counter()
         for _ in range(e2e_steps):
             step()
             if rank == 0:
-                host_img.copy_(accum, non_blocking=True)
+                r.read_rgb(host_rgb, stream.cuda_stream)
             fence()
         e2e_s = (time.perf_counter() - t0) / e2e_steps
-        d2h = n_pix * 16
+        d2h = n_pix * 12
     te = torch.tensor([e2e_s], dtype=torch.float64, device=dev)
     if world > 1:
         dist.all_reduce(te, op=dist.ReduceOp.MAX)
     e2e_s = float(te.item())
     h2d = rtm_scene_bytes(sc)
+
+    # untimed: the N-rank image against the SAME frame rendered by one handle on rank 0 (full sample / sub-pixel range).
+    # The RNG is keyed by global indices and the divisor is global, so the two may differ by FP32 summation order only.
+    image_check = None
+    if world > 1:
+        step()
+        fence()
+        if rank == 0:
+            got = accum[..., :3].clone()
+            with rtm.Renderer(sc, device=local, seed=0x5EED, variant=args.variant, estimator=args.estimator, **knobs) as r1:
+                one = torch.from_numpy(r1.render().image).to(dev)
+            diff = (got - one).abs()
+            image_check = {"max_abs_diff": float(diff.max().item()), "max_rel_diff": float((diff / one.abs().clamp_min(1e-3)).max().item()),
+                           "image_max": float(one.max().item()), "what": f"{world}-rank reduced framebuffer vs one handle rendering the whole frame on rank 0"}
+            del got, one, diff
+        fence()
 
     reduce_check = None
     if peer:
@@ -373,16 +429,22 @@ def run_gpu_arm(args):
                        "semantics": "L-ABC (SURVEY.md §0.1), FP64 bit-exact primary pass + FP32 bounces, counter-based pcg3d hash per (sub-pixel, sample, depth)"},
             "msamples_per_s": samples_all / (ms_step * 1e-3) / 1e6,
             "rays_per_sample": rays_all / samples_all,
+            # `value` counts the reference's rays (sum of path lengths: one PathTracing call each, src/Renderer.cpp:57), primary
+            # rays included; the device traces the primary ray once per sub-pixel, not once per sample:
+            "rays_traced_per_s_M": traced_all / (ms_step * 1e-3) / 1e6,
+            "rays_traced_note": "closest-hit queries actually executed per second (primary query shared by a sub-pixel's samples)",
             "e2e": {"value": rays_all / e2e_s / 1e6, "unit": "Mrays/s", "h2d_bytes_per_step": h2d,
                     "d2h_bytes_per_step": d2h, "ms_per_step": e2e_s * 1e3, "steps": e2e_steps},
-            "gpu_launches": (3 + (1 if peer else 0)) * args.steps,
+            "gpu_launches": (3 + (1 if peer else 0)) * args.steps,   # primary_f64 + radiance + accumulate per step (+ the sum kernel of --reduce peer)
             "kernel_ms": {"primary_f64": kms[0], "radiance_mega": kms[1], "accumulate": kms[2]},
             "roofline": {"bound": "fp32", "achieved": achieved, "peak": fp32_peak, "unit": "TFLOP/s",
                          "frac": achieved / fp32_peak if fp32_peak else None,
                          "traffic": ncu_traffic_bytes(args.workload, args.variant) if (world == 1 and args.estimator == "reference") else None,
-                         "traffic_note": "bytes per launch, dram read+write from the committed ncu --set full capture "
-                                         "(profiles/r01); algorithmic = records read + written = 32 B per sub-pixel",
-                         "algorithmic_bytes_per_launch": 32.0 * n_sub,
+                         "traffic_note": "bytes per launch, dram read+write from the committed ncu --set full capture (profiles/); "
+                                         "the design's record round trip (16 B read + 16 B written per sub-pixel) explains it; the "
+                                         "ALGORITHMIC bytes of SURVEY.md 8(d) are one framebuffer write (16 B per pixel)",
+                         "record_roundtrip_bytes_per_launch": 32.0 * n_sub,
+                         "algorithmic_bytes_per_launch": 16.0 * n_pix,
                          "kernel": ("radiance_mega_kernel" if sc.n <= 64 else "radiance_bvh_kernel") if args.variant == "mega"
                                    else "wf_shade_kernel + wf_extend_*_kernel (all waves)",
                          "peak_source": f"FP32 FMA-chain microbenchmark run live on this GPU (implied {implied_mhz:.0f} MHz); "
@@ -391,6 +453,8 @@ def run_gpu_arm(args):
                          "framebuffer_store_GBs": fb_gbs, "hbm_peak_GBs": peaks.get("hbm_gbs")},
             "clocks": clocks,
         }
+        if image_check is not None:
+            line["image_check"] = image_check
         if reduce_check is not None:
             line["reduce_check_max_abs_diff_vs_nccl"] = reduce_check
     if world > 1:
@@ -400,26 +464,30 @@ def run_gpu_arm(args):
 
 def ncu_traffic_bytes(workload: str, variant: str):
     """dram__bytes_read.sum + dram__bytes_write.sum of the dominant kernel, per launch, from the committed
-    `ncu --set full` capture of this very command (profiles/r01/); None when no capture exists for it."""
-    name = {("c4", "mega"): "ncu_megav6_c4_summary.txt", ("c3", "mega"): "ncu_megav5_rt_c3_summary.txt", ("c2p", "mega"): "ncu_planes_v2_c2p_summary.txt", ("c5", "mega"): "ncu_bvh_v4_c5_summary.txt"}.get((workload, variant))
-    if not name:
-        return None
+    `ncu --set full` capture of this very command (profiles/r02, else r01); None when no capture exists for it."""
+    names = {("c4", "mega"): ["r02/ncu_mega_r02_c4_summary.txt", "r02/ncu_mega_r02a_c4_summary.txt", "r01/ncu_megav6_c4_summary.txt"],
+             ("c3", "mega"): ["r01/ncu_megav5_rt_c3_summary.txt"], ("c2p", "mega"): ["r01/ncu_planes_v2_c2p_summary.txt"],
+             ("c5", "mega"): ["r02/ncu_bvh_r02_c5_summary.txt", "r02/ncu_bvh_r02a_c5_summary.txt", "r01/ncu_bvh_v4_c5_summary.txt"]}.get((workload, variant), [])
     unit = {"Gbyte": 1e9, "Mbyte": 1e6, "Kbyte": 1e3, "byte": 1.0}
-    total, seen = 0.0, 0
-    try:
-        for ln in open(os.path.join(ROOT, "profiles", "r01", name)):
-            if ln.startswith(("dram__bytes_read.sum", "dram__bytes_write.sum")):
-                u = ln[ln.index("[") + 1:ln.index("]")]
-                total += float(ln.split("=")[1]) * unit[u]
-                seen += 1
-    except Exception:
-        return None
-    return total if seen == 2 else None
+    for name in names:
+        total, seen = 0.0, 0
+        try:
+            for ln in open(os.path.join(ROOT, "profiles", name)):
+                if ln.startswith(("dram__bytes_read.sum", "dram__bytes_write.sum")):
+                    u = ln[ln.index("[") + 1:ln.index("]")]
+                    total += float(ln.split("=")[1]) * unit[u]
+                    seen += 1
+        except Exception:
+            continue
+        if seen == 2:
+            return total
+    return None
 
 
 def rtm_scene_bytes(sc) -> int:
-    """bytes of scene data uploaded per pass (the __constant__ SoA block of the FP32 path)."""
-    return 4 + 15 * 256 * 4
+    """bytes of scene data renderer_render uploads per call: the handle's FP32 per-sphere block (RtmSceneF32Host) plus the
+    kernel parameters (RtmHotScene + RtmPassParams) of the three launches."""
+    return 19248 + 2 * (1312 + 248) + 248   # sizeof(RtmSceneF32Host) + params of primary (RtmPassParams), radiance (hot + params), accumulate
 
 
 def main():
@@ -447,6 +515,9 @@ def main():
         if int(os.environ.get("WORLD_SIZE", "1")) == 1 and not args.no_cpu_baseline:
             cb = cpu_render_sample(sc, wl, 12.0)
             cb.pop("seconds")
+            cli = cpu_cli_as_is(sc, wl)
+            if cli is not None:
+                cb["cli_as_is"] = cli     # BOTH CPU figures — the stock CLI and the fair harness — in one record
             line["cpu_baseline"] = cb
         print(json.dumps(line), flush=True)
     r.close()
