@@ -27,7 +27,7 @@ int rtmh_load_scene(const char* path, int compat_head, int* dims, double* cam, f
         }
         if (fov) *fov = d.camera.fov;
         const int n = (int)d.object.size();
-        if (position && n <= cap) {
+        if (position && n > 0 && n <= cap) {   // n == 0: empty vectors hand memcpy a null source (UB even for 0 bytes)
             std::memcpy(position, d.object.position.data(), sizeof(double) * 3 * n);
             std::memcpy(radius, d.object.radius.data(), sizeof(float) * n);
             std::memcpy(color, d.object.color.data(), sizeof(double) * 3 * n);
@@ -48,7 +48,7 @@ int rtmh_load_planes(const char* path, int cap, double* position, double* up, do
         png::LoadData ld(path, png::Compat::Abc);
         const png::PlaneList& P = ld.data.plane;
         const int m = (int)P.size();
-        if (position && m <= cap) {
+        if (position && m > 0 && m <= cap) {
             std::memcpy(position, P.position.data(), sizeof(double) * 3 * m);
             std::memcpy(up, P.up.data(), sizeof(double) * 3 * m);
             std::memcpy(target, P.target.data(), sizeof(double) * 3 * m);
@@ -56,7 +56,7 @@ int rtmh_load_planes(const char* path, int cap, double* position, double* up, do
             std::memcpy(color, P.color.data(), sizeof(double) * 3 * m);
             std::memcpy(emission, P.emission.data(), sizeof(double) * 3 * m);
         }
-        if (order_out && (int)ld.data.order.size() <= order_cap)
+        if (order_out && !ld.data.order.empty() && (int)ld.data.order.size() <= order_cap)
             std::memcpy(order_out, ld.data.order.data(), sizeof(int) * ld.data.order.size());
         return m;
     } catch (const std::exception& e) {

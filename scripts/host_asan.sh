@@ -1,18 +1,14 @@
 #!/bin/bash
-# -fsanitize=address,undefined build of the host front end (loader, writers, C surface) under the CPU
-# tests that exercise it.  The sanitised librtm_host.so replaces the normal one for the run and is removed afterwards.
-set -e
+# -fsanitize=address,undefined build of the host front end (loader, JSON reader/writer, BMP/JPEG
+# writers, C surface) driven by tests/native/host_sanitize_driver.cpp.  Log: profiles/r02/host_asan_ubsan.log
 cd "$(dirname "$0")/.."
 H=raytracingmin_b200/host
-CXX=${CXX:-g++}
-cp $H/librtm_host.so /tmp/librtm_host.keep.so
-$CXX -std=c++17 -O1 -g -fno-omit-frame-pointer -fsanitize=address,undefined -fno-sanitize-recover=undefined -fPIC -ffp-contract=off \
-    -shared -o $H/librtm_host.so $H/host_capi.cpp $H/SettingData.cpp
-ASAN=$($CXX -print-file-name=libasan.so)
-set +e
-LD_PRELOAD=$ASAN ASAN_OPTIONS=detect_leaks=0:abort_on_error=1 UBSAN_OPTIONS=print_stacktrace=1 \
-    python -m pytest tests/test_host_frontend.py tests/test_planes_host.py -q -m "not gpu" 2>&1 | tail -15
-rc=${PIPESTATUS[0]}
-cp /tmp/librtm_host.keep.so $H/librtm_host.so
+CXX=${CXX:-/usr/bin/g++}
+T=$(mktemp -d)
+$CXX -std=c++17 -O1 -g -fno-omit-frame-pointer -fsanitize=address,undefined -fno-sanitize-recover=undefined -ffp-contract=off \
+    -o $T/host_san tests/native/host_sanitize_driver.cpp $H/host_capi.cpp $H/SettingData.cpp -B/usr/lib/gcc/x86_64-linux-gnu/13 -L/usr/lib/gcc/x86_64-linux-gnu/13 || exit 2
+ASAN_OPTIONS=detect_leaks=1 UBSAN_OPTIONS=print_stacktrace=1 $T/host_san scenes $T
+rc=$?
 echo "host asan/ubsan rc=$rc"
+rm -rf $T
 exit $rc
