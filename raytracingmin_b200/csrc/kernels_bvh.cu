@@ -17,7 +17,7 @@ namespace {
 // only then is the S block run (for those lanes together), so S code runs at >= 25 % and T code
 // at >= 75 % lane occupancy (Aila & Laine's persistent threads with a refill threshold).
 #ifndef RTM_BVH_S_THRESH
-#define RTM_BVH_S_THRESH 16
+#define RTM_BVH_S_THRESH 12   // swept again on the compact-node walk (r02): 12 6.18, 16 6.11, 20 5.95, 24 5.60 Grays/s on C5
 #endif
 #ifndef RTM_BVH_BURST
 #define RTM_BVH_BURST 8
@@ -62,28 +62,16 @@ radiance_bvh_kernel(const __grid_constant__ RtmHotScene hot, const __grid_consta
 
     unsigned w_next = 0, w_end = 0;
     bool have = false, done = false, tracing = false, pending = false;
+    bool fresh = false;              // the lane stands on its sub-pixel's primary hit, and the S block has yet to load it
     unsigned q = 0, ql = 0;
     f3 acc = mk(0, 0, 0);
-    f3 o = mk(0, 0, 0), w = mk(0, 0, 1), T = mk(1, 1, 1), L = mk(0, 0, 0), d = mk(0, 0, 1);
+    f3 o = mk(0, 0, 0), T = mk(1, 1, 1), L = mk(0, 0, 0), d = mk(0, 0, 1);
     int id = 0, s = 0, depth = 0;
-    float cpsn = 0.f;
+    // The oriented normal w and the ACNE state cpsn are NOT lane state: they are produced (apply_hit / stand_on_primary) and
+    // consumed (roulette, direction sampling) inside one S block, so they are locals of that block — four registers that
+    // the T block's |1/d| needs (72 registers = 7 resident blocks either way).
     int sslot = -1;                  // leaf slot of the sphere the current ray leaves (self test inside the leaves)
     uint32_t eps_bits = 0;
-    // the primary hit of the lane's sub-pixel is NOT lane state here: it is re-read from records[ql] (which holds it
-    // until the sub-pixel's sum is written) at every sample restart — 8 registers less, which is what lets
-    // RTM_BVH_MINBLOCKS blocks stay resident
-    auto stand_on_primary = [&](const float4 rec) {
-        const unsigned wbits = __float_as_uint(rec.w);
-        const int pid = (int)(wbits & RTM_REC_IDMASK);
-        const float4 g = __ldg(mat.geo + pid), e0 = __ldg(mat.emi + pid);
-        const float ir = (wbits & RTM_REC_FLIP) ? -g.w : g.w;
-        o = mk(rec.x, rec.y, rec.z);
-        w = mk((o.x - g.x) * ir, (o.y - g.y) * ir, (o.z - g.z) * ir);
-        if (PL && pid >= n_sph) w = (wbits & RTM_REC_FLIP) ? mk(-g.x, -g.y, -g.z) : mk(g.x, g.y, g.z);
-        id = pid;
-        T = mk(1, 1, 1); L = mk(e0.x, e0.y, e0.z); depth = 0;
-        if (ACNE) cpsn = (wbits & RTM_REC_FLIP) ? 0.f : cps0[ql] * g.w * RTM_ACNE_INV2TAU;
-    };
     BvhRay ray;
     ray.node = RTM_BVH_NONE_DEV;
     constexpr int ST = SST ? RTM_MEGA_THREADS : 1;
@@ -141,7 +129,7 @@ radiance_bvh_kernel(const __grid_constant__ RtmHotScene hot, const __grid_consta
                     have = true;
                     acc = mk(0, 0, 0);
                     s = s_begin;
-                    stand_on_primary(rec);
+                    fresh = true;   // the S block of this very iteration stands the lane on its primary hit
                 }
             }
             const unsigned took = (__popc(need) < avail) ? __popc(need) : avail;
@@ -164,6 +152,23 @@ radiance_bvh_kernel(const __grid_constant__ RtmHotScene hot, const __grid_consta
         // need one.
         const bool in_s = (tr == 0u || __popc(sready) >= RTM_BVH_S_THRESH) && have && !tracing;
         if (__any_sync(0xffffffffu, in_s)) {
+            f3 w = mk(0, 0, 1);
+            float cpsn = 0.f;
+    // the primary hit of the lane's sub-pixel is NOT lane state here: it is re-read from records[ql] (which holds it
+            // until the sub-pixel's sum is written) at every sample restart — 8 registers less, which is what lets
+            // RTM_BVH_MINBLOCKS blocks stay resident
+            auto stand_on_primary = [&](const float4 rec) {
+                const unsigned wbits = __float_as_uint(rec.w);
+                const int pid = (int)(wbits & RTM_REC_IDMASK);
+                const float4 g = __ldg(mat.geo + pid), e0 = __ldg(mat.emi + pid);
+                const float ir = (wbits & RTM_REC_FLIP) ? -g.w : g.w;
+                o = mk(rec.x, rec.y, rec.z);
+                w = mk((o.x - g.x) * ir, (o.y - g.y) * ir, (o.z - g.z) * ir);
+                if (PL && pid >= n_sph) w = (wbits & RTM_REC_FLIP) ? mk(-g.x, -g.y, -g.z) : mk(g.x, g.y, g.z);
+                id = pid;
+                T = mk(1, 1, 1); L = mk(e0.x, e0.y, e0.z); depth = 0;
+                if (ACNE) cpsn = (wbits & RTM_REC_FLIP) ? 0.f : cps0[ql] * g.w * RTM_ACNE_INV2TAU;
+            };
             // a finished ray is applied to the path; returns true when the path ends there
             auto apply_hit = [&](int id2, float t) -> bool {
                 if (id2 < 0) return true;                                            // miss: Renderer.cpp:116
@@ -189,6 +194,10 @@ radiance_bvh_kernel(const __grid_constant__ RtmHotScene hot, const __grid_consta
                 return __float_as_uint(e2.w) == 0u;                                  // kd == 0: the next roulette cannot continue
             };
             bool end = false;
+            if (in_s && fresh) {
+                fresh = false;
+                stand_on_primary(records[ql]);
+            }
             if (in_s && pending) {
                 pending = false;
                 end = apply_hit(bvh_resolve_hit(bvh, ray.hit), ray.best + RTM_T_EPS);
@@ -244,6 +253,7 @@ radiance_bvh_kernel(const __grid_constant__ RtmHotScene hot, const __grid_consta
                 }
                 if (__popc(__ballot_sync(0xffffffffu, deciding)) < RTM_BVH_S_ROUND) break;
             }
+            if (deciding && have) fresh = true;   // (only with RTM_BVH_S_ROUND > 1) restarted in the last round: stands on its primary hit
             if (start) {
                 // the packed big-sphere test (~140 instructions) and the planes: once, for all lanes that start a ray
                 bvh_ray_begin<NP, ST, H16>(hot, sh_mask, sh_big, bvh, bvh_big_slot(ocode), o, d, key_mask, ray, stack, n_tests);
@@ -279,11 +289,13 @@ radiance_bvh_kernel(const __grid_constant__ RtmHotScene hot, const __grid_consta
             else if (tracing && ray.node < 0) bvh_leaf_step<ST>(bvh, sslot, o, d, ray, stack, n_tests);
 #else
 #pragma unroll 1
-            for (int k = 0; k < RTM_BVH_BURST && tracing && bvh_is_inner(ray.node); ++k) {
+            int k = 0;
+#pragma unroll 1
+            for (; k < RTM_BVH_BURST && tracing && bvh_is_inner(ray.node); ++k) {
                 if (H16) bvh16_inner_step<ST>(bvh, ray, stack);
                 else bvh_inner_step<ST>(bvh, ray, stack);
-                ++n_nodes;
             }
+            n_nodes += (unsigned)k;   // visits counted once per burst, not once per step
             if (tracing && ray.node < 0) bvh_leaf_step<ST>(bvh, sslot, o, d, ray, stack, n_tests);
 #endif
             if (tracing && ray.node == RTM_BVH_NONE_DEV) {

@@ -285,6 +285,7 @@ __device__ __forceinline__ bool bvh_is_inner(int node) { return (unsigned)node <
 // Ray state of one lane inside the hierarchy.  best = candidate (root - eps), as in the packed test.
 struct BvhRay {
     f3 inv, oi;      // 1/d and o/d
+    f3 ainv;         // |1/d| (compact-node walk only: near/far = t_c -+ h |1/d| as two FFMA)
     float best;
     int hit;         // original sphere index of the current winner, -1 = none
     int node;        // current node (child code), RTM_BVH_NONE_DEV when the traversal is over
@@ -313,6 +314,7 @@ __device__ __forceinline__ void bvh_ray_begin(const RtmHotScene& hot, const Self
     if (H16) {
         r.oi = mk((o.x - bvh.ref16[0]) * r.inv.x, (o.y - bvh.ref16[1]) * r.inv.y, (o.z - bvh.ref16[2]) * r.inv.z);
         r.inv = mk(r.inv.x * bvh.inv_scale16, r.inv.y * bvh.inv_scale16, r.inv.z * bvh.inv_scale16);
+        r.ainv = mk(fabsf(r.inv.x), fabsf(r.inv.y), fabsf(r.inv.z));
     } else {
         r.oi = mk(o.x * r.inv.x, o.y * r.inv.y, o.z * r.inv.z);
     }
@@ -360,14 +362,13 @@ __device__ __forceinline__ void bvh_inner_step(const RtmBvhDev& bvh, BvhRay& r, 
 // ---- the same step on the compact node (bvh.h: RtmBvh16Host): ONE 32-byte request, (centre, half-extent) boxes in half
 // precision.  near/far = (c.inv - oi) -+ |h.inv|: no per-axis min/max.  NaN (0 * inf) drops out of the min/max as in
 // box_test_f32: that slab is ignored.
-__device__ __forceinline__ bool box_test_h16(unsigned w0, unsigned w1, unsigned w2, f3 oi, f3 inv, float tmax_in, float& tnear) {
+__device__ __forceinline__ bool box_test_h16(unsigned w0, unsigned w1, unsigned w2, f3 oi, f3 inv, f3 ainv, float tmax_in, float& tnear) {
     const float2 a = __half22float2(*reinterpret_cast<const __half2*>(&w0));   // cx, cy
     const float2 b = __half22float2(*reinterpret_cast<const __half2*>(&w1));   // cz, hx
     const float2 c = __half22float2(*reinterpret_cast<const __half2*>(&w2));   // hy, hz
     const float tx = fmaf(a.x, inv.x, -oi.x), ty = fmaf(a.y, inv.y, -oi.y), tz = fmaf(b.x, inv.z, -oi.z);
-    const float px = fabsf(b.y * inv.x), py = fabsf(c.x * inv.y), pz = fabsf(c.y * inv.z);
-    const float tmin = fmaxf(fmaxf(tx - px, ty - py), fmaxf(tz - pz, 0.f));
-    const float tmax = fminf(fminf(tx + px, ty + py), fminf(tz + pz, tmax_in));
+    const float tmin = fmaxf(fmaxf(fmaf(-b.y, ainv.x, tx), fmaf(-c.x, ainv.y, ty)), fmaxf(fmaf(-c.y, ainv.z, tz), 0.f));
+    const float tmax = fminf(fminf(fmaf(b.y, ainv.x, tx), fmaf(c.x, ainv.y, ty)), fminf(fmaf(c.y, ainv.z, tz), tmax_in));
     tnear = tmin;
     return tmin <= tmax;
 }
@@ -382,8 +383,8 @@ __device__ __forceinline__ void bvh16_inner_step(const RtmBvhDev& bvh, BvhRay& r
     ldg256u(bvh.nodes16 + 8 * r.node, a, b);
     float n0, n1;
     const float tm = r.best + 2.f * RTM_T_EPS;
-    const bool h0 = box_test_h16(a.x, a.y, a.z, r.oi, r.inv, tm, n0);
-    const bool h1 = box_test_h16(a.w, b.x, b.y, r.oi, r.inv, tm, n1);
+    const bool h0 = box_test_h16(a.x, a.y, a.z, r.oi, r.inv, r.ainv, tm, n0);
+    const bool h1 = box_test_h16(a.w, b.x, b.y, r.oi, r.inv, r.ainv, tm, n1);
     const int c0 = (int)b.z, c1 = (int)b.w;
     if (h0 && h1) {
         const bool swap = n1 < n0;

@@ -13,6 +13,11 @@ namespace {
 #ifndef RTM_MEGA_RETRY
 #define RTM_MEGA_RETRY 12   // lanes killed by the roulette in one round that trigger another round before the bounce block
 #endif
+// Sub-pixels a warp reserves per global atomic.  16, not round 1's 64: a warp keeps at most half a round of private
+// backlog when the cursor runs dry (the persistent kernel's tail was 0.86 ms of a 45.9 ms step at 8 GPUs, SCALE_r01), and
+// short frames gain (C3 166.0 -> 169.3 Grays/s, C4 unchanged: profiles/r02/mega_variants_ab2.jsonl).  A "guided" cursor
+// (chunks shrinking near the end) was measured too: C3 +3.6 % but C4 -3.5 %, its refill code changes the hot loop's schedule.
+#define RTM_MEGA_FETCH 16u
 #ifndef RTM_MEGA_MINBLOCKS
 #define RTM_MEGA_MINBLOCKS 6
 #endif
@@ -86,9 +91,8 @@ radiance_mega_kernel(const __grid_constant__ RtmHotScene hot, const __grid_const
     const unsigned sub_begin = (unsigned)p.sub_begin, sub_count = (unsigned)p.sub_count;
     const unsigned grid = (unsigned)(p.frame.ss * p.frame.ss);
     const bool full_grid = (sub_count == grid);
-    // unit (sub-pixel) state: ql = record index in this handle's slice, qx = rtm_bounce_prep(global sub-pixel index)
-    unsigned qx = 0, ql = 0;
-    const unsigned total_warps = gridDim.x * (RTM_MEGA_THREADS / 32);
+    // unit (sub-pixel) state: ql = record index in this handle's slice, q = global sub-pixel index
+    unsigned q = 0, ql = 0;
     f3 acc = mk(0, 0, 0);            // CL only
     // path state
     f3 o = mk(0, 0, 0), w = mk(0, 0, 1), T = mk(1, 1, 1), L = mk(0, 0, 0);
@@ -107,25 +111,15 @@ radiance_mega_kernel(const __grid_constant__ RtmHotScene hot, const __grid_const
             unsigned need = wdone ? 0u : __ballot_sync(0xffffffffu, !have);
             while (need) {
                 if (w_next == w_end) {
-                    // guided self-scheduling: RTM_MEGA_CHUNK sub-pixels per fetch while plenty are left, half of an even
-                    // share (at least 4) near the end, so that no warp sits on a private backlog of two more rounds when the
-                    // cursor runs dry (the tail was 0.86 ms of a 45.9 ms step at 8 GPUs, SCALE_r01)
                     unsigned long long start = 0;
-                    unsigned chunk = RTM_MEGA_CHUNK;
-                    if (lane == 0) {
-                        const unsigned long long seen = *(volatile unsigned long long*)&counters->work_next;
-                        const unsigned long long fair = (seen < n_sub ? n_sub - seen : 0ull) / (2ull * total_warps);
-                        chunk = fair >= RTM_MEGA_CHUNK ? RTM_MEGA_CHUNK : (fair < 4ull ? 4u : (unsigned)fair);
-                        start = atomicAdd(&counters->work_next, (unsigned long long)chunk);
-                    }
+                    if (lane == 0) start = atomicAdd(&counters->work_next, (unsigned long long)RTM_MEGA_FETCH);
                     start = __shfl_sync(0xffffffffu, start, 0);
-                    chunk = __shfl_sync(0xffffffffu, chunk, 0);
                     if (start >= (unsigned long long)n_sub) {
                         wdone = true;
                         break;
                     }
                     w_next = (unsigned)start;
-                    w_end = (start + chunk < (unsigned long long)n_sub) ? (unsigned)start + chunk : n_sub;
+                    w_end = (start + RTM_MEGA_FETCH < (unsigned long long)n_sub) ? (unsigned)start + RTM_MEGA_FETCH : n_sub;
                 }
                 const unsigned avail = w_end - w_next;
                 const unsigned rank = __popc(need & lt_mask);
@@ -133,7 +127,7 @@ radiance_mega_kernel(const __grid_constant__ RtmHotScene hot, const __grid_const
                 if (mine) {
                     ql = w_next + rank;
                     // RNG counter = GLOBAL sub-pixel index, so the image does not depend on the partition
-                    qx = rtm_bounce_prep(full_grid ? ql : (ql / sub_count) * grid + sub_begin + (ql % sub_count));
+                    q = full_grid ? ql : (ql / sub_count) * grid + sub_begin + (ql % sub_count);
                     const float4 rec = records[ql];
                     const unsigned wbits = __float_as_uint(rec.w);
                     const bool miss = (wbits == RTM_REC_MISS);
@@ -213,14 +207,14 @@ radiance_mega_kernel(const __grid_constant__ RtmHotScene hot, const __grid_const
         // trigger, but the loop's mere presence costs 8 % (111 vs 120.5 Grays/s), hence a template flag set by the
         // host from the scene (rtm_api.cu).  Draws are keyed by (sub-pixel, sample, depth): the image does not depend
         // on the number of rounds, nor on the flag.
-        uint2 rnd = rtm_bounce_rng_pre(qx, sd, p.rk);
+        uint2 rnd = rtm_bounce_rng(make_uint2(q, sd), p.rk);
         bool go = have && (rnd.x < thr) && ((sd & 511u) < dcap);
         if (RT) {
             bool killed = have && !go;
             while (__popc(__ballot_sync(0xffffffffu, killed)) >= RTM_MEGA_RETRY) {   // warp-uniform
                 if (killed) {
                     close_sample();
-                    rnd = rtm_bounce_rng_pre(qx, sd, p.rk);
+                    rnd = rtm_bounce_rng(make_uint2(q, sd), p.rk);
                     go = have && (rnd.x < thr) && ((sd & 511u) < dcap);
                     killed = have && !go;
                 }
@@ -232,7 +226,7 @@ radiance_mega_kernel(const __grid_constant__ RtmHotScene hot, const __grid_const
             const float4 al = sh.alb[id];
             T.x *= al.x; T.y *= al.y; T.z *= al.z;   // colorKD, SettingData.h:11-13
             if (NEE) {
-                const uint2 r2 = rtm_bounce_rng_pre(qx, sd, p.rk + 1);
+                const uint2 r2 = rtm_bounce_rng(make_uint2(q, sd), p.rk + 1);
                 const unsigned nl = (unsigned)hot.n_lights;
                 const unsigned k = __umulhi(r2.x, nl);
                 const float4 lg = sh_lgeo[k], le = sh_lemi[k];

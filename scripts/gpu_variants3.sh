@@ -2,7 +2,7 @@
 # A/B of prebuilt library variants (variants_<name>.so in the repo root) on several workloads: W="c4 c2 c3"
 mkdir -p gpurun_out
 cp raytracingmin_b200/librtm_b200.so /tmp/librtm_keep.so
-for f in variants_*.so; do
+for f in ${PAT:-variants_*.so}; do
   name=${f#variants_}; name=${name%.so}
   cp $f raytracingmin_b200/librtm_b200.so
   for w in ${W:-c4}; do
