@@ -55,6 +55,12 @@ struct Builder {
         Sub s;
         s.box.reset();
         s.rmin = DBL_MAX;
+        // a leaf of two or more spheres starts on an EVEN slot: the FP32 walk fetches its spheres two per 32-byte request.
+        // The pad slot holds a sphere nothing can hit (id -1); no leaf code covers it.
+        if (e - b >= 2 && (out->leaf_id.size() & 1u)) {
+            out->leaf_geo.push_back(make_float4(3e18f, 3e18f, 3e18f, 0.f));
+            out->leaf_id.push_back(-1);
+        }
         const uint32_t first = (uint32_t)out->leaf_id.size();
         for (int i = b; i < e; ++i) {
             const Prim& p = prims[i];
@@ -229,6 +235,10 @@ bool rtm_bvh_build(int32_t n, const double* position, const float* radius, const
     const Builder::Sub root = bl.build(0, (int)bl.prims.size(), 0);
     out.root = root.code;
     out.depth = bl.max_depth;
+    if (out.leaf_id.size() & 1u) {   // even length: the last pair fetch stays inside the array
+        out.leaf_geo.push_back(make_float4(3e18f, 3e18f, 3e18f, 0.f));
+        out.leaf_id.push_back(-1);
+    }
     if (root.code >= 0) {
         // renumber the inner nodes breadth-first: node 0 is the root and the first 2^k - 1 indices are the top
         // k levels (neighbouring cache lines for the part of the tree every ray walks; a shared-memory copy of

@@ -63,10 +63,12 @@ radiance_bvh_kernel(const __grid_constant__ RtmHotScene hot, const __grid_consta
     unsigned w_next = 0, w_end = 0;
     bool have = false, done = false, tracing = false, pending = false;
     bool fresh = false;              // the lane stands on its sub-pixel's primary hit, and the S block has yet to load it
-    unsigned q = 0, ql = 0;
+    unsigned ql = 0;                 // record index; the global sub-pixel index (RNG counter) is derived from it where it is needed
     f3 acc = mk(0, 0, 0);
     f3 o = mk(0, 0, 0), T = mk(1, 1, 1), L = mk(0, 0, 0), d = mk(0, 0, 1);
-    int id = 0, s = 0, depth = 0;
+    int id = 0;
+    unsigned sd = 0;                 // sample << 9 | depth: the RNG counter word itself (as in radiance_mega_kernel)
+    const unsigned sd_end = (unsigned)p.s_end << 9;
     // The oriented normal w and the ACNE state cpsn are NOT lane state: they are produced (apply_hit / stand_on_primary) and
     // consumed (roulette, direction sampling) inside one S block, so they are locals of that block — four registers that
     // the T block's |1/d| needs (72 registers = 7 resident blocks either way).
@@ -78,8 +80,20 @@ radiance_bvh_kernel(const __grid_constant__ RtmHotScene hot, const __grid_consta
     __shared__ int sh_stack[SST ? RTM_BVH_SSTACK * RTM_MEGA_THREADS : 1];
     int lstack[SST ? 1 : RTM_BVH_STACK_DEV];
     int* const stack = SST ? (sh_stack + threadIdx.x) : lstack;
-    unsigned long long rays_ref = 0, traced = 0;
+    // per-lane counters, all 32-bit (register pressure: the kernel sits at 72): sub-pixels done, bounce rays, sphere tests,
+    // node visits.  They are flushed to the 64-bit device counters whenever one passes 2^31, checked when a sub-pixel ends.
+    unsigned units = 0, traced = 0;
     unsigned n_tests = 0, n_nodes = 0;
+    const unsigned ns_all = (unsigned)(p.s_end - p.s_begin);
+    auto flush_if_big = [&]() {
+        if ((traced | n_tests | n_nodes) & 0x80000000u) {
+            atomicAdd(&counters->rays_ref, (unsigned long long)traced);
+            atomicAdd(&counters->rays_traced, (unsigned long long)traced);
+            atomicAdd(&counters->tests, (unsigned long long)n_tests);
+            atomicAdd(&counters->nodes, (unsigned long long)n_nodes);
+            traced = n_tests = n_nodes = 0;
+        }
+    };
 
     for (;;) {
         // ---- refill (warp-uniform): lanes without a sub-pixel take the next ones of the warp's chunk
@@ -109,7 +123,6 @@ radiance_bvh_kernel(const __grid_constant__ RtmHotScene hot, const __grid_consta
             const bool mine = ((need >> lane) & 1u) && rank < avail;
             if (mine) {
                 ql = w_next + rank;
-                q = full_grid ? ql : (ql / sub_count) * grid + sub_begin + (ql % sub_count);
                 const float4 rec = records[ql];
                 const unsigned wbits = __float_as_uint(rec.w);
                 const unsigned ns = (unsigned)(s_end - s_begin);
@@ -124,11 +137,11 @@ radiance_bvh_kernel(const __grid_constant__ RtmHotScene hot, const __grid_consta
                         out.z = clamp01f(e0.z * inv_norm) * (float)ns;
                     }
                     records[ql] = out;
-                    rays_ref += ns;
+                    ++units;
                 } else {
                     have = true;
                     acc = mk(0, 0, 0);
-                    s = s_begin;
+                    sd = (unsigned)s_begin << 9;
                     fresh = true;   // the S block of this very iteration stands the lane on its primary hit
                 }
             }
@@ -166,7 +179,7 @@ radiance_bvh_kernel(const __grid_constant__ RtmHotScene hot, const __grid_consta
                 w = mk((o.x - g.x) * ir, (o.y - g.y) * ir, (o.z - g.z) * ir);
                 if (PL && pid >= n_sph) w = (wbits & RTM_REC_FLIP) ? mk(-g.x, -g.y, -g.z) : mk(g.x, g.y, g.z);
                 id = pid;
-                T = mk(1, 1, 1); L = mk(e0.x, e0.y, e0.z); depth = 0;
+                T = mk(1, 1, 1); L = mk(e0.x, e0.y, e0.z); sd &= ~511u;
                 if (ACNE) cpsn = (wbits & RTM_REC_FLIP) ? 0.f : cps0[ql] * g.w * RTM_ACNE_INV2TAU;
             };
             // a finished ray is applied to the path; returns true when the path ends there
@@ -187,7 +200,7 @@ radiance_bvh_kernel(const __grid_constant__ RtmHotScene hot, const __grid_consta
                 const bool flip = !(dot(nn, d) < 0.f);                               // :82-83
                 w = flip ? mk(-nn.x, -nn.y, -nn.z) : nn;
                 id = id2;
-                ++depth;
+                ++sd;
                 if (ACNE) cpsn = flip ? 0.f : t * t * ref_normalize_eps(eps_bits) * g.w * RTM_ACNE_INV2TAU;
                 const float4 e2 = __ldg(mat.emi + id2);
                 L.x = fmaf(T.x, e2.x, L.x); L.y = fmaf(T.y, e2.y, L.y); L.z = fmaf(T.z, e2.z, L.z);
@@ -207,9 +220,12 @@ radiance_bvh_kernel(const __grid_constant__ RtmHotScene hot, const __grid_consta
             for (;;) {
                 if (deciding) {
                     if (!end) {
-                        const uint2 rnd = rtm_bounce_rng(make_uint2(q, ((unsigned)s << 9) | (unsigned)depth), p.rk);
+                        // RNG counter = GLOBAL sub-pixel index: the image does not depend on the partition (one register less
+                        // than carrying it; the division only exists for sub-pixel-sliced multi-GPU handles)
+                        const unsigned q = full_grid ? ql : (ql / sub_count) * grid + sub_begin + (ql % sub_count);
+                        const uint2 rnd = rtm_bounce_rng(make_uint2(q, sd), p.rk);
                         const float4 em = __ldg(mat.emi + id);
-                        end = !((rnd.x < __float_as_uint(em.w)) && (depth + 1 < p.max_depth));   // Renderer.cpp:78
+                        end = !((rnd.x < __float_as_uint(em.w)) && ((sd & 511u) + 1u < (unsigned)p.max_depth));   // Renderer.cpp:78
                         if (!end) {
                             const float4 al = __ldg(mat.alb + id);
                             T.x *= al.x; T.y *= al.y; T.z *= al.z;                               // colorKD
@@ -239,10 +255,11 @@ radiance_bvh_kernel(const __grid_constant__ RtmHotScene hot, const __grid_consta
                         acc.x += clamp01f(L.x * inv_norm);
                         acc.y += clamp01f(L.y * inv_norm);
                         acc.z += clamp01f(L.z * inv_norm);
-                        ++s;
-                        if (s == s_end) {
+                        sd = (sd | 511u) + 1u;   // next sample, depth 0
+                        if (sd == sd_end) {
                             records[ql] = make_float4(acc.x, acc.y, acc.z, 0.f);
-                            rays_ref += (unsigned)(s_end - s_begin);
+                            ++units;
+                            flush_if_big();
                             have = false;
                             deciding = false;
                         } else {
@@ -288,7 +305,6 @@ radiance_bvh_kernel(const __grid_constant__ RtmHotScene hot, const __grid_consta
             if (tracing && held != 0) bvh_leaf_test(bvh, held, sslot, o, d, ray, n_tests);
             else if (tracing && ray.node < 0) bvh_leaf_step<ST>(bvh, sslot, o, d, ray, stack, n_tests);
 #else
-#pragma unroll 1
             int k = 0;
 #pragma unroll 1
             for (; k < RTM_BVH_BURST && tracing && bvh_is_inner(ray.node); ++k) {
@@ -308,17 +324,17 @@ radiance_bvh_kernel(const __grid_constant__ RtmHotScene hot, const __grid_consta
         }
     }
 
-    rays_ref += traced;
+    unsigned long long rays_ref = (unsigned long long)units * ns_all + traced, traced64 = traced;
     unsigned long long tests = n_tests, nodes = n_nodes;
     for (int off = 16; off > 0; off >>= 1) {
         rays_ref += __shfl_down_sync(0xffffffffu, rays_ref, off);
-        traced += __shfl_down_sync(0xffffffffu, traced, off);
+        traced64 += __shfl_down_sync(0xffffffffu, traced64, off);
         tests += __shfl_down_sync(0xffffffffu, tests, off);
         nodes += __shfl_down_sync(0xffffffffu, nodes, off);
     }
     if (lane == 0) {
         atomicAdd(&counters->rays_ref, rays_ref);
-        atomicAdd(&counters->rays_traced, traced);
+        atomicAdd(&counters->rays_traced, traced64);
         atomicAdd(&counters->tests, tests);
         atomicAdd(&counters->nodes, nodes);
     }

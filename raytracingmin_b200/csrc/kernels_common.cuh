@@ -406,7 +406,67 @@ __device__ __forceinline__ int bvh_resolve_hit(const RtmBvhDev& bvh, int hit) { 
 __device__ __forceinline__ int bvh_big_slot(int code) { return (code >= 8) ? -1 : code; }
 __device__ __forceinline__ int bvh_leaf_slot(int code) { return code - 8; }
 
-// one leaf: 1..4 spheres in the direct form; self_slot = leaf slot of the sphere the ray leaves (negative: none)
+// one leaf: 1..4 spheres in the direct form; self_slot = leaf slot of the sphere the ray leaves (negative: none).
+// The spheres are tested in PAIRS: the builder starts every leaf of two or more spheres on an even slot, so one 32-byte
+// request (LDG.256) brings two of them, and the 17 multiply-adds of the direct form run as f32x2 for both (p = c - o,
+// b = p.d, l = p - b d, D = r^2 - |l|^2, c' = |p|^2 - r^2).  The discriminant is taken as r^2 - |p - b d|^2:
+// b^2 - (|p|^2 - r^2) cancels at |p|^2 ~ 400 and leaves an error of 3e-4 against r^2 = 2.5e-3 for the smallest spheres.
+// The candidate (root - eps) is compared as an unsigned integer: NaN (negative discriminant) and negative roots have bit
+// patterns above +inf and drop out without a compare of their own.
+#ifndef RTM_BVH_LEAF_SCALAR
+// candidate key of one sphere: bits of (smallest root > eps) - eps, or a pattern above +inf when there is none
+__device__ __forceinline__ unsigned bvh_leaf_key(bool self, float nb, float D, float cp) {
+    const float b = -nb;
+    cp = self ? 0.f : cp;                                  // leaving this sphere's surface
+    D = self ? b * b : D;
+    const float s = fast_sqrt(D);                          // NaN: the ray misses
+    const float tq = b + copysignf(s, b);
+    const float ta = tq - RTM_T_EPS, tb = fmaf(cp, fast_rcp(tq), -RTM_T_EPS);
+    return min(__float_as_uint(ta), __float_as_uint(tb));
+}
+__device__ __forceinline__ void bvh_leaf_update(const RtmBvhDev& bvh, int slot, unsigned key, BvhRay& r) {
+    const unsigned best = __float_as_uint(r.best);
+    bool ok = key < best;
+    if (key == best && r.hit != -1 && key < RTM_KEY_INF)   // exact tie (measure zero): the lowest ORIGINAL index wins, Renderer.cpp:67
+        ok = __ldg(bvh.leaf_id + slot) < bvh_resolve_hit(bvh, r.hit);
+    r.best = ok ? __uint_as_float(key) : r.best;
+    r.hit = ok ? (-2 - slot) : r.hit;
+}
+__device__ __forceinline__ void bvh_leaf_test(const RtmBvhDev& bvh, int leaf, int self_slot, f3 o, f3 d, BvhRay& r, unsigned& n_tests) {
+    const unsigned code = ~(unsigned)leaf;
+    const unsigned first = code >> 3, cnt = (code & 7u) + 1u;
+    const u64 nox = pk(-o.x, -o.x), noy = pk(-o.y, -o.y), noz = pk(-o.z, -o.z);
+    const u64 dx = pk(d.x, d.x), dy = pk(d.y, d.y), dz = pk(d.z, d.z);
+    const u64 ndx = pk(-d.x, -d.x), ndy = pk(-d.y, -d.y), ndz = pk(-d.z, -d.z);
+    const u64 m1 = pk(-1.f, -1.f);
+    for (unsigned k = 0; k < cnt; k += 2) {
+        const unsigned s0 = first + k;
+        float4 g0, g1;
+        if (s0 & 1u) {                                     // only a single-sphere leaf can sit on an odd slot
+            g0 = __ldg(bvh.leaf_geo + s0);
+            g1 = g0;
+        } else {
+            ldg256(bvh.leaf_geo + s0, g0, g1);             // the array is padded to an even length
+        }
+        const u64 px = add2(pk(g0.x, g1.x), nox), py = add2(pk(g0.y, g1.y), noy), pz = add2(pk(g0.z, g1.z), noz);
+        const u64 nb = fma2(px, ndx, fma2(py, ndy, mul2(pz, ndz)));                     // -(p.d)
+        const u64 lx = fma2(nb, dx, px), ly = fma2(nb, dy, py), lz = fma2(nb, dz, pz);  // p - b d
+        const u64 r2 = pk(g0.w, g1.w);
+        const u64 D2 = fma2(fma2(lx, lx, fma2(ly, ly, mul2(lz, lz))), m1, r2);          // r^2 - |l|^2
+        const u64 cp2 = fma2(r2, m1, fma2(px, px, fma2(py, py, mul2(pz, pz))));         // |p|^2 - r^2
+        float nb0, nb1, D0, D1, c0, c1;
+        unpk(nb, nb0, nb1);
+        unpk(D2, D0, D1);
+        unpk(cp2, c0, c1);
+        const unsigned k0 = bvh_leaf_key((int)s0 == self_slot, nb0, D0, c0);
+        unsigned k1 = bvh_leaf_key((int)s0 + 1 == self_slot, nb1, D1, c1);
+        k1 = (k + 1u < cnt) ? k1 : 0xFFFFFFFFu;            // the upper half of an odd leaf's last pair is somebody else's sphere
+        bvh_leaf_update(bvh, (int)s0, k0, r);
+        bvh_leaf_update(bvh, (int)s0 + 1, k1, r);
+    }
+    n_tests += cnt;
+}
+#else
 __device__ __forceinline__ void bvh_leaf_test(const RtmBvhDev& bvh, int leaf, int self_slot, f3 o, f3 d, BvhRay& r, unsigned& n_tests) {
     const unsigned code = ~(unsigned)leaf;
     const unsigned first = code >> 3, cnt = (code & 7u) + 1u;
@@ -436,6 +496,7 @@ __device__ __forceinline__ void bvh_leaf_test(const RtmBvhDev& bvh, int leaf, in
     }
     n_tests += cnt;
 }
+#endif
 // ... then pop
 template <int ST = 1>
 __device__ __forceinline__ void bvh_leaf_step(const RtmBvhDev& bvh, int self_slot, f3 o, f3 d, BvhRay& r, int* stack, unsigned& n_tests) {

@@ -650,6 +650,7 @@ int renderer_create(const rtm_scene_desc* sc, const rtm_options* opt_in, rtm_ren
             // alb.w of a sphere: its slot in the big list (0..7) or 8 + its leaf slot (kernels_common.cuh: bvh_big_slot / bvh_leaf_slot)
             for (int j = 0; j < r->bvh_host.n_big; ++j) memcpy(&r->mat_alb[r->bvh_host.big_id[j]].w, &j, 4);
             for (size_t sl = 0; sl < r->bvh_host.leaf_id.size(); ++sl) {
+                if (r->bvh_host.leaf_id[sl] < 0) continue;   // pad slot (bvh_build.cpp: even-aligned leaves)
                 const int32_t code = 8 + (int32_t)sl;
                 memcpy(&r->mat_alb[r->bvh_host.leaf_id[sl]].w, &code, 4);
             }

@@ -50,9 +50,27 @@ def synth():
     return sc, api.build_bvh(sc)
 
 
+def _real(leaf_id):
+    """leaf slots without the pad entries (id -1) that keep leaves of two or more spheres on even slots"""
+    return [int(v) for v in leaf_id if v >= 0]
+
+
+def test_leaves_of_two_or_more_start_on_even_slots(synth):
+    sc, b = synth
+    seen = 0
+    for nd in b["nodes"]:
+        for code in _children(nd):
+            if code < 0:
+                first, cnt = _leaf(int(code))
+                assert cnt == 1 or first % 2 == 0, (first, cnt)
+                assert (b["leaf_id"][first:first + cnt] >= 0).all()
+                seen += cnt
+    assert seen == sc.n - len(b["big_id"])
+
+
 def test_every_sphere_exactly_once(synth):
     sc, b = synth
-    assert sorted(list(b["leaf_id"]) + b["big_id"]) == list(range(sc.n))
+    assert sorted(_real(b["leaf_id"]) + b["big_id"]) == list(range(sc.n))
     assert b["big_id"] == [0, 1, 2, 3, 4, 5, 6]           # the Cornell room of scenes/make_scenes.py
     assert b["depth"] + 2 < 64
 
@@ -74,9 +92,11 @@ def test_boxes_contain_their_spheres_and_rmin_is_a_lower_bound(synth):
             assert box[1] > hi[0] and box[3] > hi[1] and box[5] > hi[2]
             assert rmin <= rad[ids].min()
     # leaf slots carry the float centre the FP32 kernels use and r^2
-    k = b["leaf_id"]
-    assert np.array_equal(b["leaf_geo"][:, :3], rel[k].astype(np.float32))
-    assert np.array_equal(b["leaf_geo"][:, 3], (rad[k] * rad[k]).astype(np.float32))
+    real = b["leaf_id"] >= 0                               # pad slots (id -1) keep leaves of 2+ spheres on even slots
+    k = b["leaf_id"][real]
+    assert np.array_equal(b["leaf_geo"][real][:, :3], rel[k].astype(np.float32))
+    assert np.array_equal(b["leaf_geo"][real][:, 3], (rad[k] * rad[k]).astype(np.float32))
+    assert len(b["leaf_id"]) % 2 == 0 and (b["leaf_geo"][~real][:, 3] == 0).all()
 
 
 def _sphere_test(c, r, o, d):
@@ -189,13 +209,13 @@ def test_small_and_degenerate_inputs():
     for seed, n, closed in [(1, 0, False), (2, 1, False), (3, 2, True), (4, 5, True), (5, 70, False)]:
         sc = rtm.random_scene(seed, n, closed=closed)
         b = api.build_bvh(sc)
-        assert sorted(list(b["leaf_id"]) + b["big_id"]) == list(range(sc.n))
+        assert sorted(_real(b["leaf_id"]) + b["big_id"]) == list(range(sc.n))
     # many identical spheres (what COMPAT_HEAD's position collapse produces): median splits must terminate
     sc = rtm.random_scene(7, 300, closed=False)
     sc.position[:] = sc.position[0]
     sc.radius[:] = sc.radius[0]
     b = api.build_bvh(sc.normalized())
-    assert sorted(list(b["leaf_id"]) + b["big_id"]) == list(range(sc.n))
+    assert sorted(_real(b["leaf_id"]) + b["big_id"]) == list(range(sc.n))
     assert b["depth"] < 40
 
 
@@ -237,7 +257,7 @@ def test_wide_collapse_structure(synth):
                 seen_leaf_slots.extend(range(first, first + cnt))
                 depth = max(depth, lvl + 1)
     assert len(seen_nodes) == len(w["nodes"])
-    assert sorted(seen_leaf_slots) == list(range(len(b["leaf_id"])))   # every leaf slot exactly once
+    assert sorted(seen_leaf_slots) == [k for k in range(len(b["leaf_id"])) if b["leaf_id"][k] >= 0]   # every real leaf slot exactly once
     assert depth == w["depth"]
 
 
