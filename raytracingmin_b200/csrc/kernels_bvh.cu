@@ -28,6 +28,12 @@ namespace {
 #ifndef RTM_BVH_HOLD
 #define RTM_BVH_HOLD 0
 #endif
+#ifndef RTM_BVH_TVOTE
+#define RTM_BVH_TVOTE 0
+#endif
+#ifndef RTM_BVH_TVOTE_BURST
+#define RTM_BVH_TVOTE_BURST 3
+#endif
 #ifndef RTM_BVH_S_ROUND
 #define RTM_BVH_S_ROUND 1   // lanes that must need another roulette decision for the S block to run another round (swept: 1 4.50, 2 4.46, 4 4.45, 8 4.34 Grays/s on C5)
 #endif
@@ -304,6 +310,22 @@ radiance_bvh_kernel(const __grid_constant__ RtmHotScene hot, const __grid_consta
             }
             if (tracing && held != 0) bvh_leaf_test(bvh, held, sslot, o, d, ray, n_tests);
             else if (tracing && ray.node < 0) bvh_leaf_step<ST>(bvh, sslot, o, d, ray, stack, n_tests);
+#elif RTM_BVH_TVOTE
+            // experiment: the warp picks the phase by vote — the leaf block runs as soon as RTM_BVH_TVOTE lanes hold a leaf
+            // (or no lane is on an inner node), else a short burst of inner steps
+            const unsigned m_in = __ballot_sync(0xffffffffu, tracing && bvh_is_inner(ray.node));
+            const unsigned m_lf = __ballot_sync(0xffffffffu, tracing && ray.node < 0);
+            if (m_in != 0u && __popc(m_lf) < RTM_BVH_TVOTE) {
+                int k = 0;
+#pragma unroll 1
+                for (; k < RTM_BVH_TVOTE_BURST && tracing && bvh_is_inner(ray.node); ++k) {
+                    if (H16) bvh16_inner_step<ST>(bvh, ray, stack);
+                    else bvh_inner_step<ST>(bvh, ray, stack);
+                }
+                n_nodes += (unsigned)k;
+            } else if (tracing && ray.node < 0) {
+                bvh_leaf_step<ST>(bvh, sslot, o, d, ray, stack, n_tests);
+            }
 #else
             int k = 0;
 #pragma unroll 1

@@ -51,6 +51,33 @@ def test_bvh_forced_on_shipped_scenes(golden, scene_path, name, level):
     assert np.array_equal(res.hits, golden[f"{name}.{level}.hits_small"].astype(np.int32))
 
 
+@pytest.mark.parametrize("name", ["cornellBox", "simple1", "settingData"])
+def test_bvh_forced_radiance_matches_brute_force(scene_path, name):
+    """with accel=bvh on the Cornell box six of seven radii are 1e4, so "big = 8 x the median" classed none as big
+    and the r = 1e4 walls went through the FP32 leaf test, whose direct form cancels at 1e8.  Big is now also an absolute
+    radius (>= 256); the FP32 bounce radiance of the forced hierarchy must agree with the brute-force megakernel: same
+    primary hits, rays/sample within 0.5 %, image means within 1 % (same RNG keys, different arithmetic of the leaf test)."""
+    sc = rtm.load_scene(scene_path(name), "abc").with_dims(96, 54, 256, 1)
+    with rtm.Renderer(sc, accel="brute", seed=5) as r:
+        a = r.render(want_hits=True)
+    with rtm.Renderer(sc, accel="bvh", seed=5) as r:
+        b = r.render(want_hits=True)
+    assert np.array_equal(a.hits, b.hits)
+    ra, rb = a.stats.rays / a.stats.samples, b.stats.rays / b.stats.samples
+    assert abs(ra - rb) < 0.005 * ra, (ra, rb)
+    assert abs(float(a.image.mean()) - float(b.image.mean())) < 0.01 * float(a.image.mean()) + 1e-5
+
+
+def test_more_big_spheres_than_the_hierarchy_path_holds_is_refused():
+    sc = rtm.random_scene(9, 80, width=8, height=8, samples=1, superSamples=1, closed=False)
+    sc.radius[:12] = 1000.0
+    with pytest.raises(rtm.RtmError) as e:
+        rtm.Renderer(sc.normalized(), accel="bvh")
+    assert e.value.code == -4
+    with rtm.Renderer(sc.normalized(), accel="bvh", precision="f64") as r:   # the exact walk takes them in its leaves
+        assert r.render(want_image=False, want_hits=True).hits.shape == (8, 8, 1, 1)
+
+
 def test_synth10k_hits_480_vs_reference_objects(synth, golden10k):
     sc = synth.with_dims(480, 270, 1, 1)
     with rtm.Renderer(sc) as r:                      # accel=auto -> hierarchy for n > 64
