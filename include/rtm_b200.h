@@ -210,7 +210,8 @@ int renderer_sum_partials(rtm_renderer* r, const void* partials, int32_t n_slots
 /* The accumulation buffer as renderer_render returns it — float[H][W][3] in HOST memory — for callers that drive the
  * device-resident entry points themselves (one process per GPU: render_async on every rank, a sum-reduce of the partial
  * framebuffers into rank 0's buffer, then this call on rank 0).  The repack kernel and the copy are enqueued on `stream`
- * (a cudaStream_t, the one the reduce ran on; NULL = the handle's own stream), which is synchronised before returning. */
+ * (a cudaStream_t, the one the pass / the reduce ran on; NULL = the legacy default stream, as in renderer_render_async),
+ * which is synchronised before returning.  After a renderer_render call any stream will do (that call has synchronised). */
 int renderer_read_rgb(rtm_renderer* r, float* rgb_out, void* stream);
 
 /* COMPAT_HEAD only: the double image double[H][W][3], bit-exact against the reference. */

@@ -954,7 +954,10 @@ int renderer_read_rgb(rtm_renderer* r, float* rgb_out, void* stream) {
     if (!r || !rgb_out) return fail(RTM_E_INVALID, "null argument");
     GpuCtx& c = r->gpus[0];
     CU(cudaSetDevice(c.device));
-    cudaStream_t st = stream ? (cudaStream_t)stream : c.stream;
+    // `stream` as in renderer_render_async: the caller's stream, NULL = the legacy default stream — the copy is ordered behind
+    // whatever the caller enqueued there (its render_async pass, its reduce).  (The handle's own stream is non-blocking: using
+    // it for NULL would read the buffer before a reduce on the default stream has finished.)
+    cudaStream_t st = (cudaStream_t)stream;
     if (!c.d_rgb) CU(cudaMalloc(&c.d_rgb, r->n_pix * 3 * sizeof(float)));
     rtm_launch_pack_rgb(c.accum, c.d_rgb, r->n_pix, st);
     CU(cudaGetLastError());

@@ -474,3 +474,23 @@ def test_head_u8_comes_from_the_double_image():
         # the known answers of the advisor's example, wherever a pixel is fully covered by the emitter
         full = np.isclose(img64, img64.max())
         assert set(np.unique(u8[full])) <= {int(255 * min(img64.max(), 1.0))}
+
+
+def test_read_rgb_is_ordered_behind_the_pass_on_the_callers_stream(scene_path):
+    """renderer_read_rgb(handle, out, stream): the repack + copy run on the CALLER's stream (NULL = the legacy default
+    stream, as in renderer_render_async), behind the pass enqueued there.  The accumulation buffer is a caller-owned tensor
+    zeroed before every pass, so a read that ran ahead of the pass would come back black."""
+    import torch
+    sc = rtm.load_scene(scene_path("cornellBox"), "abc").with_dims(960, 504, 16, 2)
+    with rtm.Renderer(sc, seed=3) as r:
+        want = r.render().image.copy()
+        accum = torch.zeros((sc.height, sc.width, 4), dtype=torch.float32, device="cuda:0")
+        r.set_accum_buffer(accum.data_ptr())
+        side = torch.cuda.Stream()
+        for st in (torch.cuda.current_stream(), side):
+            for _ in range(3):
+                with torch.cuda.stream(st):
+                    accum.zero_()
+                    r.render_async(st.cuda_stream)
+                    got = r.read_rgb(stream=st.cuda_stream)
+                assert np.array_equal(got, want)
