@@ -453,6 +453,9 @@ def run_gpu_arm(args):
                          "framebuffer_store_GBs": fb_gbs, "hbm_peak_GBs": peaks.get("hbm_gbs")},
             "clocks": clocks,
         }
+        if ms_step < 2.0:
+            line["note"] = ("frame of %.2f ms: launch-bound (3 kernel launches + counters memset per pass), the device rate is not "
+                            "sustained work and the end-to-end rate is dominated by the framebuffer copy" % ms_step)
         if image_check is not None:
             line["image_check"] = image_check
         if reduce_check is not None:

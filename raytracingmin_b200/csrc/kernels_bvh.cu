@@ -28,12 +28,6 @@ namespace {
 #ifndef RTM_BVH_HOLD
 #define RTM_BVH_HOLD 0
 #endif
-#ifndef RTM_BVH_TVOTE
-#define RTM_BVH_TVOTE 0
-#endif
-#ifndef RTM_BVH_TVOTE_BURST
-#define RTM_BVH_TVOTE_BURST 3
-#endif
 #ifndef RTM_BVH_S_ROUND
 #define RTM_BVH_S_ROUND 1   // lanes that must need another roulette decision for the S block to run another round (swept: 1 4.50, 2 4.46, 4 4.45, 8 4.34 Grays/s on C5)
 #endif
@@ -134,6 +128,7 @@ radiance_bvh_kernel(const __grid_constant__ RtmHotScene hot, const __grid_consta
                 const unsigned ns = (unsigned)(s_end - s_begin);
                 const bool miss = (wbits == RTM_REC_MISS);
                 const int Pid = miss ? 0 : (int)(wbits & RTM_REC_IDMASK);
+                RTM_ASSERT(ql < n_sub && Pid < n_sph + n_pl);
                 const float4 e0 = __ldg(mat.emi + Pid);
                 if (miss || __float_as_uint(e0.w) == 0u) {
                     float4 out = make_float4(0.f, 0.f, 0.f, 0.f);
@@ -191,6 +186,7 @@ radiance_bvh_kernel(const __grid_constant__ RtmHotScene hot, const __grid_consta
             // a finished ray is applied to the path; returns true when the path ends there
             auto apply_hit = [&](int id2, float t) -> bool {
                 if (id2 < 0) return true;                                            // miss: Renderer.cpp:116
+                RTM_ASSERT(id2 < n_sph + n_pl);
                 o = mk(fmaf(d.x, t, o.x), fmaf(d.y, t, o.y), fmaf(d.z, t, o.z));     // :79
                 const float4 g = __ldg(mat.geo + id2);
                 f3 nn = mk((o.x - g.x) * g.w, (o.y - g.y) * g.w, (o.z - g.z) * g.w);
@@ -310,22 +306,6 @@ radiance_bvh_kernel(const __grid_constant__ RtmHotScene hot, const __grid_consta
             }
             if (tracing && held != 0) bvh_leaf_test(bvh, held, sslot, o, d, ray, n_tests);
             else if (tracing && ray.node < 0) bvh_leaf_step<ST>(bvh, sslot, o, d, ray, stack, n_tests);
-#elif RTM_BVH_TVOTE
-            // experiment: the warp picks the phase by vote — the leaf block runs as soon as RTM_BVH_TVOTE lanes hold a leaf
-            // (or no lane is on an inner node), else a short burst of inner steps
-            const unsigned m_in = __ballot_sync(0xffffffffu, tracing && bvh_is_inner(ray.node));
-            const unsigned m_lf = __ballot_sync(0xffffffffu, tracing && ray.node < 0);
-            if (m_in != 0u && __popc(m_lf) < RTM_BVH_TVOTE) {
-                int k = 0;
-#pragma unroll 1
-                for (; k < RTM_BVH_TVOTE_BURST && tracing && bvh_is_inner(ray.node); ++k) {
-                    if (H16) bvh16_inner_step<ST>(bvh, ray, stack);
-                    else bvh_inner_step<ST>(bvh, ray, stack);
-                }
-                n_nodes += (unsigned)k;
-            } else if (tracing && ray.node < 0) {
-                bvh_leaf_step<ST>(bvh, sslot, o, d, ray, stack, n_tests);
-            }
 #else
             int k = 0;
 #pragma unroll 1

@@ -283,6 +283,13 @@ struct SharedBig {
 __device__ __forceinline__ bool bvh_is_inner(int node) { return (unsigned)node < 0x7FFFFFFFu; }   // leaves are negative
 
 // Ray state of one lane inside the hierarchy.  best = candidate (root - eps), as in the packed test.
+// entries a lane's traversal stack holds: the interleaved shared-memory layout (ST = block size) has RTM_BVH_SSTACK levels,
+// a private array RTM_BVH_STACK_DEV
+#ifndef RTM_BVH_SSTACK
+#define RTM_BVH_SSTACK 24
+#endif
+#define RTM_STACK_CAP(ST) ((ST) == 1 ? RTM_BVH_STACK_DEV : RTM_BVH_SSTACK)
+
 struct BvhRay {
     f3 inv, oi;      // 1/d and o/d
     f3 ainv;         // |1/d| (compact-node walk only: near/far = t_c -+ h |1/d| as two FFMA)
@@ -339,6 +346,7 @@ __device__ __forceinline__ void ldg256(const float4* p, float4& a, float4& b) { 
 // one inner node: test both children, descend into the nearer one, push the other
 template <int ST = 1>
 __device__ __forceinline__ void bvh_inner_step(const RtmBvhDev& bvh, BvhRay& r, int* stack) {
+    RTM_ASSERT(r.node >= 0 && r.node < bvh.n_nodes);
     const float4* q = bvh.nodes + 4 * r.node;
     float4 q0, q1, q2, q3;
     ldg256(q, q0, q1);
@@ -350,11 +358,13 @@ __device__ __forceinline__ void bvh_inner_step(const RtmBvhDev& bvh, BvhRay& r, 
     const int c0 = __float_as_int(q3.x), c1 = __float_as_int(q3.y);
     if (h0 && h1) {
         const bool swap = n1 < n0;
+        RTM_ASSERT(r.sp >= 0 && r.sp < RTM_STACK_CAP(ST));
         stack[ST * r.sp++] = swap ? c0 : c1;
         r.node = swap ? c1 : c0;
     } else if (h0 || h1) {
         r.node = h0 ? c0 : c1;
     } else {
+        RTM_ASSERT(r.sp > 0);
         r.node = stack[ST * --r.sp];
     }
 }
@@ -379,6 +389,7 @@ __device__ __forceinline__ void ldg256u(const uint32_t* p, uint4& a, uint4& b) {
 }
 template <int ST = 1>
 __device__ __forceinline__ void bvh16_inner_step(const RtmBvhDev& bvh, BvhRay& r, int* stack) {
+    RTM_ASSERT(r.node >= 0 && r.node < bvh.n_nodes);
     uint4 a, b;
     ldg256u(bvh.nodes16 + 8 * r.node, a, b);
     float n0, n1;
@@ -388,11 +399,13 @@ __device__ __forceinline__ void bvh16_inner_step(const RtmBvhDev& bvh, BvhRay& r
     const int c0 = (int)b.z, c1 = (int)b.w;
     if (h0 && h1) {
         const bool swap = n1 < n0;
+        RTM_ASSERT(r.sp >= 0 && r.sp < RTM_STACK_CAP(ST));
         stack[ST * r.sp++] = swap ? c0 : c1;
         r.node = swap ? c1 : c0;
     } else if (h0 || h1) {
         r.node = h0 ? c0 : c1;
     } else {
+        RTM_ASSERT(r.sp > 0);
         r.node = stack[ST * --r.sp];
     }
 }
@@ -401,7 +414,10 @@ __device__ __forceinline__ void bvh16_inner_step(const RtmBvhDev& bvh, BvhRay& r
 // leaf SLOT s of a hierarchy sphere coded as -2 - s.  Every sphere sits in exactly one slot, so the slot identifies it
 // during the walk; the original index (bvh.leaf_id) is fetched once per ray for the winner, not once per candidate
 // (10.9 candidates per ray on synth10k).
-__device__ __forceinline__ int bvh_resolve_hit(const RtmBvhDev& bvh, int hit) { return (hit < -1) ? __ldg(bvh.leaf_id + (-2 - hit)) : hit; }
+__device__ __forceinline__ int bvh_resolve_hit(const RtmBvhDev& bvh, int hit) {
+    RTM_ASSERT(hit >= -1 || (-2 - hit) < bvh.n_slots);
+    return (hit < -1) ? __ldg(bvh.leaf_id + (-2 - hit)) : hit;
+}
 // alb.w of an object: its slot in the big list (0..7), 8 + its leaf slot, or -1 (a plane)
 __device__ __forceinline__ int bvh_big_slot(int code) { return (code >= 8) ? -1 : code; }
 __device__ __forceinline__ int bvh_leaf_slot(int code) { return code - 8; }
@@ -435,6 +451,7 @@ __device__ __forceinline__ void bvh_leaf_update(const RtmBvhDev& bvh, int slot, 
 __device__ __forceinline__ void bvh_leaf_test(const RtmBvhDev& bvh, int leaf, int self_slot, f3 o, f3 d, BvhRay& r, unsigned& n_tests) {
     const unsigned code = ~(unsigned)leaf;
     const unsigned first = code >> 3, cnt = (code & 7u) + 1u;
+    RTM_ASSERT((int)((first + cnt + 1u) & ~1u) <= bvh.n_slots);   // the last pair fetch stays inside the (even-length) array
     const u64 nox = pk(-o.x, -o.x), noy = pk(-o.y, -o.y), noz = pk(-o.z, -o.z);
     const u64 dx = pk(d.x, d.x), dy = pk(d.y, d.y), dz = pk(d.z, d.z);
     const u64 ndx = pk(-d.x, -d.x), ndy = pk(-d.y, -d.y), ndz = pk(-d.z, -d.z);
@@ -501,6 +518,7 @@ __device__ __forceinline__ void bvh_leaf_test(const RtmBvhDev& bvh, int leaf, in
 template <int ST = 1>
 __device__ __forceinline__ void bvh_leaf_step(const RtmBvhDev& bvh, int self_slot, f3 o, f3 d, BvhRay& r, int* stack, unsigned& n_tests) {
     bvh_leaf_test(bvh, r.node, self_slot, o, d, r, n_tests);
+    RTM_ASSERT(r.sp > 0);
     r.node = stack[ST * --r.sp];
 }
 

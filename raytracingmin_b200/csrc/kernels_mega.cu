@@ -132,6 +132,7 @@ radiance_mega_kernel(const __grid_constant__ RtmHotScene hot, const __grid_const
                     const unsigned wbits = __float_as_uint(rec.w);
                     const bool miss = (wbits == RTM_REC_MISS);
                     const int Pid = miss ? 0 : (int)(wbits & RTM_REC_IDMASK);
+                    RTM_ASSERT(ql < n_sub && Pid < n + (PL ? n_pl : 0));
                     const float4 e0 = sh.emi[Pid];
                     if (miss || __float_as_uint(e0.w) == 0u) {
                         // every sample of this sub-pixel is the same: nothing (miss) or the
@@ -281,6 +282,7 @@ radiance_mega_kernel(const __grid_constant__ RtmHotScene hot, const __grid_const
             }
             ++sd;                                                                 // one more bounce ray (hit or miss)
             if (id2 >= 0) {
+                RTM_ASSERT(id2 < n + (PL ? n_pl : 0) && (sd & 511u) != 0u);
                 o = mk(fmaf(d.x, t, o.x), fmaf(d.y, t, o.y), fmaf(d.z, t, o.z));  // Renderer.cpp:79
                 const float4 g = sh.geo[id2];
                 f3 nn = mk((o.x - g.x) * g.w, (o.y - g.y) * g.w, (o.z - g.z) * g.w);

@@ -272,6 +272,7 @@ __global__ void __launch_bounds__(128) wf_extend_brute_kernel(const __grid_const
     }
     if (i >= count) return;
     const int slot = wv.queue[parity][i];
+    RTM_ASSERT(slot >= 0 && slot < wv.n_slots && count <= (unsigned)wv.n_slots);
     const float4 v0 = wv.a0[slot], rv = wv.ray[slot];
     float t;
     const int id2 = trace_f32<N>(hot, sh, sh_mask, n_rt, __float_as_int(v0.w), mk(v0.x, v0.y, v0.z), mk(rv.x, rv.y, rv.z), t, key_mask);
@@ -308,6 +309,7 @@ __global__ void __launch_bounds__(128, 6) wf_extend_bvh_kernel(RtmBvhDev bvh, Rt
             const unsigned my = base + __popc(idle & lt_mask);
             if (!active && my < total) {
                 slot = queue[my];
+                RTM_ASSERT(slot >= 0 && slot < wv.n_slots);
                 const float4 v0 = wv.a0[slot], rv = wv.ray[slot];
                 const float2 hv = wv.hit[slot];
                 o = mk(v0.x, v0.y, v0.z); oid = __float_as_int(v0.w);

@@ -744,6 +744,8 @@ int renderer_create(const rtm_scene_desc* sc, const rtm_options* opt_in, rtm_ren
                 c.bvh.n_big = B.n_big;
                 for (int j = 0; j < 8; ++j) c.bvh.big_id[j] = B.big_id[j];
                 c.bvh.depth = B.depth;
+                c.bvh.n_nodes = (int32_t)(n_nodes4 / 4);
+                c.bvh.n_slots = (int32_t)n_slots;
                 c.s64.use_bvh = 1;
                 c.s64.bvh = c.bvh;
                 for (int k = 0; k < 3; ++k) c.s64.ref[k] = r->refd[k];

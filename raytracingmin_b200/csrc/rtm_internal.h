@@ -6,6 +6,15 @@
 
 #define RTM_MAX_CONST_SPHERES 256  // FP32 brute-force scene lives in __constant__ memory up to this size
 #define RTM_WARP 32
+// Device-side invariants (array bounds, traversal-stack depth, object ids).  compute-sanitizer is closed on the GPU pool this
+// was developed on, so the memory-safety evidence is a build with these asserts compiled in (make checks -> librtm_b200_checks.so)
+// run under the GPU test-suite: a violated invariant fails the launch with cudaErrorAssert.  The product build compiles them out.
+#ifdef RTM_DEVICE_CHECKS
+#include <cassert>
+#define RTM_ASSERT(x) assert(x)
+#else
+#define RTM_ASSERT(x) ((void)0)
+#endif
 #define RTM_BVH_STACK_DEV 64       // traversal stack entries per lane (bvh.h: the build caps the depth below this)
 
 // Camera frame of reference src/Renderer.cpp:202-208, precomputed on the host
@@ -26,6 +35,7 @@ struct RtmBvhDev {
     int32_t n_big;            // spheres kept out of the hierarchy, tested for every ray
     int32_t big_id[8];        //   ascending original index
     int32_t depth;            // levels of the tree (a walk holds at most depth + 2 stack entries)
+    int32_t n_nodes, n_slots; // array sizes (device-side checks: -DRTM_DEVICE_CHECKS)
     // compact form for the FP32 walk (bvh.h: RtmBvh16Host): 8 x u32 per inner node, NULL = not used
     const uint32_t* nodes16;
     float ref16[3];           // centre of the half-precision frame, relative to the scene reference point
