@@ -128,8 +128,8 @@ radiance_bvh_kernel(const __grid_constant__ RtmHotScene hot, const __grid_consta
                 const unsigned ns = (unsigned)(s_end - s_begin);
                 const bool miss = (wbits == RTM_REC_MISS);
                 const int Pid = miss ? 0 : (int)(wbits & RTM_REC_IDMASK);
-                RTM_ASSERT(ql < n_sub && Pid < n_sph + n_pl);
-                const float4 e0 = __ldg(mat.emi + Pid);
+                RTM_ASSERT(ql < n_sub && (miss || Pid < n_sph + n_pl));
+                const float4 e0 = miss ? make_float4(0.f, 0.f, 0.f, 0.f) : __ldg(mat.emi + Pid);   // no record to read for a miss (n may be 0)
                 if (miss || __float_as_uint(e0.w) == 0u) {
                     float4 out = make_float4(0.f, 0.f, 0.f, 0.f);
                     if (!miss) {

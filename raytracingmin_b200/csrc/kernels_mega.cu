@@ -132,7 +132,7 @@ radiance_mega_kernel(const __grid_constant__ RtmHotScene hot, const __grid_const
                     const unsigned wbits = __float_as_uint(rec.w);
                     const bool miss = (wbits == RTM_REC_MISS);
                     const int Pid = miss ? 0 : (int)(wbits & RTM_REC_IDMASK);
-                    RTM_ASSERT(ql < n_sub && Pid < n + (PL ? n_pl : 0));
+                    RTM_ASSERT(ql < n_sub && (miss || Pid < n + (PL ? n_pl : 0)));
                     const float4 e0 = sh.emi[Pid];
                     if (miss || __float_as_uint(e0.w) == 0u) {
                         // every sample of this sub-pixel is the same: nothing (miss) or the
