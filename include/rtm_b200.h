@@ -221,6 +221,24 @@ int renderer_read_image_f64(rtm_renderer* r, double* image_out);
  * DOUBLE image (bytes identical to the reference's); COMPAT_ABC converts the float accumulation buffer. */
 int renderer_read_u8(rtm_renderer* r, unsigned char* rgb8_out);
 
+/* One FP32 pass that allocates nothing, for callers that may not call cudaMalloc (CUDA graph capture, tight serving
+ * loops, harnesses that forbid it).  No counterpart in the reference.
+ * Same kernels and same result as renderer_render_async (primary pass, bounce kernel, sub-pixel accumulate), but the
+ * pass's scratch — 16 B of record per sub-pixel (+ 4 B on scenes with very small spheres) and the work cursor — lives in
+ * ONE fixed array of RTM_NOALLOC_SCRATCH_BYTES inside the library (every GPU that loads the library holds it until the
+ * process exits) instead of the handle's own buffers.
+ *   r                  a COMPAT_ABC / PRECISION_F32 / VARIANT_MEGA handle on one GPU (inputs: its scene and options)
+ *   accum_out_float4   output, caller-owned device memory on the handle's device: float4[H][W] = {r,g,b,0}, overwritten
+ *   stream             a cudaStream_t (NULL = the legacy default stream); the call enqueues and returns
+ * Limit: W*H*(sub_end-sub_begin) sub-pixels must fit the array — at most 1,048,560 (838,848 on scenes with very small
+ * spheres); larger frames are refused with RTM_E_UNSUPPORTED and a message naming both sizes.  The call runs no
+ * cudaMalloc / cudaFree and no allocating library routine.  All calls on a device share the array: it keeps the last
+ * call's contents (the call clears what must start at zero, the counters and the work cursor), and two calls that
+ * overlap on the GPU — different streams, or two handles — race; order them on one stream or with events.
+ * renderer_read_stats / renderer_read_kernel_ms keep describing the handle's last ordinary pass. */
+#define RTM_NOALLOC_SCRATCH_BYTES (16u << 20)
+int renderer_render_noalloc(rtm_renderer* r, void* accum_out_float4, void* stream);
+
 void renderer_destroy(rtm_renderer* r);
 
 const char* renderer_last_error(void);

@@ -90,7 +90,7 @@ class RenderResult:
 
 EXPORTS = [
     "renderer_abi_version", "renderer_default_options", "renderer_create", "renderer_render",
-    "renderer_render_async", "renderer_read_stats", "renderer_read_kernel_ms", "renderer_device_accum", "renderer_device_hits",
+    "renderer_render_async", "renderer_render_noalloc", "renderer_read_stats", "renderer_read_kernel_ms", "renderer_device_accum", "renderer_device_hits",
     "renderer_set_accum_buffer", "renderer_peer_export", "renderer_peer_open", "renderer_sum_partials", "renderer_read_rgb", "renderer_read_image_f64", "renderer_read_u8", "renderer_destroy",
     "renderer_last_error", "rtm_debug_philox", "rtm_debug_closest_hit", "rtm_debug_fp32_peak", "rtm_debug_bvh", "rtm_debug_bvh16", "rtm_debug_bvh4", "rtm_debug_acne_eps",
 ]
@@ -120,6 +120,8 @@ def load_library():
     lib.renderer_create.argtypes = [P(_SceneDesc), P(_Options), P(vp)]
     lib.renderer_render.argtypes = [vp, vp, vp, P(_Stats)]
     lib.renderer_render_async.argtypes = [vp, vp]
+    lib.renderer_render_noalloc.argtypes = [vp, vp, vp]
+    lib.renderer_render_noalloc.restype = C.c_int
     lib.renderer_read_stats.argtypes = [vp, P(_Stats)]
     lib.renderer_read_kernel_ms.argtypes = [vp, vp]
     lib.renderer_device_accum.argtypes = [vp]
@@ -220,6 +222,11 @@ class Renderer:
     # -- device-resident pass on a caller-supplied CUDA stream (0 = default stream)
     def render_async(self, stream: int = 0) -> None:
         _check(self._lib, self._lib.renderer_render_async(self._h, C.c_void_p(stream)))
+
+    def render_noalloc(self, accum_device_ptr: int, stream: int = 0) -> None:
+        """renderer_render_noalloc: one FP32 pass into the caller's float4[H][W] device buffer with the pass's scratch in
+        the library's fixed device array (no cudaMalloc in the call; include/rtm_b200.h for the limit and the sharing rule)."""
+        _check(self._lib, self._lib.renderer_render_noalloc(self._h, C.c_void_p(accum_device_ptr), C.c_void_p(stream)))
 
     def read_stats(self) -> Stats:
         st = _Stats()

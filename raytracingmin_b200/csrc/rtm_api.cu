@@ -304,7 +304,71 @@ int fill_stats(rtm_renderer* r, rtm_stats* st) {
 
 }  // namespace
 
+// ---- renderer_render_noalloc: the pass with its scratch in a fixed device array -------------------------------
+// Scratch of one FP32 pass = the sub-pixel records the primary pass hands to the bounce kernel (16 B each), the
+// per-sub-pixel c' of ACNE scenes (4 B each) and the counter block with the work cursor.  The handle keeps them in
+// cudaMalloc'd buffers; this entry point keeps them HERE, in an array that every device which loads the library holds
+// until the process exits, so the call itself allocates nothing.  All calls on a device share the array.
+namespace {
+
+__device__ __align__(256) static unsigned char g_noalloc_scratch[RTM_NOALLOC_SCRATCH_BYTES];
+
+constexpr int kNoallocMaxDevices = 64;
+std::mutex g_noalloc_mu;
+unsigned char* g_noalloc_dev[kNoallocMaxDevices];   // device address of g_noalloc_scratch per device, resolved once
+
+// In host code `g_noalloc_scratch` is only the symbol's host-side stand-in; the address a kernel may use comes from
+// cudaGetSymbolAddress with the owning device current.
+int noalloc_scratch(int device, unsigned char** out) {
+    if (device < 0 || device >= kNoallocMaxDevices) return fail(RTM_E_UNSUPPORTED, "device %d beyond the no-alloc table (%d)", device, kNoallocMaxDevices);
+    std::lock_guard<std::mutex> lk(g_noalloc_mu);
+    if (!g_noalloc_dev[device]) {
+        CU(cudaSetDevice(device));
+        void* ptr = nullptr;
+        CU(cudaGetSymbolAddress(&ptr, g_noalloc_scratch));
+        if (!ptr || ((uintptr_t)ptr & 255u)) return fail(RTM_E_CUDA, "scratch symbol resolved to %p", ptr);
+        g_noalloc_dev[device] = (unsigned char*)ptr;
+    }
+    *out = g_noalloc_dev[device];
+    return RTM_OK;
+}
+
+}  // namespace
+
 extern "C" {
+
+int renderer_render_noalloc(rtm_renderer* r, void* accum_out_float4, void* stream) {
+    if (!r || !accum_out_float4) return fail(RTM_E_INVALID, "null argument");
+    if (r->gpus.size() != 1) return fail(RTM_E_UNSUPPORTED, "renderer_render_noalloc drives one GPU per handle");
+    if (r->opt.compat != RTM_COMPAT_ABC || r->opt.precision != RTM_PRECISION_F32 || r->opt.variant == RTM_VARIANT_WAVEFRONT)
+        return fail(RTM_E_UNSUPPORTED, "renderer_render_noalloc runs the FP32 ABC megakernel pass only");
+    GpuCtx& c = r->gpus[0];
+    // layout: [counters, 256 B] [records, 16 B x n_sub] [c', 4 B x n_sub (ACNE scenes)]
+    const uint64_t per_sub = sizeof(float4) + (c.cps0 ? sizeof(float) : 0);
+    const uint64_t max_sub = ((uint64_t)RTM_NOALLOC_SCRATCH_BYTES - 256u) / per_sub;
+    if (r->n_sub > max_sub)
+        return fail(RTM_E_UNSUPPORTED, "renderer_render_noalloc: %llu sub-pixels need %llu bytes of scratch, the fixed array holds %llu (at most %llu sub-pixels of this scene)",
+                    (unsigned long long)r->n_sub, (unsigned long long)(256u + r->n_sub * per_sub),
+                    (unsigned long long)RTM_NOALLOC_SCRATCH_BYTES, (unsigned long long)max_sub);
+    unsigned char* base = nullptr;
+    int rc = noalloc_scratch(c.device, &base);
+    if (rc) return rc;
+    CU(cudaSetDevice(c.device));
+    cudaStream_t st = (cudaStream_t)stream;
+    RtmCounters* counters = (RtmCounters*)base;
+    float4* records = (float4*)(base + 256);
+    float* cps0 = c.cps0 ? (float*)(base + 256 + r->n_sub * sizeof(float4)) : nullptr;
+    const RtmPassParams p = make_params(r, c);
+    // the array keeps the previous call's contents: the work cursor and the counters must start at zero; every record
+    // (and c') is written by the primary pass before the bounce kernel reads it
+    CU(cudaMemsetAsync(counters, 0, sizeof(RtmCounters), st));
+    rtm_launch_primary_f64(c.s64, p, nullptr, records, counters, cps0, st);
+    if (r->use_bvh) rtm_launch_radiance_bvh(c.hot, c.bvh, c.mat, p, records, counters, c.sm_count, cps0, r->n, r->n_planes, r->opt.debug_bvh_walk, st);
+    else rtm_launch_radiance_mega(c.hot, r->n, r->n_planes, r->nee, r->retry, r->clamp, p, records, counters, c.sm_count, cps0, st);
+    rtm_launch_accumulate(p, records, (float4*)accum_out_float4, st);
+    CU(cudaGetLastError());
+    return RTM_OK;
+}
 
 int renderer_abi_version(void) { return RTM_ABI_VERSION; }
 
