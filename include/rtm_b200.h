@@ -139,7 +139,13 @@ typedef struct rtm_options {
                                    (both render the same image bit for bit) */
     int32_t debug_bvh_walk;     /* hierarchy kernel, bit mask: 0 = default (traversal stack in shared memory when the tree
                                    is shallow enough; compact half-precision nodes when they fit the scene),
-                                   bit 0 = stack in local memory, bit 1 = full-precision 64-byte nodes */
+                                   bit 0 = stack in local memory, bit 1 = full-precision 64-byte nodes,
+                                   bit 2 = inner nodes numbered breadth-first at the top and in 4-node treelets (one
+                                   128-byte line each) below (default: breadth-first throughout; same walk, same image),
+                                   bit 3 = the 4-wide collapse of the compact nodes (default: two children per node),
+                                   bit 4 = the ray-pool kernel (64 rays per warp parked in shared memory, phases pick 32 in
+                                   the same phase; default: one ray per lane).  Bits 3 and 4 are measured design
+                                   alternatives that render the same image, not faster */
     int32_t debug_bvh_leaf_max; /* SAH build: largest leaf, 1..8; 0 = default (4) */
     float   debug_bvh_ctrav;    /* SAH build: cost of an inner-node visit in sphere tests; 0 = default (1.0) */
     int32_t debug_clamp;        /* 0 = the per-sample clamp (src/Renderer.cpp:240-241) is compiled out when the host can
@@ -272,7 +278,13 @@ int rtm_debug_bvh(const rtm_scene_desc* scene, int32_t* info, float* nodes_out, 
  * nodes16_out uint32[8*nodes] or NULL: cx|cy, cz|hx, hy|hz of child 0, the same of child 1, the two child codes. */
 int rtm_debug_bvh16(const rtm_scene_desc* scene, int32_t* n_nodes_out, float* meta6, uint32_t* nodes16_out);
 
-/* The 4-wide collapse of that hierarchy (design study; host only).
+/* The 4-wide collapse of the compact form (the walk behind rtm_options.debug_bvh_walk bit 3; host only).
+ * info2 = {nodes (0: not usable), depth}; nodes_out uint32[16*nodes] or NULL: two halves laid out like a node of
+ * rtm_debug_bvh16 — children 0,1 + their codes, children 2,3 + their codes; codes >= 0 index this array, negative codes
+ * are the leaf codes of rtm_debug_bvh, 0x7FFFFFFF marks an empty slot (behind a box no ray hits). */
+int rtm_debug_bvh16x4(const rtm_scene_desc* scene, int32_t* info2, uint32_t* nodes_out);
+
+/* The 4-wide collapse of that hierarchy with float boxes (design study; host only).
  * info4[3] = {wide nodes, root code, depth}.  nodes4_out float[32*nodes] or NULL: 8 float4 per node —
  * lo.x[4] hi.x[4] lo.y[4] hi.y[4] lo.z[4] hi.z[4], child codes[4] (int bits, 0x7FFFFFFF = empty), rmin[4].
  * Leaf codes index the leaf arrays of rtm_debug_bvh. */

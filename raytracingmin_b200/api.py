@@ -92,7 +92,7 @@ EXPORTS = [
     "renderer_abi_version", "renderer_default_options", "renderer_create", "renderer_render",
     "renderer_render_async", "renderer_render_noalloc", "renderer_read_stats", "renderer_read_kernel_ms", "renderer_device_accum", "renderer_device_hits",
     "renderer_set_accum_buffer", "renderer_peer_export", "renderer_peer_open", "renderer_sum_partials", "renderer_read_rgb", "renderer_read_image_f64", "renderer_read_u8", "renderer_destroy",
-    "renderer_last_error", "rtm_debug_philox", "rtm_debug_closest_hit", "rtm_debug_fp32_peak", "rtm_debug_bvh", "rtm_debug_bvh16", "rtm_debug_bvh4", "rtm_debug_acne_eps",
+    "renderer_last_error", "rtm_debug_philox", "rtm_debug_closest_hit", "rtm_debug_fp32_peak", "rtm_debug_bvh", "rtm_debug_bvh16", "rtm_debug_bvh16x4", "rtm_debug_bvh4", "rtm_debug_acne_eps",
 ]
 
 
@@ -143,6 +143,7 @@ def load_library():
     lib.rtm_debug_fp32_peak.argtypes = [C.c_int32, P(C.c_double), P(C.c_double)]
     lib.rtm_debug_bvh.argtypes = [P(_SceneDesc), vp, vp, vp, vp]
     lib.rtm_debug_bvh16.argtypes = [P(_SceneDesc), vp, vp, vp]
+    lib.rtm_debug_bvh16x4.argtypes = [P(_SceneDesc), vp, vp]
     lib.rtm_debug_bvh4.argtypes = [P(_SceneDesc), vp, vp]
     lib.rtm_debug_acne_eps.argtypes = [C.c_int32, C.c_uint32, vp, vp]
     _lib = lib
@@ -345,6 +346,17 @@ def build_bvh16(scene: Scene) -> dict:
     nodes = np.zeros((n.value, 8), np.uint32)
     _check(lib, lib.rtm_debug_bvh16(C.byref(d), C.byref(n), meta.ctypes.data, nodes.ctypes.data))
     return dict(nodes=nodes, ref=meta[:3].astype(np.float64), inv_scale=float(meta[3]), inflation=float(meta[4]), ok=bool(meta[5]))
+
+
+def build_bvh16x4(scene: Scene) -> dict:
+    """The 4-wide collapse of build_bvh16's tree, which the FP32 walk uses (host code only): nodes[k] = 16 uint32."""
+    lib = load_library()
+    d = Renderer._desc(scene.normalized())
+    info = np.zeros(2, np.int32)
+    _check(lib, lib.rtm_debug_bvh16x4(C.byref(d), info.ctypes.data, None))
+    nodes = np.zeros((int(info[0]), 16), np.uint32)
+    _check(lib, lib.rtm_debug_bvh16x4(C.byref(d), info.ctypes.data, nodes.ctypes.data))
+    return dict(nodes=nodes, depth=int(info[1]), ok=bool(info[0] > 0))
 
 
 def build_bvh4(scene: Scene) -> dict:

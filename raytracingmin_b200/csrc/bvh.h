@@ -17,6 +17,9 @@
 #define RTM_BVH_CTRAV 1.0         // SAH: cost of an inner-node visit in sphere tests
 #define RTM_BVH_STACK 64
 #define RTM_BVH_BIG_RADIUS 256.0  // absolute "too large for the FP32 leaf test" radius
+#ifndef RTM_BVH_LAYOUT_TOP
+#define RTM_BVH_LAYOUT_TOP 1024   // layout 1: inner nodes numbered breadth-first (32 KB of compact nodes) before the treelets start
+#endif
 
 // child code: >= 0  inner node index
 //             <  0  leaf: ~code = (first_slot << 3) | (count - 1)
@@ -45,8 +48,9 @@ struct RtmBvhHost {
 // exceeds 8 x the median radius or RTM_BVH_BIG_RADIUS: the FP32 leaf test evaluates |c - o|^2 - r^2 directly, which is
 // only accurate for small r; out.n_big_overflow counts the big spheres beyond RTM_BVH_MAX_BIG that had to stay in leaves
 // (fine for the exact FP64 walk; the FP32 path refuses such a scene).
+// layout: numbering of the inner nodes — 0 = breadth-first (default), 1 = breadth-first top + treelets of 4 below (A/B knob).
 bool rtm_bvh_build(int32_t n, const double* position, const float* radius, const double ref[3], RtmBvhHost& out,
-                   double c_trav = 0.0, int leaf_max = 0);
+                   double c_trav = 0.0, int leaf_max = 0, int layout = 0);
 
 // ---- compact form of the same tree for the FP32 walk: 32 bytes per inner node ---------------------------------
 // The FP32 hierarchy kernel is bound by L1 wavefronts (one per lane per load instruction, every lane on a different
@@ -68,7 +72,24 @@ struct RtmBvh16Host {
 };
 void rtm_bvh_compact16(const RtmBvhHost& in, RtmBvh16Host& out);
 
-// ---- 4-wide form of the same tree (host-side design study) ----------------
+// ---- 4-wide compact form (A/B alternative of the FP32 walk: rtm_options.debug_bvh_walk bit 3) ---------------------
+// A node that holds up to four children — greedy collapse of the two-child tree: the inner child with the largest box is
+// replaced by its own two children until there are four — halves the DEPENDENT fetches of a walk (synth10k: 29.4 -> 15.6
+// per ray for the same 59 box tests: scripts/study_bvh4.py).  Built to test whether the walk is bound by the latency of
+// those fetches; it is not: 6.42 Grays/s on C5 against 6.44 for the two-child walk (equal work per burst), because a step
+// costs 125 instructions against 66 and the instruction stream, not the fetch latency, is what the kernel waits for.
+// 64 bytes = two halves laid out exactly like a two-child compact node:
+//   u32[0..2] child 0   u32[3..5] child 1   u32[6], u32[7] codes 0, 1   |   u32[8..10] child 2   u32[11..13] child 3   u32[14], u32[15] codes 2, 3
+// The child boxes ARE RtmBvh16Host's (same words, same frame), the leaves are shared, child codes >= 0 index THIS array;
+// an empty slot holds the RTM_BVH_NONE code behind a box that no ray hits (half-extents = -infinity).
+struct RtmBvh16x4Host {
+    std::vector<uint32_t> nodes;     // 16 per node, breadth-first, node 0 = root
+    int32_t depth = 0;               // deepest leaf, root = 0: a walk holds at most 3 * depth + 1 stack entries
+    bool ok = false;
+};
+void rtm_bvh_compact16x4(const RtmBvhHost& in, const RtmBvh16Host& c16, RtmBvh16x4Host& out);
+
+// ---- 4-wide form of the same tree with float boxes (host-side design study) ----------------
 // Greedy collapse of the two-child tree: a node adopts its grandchildren (largest box first) until it holds 4
 // children.  The child boxes ARE the two-child tree's boxes, the leaves are shared (same leaf codes, same
 // leaf_geo / leaf_id), so the set of candidates a ray reaches can only shrink in visits, never change in winners.

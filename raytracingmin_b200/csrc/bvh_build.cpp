@@ -191,7 +191,7 @@ struct Builder {
 }  // namespace
 
 bool rtm_bvh_build(int32_t n, const double* position, const float* radius, const double ref[3], RtmBvhHost& out, double c_trav,
-                   int leaf_max) {
+                   int leaf_max, int layout) {
     out = RtmBvhHost();
     if (n <= 0) return true;
     // Spheres far larger than the typical one (the r = 1e4 "walls" of the Cornell scenes) would
@@ -240,25 +240,54 @@ bool rtm_bvh_build(int32_t n, const double* position, const float* radius, const
         out.leaf_id.push_back(-1);
     }
     if (root.code >= 0) {
-        // renumber the inner nodes breadth-first: node 0 is the root and the first 2^k - 1 indices are the top
-        // k levels (neighbouring cache lines for the part of the tree every ray walks; a shared-memory copy of
-        // these levels was measured and was slower than L1: profiles/r01)
+        // Renumber the inner nodes.  layout 0 (default): breadth-first — node 0 is the root and the first 2^k - 1 indices
+        // are the top k levels (neighbouring cache lines for the part of the tree every ray walks; a shared-memory copy of
+        // these levels was measured and was slower than L1: profiles/r01).  layout 1 (A/B knob): the first
+        // RTM_BVH_LAYOUT_TOP nodes breadth-first, the rest in TREELETS of 4 (a node, its inner children, one grandchild:
+        // four compact 32-byte nodes in one 128-byte line).  Measured equal (6.44 Grays/s either way on C5, and an LRU
+        // model of the L1 agrees: scripts/study_bvh_layout.py) — a warp waits for its slowest lane, and with 17 lanes on
+        // 17 different nodes some lane misses L1 under any numbering.  Only addresses change: same walk, same image.
         const size_t n_nodes = out.nodes.size() / 4;
-        std::vector<int32_t> order, new_id(n_nodes, -1);
-        order.reserve(n_nodes);
-        order.push_back(root.code);
-        new_id[root.code] = 0;
-        for (size_t k = 0; k < order.size(); ++k) {
-            const float4 c = out.nodes[4 * (size_t)order[k] + 3];
-            int32_t ch[2];
+        auto kids = [&](int32_t node, int32_t ch[2]) {
+            const float4 c = out.nodes[4 * (size_t)node + 3];
             memcpy(&ch[0], &c.x, 4);
             memcpy(&ch[1], &c.y, 4);
+        };
+        std::vector<int32_t> order, new_id(n_nodes, -1);
+        order.reserve(n_nodes);
+        std::vector<int32_t> fifo{root.code};
+        size_t head = 0;
+        const size_t top = (layout == 1) ? (size_t)RTM_BVH_LAYOUT_TOP : n_nodes;
+        while (head < fifo.size() && order.size() < top) {
+            const int32_t node = fifo[head++];
+            order.push_back(node);
+            int32_t ch[2];
+            kids(node, ch);
             for (int j = 0; j < 2; ++j)
-                if (ch[j] >= 0) {
-                    new_id[ch[j]] = (int32_t)order.size();
-                    order.push_back(ch[j]);
-                }
+                if (ch[j] >= 0) fifo.push_back(ch[j]);
         }
+        // the subtrees hanging below the top, depth-first so that neighbouring subtrees get neighbouring addresses
+        std::vector<int32_t> stack(fifo.rbegin(), fifo.rend() - (ptrdiff_t)head);
+        std::vector<int32_t> lq;
+        while (!stack.empty()) {
+            lq.clear();
+            size_t lh = 0, in_line = order.size() & 3u;   // keep filling the line the top part left open
+            do {
+                if (lh == lq.size()) {
+                    if (stack.empty()) break;
+                    lq.push_back(stack.back());
+                    stack.pop_back();
+                }
+                const int32_t node = lq[lh++];
+                order.push_back(node);
+                int32_t ch[2];
+                kids(node, ch);
+                for (int j = 0; j < 2; ++j)
+                    if (ch[j] >= 0) lq.push_back(ch[j]);
+            } while (++in_line < 4);
+            for (size_t k = lq.size(); k > lh; --k) stack.push_back(lq[k - 1]);
+        }
+        for (size_t k = 0; k < order.size(); ++k) new_id[order[k]] = (int32_t)k;
         std::vector<float4> nn(out.nodes.size());
         for (size_t k = 0; k < order.size(); ++k) {
             for (int j = 0; j < 4; ++j) nn[4 * k + j] = out.nodes[4 * (size_t)order[k] + j];
@@ -383,6 +412,68 @@ void rtm_bvh_compact16(const RtmBvhHost& in, RtmBvh16Host& out) {
     if (!infl.empty()) {
         std::nth_element(infl.begin(), infl.begin() + infl.size() / 2, infl.end());
         out.inflation = infl[infl.size() / 2];
+    }
+    out.ok = true;
+}
+
+// ---- 4-wide compact form (bvh.h: RtmBvh16x4Host) -----------------------------------------------------------------
+void rtm_bvh_compact16x4(const RtmBvhHost& in, const RtmBvh16Host& c16, RtmBvh16x4Host& out) {
+    out = RtmBvh16x4Host();
+    if (!c16.ok || in.root < 0 || in.root == RTM_BVH_NONE) return;
+    struct Wide {
+        int32_t code;      // the two-child tree's child code
+        double area;
+        uint32_t w[3];     // its half-precision box: the words of the two-child compact node that holds it
+    };
+    auto kids2 = [&](int32_t node, Wide k[2]) {
+        Kid4 f[2];
+        kids_of(in, node, f);
+        for (int j = 0; j < 2; ++j) {
+            k[j].code = f[j].code;
+            k[j].area = f[j].area();
+            for (int a = 0; a < 3; ++a) k[j].w[a] = c16.nodes[8 * (size_t)node + 3 * j + a];
+        }
+    };
+    std::vector<int32_t> src{in.root}, level{0};
+    for (size_t k = 0; k < src.size(); ++k) {
+        std::vector<Wide> kids(2);
+        kids2(src[k], kids.data());
+        while (kids.size() < 4) {
+            int pick = -1;
+            double best = -1.0;
+            for (size_t i = 0; i < kids.size(); ++i)
+                if (kids[i].code >= 0 && kids[i].area > best) {
+                    best = kids[i].area;
+                    pick = (int)i;
+                }
+            if (pick < 0) break;
+            Wide two[2];
+            kids2(kids[pick].code, two);
+            kids[pick] = two[0];
+            kids.push_back(two[1]);
+        }
+        uint32_t w[16];
+        for (int j = 0; j < 4; ++j) {
+            uint32_t* box = w + 8 * (j >> 1) + 3 * (j & 1);
+            uint32_t& code = w[8 * (j >> 1) + 6 + (j & 1)];
+            if (j < (int)kids.size()) {
+                for (int a = 0; a < 3; ++a) box[a] = kids[j].w[a];
+                if (kids[j].code >= 0) {
+                    code = (uint32_t)src.size();                   // index the child will get
+                    src.push_back(kids[j].code);
+                    level.push_back(level[k] + 1);
+                } else {
+                    code = (uint32_t)kids[j].code;                 // leaf: the two-child tree's leaf code
+                    out.depth = std::max(out.depth, level[k] + 1);
+                }
+            } else {
+                box[0] = 0u;                                       // centre 0, half-extents -inf: near = +inf, far = -inf
+                box[1] = 0xFC000000u;
+                box[2] = 0xFC00FC00u;
+                code = (uint32_t)RTM_BVH_NONE;
+            }
+        }
+        out.nodes.insert(out.nodes.end(), w, w + 16);
     }
     out.ok = true;
 }

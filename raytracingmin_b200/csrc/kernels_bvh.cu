@@ -32,16 +32,35 @@ namespace {
 #define RTM_BVH_S_ROUND 1   // lanes that must need another roulette decision for the S block to run another round (swept: 1 4.50, 2 4.46, 4 4.45, 8 4.34 Grays/s on C5)
 #endif
 
+// Material records (geo / emi / alb: 48 bytes per sphere, 480 KB at 10^4 spheres, one random sphere per hit) have no reuse
+// worth an L1 line, and an LRU model of the SM's L1 (scripts/study_bvh_layout.py) puts the node hit rate at 62 % with them
+// allocating (ncu measured 60 %) and at 75 % without.  Reading them with L1::no_allocate (RTM_BVH_MAT_NA=1) was measured:
+// 6.30 against 6.38 Grays/s on C5 (same box, profiles/r02/c5_alternatives_r02g.jsonl) — the hit rate is not what the walk
+// waits for (a warp waits for its slowest lane; with 17 lanes on 17 nodes one of them misses either way).  Left off.
+#ifndef RTM_BVH_MAT_NA
+#define RTM_BVH_MAT_NA 0
+#endif
+__device__ __forceinline__ float4 mat_ld(const float4* p) {
+#if RTM_BVH_MAT_NA
+    float4 v;
+    asm("ld.global.nc.L1::no_allocate.v4.f32 {%0, %1, %2, %3}, [%4];" : "=f"(v.x), "=f"(v.y), "=f"(v.z), "=f"(v.w) : "l"(p));
+    return v;
+#else
+    return __ldg(p);
+#endif
+}
+
 // PL: n_pl planes (extension) behind the n_sph spheres in the material records, tested at the start of every ray
 // SST: the per-lane traversal stack lives in shared memory, stack[level][thread], RTM_BVH_SSTACK levels (the host
 // picks it when the tree is shallow enough: depth + 2 entries are the most a walk can hold); otherwise a private
 // 64-entry array in local memory.
-#ifndef RTM_BVH_SSTACK
-#define RTM_BVH_SSTACK 24
+// WK: the nodes walked — 0 = 64-byte float nodes, 1 = compact half-precision two-child nodes (one 32-byte request per visit;
+// bvh.h: RtmBvh16Host), 2 = compact 4-wide nodes (two requests per visit, half the visits; bvh.h: RtmBvh16x4Host)
+#ifndef RTM_BVH4_MINBLOCKS
+#define RTM_BVH4_MINBLOCKS 7
 #endif
-// H16: walk the compact half-precision nodes (one 32-byte request per visit; bvh.h: RtmBvh16Host)
-template <int NP, bool ACNE, bool PL, bool SST, bool H16>
-__global__ void __launch_bounds__(RTM_MEGA_THREADS, RTM_BVH_MINBLOCKS)
+template <int NP, bool ACNE, bool PL, bool SST, int WK>
+__global__ void __launch_bounds__(RTM_MEGA_THREADS, WK == 2 ? RTM_BVH4_MINBLOCKS : RTM_BVH_MINBLOCKS)
 radiance_bvh_kernel(const __grid_constant__ RtmHotScene hot, const __grid_constant__ RtmPassParams p, float4* __restrict__ records,
                     RtmCounters* __restrict__ counters, RtmBvhDev bvh, RtmMatDev mat, const float* __restrict__ cps0, int n_sph, int n_pl) {
     __shared__ SelfMask sh_mask;
@@ -129,7 +148,7 @@ radiance_bvh_kernel(const __grid_constant__ RtmHotScene hot, const __grid_consta
                 const bool miss = (wbits == RTM_REC_MISS);
                 const int Pid = miss ? 0 : (int)(wbits & RTM_REC_IDMASK);
                 RTM_ASSERT(ql < n_sub && (miss || Pid < n_sph + n_pl));
-                const float4 e0 = miss ? make_float4(0.f, 0.f, 0.f, 0.f) : __ldg(mat.emi + Pid);   // no record to read for a miss (n may be 0)
+                const float4 e0 = miss ? make_float4(0.f, 0.f, 0.f, 0.f) : mat_ld(mat.emi + Pid);   // no record to read for a miss (n may be 0)
                 if (miss || __float_as_uint(e0.w) == 0u) {
                     float4 out = make_float4(0.f, 0.f, 0.f, 0.f);
                     if (!miss) {
@@ -168,19 +187,21 @@ radiance_bvh_kernel(const __grid_constant__ RtmHotScene hot, const __grid_consta
         if (__any_sync(0xffffffffu, in_s)) {
             f3 w = mk(0, 0, 1);
             float cpsn = 0.f;
+            unsigned thr = 0;   // roulette threshold kd * 2^32 of the surface the lane stands on (from the emission record read there)
     // the primary hit of the lane's sub-pixel is NOT lane state here: it is re-read from records[ql] (which holds it
             // until the sub-pixel's sum is written) at every sample restart — 8 registers less, which is what lets
             // RTM_BVH_MINBLOCKS blocks stay resident
             auto stand_on_primary = [&](const float4 rec) {
                 const unsigned wbits = __float_as_uint(rec.w);
                 const int pid = (int)(wbits & RTM_REC_IDMASK);
-                const float4 g = __ldg(mat.geo + pid), e0 = __ldg(mat.emi + pid);
+                const float4 g = mat_ld(mat.geo + pid), e0 = mat_ld(mat.emi + pid);
                 const float ir = (wbits & RTM_REC_FLIP) ? -g.w : g.w;
                 o = mk(rec.x, rec.y, rec.z);
                 w = mk((o.x - g.x) * ir, (o.y - g.y) * ir, (o.z - g.z) * ir);
                 if (PL && pid >= n_sph) w = (wbits & RTM_REC_FLIP) ? mk(-g.x, -g.y, -g.z) : mk(g.x, g.y, g.z);
                 id = pid;
                 T = mk(1, 1, 1); L = mk(e0.x, e0.y, e0.z); sd &= ~511u;
+                thr = __float_as_uint(e0.w);
                 if (ACNE) cpsn = (wbits & RTM_REC_FLIP) ? 0.f : cps0[ql] * g.w * RTM_ACNE_INV2TAU;
             };
             // a finished ray is applied to the path; returns true when the path ends there
@@ -188,7 +209,7 @@ radiance_bvh_kernel(const __grid_constant__ RtmHotScene hot, const __grid_consta
                 if (id2 < 0) return true;                                            // miss: Renderer.cpp:116
                 RTM_ASSERT(id2 < n_sph + n_pl);
                 o = mk(fmaf(d.x, t, o.x), fmaf(d.y, t, o.y), fmaf(d.z, t, o.z));     // :79
-                const float4 g = __ldg(mat.geo + id2);
+                const float4 g = mat_ld(mat.geo + id2);
                 f3 nn = mk((o.x - g.x) * g.w, (o.y - g.y) * g.w, (o.z - g.z) * g.w);
                 if (PL && id2 >= n_sph) nn = mk(g.x, g.y, g.z);   // a plane's record holds its normal, 1/r = 0
                 if (g.w > 1e-2f) {
@@ -204,9 +225,10 @@ radiance_bvh_kernel(const __grid_constant__ RtmHotScene hot, const __grid_consta
                 id = id2;
                 ++sd;
                 if (ACNE) cpsn = flip ? 0.f : t * t * ref_normalize_eps(eps_bits) * g.w * RTM_ACNE_INV2TAU;
-                const float4 e2 = __ldg(mat.emi + id2);
+                const float4 e2 = mat_ld(mat.emi + id2);
                 L.x = fmaf(T.x, e2.x, L.x); L.y = fmaf(T.y, e2.y, L.y); L.z = fmaf(T.z, e2.z, L.z);
-                return __float_as_uint(e2.w) == 0u;                                  // kd == 0: the next roulette cannot continue
+                thr = __float_as_uint(e2.w);
+                return thr == 0u;                                  // kd == 0: the next roulette cannot continue
             };
             bool end = false;
             if (in_s && fresh) {
@@ -226,10 +248,9 @@ radiance_bvh_kernel(const __grid_constant__ RtmHotScene hot, const __grid_consta
                         // than carrying it; the division only exists for sub-pixel-sliced multi-GPU handles)
                         const unsigned q = full_grid ? ql : (ql / sub_count) * grid + sub_begin + (ql % sub_count);
                         const uint2 rnd = rtm_bounce_rng(make_uint2(q, sd), p.rk);
-                        const float4 em = __ldg(mat.emi + id);
-                        end = !((rnd.x < __float_as_uint(em.w)) && ((sd & 511u) + 1u < (unsigned)p.max_depth));   // Renderer.cpp:78
+                        end = !((rnd.x < thr) && ((sd & 511u) + 1u < (unsigned)p.max_depth));   // Renderer.cpp:78
                         if (!end) {
-                            const float4 al = __ldg(mat.alb + id);
+                            const float4 al = mat_ld(mat.alb + id);
                             T.x *= al.x; T.y *= al.y; T.z *= al.z;                               // colorKD
                             d = cosine_dir(w, rnd.y, ((rnd.x & 0xFFFu) << 10) | (rnd.y & 0x3FFu));
                             eps_bits = rnd.x ^ (rnd.y * 0x9E3779B9u);
@@ -239,7 +260,7 @@ radiance_bvh_kernel(const __grid_constant__ RtmHotScene hot, const __grid_consta
                                 const float cosw = dot(w, d);
                                 if (cpsn + cosw <= 0.f && !(PL && id >= n_sph)) {
                                     // SettingData.cpp:208-212: the far root of the sphere the ray stands (just) inside
-                                    const float rr = fast_rcp(__ldg(mat.geo + id).w);
+                                    const float rr = fast_rcp(mat_ld(mat.geo + id).w);
                                     const float qq = -cpsn * rr * RTM_ACNE_2TAU, bq = rr * cosw;
                                     end = apply_hit(id, qq * fast_rcp(bq + fast_sqrt(fmaf(bq, bq, qq))));
                                     self = true;   // stands on the next vertex: decide again
@@ -275,7 +296,7 @@ radiance_bvh_kernel(const __grid_constant__ RtmHotScene hot, const __grid_consta
             if (deciding && have) fresh = true;   // (only with RTM_BVH_S_ROUND > 1) restarted in the last round: stands on its primary hit
             if (start) {
                 // the packed big-sphere test (~140 instructions) and the planes: once, for all lanes that start a ray
-                bvh_ray_begin<NP, ST, H16>(hot, sh_mask, sh_big, bvh, bvh_big_slot(ocode), o, d, key_mask, ray, stack, n_tests);
+                bvh_ray_begin<NP, ST, WK != 0>(hot, sh_mask, sh_big, bvh, bvh_big_slot(ocode), o, d, key_mask, ray, stack, n_tests);
                 sslot = bvh_leaf_slot(ocode);
                 if (PL) bvh_ray_planes(hot, n_sph, n_pl, id, o, d, ray);
                 if (ray.node != RTM_BVH_NONE_DEV) tracing = true;
@@ -297,10 +318,11 @@ radiance_bvh_kernel(const __grid_constant__ RtmHotScene hot, const __grid_consta
             for (int k = 0; k < RTM_BVH_BURST; ++k) {
                 if (tracing && ray.node < 0 && held == 0) {
                     held = ray.node;
-                    ray.node = stack[ST * --ray.sp];
+                    ray.node = bvh_pop<ST>(stack, ray);
                 }
                 if (!(tracing && bvh_is_inner(ray.node))) break;
-                if (H16) bvh16_inner_step<ST>(bvh, ray, stack);
+                if (WK == 2) bvh16x4_inner_step<ST>(bvh, ray, stack);
+                else if (WK == 1) bvh16_inner_step<ST>(bvh, ray, stack);
                 else bvh_inner_step<ST>(bvh, ray, stack);
                 ++n_nodes;
             }
@@ -310,7 +332,8 @@ radiance_bvh_kernel(const __grid_constant__ RtmHotScene hot, const __grid_consta
             int k = 0;
 #pragma unroll 1
             for (; k < RTM_BVH_BURST && tracing && bvh_is_inner(ray.node); ++k) {
-                if (H16) bvh16_inner_step<ST>(bvh, ray, stack);
+                if (WK == 2) bvh16x4_inner_step<ST>(bvh, ray, stack);
+                else if (WK == 1) bvh16_inner_step<ST>(bvh, ray, stack);
                 else bvh_inner_step<ST>(bvh, ray, stack);
             }
             n_nodes += (unsigned)k;   // visits counted once per burst, not once per step
@@ -343,7 +366,7 @@ radiance_bvh_kernel(const __grid_constant__ RtmHotScene hot, const __grid_consta
 }
 
 // the hierarchy variant of the hook: same trace function as radiance_mega_kernel<*, true>
-template <int NP, bool H16>
+template <int NP, int WK>
 __global__ void closest_hit_bvh_f32_kernel(const __grid_constant__ RtmHotScene hot, RtmBvhDev bvh, RtmMatDev mat, unsigned key_mask, double rx, double ry, double rz, uint32_t n,
                                            const double* __restrict__ org, const double* __restrict__ dir,
                                            const int32_t* __restrict__ origin_id, int n_sph, int n_pl, int32_t* __restrict__ hit,
@@ -362,30 +385,32 @@ __global__ void closest_hit_bvh_f32_kernel(const __grid_constant__ RtmHotScene h
     const int ocode = (oid >= 0) ? __float_as_int(__ldg(mat.alb + oid).w) : -1;
     float t;
     unsigned a = 0, b = 0;
-    hit[i] = trace_bvh_f32<NP, H16>(hot, sh_mask, sh_big, bvh, oid, ocode, o, d, t, key_mask, a, b, n_sph, n_pl);
+    hit[i] = trace_bvh_f32<NP, WK>(hot, sh_mask, sh_big, bvh, oid, ocode, o, d, t, key_mask, a, b, n_sph, n_pl);
     tout[i] = (double)t;
 }
 
-template <int NP, bool ACNE, bool PL, bool SST, bool H16>
+template <int NP, bool ACNE, bool PL, bool SST, int WK>
 void launch_bvh4(const RtmHotScene& hot, const RtmBvhDev& bvh, const RtmMatDev& mat, const RtmPassParams& p, float4* records, RtmCounters* counters,
                  int sm_count, const float* cps0, int n_sph, int n_pl, cudaStream_t st) {
     int per_sm = 0;
-    cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, radiance_bvh_kernel<NP, ACNE, PL, SST, H16>, RTM_MEGA_THREADS, 0);
+    cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, radiance_bvh_kernel<NP, ACNE, PL, SST, WK>, RTM_MEGA_THREADS, 0);
     if (per_sm < 1) per_sm = 1;
-    radiance_bvh_kernel<NP, ACNE, PL, SST, H16><<<sm_count * per_sm, RTM_MEGA_THREADS, 0, st>>>(hot, p, records, counters, bvh, mat, cps0, n_sph, n_pl);
+    radiance_bvh_kernel<NP, ACNE, PL, SST, WK><<<sm_count * per_sm, RTM_MEGA_THREADS, 0, st>>>(hot, p, records, counters, bvh, mat, cps0, n_sph, n_pl);
 }
 template <int NP, bool ACNE, bool PL, bool SST>
 void launch_bvh3(const RtmHotScene& hot, const RtmBvhDev& bvh, const RtmMatDev& mat, const RtmPassParams& p, float4* records, RtmCounters* counters,
                  int sm_count, const float* cps0, int n_sph, int n_pl, cudaStream_t st) {
-    if (bvh.nodes16) launch_bvh4<NP, ACNE, PL, SST, true>(hot, bvh, mat, p, records, counters, sm_count, cps0, n_sph, n_pl, st);
-    else launch_bvh4<NP, ACNE, PL, SST, false>(hot, bvh, mat, p, records, counters, sm_count, cps0, n_sph, n_pl, st);
+    if (bvh.nodes16x4) launch_bvh4<NP, ACNE, PL, SST, 2>(hot, bvh, mat, p, records, counters, sm_count, cps0, n_sph, n_pl, st);
+    else if (bvh.nodes16) launch_bvh4<NP, ACNE, PL, SST, 1>(hot, bvh, mat, p, records, counters, sm_count, cps0, n_sph, n_pl, st);
+    else launch_bvh4<NP, ACNE, PL, SST, 0>(hot, bvh, mat, p, records, counters, sm_count, cps0, n_sph, n_pl, st);
 }
 template <int NP, bool ACNE, bool PL>
 void launch_bvh2(const RtmHotScene& hot, const RtmBvhDev& bvh, const RtmMatDev& mat, const RtmPassParams& p, float4* records, RtmCounters* counters,
                  int sm_count, const float* cps0, int n_sph, int n_pl, int walk, cudaStream_t st) {
     // a walk holds at most depth + 2 stack entries (one per level + the sentinel); walk & 1 (rtm_options.debug_bvh_walk,
     // A/B runs) keeps the stack in local memory
-    if (!(walk & 1) && bvh.depth + 2 <= RTM_BVH_SSTACK) launch_bvh3<NP, ACNE, PL, true>(hot, bvh, mat, p, records, counters, sm_count, cps0, n_sph, n_pl, st);
+    const int need = bvh.nodes16x4 ? 3 * bvh.depth4 + 1 : bvh.depth + 2;
+    if (!(walk & 1) && need <= RTM_BVH_SSTACK) launch_bvh3<NP, ACNE, PL, true>(hot, bvh, mat, p, records, counters, sm_count, cps0, n_sph, n_pl, st);
     else launch_bvh3<NP, ACNE, PL, false>(hot, bvh, mat, p, records, counters, sm_count, cps0, n_sph, n_pl, st);
 }
 template <int NP>
@@ -404,6 +429,12 @@ void launch_bvh(const RtmHotScene& hot, const RtmBvhDev& bvh, const RtmMatDev& m
 void rtm_launch_radiance_bvh(const RtmHotScene& hot, const RtmBvhDev& bvh, const RtmMatDev& mat, const RtmPassParams& p, float4* records,
                              RtmCounters* counters, int32_t sm_count, const float* cps0, int32_t n_sph, int32_t n_pl, int32_t walk,
                              cudaStream_t st) {
+    // walk (rtm_options.debug_bvh_walk) bit 4: the ray-pool kernel (kernels_bvh_pool.cu), where it takes the scene.  An A/B
+    // variant: bit-identical image, measured slower than this file's kernel (5.5-5.7 against 6.44 Grays/s on C5)
+    if ((walk & 16) && !(walk & (1 | 8)) && rtm_pool_kernel_takes(bvh, n_pl)) {
+        rtm_launch_radiance_bvh_pool(hot, bvh, mat, p, records, counters, sm_count, cps0, n_sph, st);
+        return;
+    }
     switch ((bvh.n_big + 1) / 2) {
         case 0: launch_bvh<0>(hot, bvh, mat, p, records, counters, sm_count, cps0, n_sph, n_pl, walk, st); break;
         case 1: launch_bvh<1>(hot, bvh, mat, p, records, counters, sm_count, cps0, n_sph, n_pl, walk, st); break;
@@ -420,8 +451,9 @@ void rtm_launch_closest_hit_bvh_f32(const RtmHotScene& hot, const RtmBvhDev& bvh
     switch ((bvh.n_big + 1) / 2) {
 #define RTM_CASE(NP)                                                                                                                              \
     do {                                                                                                                                          \
-        if (bvh.nodes16) closest_hit_bvh_f32_kernel<NP, true><<<g, 128, 0, st>>>(hot, bvh, mat, 0xFFFFFFF8u, refd[0], refd[1], refd[2], n, org, dir, origin_id, n_spheres, n_planes, hit, t); \
-        else closest_hit_bvh_f32_kernel<NP, false><<<g, 128, 0, st>>>(hot, bvh, mat, 0xFFFFFFF8u, refd[0], refd[1], refd[2], n, org, dir, origin_id, n_spheres, n_planes, hit, t);          \
+        if (bvh.nodes16x4) closest_hit_bvh_f32_kernel<NP, 2><<<g, 128, 0, st>>>(hot, bvh, mat, 0xFFFFFFF8u, refd[0], refd[1], refd[2], n, org, dir, origin_id, n_spheres, n_planes, hit, t); \
+        else if (bvh.nodes16) closest_hit_bvh_f32_kernel<NP, 1><<<g, 128, 0, st>>>(hot, bvh, mat, 0xFFFFFFF8u, refd[0], refd[1], refd[2], n, org, dir, origin_id, n_spheres, n_planes, hit, t); \
+        else closest_hit_bvh_f32_kernel<NP, 0><<<g, 128, 0, st>>>(hot, bvh, mat, 0xFFFFFFF8u, refd[0], refd[1], refd[2], n, org, dir, origin_id, n_spheres, n_planes, hit, t);          \
     } while (0)
         case 0: RTM_CASE(0); break;
         case 1: RTM_CASE(1); break;

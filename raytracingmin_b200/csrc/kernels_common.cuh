@@ -286,9 +286,15 @@ __device__ __forceinline__ bool bvh_is_inner(int node) { return (unsigned)node <
 // entries a lane's traversal stack holds: the interleaved shared-memory layout (ST = block size) has RTM_BVH_SSTACK levels,
 // a private array RTM_BVH_STACK_DEV
 #ifndef RTM_BVH_SSTACK
-#define RTM_BVH_SSTACK 24
+#define RTM_BVH_SSTACK 26   // the 4-wide walk of a depth-8 tree (10^4 spheres) can hold 3 * 8 + 1 entries
 #endif
-#define RTM_STACK_CAP(ST) ((ST) == 1 ? RTM_BVH_STACK_DEV : RTM_BVH_SSTACK)
+// the ray-pool kernel (kernels_bvh_pool.cu): slots per warp / per block, levels of a slot's shared-memory stack
+#define RTM_POOL_SLOTS 64
+#define RTM_POOL_BLOCK_SLOTS (RTM_POOL_SLOTS * (RTM_MEGA_THREADS / 32))
+#ifndef RTM_POOL_LEVELS
+#define RTM_POOL_LEVELS 18
+#endif
+#define RTM_STACK_CAP(ST) ((ST) == 1 ? RTM_BVH_STACK_DEV : ((ST) == RTM_POOL_BLOCK_SLOTS ? RTM_POOL_LEVELS : RTM_BVH_SSTACK))
 
 struct BvhRay {
     f3 inv, oi;      // 1/d and o/d
@@ -298,6 +304,47 @@ struct BvhRay {
     int node;        // current node (child code), RTM_BVH_NONE_DEV when the traversal is over
     int sp;
 };
+
+// The traversal stack of a lane.  ST == 1: a private array indexed by r.sp.  ST > 1 (the interleaved shared-memory layout
+// stack[level][thread]): r.sp IS the shared-memory byte address of the lane's next free entry — a push is one STS and one
+// add, a pop one add and one LDS, with no base pointer to keep (or to rematerialise) in the walk's loops.
+#define RTM_STACK_IDX(ST, stack, r) ((ST) == 1 ? (r).sp : (int)(((unsigned)(r).sp - (unsigned)__cvta_generic_to_shared(stack)) / (4u * (ST))))
+template <int ST>
+__device__ __forceinline__ void bvh_stack_reset(int* stack, BvhRay& r) {
+    r.sp = (ST == 1) ? 0 : (int)(unsigned)__cvta_generic_to_shared(stack);
+}
+template <int ST>
+__device__ __forceinline__ void bvh_push(int* stack, BvhRay& r, int v) {
+    RTM_ASSERT(RTM_STACK_IDX(ST, stack, r) >= 0 && RTM_STACK_IDX(ST, stack, r) < RTM_STACK_CAP(ST));
+    if (ST == 1) stack[r.sp++] = v;
+    else {
+        asm volatile("st.shared.b32 [%0], %1;" :: "r"(r.sp), "r"(v));
+        r.sp += 4 * ST;
+    }
+}
+template <int ST>
+__device__ __forceinline__ int bvh_pop(int* stack, BvhRay& r) {
+    RTM_ASSERT(RTM_STACK_IDX(ST, stack, r) > 0);
+    if (ST == 1) return stack[--r.sp];
+    r.sp -= 4 * ST;
+    int v;
+    asm volatile("ld.shared.b32 %0, [%1];" : "=r"(v) : "r"(r.sp));
+    return v;
+}
+
+// the slab-test constants of a ray: a pure function of (o, d), so a kernel that parks rays in shared memory keeps o and d
+// only and derives these again when it picks the ray up (kernels_bvh_pool.cu)
+template <bool H16>
+__device__ __forceinline__ void bvh_ray_frame(const RtmBvhDev& bvh, f3 o, f3 d, BvhRay& r) {
+    r.inv = mk(fast_rcp(d.x), fast_rcp(d.y), fast_rcp(d.z));
+    if (H16) {
+        r.oi = mk((o.x - bvh.ref16[0]) * r.inv.x, (o.y - bvh.ref16[1]) * r.inv.y, (o.z - bvh.ref16[2]) * r.inv.z);
+        r.inv = mk(r.inv.x * bvh.inv_scale16, r.inv.y * bvh.inv_scale16, r.inv.z * bvh.inv_scale16);
+        r.ainv = mk(fabsf(r.inv.x), fabsf(r.inv.y), fabsf(r.inv.z));
+    } else {
+        r.oi = mk(o.x * r.inv.x, o.y * r.inv.y, o.z * r.inv.z);
+    }
+}
 
 // the packed test over the big list, then position the lane on the root
 // ST = distance in ints between two consecutive entries of a lane's stack: 1 for a private (local-memory) array,
@@ -317,17 +364,10 @@ __device__ __forceinline__ void bvh_ray_begin(const RtmHotScene& hot, const Self
         }
         n_tests += 2 * NP;
     }
-    r.inv = mk(fast_rcp(d.x), fast_rcp(d.y), fast_rcp(d.z));
-    if (H16) {
-        r.oi = mk((o.x - bvh.ref16[0]) * r.inv.x, (o.y - bvh.ref16[1]) * r.inv.y, (o.z - bvh.ref16[2]) * r.inv.z);
-        r.inv = mk(r.inv.x * bvh.inv_scale16, r.inv.y * bvh.inv_scale16, r.inv.z * bvh.inv_scale16);
-        r.ainv = mk(fabsf(r.inv.x), fabsf(r.inv.y), fabsf(r.inv.z));
-    } else {
-        r.oi = mk(o.x * r.inv.x, o.y * r.inv.y, o.z * r.inv.z);
-    }
+    bvh_ray_frame<H16>(bvh, o, d, r);
     r.node = bvh.root;
-    r.sp = 0;
-    stack[ST * r.sp++] = RTM_BVH_NONE_DEV;
+    bvh_stack_reset<ST>(stack, r);
+    bvh_push<ST>(stack, r, RTM_BVH_NONE_DEV);
 }
 
 // 32 bytes per lane in ONE request (sm_100: LDG.E.256).  The walk is bound by L1 wavefronts (every lane of a warp
@@ -358,14 +398,12 @@ __device__ __forceinline__ void bvh_inner_step(const RtmBvhDev& bvh, BvhRay& r, 
     const int c0 = __float_as_int(q3.x), c1 = __float_as_int(q3.y);
     if (h0 && h1) {
         const bool swap = n1 < n0;
-        RTM_ASSERT(r.sp >= 0 && r.sp < RTM_STACK_CAP(ST));
-        stack[ST * r.sp++] = swap ? c0 : c1;
+        bvh_push<ST>(stack, r, swap ? c0 : c1);
         r.node = swap ? c1 : c0;
     } else if (h0 || h1) {
         r.node = h0 ? c0 : c1;
     } else {
-        RTM_ASSERT(r.sp > 0);
-        r.node = stack[ST * --r.sp];
+        r.node = bvh_pop<ST>(stack, r);
     }
 }
 
@@ -399,14 +437,49 @@ __device__ __forceinline__ void bvh16_inner_step(const RtmBvhDev& bvh, BvhRay& r
     const int c0 = (int)b.z, c1 = (int)b.w;
     if (h0 && h1) {
         const bool swap = n1 < n0;
-        RTM_ASSERT(r.sp >= 0 && r.sp < RTM_STACK_CAP(ST));
-        stack[ST * r.sp++] = swap ? c0 : c1;
+        bvh_push<ST>(stack, r, swap ? c0 : c1);
         r.node = swap ? c1 : c0;
     } else if (h0 || h1) {
         r.node = h0 ? c0 : c1;
     } else {
-        RTM_ASSERT(r.sp > 0);
-        r.node = stack[ST * --r.sp];
+        r.node = bvh_pop<ST>(stack, r);
+    }
+}
+
+// ---- the step on the 4-wide compact node (bvh.h: RtmBvh16x4Host): two 32-byte requests issued together, four box tests,
+// descend into the nearest child that was hit and push the others.  The pushed ones go in SLOT order, not by distance:
+// sorting four (distance, code) pairs costs ~25 instructions per step against 2.7 % more node visits without it
+// (scripts/study_bvh4.py, synth10k).  Half the dependent fetches of the two-child walk for the same number of box tests.
+template <int ST = 1>
+__device__ __forceinline__ void bvh16x4_inner_step(const RtmBvhDev& bvh, BvhRay& r, int* stack) {
+    RTM_ASSERT(r.node >= 0 && r.node < bvh.n_nodes4);
+    uint4 a, b, c, e;
+    const uint32_t* q = bvh.nodes16x4 + 16 * r.node;
+    ldg256u(q, a, b);
+    ldg256u(q + 8, c, e);
+    float n0, n1, n2, n3;
+    const float tm = r.best + 2.f * RTM_T_EPS;
+    const bool h0 = box_test_h16(a.x, a.y, a.z, r.oi, r.inv, r.ainv, tm, n0);
+    const bool h1 = box_test_h16(a.w, b.x, b.y, r.oi, r.inv, r.ainv, tm, n1);
+    const bool h2 = box_test_h16(c.x, c.y, c.z, r.oi, r.inv, r.ainv, tm, n2);
+    const bool h3 = box_test_h16(c.w, e.x, e.y, r.oi, r.inv, r.ainv, tm, n3);
+    // near distances are >= 0, so their bit patterns order like the values; the slot rides in the two low bits and a
+    // child that was missed sorts behind every hit
+    const unsigned k0 = h0 ? (__float_as_uint(n0) & ~3u) : 0xFFFFFFFCu;
+    const unsigned k1 = h1 ? ((__float_as_uint(n1) & ~3u) | 1u) : 0xFFFFFFFDu;
+    const unsigned k2 = h2 ? ((__float_as_uint(n2) & ~3u) | 2u) : 0xFFFFFFFEu;
+    const unsigned k3 = h3 ? ((__float_as_uint(n3) & ~3u) | 3u) : 0xFFFFFFFFu;
+    const unsigned kn = min(min(k0, k1), min(k2, k3));
+    if (kn < 0xFFFFFFFCu) {
+        const unsigned near = kn & 3u;
+        if (h0 && near != 0u) bvh_push<ST>(stack, r, (int)b.z);
+        if (h1 && near != 1u) bvh_push<ST>(stack, r, (int)b.w);
+        if (h2 && near != 2u) bvh_push<ST>(stack, r, (int)e.z);
+        if (h3 && near != 3u) bvh_push<ST>(stack, r, (int)e.w);
+        const unsigned lo = (near & 1u) ? b.w : b.z, hi = (near & 1u) ? e.w : e.z;
+        r.node = (int)((near & 2u) ? hi : lo);
+    } else {
+        r.node = bvh_pop<ST>(stack, r);
     }
 }
 
@@ -518,8 +591,7 @@ __device__ __forceinline__ void bvh_leaf_test(const RtmBvhDev& bvh, int leaf, in
 template <int ST = 1>
 __device__ __forceinline__ void bvh_leaf_step(const RtmBvhDev& bvh, int self_slot, f3 o, f3 d, BvhRay& r, int* stack, unsigned& n_tests) {
     bvh_leaf_test(bvh, r.node, self_slot, o, d, r, n_tests);
-    RTM_ASSERT(r.sp > 0);
-    r.node = stack[ST * --r.sp];
+    r.node = bvh_pop<ST>(stack, r);
 }
 
 // the wavefront variant's leaf step: candidates identified by their original index (one more 4-byte load per candidate)
@@ -564,17 +636,19 @@ __device__ __forceinline__ void bvh_ray_planes(const RtmHotScene& hot, int n_sph
 
 // whole query (test hook; the render kernel interleaves the same steps across its lanes).  ocode = alb.w of the
 // object the ray leaves (or -1)
-template <int NP, bool H16>
+// WK: 0 = float nodes, 1 = compact two-child nodes, 2 = compact 4-wide nodes
+template <int NP, int WK>
 __device__ __forceinline__ int trace_bvh_f32(const RtmHotScene& hot, const SelfMask& sm, const SharedBig& big, const RtmBvhDev& bvh, int oid, int ocode,
                                              f3 o, f3 d, float& t, unsigned key_mask, unsigned& n_tests, unsigned& n_nodes,
                                              int n_sph = 0, int n_pl = 0) {
     BvhRay r;
     int stack[RTM_BVH_STACK_DEV];
-    bvh_ray_begin<NP, 1, H16>(hot, sm, big, bvh, bvh_big_slot(ocode), o, d, key_mask, r, stack, n_tests);
+    bvh_ray_begin<NP, 1, WK != 0>(hot, sm, big, bvh, bvh_big_slot(ocode), o, d, key_mask, r, stack, n_tests);
     if (n_pl > 0) bvh_ray_planes(hot, n_sph, n_pl, oid, o, d, r);
     while (r.node != RTM_BVH_NONE_DEV) {
         while (bvh_is_inner(r.node)) {
-            if (H16) bvh16_inner_step(bvh, r, stack);
+            if (WK == 2) bvh16x4_inner_step(bvh, r, stack);
+            else if (WK == 1) bvh16_inner_step(bvh, r, stack);
             else bvh_inner_step(bvh, r, stack);
             ++n_nodes;
         }

@@ -152,6 +152,7 @@ struct rtm_renderer {
     bool use_bvh = false;       // closest hit through the hierarchy (bvh.h) instead of the O(N) loop
     RtmBvhHost bvh_host;
     RtmBvh16Host bvh16;         // compact form of bvh_host for the FP32 walk (ok = false: the float nodes are walked)
+    RtmBvh16x4Host bvh16x4;     // its 4-wide collapse (ok = false: the two-child compact nodes are walked)
     std::vector<float4> mat_geo, mat_emi, mat_alb;
 };
 
@@ -443,7 +444,7 @@ int renderer_create(const rtm_scene_desc* sc, const rtm_options* opt_in, rtm_ren
     if (f32_path && !use_bvh && sc->n_spheres + m > RTM_MAX_CONST_SPHERES)
         return fail(RTM_E_UNSUPPORTED, "FP32 brute-force path holds at most %d objects (use RTM_ACCEL_BVH / AUTO)",
                     RTM_MAX_CONST_SPHERES);
-    if (opt.debug_retry < 0 || opt.debug_retry > 2 || opt.debug_bvh_walk < 0 || opt.debug_bvh_walk > 3 || opt.debug_bvh_leaf_max < 0 ||
+    if (opt.debug_retry < 0 || opt.debug_retry > 2 || opt.debug_bvh_walk < 0 || opt.debug_bvh_walk > 31 || opt.debug_bvh_leaf_max < 0 ||
         opt.debug_bvh_leaf_max > 8 || !(opt.debug_bvh_ctrav >= 0.f) || opt.debug_clamp < 0 || opt.debug_clamp > 1)
         return fail(RTM_E_INVALID, "bad debug_* option");
     if (opt.variant == RTM_VARIANT_WAVEFRONT && sc->samples >= (1 << 22))
@@ -693,7 +694,7 @@ int renderer_create(const rtm_scene_desc* sc, const rtm_options* opt_in, rtm_ren
     }
 
     if (use_bvh) {
-        if (!rtm_bvh_build(n, sc->position, sc->radius, r->refd, r->bvh_host, (double)opt.debug_bvh_ctrav, opt.debug_bvh_leaf_max)) {
+        if (!rtm_bvh_build(n, sc->position, sc->radius, r->refd, r->bvh_host, (double)opt.debug_bvh_ctrav, opt.debug_bvh_leaf_max, (opt.debug_bvh_walk & 4) ? 1 : 0 /* treelet numbering */)) {
             const int d = r->bvh_host.depth;
             delete r;
             return fail(RTM_E_UNSUPPORTED, "sphere hierarchy too deep (%d levels)", d);
@@ -709,6 +710,13 @@ int renderer_create(const rtm_scene_desc* sc, const rtm_options* opt_in, rtm_ren
             // the typical leaf box by more than a quarter (features tiny against the scene's extent)
             rtm_bvh_compact16(r->bvh_host, r->bvh16);
             if (r->bvh16.ok && r->bvh16.inflation > 0.25) r->bvh16.ok = false;
+            // ... and, on request (A/B knob), their 4-wide collapse: half the dependent fetches per ray for the same box tests,
+            // measured no faster than the two-child walk (profiles/r02); needs a walk's worst-case stack (3 entries per
+            // level + the sentinel) to fit the kernels' private array
+            if (r->bvh16.ok && (opt.debug_bvh_walk & 8)) {
+                rtm_bvh_compact16x4(r->bvh_host, r->bvh16, r->bvh16x4);
+                if (r->bvh16x4.ok && 3 * r->bvh16x4.depth + 1 > RTM_BVH_STACK_DEV) r->bvh16x4.ok = false;
+            }
         }
         if (f32_path) {
             // alb.w of a sphere: its slot in the big list (0..7) or 8 + its leaf slot (kernels_common.cuh: bvh_big_slot / bvh_leaf_slot)
@@ -783,7 +791,8 @@ int renderer_create(const rtm_scene_desc* sc, const rtm_options* opt_in, rtm_ren
                 const RtmBvhHost& B = r->bvh_host;
                 const size_t n_nodes4 = B.nodes.size(), n_slots = B.leaf_geo.size(), n_mat = r->mat_geo.size();
                 const size_t n_16 = r->bvh16.ok ? r->bvh16.nodes.size() / 4 : 0;     // float4 units: 2 per node
-                const size_t total4 = n_nodes4 + n_16 + n_slots + 3 * n_mat + (n_slots + 3) / 4 + 1;
+                const size_t n_16x4 = r->bvh16x4.ok ? r->bvh16x4.nodes.size() / 4 : 0; // float4 units: 4 per node
+                const size_t total4 = n_nodes4 + n_16x4 + n_16 + n_slots + 3 * n_mat + (n_slots + 3) / 4 + 1;
                 CU(cudaMalloc(&c.d_bvh, total4 * sizeof(float4)));
                 float4* d = c.d_bvh;
                 cudaError_t put_err = cudaSuccess;
@@ -794,7 +803,11 @@ int renderer_create(const rtm_scene_desc* sc, const rtm_options* opt_in, rtm_ren
                     return at;
                 };
                 c.bvh.nodes = put(B.nodes.data(), n_nodes4, n_nodes4 * sizeof(float4));
-                // right behind the 64-byte float nodes: 32-byte aligned, as the 256-bit loads need
+                // right behind the 64-byte float nodes: 64-byte aligned (both halves of a 4-wide node in one line), then
+                // 32-byte aligned, as the 256-bit loads need
+                c.bvh.nodes16x4 = n_16x4 ? (const uint32_t*)put(r->bvh16x4.nodes.data(), n_16x4, n_16x4 * sizeof(float4)) : nullptr;
+                c.bvh.n_nodes4 = (int32_t)(n_16x4 / 4);
+                c.bvh.depth4 = r->bvh16x4.depth;
                 c.bvh.nodes16 = n_16 ? (const uint32_t*)put(r->bvh16.nodes.data(), n_16, n_16 * sizeof(float4)) : nullptr;
                 for (int k = 0; k < 3; ++k) c.bvh.ref16[k] = r->bvh16.ref[k];
                 c.bvh.inv_scale16 = r->bvh16.inv_scale;
@@ -1156,6 +1169,21 @@ int rtm_debug_bvh16(const rtm_scene_desc* sc, int32_t* n_nodes_out, float* meta6
     meta6[0] = H.ref[0]; meta6[1] = H.ref[1]; meta6[2] = H.ref[2];
     meta6[3] = H.inv_scale; meta6[4] = (float)H.inflation; meta6[5] = H.ok ? 1.f : 0.f;
     if (nodes16_out && H.ok) memcpy(nodes16_out, H.nodes.data(), H.nodes.size() * sizeof(uint32_t));
+    return RTM_OK;
+}
+
+int rtm_debug_bvh16x4(const rtm_scene_desc* sc, int32_t* info2, uint32_t* nodes_out) {
+    if (!sc || !info2) return fail(RTM_E_INVALID, "null argument");
+    RtmBvhHost B;
+    if (!rtm_bvh_build(sc->n_spheres, sc->position, sc->radius, sc->cam_origin, B))
+        return fail(RTM_E_UNSUPPORTED, "hierarchy deeper than %d levels", RTM_BVH_STACK);
+    RtmBvh16Host H;
+    rtm_bvh_compact16(B, H);
+    RtmBvh16x4Host Q;
+    rtm_bvh_compact16x4(B, H, Q);
+    info2[0] = Q.ok ? (int32_t)(Q.nodes.size() / 16) : 0;
+    info2[1] = Q.depth;
+    if (nodes_out && Q.ok) memcpy(nodes_out, Q.nodes.data(), Q.nodes.size() * sizeof(uint32_t));
     return RTM_OK;
 }
 

@@ -40,6 +40,10 @@ struct RtmBvhDev {
     const uint32_t* nodes16;
     float ref16[3];           // centre of the half-precision frame, relative to the scene reference point
     float inv_scale16;        // 1 / (power-of-two scale of that frame)
+    // 4-wide compact form (bvh.h: RtmBvh16x4Host): 16 x u32 per node in the same frame, NULL = not used.  When set, the
+    // FP32 walk starts at its node 0 and child codes >= 0 index THIS array; the leaves are shared with the other forms
+    const uint32_t* nodes16x4;
+    int32_t n_nodes4, depth4;
 };
 
 // Per-sphere records of the FP32 path in GLOBAL memory (hierarchy path, any N): the
@@ -195,6 +199,11 @@ void rtm_launch_radiance_mega(const RtmHotScene& hot, int32_t n_spheres, int32_t
 void rtm_launch_radiance_bvh(const RtmHotScene& hot, const RtmBvhDev& bvh, const RtmMatDev& mat, const RtmPassParams& p, float4* records,
                              RtmCounters* counters, int32_t sm_count, const float* cps0, int32_t n_spheres, int32_t n_planes,
                              int32_t walk, cudaStream_t st);
+// the same pass with 64 rays per warp parked in shared memory (kernels_bvh_pool.cu); rtm_launch_radiance_bvh picks it when
+// rtm_pool_kernel_takes() the scene (compact nodes, no planes, a tree its per-slot stacks can hold)
+bool rtm_pool_kernel_takes(const RtmBvhDev& bvh, int32_t n_planes);
+void rtm_launch_radiance_bvh_pool(const RtmHotScene& hot, const RtmBvhDev& bvh, const RtmMatDev& mat, const RtmPassParams& p, float4* records,
+                                  RtmCounters* counters, int32_t sm_count, const float* cps0, int32_t n_spheres, cudaStream_t st);
 // one wave of the wavefront variant; `wave` counts from 0 (its parity selects the queue)
 void rtm_launch_wf_shade(const RtmHotScene& hot, int32_t n_spheres, bool use_bvh, const RtmBvhDev& bvh, const RtmMatDev& mat,
                          const RtmPassParams& p, float4* records, RtmCounters* counters, const float* cps0, const RtmWaveDev& wv,

@@ -370,3 +370,114 @@ def test_compact16_reports_what_half_precision_cannot_hold():
     sc.position[:100, 0] += 1e6
     h = api.build_bvh16(sc.normalized())
     assert (not h["ok"]) or h["inflation"] > 0.25, h
+
+
+# ---------------- 4-wide compact nodes (bvh.h: RtmBvh16x4Host): what the FP32 walk uses by default ----------------
+def test_compact16x4_is_a_collapse_of_the_compact_tree(synth):
+    """Every child of a 4-wide node is a child of SOME two-child compact node with the very same box words and, below it,
+    the very same leaves; every leaf slot is reached exactly once; empty slots carry the NONE code behind a box that no
+    ray can hit; the depth that bounds the walk's stack (3 entries per level + the sentinel) is the real one."""
+    sc, b = synth
+    h2, h4 = api.build_bvh16(sc), api.build_bvh16x4(sc)
+    assert h4["ok"] and 0 < len(h4["nodes"]) < len(h2["nodes"])
+    by_words = {}
+    for k, w in enumerate(h2["nodes"]):
+        for j in range(2):
+            by_words.setdefault((int(w[3 * j]), int(w[3 * j + 1]), int(w[3 * j + 2]), ), []).append(int(np.int32(w[6 + j])))
+
+    def slots_below2(code):
+        out = []
+        _collect(b, code, out)
+        return sorted(out)
+
+    seen, depth, filled = [], 0, 0
+    stack = [(0, 0)]
+    visited = set()
+    while stack:
+        k, lvl = stack.pop()
+        assert k not in visited
+        visited.add(k)
+        w = h4["nodes"][k]
+        for j in range(4):
+            box = tuple(int(v) for v in w[8 * (j >> 1) + 3 * (j & 1):8 * (j >> 1) + 3 * (j & 1) + 3])
+            code = int(np.int32(w[8 * (j >> 1) + 6 + (j & 1)]))
+            if code == NONE:
+                assert box == (0, 0xFC000000, 0xFC00FC00)          # centre 0, half-extents -inf
+                continue
+            filled += 1
+            assert box in by_words, (k, j)
+            if code < 0:
+                assert code in by_words[box]                        # the same leaf behind the same box
+                first, cnt = _leaf(code)
+                seen.extend(range(first, first + cnt))
+                depth = max(depth, lvl + 1)
+            else:
+                stack.append((code, lvl + 1))
+    assert len(visited) == len(h4["nodes"])
+    real = [s for s in seen if b["leaf_id"][s] >= 0]
+    assert sorted(int(b["leaf_id"][s]) for s in real) == sorted(_real(b["leaf_id"]))
+    assert len(set(seen)) == len(seen)
+    assert depth == h4["depth"] and 3 * depth + 1 <= 64
+    assert filled / (4 * len(h4["nodes"])) > 0.7                   # synth10k: 2.98 of 4 slots in use
+
+
+def test_compact16x4_walk_finds_the_brute_force_hit(synth):
+    """The walk as the kernel does it (nearest hit child first, the others pushed in slot order, half-precision boxes)
+    against brute force over all spheres, for bounce-like rays."""
+    sc, b = synth
+    h2, h4 = api.build_bvh16(sc), api.build_bvh16x4(sc)
+    rng = np.random.default_rng(5)
+    n = 300
+    pos, rad = np.asarray(sc.position, np.float64), np.asarray(sc.radius, np.float64)
+    src = rng.integers(0, sc.n, n)
+    nrm = rng.normal(size=(n, 3))
+    nrm /= np.linalg.norm(nrm, axis=1, keepdims=True)
+    org = pos[src] + nrm * rad[src][:, None] * (1 + 1e-3)
+    d = nrm + rng.normal(size=(n, 3)) * 0.7
+    d /= np.linalg.norm(d, axis=1, keepdims=True)
+    ref = np.asarray(sc.cam_origin, np.float64)
+    fetches = 0
+    for i in range(n):
+        o, dd = org[i], d[i]
+        p = pos - o
+        bq = p @ dd
+        D = bq * bq - (p * p).sum(1) + rad * rad
+        t = np.where(D >= 0, bq - np.sqrt(np.maximum(D, 0)), np.inf)
+        t = np.where(t > 1e-6, t, np.where(D >= 0, bq + np.sqrt(np.maximum(D, 0)), np.inf))
+        t = np.where(t > 1e-6, t, np.inf)
+        want = int(np.argmin(t)) if np.isfinite(t.min()) else -1
+        best, hit = np.inf, -1
+        for j in b["big_id"]:
+            if t[j] < best:
+                best, hit = t[j], int(j)
+        with np.errstate(divide="ignore", invalid="ignore"):
+            inv = 1.0 / dd
+            st = [0]
+            while st:
+                code = st.pop()
+                if code < 0:
+                    first, cnt = _leaf(code)
+                    for s in range(first, first + cnt):
+                        k = int(b["leaf_id"][s])
+                        if k >= 0 and (t[k] < best or (t[k] == best and k < hit)):
+                            best, hit = t[k], k
+                    continue
+                fetches += 1
+                w = h4["nodes"][code]
+                cand = []
+                for j in range(4):
+                    c = int(np.int32(w[8 * (j >> 1) + 6 + (j & 1)]))
+                    # the kernel's form (box_test_h16): near / far = (c - o) / d -+ h |1 / d|; an empty slot has h = -inf
+                    hw = np.array(w[8 * (j >> 1) + 3 * (j & 1):8 * (j >> 1) + 3 * (j & 1) + 3], np.uint32).view(np.float16).astype(np.float64)
+                    tc = (hw[:3] * h2["inv_scale"] + h2["ref"] + ref - o) * inv
+                    he = hw[3:] * h2["inv_scale"] * np.abs(inv)
+                    tn, tf = max(0.0, np.nanmax(tc - he)), min(best, np.nanmin(tc + he))
+                    if tn <= tf:
+                        assert c != NONE
+                        cand.append((tn, j, c))
+                if cand:
+                    near = min(cand)[1]
+                    st.extend(c for _, j, c in cand if j != near)      # slot order
+                    st.append([c for _, j, c in cand if j == near][0])
+        assert hit == want, (i, hit, want)
+    assert fetches / n < 30

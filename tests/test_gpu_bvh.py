@@ -214,7 +214,7 @@ def test_bvh_deterministic_and_slices_add_up(synth):
 
 def test_shared_and_local_stack_instantiations_render_the_same_image(synth):
     """radiance_bvh_kernel<..., SST>: the traversal stack in shared memory (host-selected for trees of depth + 2 <= 24)
-    against the local-memory stack (rtm_options.debug_bvh_walk = 1).  Same walk, same candidates, same RNG counters:
+    against the local-memory stack (rtm_options.debug_bvh_walk bit 0).  Same walk, same candidates, same RNG counters:
     bit-identical image and counters."""
     sc = synth.with_dims(64, 36, 8, 2)
     with rtm.Renderer(sc, seed=1) as r:
@@ -228,10 +228,10 @@ def test_shared_and_local_stack_instantiations_render_the_same_image(synth):
 
 
 def test_compact_half_precision_nodes_render_the_same_image(synth):
-    """radiance_bvh_kernel<..., H16>: 32-byte nodes with half-precision (centre, half-extent) child boxes (one L1 request
-    per visit) against the 64-byte float nodes (rtm_options.debug_bvh_walk bit 1).  The compact boxes contain the float
-    ones, so the walk meets a superset of the candidates and keeps the same winner: same paths, bit-identical image and
-    ray count; only the visit counters may differ (by the few percent the boxes are wider)."""
+    """radiance_bvh_kernel<..., WK = 1>: 32-byte nodes with half-precision (centre, half-extent) child boxes (one L1 request
+    per visit) against the 64-byte float nodes (bit 1).  The compact boxes contain the
+    float ones, so the walk meets a superset of the candidates and keeps the same winner: same paths, bit-identical image
+    and ray count; only the visit counters may differ (by the few percent the boxes are wider)."""
     sc = synth.with_dims(96, 54, 8, 2)
     with rtm.Renderer(sc, seed=4) as r:
         a = r.render()
@@ -241,6 +241,62 @@ def test_compact_half_precision_nodes_render_the_same_image(synth):
     assert a.stats.rays == b.stats.rays and a.stats.rays_traced == b.stats.rays_traced
     assert b.stats.bvh_nodes <= a.stats.bvh_nodes <= 1.15 * b.stats.bvh_nodes
     assert b.stats.sphere_tests <= a.stats.sphere_tests <= 1.15 * b.stats.sphere_tests
+
+
+@pytest.mark.parametrize("stack_bit", [0, 1])
+def test_four_wide_compact_nodes_render_the_same_image_in_half_the_visits(synth, stack_bit):
+    """radiance_bvh_kernel<..., WK = 2> (rtm_options.debug_bvh_walk bit 3): 64-byte nodes of up to four children, the
+    collapse of the compact two-child tree (same boxes, same leaves).  Same winners, so the same paths and a bit-identical
+    image; about half the node visits; a few percent more sphere tests (children beyond the nearest are taken in slot
+    order, not by distance)."""
+    sc = synth.with_dims(96, 54, 8, 2)
+    with rtm.Renderer(sc, seed=4, debug_bvh_walk=8 | stack_bit) as r:
+        a = r.render()
+    with rtm.Renderer(sc, seed=4, debug_bvh_walk=stack_bit) as r:
+        b = r.render()
+    assert np.array_equal(a.image, b.image)
+    assert a.stats.rays == b.stats.rays and a.stats.rays_traced == b.stats.rays_traced
+    assert 0.4 * b.stats.bvh_nodes <= a.stats.bvh_nodes <= 0.62 * b.stats.bvh_nodes, (a.stats.bvh_nodes, b.stats.bvh_nodes)
+    assert 0.98 * b.stats.sphere_tests <= a.stats.sphere_tests <= 1.12 * b.stats.sphere_tests, (a.stats.sphere_tests, b.stats.sphere_tests)
+
+
+def test_breadth_first_and_treelet_numberings_render_the_same_image(synth):
+    """rtm_options.debug_bvh_walk bit 2: the inner nodes numbered breadth-first at the top + 4-node treelets below instead of
+    breadth-first throughout.  Only addresses change: identical image and identical counters."""
+    sc = synth.with_dims(64, 36, 8, 2)
+    for walk in (0, 8, 16):
+        with rtm.Renderer(sc, seed=9, debug_bvh_walk=walk) as r:
+            a = r.render()
+        with rtm.Renderer(sc, seed=9, debug_bvh_walk=walk | 4) as r:
+            b = r.render()
+        assert np.array_equal(a.image, b.image)
+        assert a.stats.bvh_nodes == b.stats.bvh_nodes and a.stats.sphere_tests == b.stats.sphere_tests
+
+
+@pytest.mark.parametrize("which", ["synth10k", "synth10k_sliced", "cornell_forced", "random300", "tiny_frame"])
+def test_ray_pool_kernel_renders_what_the_lane_owned_kernel_renders(synth, scene_path, which):
+    """radiance_bvh_pool_kernel (rtm_options.debug_bvh_walk bit 4: 64 rays per warp parked in shared memory, phases that
+    pick 32 rays in the same phase — a measured design alternative) against radiance_bvh_kernel (one ray per
+    lane, the default).  The same device functions run per ray with the same RNG counters, so the image and all four
+    counters are identical."""
+    kw = {}
+    if which == "synth10k":
+        sc = synth.with_dims(128, 72, 8, 2)
+    elif which == "synth10k_sliced":
+        sc, kw = synth.with_dims(64, 36, 8, 2), dict(sub_begin=1, sub_end=3, sample_begin=2, sample_end=7)
+    elif which == "cornell_forced":     # big spheres (the packed test in front of the walk), a hierarchy of three
+        sc, kw = rtm.load_scene(scene_path("cornellBox"), "abc").with_dims(96, 54, 8, 2), dict(accel="bvh")
+    elif which == "random300":
+        sc = rtm.random_scene(11, 300, width=96, height=54, samples=8, superSamples=1, closed=True)
+    else:                               # fewer sub-pixels than one block has slots
+        sc = synth.with_dims(8, 5, 4, 1)
+    with rtm.Renderer(sc, seed=21, debug_bvh_walk=16, **kw) as r:
+        a = r.render()
+    with rtm.Renderer(sc, seed=21, **kw) as r:
+        b = r.render()
+    assert np.array_equal(a.image, b.image), float(np.abs(a.image - b.image).max())
+    for f in ("rays", "rays_traced", "sphere_tests", "bvh_nodes", "samples"):
+        assert getattr(a.stats, f) == getattr(b.stats, f), f
 
 
 # ---------------- wavefront variant (same estimator, state in global memory) ----------------
