@@ -270,8 +270,22 @@ radiance_bvh_pool_kernel(const __grid_constant__ RtmHotScene hot, const __grid_c
                 if (deciding) {
                     if (!end) {
                         const unsigned q = full_grid ? ql : (ql / sub_count) * grid + sub_begin + (ql % sub_count);
-                        const uint2 rnd = rtm_bounce_rng(make_uint2(q, sd), p.rk);
+                        uint2 rnd = rtm_bounce_rng(make_uint2(q, sd), p.rk);
                         end = !((rnd.x < thr) && ((sd & 511u) + 1u < (unsigned)p.max_depth));   // Renderer.cpp:78
+#if RTM_BVH_FASTFWD
+                        // A sample killed at its PRIMARY vertex (depth 0: L = the primary hit's emission, T = 1) leaves the
+                        // lane exactly where stand_on_primary put it, so the lane closes it here and draws for the next
+                        // sample at once instead of asking the whole warp for another round (a quarter of all restarts on
+                        // synth10k).  The sub-pixel's last sample is left to the block below, which also finishes the unit.
+                        while (end && (sd & 511u) == 0u && sd + 512u != sd_end) {
+                            acc.x += clamp01f(L.x * inv_norm);
+                            acc.y += clamp01f(L.y * inv_norm);
+                            acc.z += clamp01f(L.z * inv_norm);
+                            sd += 512u;
+                            rnd = rtm_bounce_rng(make_uint2(q, sd), p.rk);
+                            end = !((rnd.x < thr) && (1u < (unsigned)p.max_depth));
+                        }
+#endif
                         if (!end) {
                             const float4 al = __ldg(mat.alb + id);
                             T.x *= al.x; T.y *= al.y; T.z *= al.z;                               // colorKD

@@ -288,6 +288,9 @@ __device__ __forceinline__ bool bvh_is_inner(int node) { return (unsigned)node <
 #ifndef RTM_BVH_SSTACK
 #define RTM_BVH_SSTACK 26   // the 4-wide walk of a depth-8 tree (10^4 spheres) can hold 3 * 8 + 1 entries
 #endif
+#ifndef RTM_BVH_FASTFWD
+#define RTM_BVH_FASTFWD 1   // hierarchy kernels: samples killed at their primary vertex are closed without another roulette round
+#endif
 // the ray-pool kernel (kernels_bvh_pool.cu): slots per warp / per block, levels of a slot's shared-memory stack
 #define RTM_POOL_SLOTS 64
 #define RTM_POOL_BLOCK_SLOTS (RTM_POOL_SLOTS * (RTM_MEGA_THREADS / 32))

@@ -1,5 +1,5 @@
 #!/bin/bash
-# C5 A/B: default library with knobs, then the prebuilt variants_*.so
+# C5 A/B: the default library (with optional knobs), then the prebuilt variants_*.so (scripts/gpu_variants3.sh), then the default again
 mkdir -p gpurun_out
 run() { # name, args
   timeout 300 python bench.py --workload c5 --steps ${STEPS:-4} --warmup 3 --no-cpu-baseline $2 > gpurun_out/ab_$1.log 2>&1
@@ -11,6 +11,6 @@ d=json.loads(l[-1]); print(sys.argv[1], "Grays/s %.3f" % (d["value"]/1e3), "ms %
 PY
 }
 run default ""
-run laneowned "--knob debug_bvh_walk=16"
-run default2 ""
 W=c5 STEPS=4 bash scripts/gpu_variants3.sh
+run default2 ""
+for k in $KNOBS; do run knob$k "--knob debug_bvh_walk=$k"; done
