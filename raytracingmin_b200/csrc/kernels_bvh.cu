@@ -28,6 +28,9 @@ namespace {
 #ifndef RTM_BVH_HOLD
 #define RTM_BVH_HOLD 0
 #endif
+#ifndef RTM_BVH_SHPRIM
+#define RTM_BVH_SHPRIM 1   // the sub-pixel's primary-hit constants in shared memory (restart = 3 LDS.128, no global load)
+#endif
 #ifndef RTM_BVH_S_ROUND
 #define RTM_BVH_S_ROUND 1   // lanes that must need another roulette decision for the S block to run another round (swept: 1 4.50, 2 4.46, 4 4.45, 8 4.34 Grays/s on C5)
 #endif
@@ -68,6 +71,13 @@ radiance_bvh_kernel(const __grid_constant__ RtmHotScene hot, const __grid_consta
                     RtmCounters* __restrict__ counters, RtmBvhDev bvh, RtmMatDev mat, const float* __restrict__ cps0, int n_sph, int n_pl) {
     __shared__ SelfMask sh_mask;
     __shared__ SharedBig sh_big;
+#if RTM_BVH_SHPRIM
+    // What a sample restart needs of the lane's sub-pixel — primary hit point + id, oriented normal there + ACNE state, its
+    // emission + roulette threshold — stays in shared memory ([k][thread], three LDS.128) for as long as the lane holds the
+    // sub-pixel: a restart costs no global load, so a lane closes and restarts samples in a private loop inside the round
+    // (kernels_mega.cu: SharedPrimary, the same idea).  6 KB a block.
+    __shared__ float4 sh_ppos[RTM_MEGA_THREADS], sh_pnrm[RTM_MEGA_THREADS], sh_pemi[RTM_MEGA_THREADS];
+#endif
     init_selfmask(sh_mask);
     if (threadIdx.x < 8) sh_big.id[threadIdx.x] = (threadIdx.x < (unsigned)bvh.n_big) ? bvh.big_id[threadIdx.x] : 0;
     __syncthreads();
@@ -206,7 +216,23 @@ radiance_bvh_kernel(const __grid_constant__ RtmHotScene hot, const __grid_consta
                 T = mk(1, 1, 1); L = mk(e0.x, e0.y, e0.z); sd &= ~511u;
                 thr = __float_as_uint(e0.w);
                 if (ACNE) cpsn = (wbits & RTM_REC_FLIP) ? 0.f : cps0[ql] * g.w * RTM_ACNE_INV2TAU;
+#if RTM_BVH_SHPRIM
+                sh_ppos[threadIdx.x] = make_float4(o.x, o.y, o.z, __int_as_float(pid));
+                sh_pnrm[threadIdx.x] = make_float4(w.x, w.y, w.z, cpsn);
+                sh_pemi[threadIdx.x] = e0;
+#endif
             };
+#if RTM_BVH_SHPRIM
+            auto restart_sample = [&]() {
+                const float4 a = sh_ppos[threadIdx.x], b = sh_pnrm[threadIdx.x], c = sh_pemi[threadIdx.x];
+                o = mk(a.x, a.y, a.z); id = __float_as_int(a.w);
+                w = mk(b.x, b.y, b.z); cpsn = b.w;
+                T = mk(1, 1, 1); L = mk(c.x, c.y, c.z); sd &= ~511u;
+                thr = __float_as_uint(c.w);
+            };
+#else
+            auto restart_sample = [&]() { stand_on_primary(records[ql]); };
+#endif
             // a finished ray is applied to the path; returns true when the path ends there
             auto apply_hit = [&](int id2, float t) -> bool {
                 if (id2 < 0) return true;                                            // miss: Renderer.cpp:116
@@ -246,51 +272,20 @@ radiance_bvh_kernel(const __grid_constant__ RtmHotScene hot, const __grid_consta
             int ocode = -1;
             for (;;) {
                 if (deciding) {
-                    if (!end) {
-                        // RNG counter = GLOBAL sub-pixel index: the image does not depend on the partition (one register less
-                        // than carrying it; the division only exists for sub-pixel-sliced multi-GPU handles)
-                        const unsigned q = full_grid ? ql : (ql / sub_count) * grid + sub_begin + (ql % sub_count);
-                        uint2 rnd = rtm_bounce_rng(make_uint2(q, sd), p.rk);
-                        end = !((rnd.x < thr) && ((sd & 511u) + 1u < (unsigned)p.max_depth));   // Renderer.cpp:78
-#if RTM_BVH_FASTFWD
-                        // A sample killed at its PRIMARY vertex (depth 0: L = the primary hit's emission, T = 1) leaves the
-                        // lane exactly where stand_on_primary put it, so the lane closes it here and draws for the next
-                        // sample at once instead of asking the whole warp for another round (a quarter of all restarts on
-                        // synth10k).  The sub-pixel's last sample is left to the block below, which also finishes the unit.
-                        while (end && (sd & 511u) == 0u && sd + 512u != sd_end) {
-                            acc.x += clamp01f(L.x * inv_norm);
-                            acc.y += clamp01f(L.y * inv_norm);
-                            acc.z += clamp01f(L.z * inv_norm);
-                            sd += 512u;
-                            rnd = rtm_bounce_rng(make_uint2(q, sd), p.rk);
-                            end = !((rnd.x < thr) && (1u < (unsigned)p.max_depth));
-                        }
-#endif
+                    // RNG counter = GLOBAL sub-pixel index: the image does not depend on the partition (one register less
+                    // than carrying it; the division only exists for sub-pixel-sliced multi-GPU handles)
+                    const unsigned q = full_grid ? ql : (ql / sub_count) * grid + sub_begin + (ql % sub_count);
+                    uint2 rnd = make_uint2(0u, 0u);
+                    // Private loop: close samples until one survives its next roulette (or the sub-pixel is finished).  A
+                    // restart is three LDS.128 (RTM_BVH_SHPRIM), so a lane whose path ended no longer asks the whole warp
+                    // for another round — rounds remain for the ACNE self-hit re-decisions only.
+#pragma unroll 1
+                    for (;;) {
                         if (!end) {
-                            const float4 al = mat_ld(mat.alb + id);
-                            T.x *= al.x; T.y *= al.y; T.z *= al.z;                               // colorKD
-                            d = cosine_dir(w, rnd.y, ((rnd.x & 0xFFFu) << 10) | (rnd.y & 0x3FFu));
-                            eps_bits = rnd.x ^ (rnd.y * 0x9E3779B9u);
-                            ++traced;
-                            bool self = false;
-                            if (ACNE) {
-                                const float cosw = dot(w, d);
-                                if (cpsn + cosw <= 0.f && !(PL && id >= n_sph)) {
-                                    // SettingData.cpp:208-212: the far root of the sphere the ray stands (just) inside
-                                    const float rr = fast_rcp(mat_ld(mat.geo + id).w);
-                                    const float qq = -cpsn * rr * RTM_ACNE_2TAU, bq = rr * cosw;
-                                    end = apply_hit(id, qq * fast_rcp(bq + fast_sqrt(fmaf(bq, bq, qq))));
-                                    self = true;   // stands on the next vertex: decide again
-                                }
-                            }
-                            if (!self) {
-                                ocode = __float_as_int(al.w);
-                                start = true;
-                                deciding = false;
-                            }
+                            rnd = rtm_bounce_rng(make_uint2(q, sd), p.rk);
+                            end = !((rnd.x < thr) && ((sd & 511u) + 1u < (unsigned)p.max_depth));   // Renderer.cpp:78
                         }
-                    }
-                    if (deciding && end) {
+                        if (!end) break;
                         // the sample is complete: Renderer.cpp:240-242
                         acc.x += clamp01f(L.x * inv_norm);
                         acc.y += clamp01f(L.y * inv_norm);
@@ -302,9 +297,32 @@ radiance_bvh_kernel(const __grid_constant__ RtmHotScene hot, const __grid_consta
                             flush_if_big();
                             have = false;
                             deciding = false;
-                        } else {
-                            stand_on_primary(records[ql]);
-                            end = false;
+                            break;
+                        }
+                        restart_sample();
+                        end = false;
+                    }
+                    if (deciding) {
+                        const float4 al = mat_ld(mat.alb + id);
+                        T.x *= al.x; T.y *= al.y; T.z *= al.z;                               // colorKD
+                        d = cosine_dir(w, rnd.y, ((rnd.x & 0xFFFu) << 10) | (rnd.y & 0x3FFu));
+                        eps_bits = rnd.x ^ (rnd.y * 0x9E3779B9u);
+                        ++traced;
+                        bool self = false;
+                        if (ACNE) {
+                            const float cosw = dot(w, d);
+                            if (cpsn + cosw <= 0.f && !(PL && id >= n_sph)) {
+                                // SettingData.cpp:208-212: the far root of the sphere the ray stands (just) inside
+                                const float rr = fast_rcp(mat_ld(mat.geo + id).w);
+                                const float qq = -cpsn * rr * RTM_ACNE_2TAU, bq = rr * cosw;
+                                end = apply_hit(id, qq * fast_rcp(bq + fast_sqrt(fmaf(bq, bq, qq))));
+                                self = true;   // stands on the next vertex: decide again
+                            }
+                        }
+                        if (!self) {
+                            ocode = __float_as_int(al.w);
+                            start = true;
+                            deciding = false;
                         }
                     }
                 }
