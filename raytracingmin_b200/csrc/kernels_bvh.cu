@@ -23,7 +23,7 @@ namespace {
 #define RTM_BVH_BURST 8
 #endif
 #ifndef RTM_BVH_MINBLOCKS
-#define RTM_BVH_MINBLOCKS 7
+#define RTM_BVH_MINBLOCKS 8   // 64 registers: reachable without spills since the S-only path state is parked in shared memory (7: 6.64, 8: 7.07 Grays/s on C5)
 #endif
 #ifndef RTM_BVH_HOLD
 #define RTM_BVH_HOLD 0
@@ -95,17 +95,19 @@ radiance_bvh_kernel(const __grid_constant__ RtmHotScene hot, const __grid_consta
     unsigned w_next = 0, w_end = 0;
     bool have = false, done = false, tracing = false, pending = false;
     bool fresh = false;              // the lane stands on its sub-pixel's primary hit, and the S block has yet to load it
-    unsigned ql = 0;                 // record index; the global sub-pixel index (RNG counter) is derived from it where it is needed
-    f3 acc = mk(0, 0, 0);
-    f3 o = mk(0, 0, 0), T = mk(1, 1, 1), L = mk(0, 0, 0), d = mk(0, 0, 1);
-    int id = 0;
-    unsigned sd = 0;                 // sample << 9 | depth: the RNG counter word itself (as in radiance_mega_kernel)
+    // Path state that only the S block touches — throughput T, the sample's radiance L, the sub-pixel's sum acc, the object
+    // the path stands on, sample << 9 | depth (the RNG counter word itself, as in radiance_mega_kernel), the record index ql
+    // (the global sub-pixel index, the RNG counter's other word, is derived from it where it is needed) and the ACNE bits —
+    // is PARKED in shared memory ([k][thread], 3 LDS.128 + 1 LDS at S entry, the same in stores at S exit) while the lane
+    // walks: 13 registers the T block does not have to carry.
+    __shared__ float4 sh_pT[RTM_MEGA_THREADS], sh_pL[RTM_MEGA_THREADS], sh_pA[RTM_MEGA_THREADS];   // T.xyz id | L.xyz sd | acc.xyz ql
+    __shared__ uint32_t sh_peps[ACNE ? RTM_MEGA_THREADS : 1];
+    f3 o = mk(0, 0, 0), d = mk(0, 0, 1);
     const unsigned sd_end = (unsigned)p.s_end << 9;
     // The oriented normal w and the ACNE state cpsn are NOT lane state: they are produced (apply_hit / stand_on_primary) and
     // consumed (roulette, direction sampling) inside one S block, so they are locals of that block — four registers that
     // the T block's |1/d| needs (72 registers = 7 resident blocks either way).
     int sslot = -1;                  // leaf slot of the sphere the current ray leaves (self test inside the leaves)
-    uint32_t eps_bits = 0;
     BvhRay ray;
     ray.node = RTM_BVH_NONE_DEV;
     constexpr int ST = SST ? RTM_MEGA_THREADS : 1;
@@ -154,7 +156,7 @@ radiance_bvh_kernel(const __grid_constant__ RtmHotScene hot, const __grid_consta
             const unsigned rank = __popc(need & lt_mask);
             const bool mine = ((need >> lane) & 1u) && rank < avail;
             if (mine) {
-                ql = w_next + rank;
+                const unsigned ql = w_next + rank;
                 const float4 rec = records[ql];
                 const unsigned wbits = __float_as_uint(rec.w);
                 const unsigned ns = (unsigned)(s_end - s_begin);
@@ -173,8 +175,8 @@ radiance_bvh_kernel(const __grid_constant__ RtmHotScene hot, const __grid_consta
                     ++units;
                 } else {
                     have = true;
-                    acc = mk(0, 0, 0);
-                    sd = (unsigned)s_begin << 9;
+                    sh_pA[threadIdx.x] = make_float4(0.f, 0.f, 0.f, __uint_as_float(ql));
+                    sh_pL[threadIdx.x] = make_float4(0.f, 0.f, 0.f, __uint_as_float((unsigned)s_begin << 9));
                     fresh = true;   // the S block of this very iteration stands the lane on its primary hit
                 }
             }
@@ -198,6 +200,13 @@ radiance_bvh_kernel(const __grid_constant__ RtmHotScene hot, const __grid_consta
         // need one.
         const bool in_s = (tr == 0u || __popc(sready) >= RTM_BVH_S_THRESH) && have && !tracing;
         if (__any_sync(0xffffffffu, in_s)) {
+            __syncwarp();   // the refill's stores above
+            const float4 pT = sh_pT[threadIdx.x], pL = sh_pL[threadIdx.x], pA = sh_pA[threadIdx.x];
+            f3 T = mk(pT.x, pT.y, pT.z), L = mk(pL.x, pL.y, pL.z), acc = mk(pA.x, pA.y, pA.z);
+            int id = __float_as_int(pT.w);
+            unsigned sd = __float_as_uint(pL.w);
+            const unsigned ql = __float_as_uint(pA.w);
+            uint32_t eps_bits = ACNE ? sh_peps[threadIdx.x] : 0u;
             f3 w = mk(0, 0, 1);
             float cpsn = 0.f;
             unsigned thr = 0;   // roulette threshold kd * 2^32 of the surface the lane stands on (from the emission record read there)
@@ -337,6 +346,12 @@ radiance_bvh_kernel(const __grid_constant__ RtmHotScene hot, const __grid_consta
                 if (ray.node != RTM_BVH_NONE_DEV) tracing = true;
                 else pending = true;   // empty hierarchy: the hit (big spheres / planes) is applied at the next entry
             }
+            if (in_s) {
+                sh_pT[threadIdx.x] = make_float4(T.x, T.y, T.z, __int_as_float(id));
+                sh_pL[threadIdx.x] = make_float4(L.x, L.y, L.z, __uint_as_float(sd));
+                sh_pA[threadIdx.x] = make_float4(acc.x, acc.y, acc.z, __uint_as_float(ql));
+                if (ACNE) sh_peps[threadIdx.x] = eps_bits;
+            }
         }
 
         // ---- T block: while-while until enough lanes are ready for the S block
@@ -427,6 +442,9 @@ __global__ void closest_hit_bvh_f32_kernel(const __grid_constant__ RtmHotScene h
 template <int NP, bool ACNE, bool PL, bool SST, int WK>
 void launch_bvh4(const RtmHotScene& hot, const RtmBvhDev& bvh, const RtmMatDev& mat, const RtmPassParams& p, float4* records, RtmCounters* counters,
                  int sm_count, const float* cps0, int n_sph, int n_pl, cudaStream_t st) {
+    // 26 KB of shared memory a block (traversal stacks, parked path state, primary-hit constants): RTM_BVH_MINBLOCKS of them
+    // need the shared-memory end of the L1 split
+    cudaFuncSetAttribute(radiance_bvh_kernel<NP, ACNE, PL, SST, WK>, cudaFuncAttributePreferredSharedMemoryCarveout, cudaSharedmemCarveoutMaxShared);
     int per_sm = 0;
     cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, radiance_bvh_kernel<NP, ACNE, PL, SST, WK>, RTM_MEGA_THREADS, 0);
     if (per_sm < 1) per_sm = 1;
