@@ -6,8 +6,9 @@
 // phase.  Here a warp owns RTM_POOL_SLOTS = 64 rays.  Their state lives in shared memory (24 words + a traversal stack
 // per ray); a phase picks 32 rays that are IN that phase, loads what the phase needs into registers, runs the very same
 // device functions as radiance_bvh_kernel, and writes back what changed:
-//   S  shade: the same block as radiance_bvh_kernel's (refill, apply the finished ray, roulette rounds, start the next
-//      ray), run when half of the warp's live rays wait for it — 32 lanes enter instead of 12;
+//   S  shade: radiance_bvh_kernel's S block as it was when this kernel was measured (refill, apply the finished ray,
+//      warp-wide roulette rounds, start the next ray; the lane-owned kernel has since moved restarts into a private loop),
+//      run when half of the warp's live rays wait for it — 32 lanes enter instead of 12;
 //   T  trace: up to RTM_POOL_BURST inner nodes, then the leaf for the lanes that reached one, RTM_POOL_ROUNDS times;
 //      all 32 lanes start on an inner node.
 // Same per-ray arithmetic, same RNG counters, same tie rules: the image is bit-identical to radiance_bvh_kernel's.
