@@ -47,6 +47,11 @@ CASES = {
     "synth10k": ("synth10k.json", 96, 54, 8, 2, {}),
     # brute-force scene pushed through the hierarchy kernel
     "simple2_bvh": ("simple2.head.json", 192, 108, 8, 1, {"accel": "bvh"}),
+    # the extensions ride the same pass: PlaneObject squares, next-event estimation, and both behind the hierarchy / together
+    "planes": ("cornellBoxPlanes.json", 160, 90, 8, 2, {}),
+    "planes_bvh": ("cornellBoxPlanes.json", 160, 90, 8, 1, {"accel": "bvh"}),
+    "nee": ("cornellBox.head.json", 160, 90, 8, 2, {"estimator": "nee"}),
+    "planes_nee": ("cornellBoxPlanes.json", 160, 90, 8, 1, {"estimator": "nee"}),
 }
 
 
