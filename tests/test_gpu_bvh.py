@@ -213,7 +213,7 @@ def test_bvh_deterministic_and_slices_add_up(synth):
 
 
 def test_shared_and_local_stack_instantiations_render_the_same_image(synth):
-    """radiance_bvh_kernel<..., SST>: the traversal stack in shared memory (host-selected for trees of depth + 2 <= 24)
+    """radiance_bvh_kernel<..., SST>: the traversal stack in shared memory (host-selected for trees of depth + 2 <= RTM_BVH_SSTACK = 26)
     against the local-memory stack (rtm_options.debug_bvh_walk bit 0).  Same walk, same candidates, same RNG counters:
     bit-identical image and counters."""
     sc = synth.with_dims(64, 36, 8, 2)
