@@ -31,6 +31,13 @@ namespace {
 #ifndef RTM_BVH_SHPRIM
 #define RTM_BVH_SHPRIM 1   // the sub-pixel's primary-hit constants in shared memory (restart = 3 LDS.128, no global load)
 #endif
+// The S block's decision loop is left by every lane on its own (the lanes meet again at a __syncwarp before the ray start,
+// which therefore still runs once): a lane that has its direction no longer sits through the re-decisions of the others
+// (ACNE self-hits), and the warp-wide ballot per round is gone.  0 = the warp-uniform rounds (RTM_BVH_S_ROUND).  7.05 -> 7.30
+// Grays/s on C5 (profiles/r02/c5_sblock_r02i.jsonl).
+#ifndef RTM_BVH_S_PERLANE
+#define RTM_BVH_S_PERLANE 1
+#endif
 #ifndef RTM_BVH_S_ROUND
 #define RTM_BVH_S_ROUND 1   // lanes that must need another roulette decision for the S block to run another round (swept: 1 4.50, 2 4.46, 4 4.45, 8 4.34 Grays/s on C5)
 #endif
@@ -335,8 +342,15 @@ radiance_bvh_kernel(const __grid_constant__ RtmHotScene hot, const __grid_consta
                         }
                     }
                 }
+#if RTM_BVH_S_PERLANE
+                if (!deciding) break;   // per-lane exit: lanes wait at the __syncwarp below
+#else
                 if (__popc(__ballot_sync(0xffffffffu, deciding)) < RTM_BVH_S_ROUND) break;
+#endif
             }
+#if RTM_BVH_S_PERLANE
+            __syncwarp();
+#endif
             if (deciding && have) fresh = true;   // (only with RTM_BVH_S_ROUND > 1) restarted in the last round: stands on its primary hit
             if (start) {
                 // the packed big-sphere test (~140 instructions) and the planes: once, for all lanes that start a ray
