@@ -288,6 +288,9 @@ __device__ __forceinline__ bool bvh_is_inner(int node) { return (unsigned)node <
 #ifndef RTM_BVH_SSTACK
 #define RTM_BVH_SSTACK 26   // the 4-wide walk of a depth-8 tree (10^4 spheres) can hold 3 * 8 + 1 entries
 #endif
+#ifndef RTM_BVH_STEP_PRED
+#define RTM_BVH_STEP_PRED 1   // compact two-child step with predicated push / pop instead of branches (C5 7.37 -> 7.54 Grays/s)
+#endif
 #ifndef RTM_BVH_FASTFWD
 #define RTM_BVH_FASTFWD 1   // hierarchy kernels: samples killed at their primary vertex are closed without another roulette round
 #endif
@@ -432,12 +435,29 @@ template <int ST = 1>
 __device__ __forceinline__ void bvh16_inner_step(const RtmBvhDev& bvh, BvhRay& r, int* stack) {
     RTM_ASSERT(r.node >= 0 && r.node < bvh.n_nodes);
     uint4 a, b;
-    ldg256u(bvh.nodes16 + 8 * r.node, a, b);
+    ldg256u(bvh.nodes16 + (size_t)(unsigned)r.node * 8u, a, b);   // one IMAD.WIDE (node x 32 bytes + base)
     float n0, n1;
     const float tm = r.best + 2.f * RTM_T_EPS;
     const bool h0 = box_test_h16(a.x, a.y, a.z, r.oi, r.inv, r.ainv, tm, n0);
     const bool h1 = box_test_h16(a.w, b.x, b.y, r.oi, r.inv, r.ainv, tm, n1);
     const int c0 = (int)b.z, c1 = (int)b.w;
+#if RTM_BVH_STEP_PRED
+    if (ST != 1) {
+        // straight-line version for the shared-memory stack: the push and the pop are PREDICATED instructions, so the
+        // lanes that push, descend and pop do not take turns through two branch targets
+        const bool both = h0 && h1, none = !(h0 || h1);
+        const bool swap = n1 < n0;
+        const int far = swap ? c0 : c1;
+        int next = (h0 && !(h1 && swap)) ? c0 : c1;
+        RTM_ASSERT(RTM_STACK_IDX(ST, stack, r) >= (none ? 1 : 0) && RTM_STACK_IDX(ST, stack, r) < RTM_STACK_CAP(ST));
+        asm volatile("{ .reg .pred p; setp.ne.b32 p, %2, 0; @p st.shared.b32 [%0], %1; }" :: "r"(r.sp), "r"(far), "r"((int)both));
+        r.sp += both ? 4 * ST : 0;
+        r.sp -= none ? 4 * ST : 0;
+        asm volatile("{ .reg .pred p; setp.ne.b32 p, %2, 0; @p ld.shared.b32 %0, [%1]; }" : "+r"(next) : "r"(r.sp), "r"((int)none));
+        r.node = next;
+        return;
+    }
+#endif
     if (h0 && h1) {
         const bool swap = n1 < n0;
         bvh_push<ST>(stack, r, swap ? c0 : c1);
