@@ -198,13 +198,13 @@ radiance_bvh_kernel(const __grid_constant__ RtmHotScene hot, const __grid_consta
             continue;
         }
 
-        // ---- S block.  Entered by the whole warp (warp-uniform control flow, lanes outside it are predicated off):
-        // the roulette runs in ROUNDS shared by all S lanes, and the packed big-sphere test + ray start run once,
-        // after the rounds, for every lane that has a direction.  (With per-lane loops the compiler let each lane
-        // leave the roulette loop on its own: the ~140-instruction ray start then ran once per group of lanes that
-        // left together, 3.3 times per entry at 6 of 32 lanes — ncu_bvh_v3.)  A lane whose path is killed in the last
-        // round closes its sample and stays S-ready; another round is run only while RTM_BVH_S_ROUND or more lanes
-        // need one.
+        // ---- S block.  Entered by the whole warp (lanes outside it are predicated off).  Each lane decides on its own until it
+        // has a direction (or its sub-pixel is finished): roulette, close-and-restart of ended samples in a private loop,
+        // direction sampling, the ACNE self-hit re-decision.  The lanes meet again at a __syncwarp and the packed
+        // big-sphere test + ray start run ONCE for every lane that has a direction.  (Round 1's per-lane loop had no such
+        // meeting point: the ~140-instruction ray start ran once per group of lanes that left the loop together, 3.3
+        // times per entry at 6 of 32 lanes — ncu_bvh_v3.  RTM_BVH_S_PERLANE = 0 is the intermediate form, warp-uniform
+        // rounds that continue while RTM_BVH_S_ROUND or more lanes need one.)
         const bool in_s = (tr == 0u || __popc(sready) >= RTM_BVH_S_THRESH) && have && !tracing;
         if (__any_sync(0xffffffffu, in_s)) {
             __syncwarp();   // the refill's stores above
